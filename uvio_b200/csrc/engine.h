@@ -1,0 +1,105 @@
+// Host side of the GPU TrackKLT: per-rig tracker state and the reference's sequential, order-dependent control flow
+// (ov_core/src/track/TrackKLT.cpp, Grider_GRID.h), plus the per-device context that batches the GPU rounds of many rigs.
+//
+// What runs where: pixel / feature arithmetic is on the GPU; decisions whose outcome depends on
+// iteration order (occupancy grids, per-cell std::sort tie order, id assignment, stereo merge) stay on the host and
+// mirror the reference statement by statement.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+
+#include "kernels.h"
+
+namespace uvio {
+
+struct Params {                 // TrackKLT ctor arguments (TrackKLT.h:54-57) + the reference's hard-coded constants
+  int num_features = 200;
+  int num_aruco = 0;
+  int use_stereo = 1;
+  int histogram_method = 1;     // TrackBase::HistogramMethod {NONE, HISTOGRAM, CLAHE} (TrackBase.h:78)
+  int fast_threshold = 20;
+  int grid_x = 5, grid_y = 5;
+  int min_px_dist = 10;
+  int pyr_levels = 5;           // TrackKLT.h:143
+  int win_size = 15;            // TrackKLT.h:144 (only 15 is implemented)
+  int lk_max_iters = 30;        // TrackKLT.cpp:670,857
+  double lk_eps = 0.01;
+};
+
+struct CamCalib {
+  size_t cam_id;
+  CamModel model;
+};
+
+struct Obs {                    // one FeatureDatabase::update_feature call (FeatureDatabase.cpp:59)
+  size_t id;
+  size_t cam_id;
+  float u, v, un, vn;
+};
+
+struct Pt { float x, y; };
+
+struct HostImage {              // caller-owned view
+  const uint8_t *p;
+  size_t stride;
+  int w, h;
+};
+
+struct CamState {               // per camera id (TrackBase.h:180-190: img_last, img_mask_last, pts_last, ids_last)
+  size_t cam_id = 0;
+  int cam_model_idx = -1;       // index into the context's CamModel table
+  double max_focal = 0;
+  int w = 0, h = 0;             // size of the images this camera has been fed (fixed after the first frame)
+  int pyr[2] = {-1, -1};        // the two pyramid slots in the context's table
+  int cur = 0;                  // slot holding the frame being fed ("curr"); 1-cur is "last"
+  int raw = -1;                 // raw upload buffer index
+  bool have_last = false;
+  std::vector<Pt> pts_last;
+  std::vector<size_t> ids_last;
+  std::vector<uint8_t> mask[2]; // host copies of the masks, indexed like pyr[]
+  bool mask_nonzero[2] = {false, false};
+  std::vector<uint8_t> paint;   // scratch for mask_updated = mask | painted boxes (always restored to zero)
+};
+
+enum Status { OK = 0, E_BADMSG = 1, E_CAMID = 2, E_CUDA = 3, E_ARG = 4, E_SIZE = 5 };
+
+class Context;
+struct FeedWork;                // per-feed scratch (engine.cpp)
+
+class Rig {                     // one tracker = one TrackKLT instance
+ public:
+  Rig(Context *ctx, const Params &p, const CamCalib *cams, int n_cams);
+  ~Rig();
+  Context *ctx;
+  Params prm;
+  std::vector<CamState> cams;                       // in the order given at creation
+  std::unordered_map<size_t, int> cam_index;        // camera id -> index in cams
+  size_t currid;                                    // TrackBase.cpp:34
+  std::vector<Obs> obs;                             // observations produced by the last feed, in update_feature order
+  float stage_us[5] = {0, 0, 0, 0, 0};              // pyramid, detection, temporal klt, stereo klt, db update
+  int last_error = 0;
+  int cuda_error = 0;
+  std::mutex mtx;                                   // serialises feed / getters on this handle
+  CamState *find_cam(size_t id);
+};
+
+struct FeedRequest {            // one feed_new_camera call (utils/sensor_data.h:55-80 CameraData)
+  Rig *rig;
+  double timestamp;
+  int n;
+  const size_t *sensor_ids;
+  const HostImage *images;
+  const HostImage *masks;       // mask[i].p may be null = all zeros
+  int status;                   // out
+};
+
+// Feeds one frame to each of the given rigs (all on one device) with batched GPU rounds. Returns the worst status.
+int feed_batch(Context *ctx, FeedRequest *reqs, int n);
+
+Context *context_for_device(int device, int *err);
+
+}  // namespace uvio

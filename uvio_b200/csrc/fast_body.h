@@ -1,0 +1,107 @@
+// FAST-9/16 with 3x3 non-max suppression on a sub-rectangle (grid cell) of an image.
+//
+// Replaces cv::FAST(img(cv::Rect(x, y, size_x, size_y)), pts, threshold, true) at
+// ov_core/src/track/Grider_GRID.h:125.  ROI semantics are kept: positions within 3 px of the
+// *cell* edge never fire and count as score 0 for their neighbours' suppression test.
+// One thread block handles a FT_W x FT_H tile of the cell; corners are appended (unordered) to the job's list as
+// packed words  x | y << 12 | score << 24  (cell-relative x, y).  The host restores cv::FAST's row-major emission
+// order by sorting on (y, x) before it applies the reference's std::sort-by-response (Grider_GRID.h:128).
+#pragma once
+#include "image_body.h"
+#include "simt.h"
+
+namespace uvio {
+
+constexpr int FT_W = 64, FT_H = 16;
+constexpr int FT_PW = FT_W + 8, FT_PH = FT_H + 8;     // pixel footprint (tile + 1 nms halo + 3 ring halo each side)
+constexpr int FT_SW = FT_W + 2, FT_SH = FT_H + 2;     // score footprint (tile + 1 nms halo each side)
+
+struct FastSmem {
+  uint8_t pix[FT_PH * FT_PW];
+  uint8_t score[FT_SH * FT_SW];
+};
+
+struct FastJob {          // one grid cell of one image
+  int img;                // index into the image table of the launch
+  int x0, y0, w, h;       // cell rectangle (Grider_GRID.h:113-114, integer-division cell size)
+  int out_off;            // first word of this job's list in the output buffer
+  int out_cap;            // capacity in words (sized to the NMS worst case, ceil(w/2)*ceil(h/2): cannot overflow)
+};
+
+UVIO_HD int fast_ring_off(int k, int pitch) {
+  // (dx,dy), k = 0..15: (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
+  const int dx = k < 4 ? k : (k < 6 ? 3 : (k < 12 ? 8 - k : (k < 14 ? -3 : k - 16)));
+  const int dy = k < 2 ? 3 : (k < 7 ? 4 - k : (k < 10 ? -3 : (k < 15 ? k - 12 : 3)));
+  return dy * pitch + dx;
+}
+
+// largest t' such that the pixel is still a corner at threshold t' (0 if it is not a corner at `threshold`)
+UVIO_HD int fast_score(const uint8_t *p, int pitch, int threshold) {
+  int d[16];
+  int v = p[0];
+  unsigned brighter = 0, darker = 0;   // ring darker than centre by > t  /  ring brighter than centre by > t
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    d[k] = v - (int)p[fast_ring_off(k, pitch)];
+    brighter |= (unsigned)(d[k] > threshold) << k;
+    darker |= (unsigned)(d[k] < -threshold) << k;
+  }
+  unsigned m1 = brighter | (brighter << 16), m2 = darker | (darker << 16);
+  unsigned r1 = m1 & (m1 >> 1), r2 = m2 & (m2 >> 1);
+  r1 &= r1 >> 2; r2 &= r2 >> 2;
+  r1 &= r1 >> 4; r2 &= r2 >> 4;
+  r1 &= m1 >> 8; r2 &= m2 >> 8;
+  if (!((r1 | r2) & 0xFFFFu)) return 0;
+  int best = -1000;
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    int mn = d[k], mx = d[k];
+#pragma unroll
+    for (int j = 1; j < 9; j++) {
+      int e = d[(k + j) & 15];
+      mn = e < mn ? e : mn;
+      mx = e > mx ? e : mx;
+    }
+    best = mn > best ? mn : best;
+    best = -mx > best ? -mx : best;
+  }
+  return best > threshold ? best - 1 : 0;
+}
+
+template <class G>
+UVIO_HD void fast_tile(G g, FastSmem &s, const ImgView &I, const FastJob &job, int tx0, int ty0, int threshold,
+                       uint32_t *out, unsigned *count) {
+  // stage pixels: cell-relative (tx0-4 .. tx0+FT_W+3, ty0-4 .. ty0+FT_H+3), clamped into the cell (clamped values are
+  // only ever read for positions whose score is forced to 0)
+  for (int i = g.lane(); i < FT_PH * FT_PW; i += g.size()) {
+    int yy = i / FT_PW, xx = i - yy * FT_PW;
+    int x = clampi(tx0 - 4 + xx, 0, job.w - 1), y = clampi(ty0 - 4 + yy, 0, job.h - 1);
+    s.pix[i] = I.p[(size_t)(job.y0 + y) * I.pitch + job.x0 + x];
+  }
+  g.sync();
+  for (int i = g.lane(); i < FT_SH * FT_SW; i += g.size()) {
+    int yy = i / FT_SW, xx = i - yy * FT_SW;
+    int x = tx0 - 1 + xx, y = ty0 - 1 + yy;
+    int sc = 0;
+    if (x >= 3 && x < job.w - 3 && y >= 3 && y < job.h - 3)
+      sc = fast_score(s.pix + (yy + 3) * FT_PW + (xx + 3), FT_PW, threshold);
+    s.score[i] = (uint8_t)sc;
+  }
+  g.sync();
+  for (int i = g.lane(); i < FT_H * FT_W; i += g.size()) {
+    int yy = i / FT_W, xx = i - yy * FT_W;
+    int x = tx0 + xx, y = ty0 + yy;
+    if (x >= job.w || y >= job.h) continue;
+    const uint8_t *c = s.score + (yy + 1) * FT_SW + (xx + 1);
+    int sc = c[0];
+    if (!sc) continue;
+    if (sc > c[-1] && sc > c[1] && sc > c[-FT_SW - 1] && sc > c[-FT_SW] && sc > c[-FT_SW + 1] && sc > c[FT_SW - 1] &&
+        sc > c[FT_SW] && sc > c[FT_SW + 1]) {
+      unsigned idx = gmem_add(count, 1u);
+      if ((int)idx < job.out_cap) out[job.out_off + idx] = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)sc << 24);
+    }
+  }
+  g.sync();
+}
+
+}  // namespace uvio

@@ -1,0 +1,330 @@
+// sm_100a kernels of the TrackKLT hot path.  The arithmetic lives in the *_body.h headers (one body per stage, written
+// against an execution-group abstraction); this file binds the bodies to thread blocks / warps, shared memory and the
+// launch geometry.  Built with -fmad=false: the CPU tracker's OpenCV build does not fuse multiply-adds.
+#include "kernels.h"
+
+#include <math.h>
+
+#include "fast_body.h"
+#include "image_body.h"
+#include "lk_body.h"
+#include "ransac_body.h"
+#include "subpix_body.h"
+
+namespace uvio {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// equalizeHist: histogram (+ LUT by the last band to finish) -> apply
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_hist(const PreJob *jobs, const ImgView *raw_tab, unsigned *hist, unsigned *ticket,
+                                              uint8_t *lut_out) {
+  const PreJob job = jobs[blockIdx.y];
+  if (job.method != 1) return;
+  __shared__ unsigned sh[256];
+  __shared__ unsigned cdf[256];
+  __shared__ int s_first, s_last;
+  const ImgView I = raw_tab[job.raw];
+  GroupBlock g;
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  int r0 = (int)((long long)I.h * blockIdx.x / gridDim.x), r1 = (int)((long long)I.h * (blockIdx.x + 1) / gridDim.x);
+  hist_rows(g, sh, I, r0, r1);
+  __syncthreads();
+  unsigned *gh = hist + (size_t)blockIdx.y * 256;
+  if (sh[threadIdx.x]) atomicAdd(&gh[threadIdx.x], sh[threadIdx.x]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(&ticket[blockIdx.y], 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  // last band of this image: LUT from the complete histogram (App. A.1), then reset the scratch for the next frame
+  __threadfence();
+  unsigned hv = __ldcg(&gh[threadIdx.x]);
+  gh[threadIdx.x] = 0;
+  if (threadIdx.x == 0) { ticket[blockIdx.y] = 0; s_first = 256; }
+  cdf[threadIdx.x] = hv;
+  __syncthreads();
+  if (hv) atomicMin(&s_first, (int)threadIdx.x);
+  for (int d = 1; d < 256; d <<= 1) {   // inclusive scan
+    unsigned v = threadIdx.x >= d ? cdf[threadIdx.x - d] : 0;
+    __syncthreads();
+    cdf[threadIdx.x] += v;
+    __syncthreads();
+  }
+  const int i0 = s_first, total = I.w * I.h;
+  const int h0 = (int)(cdf[i0] - (i0 ? cdf[i0 - 1] : 0));
+  uint8_t out;
+  if (h0 == total) out = (uint8_t)i0;
+  else if ((int)threadIdx.x <= i0) out = 0;
+  else {
+    float scale = 255.f / (float)(total - h0);
+    out = sat_u8(round_f2i(fmul((float)(int)(cdf[threadIdx.x] - cdf[i0]), scale)));
+  }
+  lut_out[(size_t)blockIdx.y * 256 + threadIdx.x] = out;
+}
+
+__global__ void __launch_bounds__(256) k_lut_apply(const PreJob *jobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
+                                                   const uint8_t *lut_in) {
+  const PreJob job = jobs[blockIdx.y];
+  if (job.method == 2) return;
+  __shared__ uint8_t lut[256];
+  const ImgView I = raw_tab[job.raw];
+  const ImgView D = pyr_tab[job.pyr].lv[0];
+  lut[threadIdx.x] = job.method == 1 ? lut_in[(size_t)blockIdx.y * 256 + threadIdx.x] : (uint8_t)threadIdx.x;
+  __syncthreads();
+  int r0 = (int)((long long)I.h * blockIdx.x / gridDim.x), r1 = (int)((long long)I.h * (blockIdx.x + 1) / gridDim.x);
+  lut_rows(GroupBlock(), lut, I, (uint8_t *)D.p, D.pitch, r0, r1);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// CLAHE: per-tile clipped LUTs -> bilinear apply
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_clahe_tiles(const PreJob *jobs, const ImgView *raw_tab, uint8_t *luts) {
+  const PreJob job = jobs[blockIdx.y];
+  if (job.method != 2) return;
+  __shared__ unsigned sh[256];
+  const ImgView I = raw_tab[job.raw];
+  const ClaheGeom q = clahe_geom(I.w, I.h, 10.0, CLAHE_TILES, CLAHE_TILES);
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  clahe_tile_hist(GroupBlock(), sh, I, q, blockIdx.x % CLAHE_TILES, blockIdx.x / CLAHE_TILES);
+  __syncthreads();
+  if (threadIdx.x == 0) clahe_tile_lut(sh, q, luts + ((size_t)blockIdx.y * CLAHE_TILES * CLAHE_TILES + blockIdx.x) * 256);
+}
+
+__global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
+                                                     const uint8_t *luts) {
+  const PreJob job = jobs[blockIdx.y];
+  if (job.method != 2) return;
+  const ImgView I = raw_tab[job.raw];
+  const ImgView D = pyr_tab[job.pyr].lv[0];
+  const ClaheGeom q = clahe_geom(I.w, I.h, 10.0, CLAHE_TILES, CLAHE_TILES);
+  const uint8_t *L = luts + (size_t)blockIdx.y * CLAHE_TILES * CLAHE_TILES * 256;
+  int r0 = (int)((long long)I.h * blockIdx.x / gridDim.x), r1 = (int)((long long)I.h * (blockIdx.x + 1) / gridDim.x);
+  for (int y = r0; y < r1; y++)
+    for (int x = threadIdx.x; x < I.w; x += blockDim.x)
+      ((uint8_t *)D.p)[(size_t)y * D.pitch + x] = clahe_pixel(L, q, x, y, I.p[(size_t)y * I.pitch + x]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// pyramid: level l-1 -> level l for every image of the launch
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_pyrdown(const PreJob *jobs, const PyrDesc *pyr_tab, int level) {
+  const PyrDesc &P = pyr_tab[jobs[blockIdx.z].pyr];
+  if (level >= P.nlv) return;
+  const ImgView S = P.lv[level - 1], D = P.lv[level];
+  int ox0 = blockIdx.x * PD_TW, oy0 = blockIdx.y * PD_TH;
+  if (ox0 >= D.w || oy0 >= D.h) return;
+  __shared__ PyrSmem s;
+  pyrdown_tile(GroupBlock(), s, S, (uint8_t *)D.p, D.w, D.h, D.pitch, ox0, oy0);
+}
+
+cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
+                              unsigned *hist, unsigned *ticket, uint8_t *lut, uint8_t *clahe_lut, int max_w, int max_h,
+                              int any_hist, int any_clahe, int max_levels) {
+  if (njobs <= 0) return cudaSuccess;
+  if (any_hist) k_hist<<<dim3(HIST_BANDS, njobs), 256, 0, st>>>(jobs, raw_tab, hist, ticket, lut);
+  k_lut_apply<<<dim3(HIST_BANDS, njobs), 256, 0, st>>>(jobs, raw_tab, pyr_tab, lut);
+  if (any_clahe) {
+    k_clahe_tiles<<<dim3(CLAHE_TILES * CLAHE_TILES, njobs), 256, 0, st>>>(jobs, raw_tab, clahe_lut);
+    k_clahe_apply<<<dim3(HIST_BANDS * 2, njobs), 256, 0, st>>>(jobs, raw_tab, pyr_tab, clahe_lut);
+  }
+  int w = max_w, h = max_h;
+  for (int l = 1; l < max_levels; l++) {
+    w = (w + 1) / 2;
+    h = (h + 1) / 2;
+    k_pyrdown<<<dim3((w + PD_TW - 1) / PD_TW, (h + PD_TH - 1) / PD_TH, njobs), 256, 0, st>>>(jobs, pyr_tab, l);
+  }
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// FAST on grid cells. grid = (max tiles per cell, jobs). The last tile of a job to finish compacts the job's list into
+// mapped host memory, so the host sees exactly `count` words per cell and nothing else crosses PCIe.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_fast(const FastJob *jobs, const int *thresholds, const PyrDesc *pyr_tab, uint32_t *out_dev,
+                                              unsigned *count_dev, unsigned *ticket_dev, uint32_t *out_host, unsigned *count_host) {
+  const FastJob job = jobs[blockIdx.y];
+  const int tiles_x = (job.w + FT_W - 1) / FT_W, tiles_y = (job.h + FT_H - 1) / FT_H;
+  const int ntiles = tiles_x * tiles_y;
+  if ((int)blockIdx.x >= ntiles) return;
+  __shared__ FastSmem s;
+  __shared__ int s_last;
+  const ImgView I = pyr_tab[job.img].lv[0];
+  fast_tile(GroupBlock(), s, I, job, (blockIdx.x % tiles_x) * FT_W, (blockIdx.x / tiles_x) * FT_H, thresholds[blockIdx.y], out_dev,
+            &count_dev[blockIdx.y]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(&ticket_dev[blockIdx.y], 1u) == (unsigned)ntiles - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  unsigned n = __ldcg(&count_dev[blockIdx.y]);
+  if (n > (unsigned)job.out_cap) n = job.out_cap;
+  for (unsigned i = threadIdx.x; i < n; i += blockDim.x) out_host[job.out_off + i] = __ldcg(&out_dev[job.out_off + i]);
+  if (threadIdx.x == 0) {
+    count_host[blockIdx.y] = n;
+    count_dev[blockIdx.y] = 0;
+    ticket_dev[blockIdx.y] = 0;
+  }
+}
+
+cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max_cell_w, int max_cell_h, const PyrDesc *pyr_tab,
+                        int, const int *thresholds, uint32_t *out_dev, unsigned *count_dev, unsigned *ticket_dev,
+                        uint32_t *out_host, unsigned *count_host) {
+  if (njobs <= 0) return cudaSuccess;
+  int tiles = ((max_cell_w + FT_W - 1) / FT_W) * ((max_cell_h + FT_H - 1) / FT_H);
+  k_fast<<<dim3(tiles, njobs), 256, 0, st>>>(jobs, thresholds, pyr_tab, out_dev, count_dev, ticket_dev, out_host, count_host);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// cornerSubPix: one warp per point
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int WARPS_PER_BLOCK = 4;
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_subpix(const SubpixItem *items, int n, const PyrDesc *pyr_tab,
+                                                                 const float *mask, float *out_xy, float *out_xy_dev) {
+  __shared__ SubpixSmem sm[WARPS_PER_BLOCK];
+  __shared__ float smask[SP_N];
+  for (int i = threadIdx.x; i < SP_N; i += blockDim.x) smask[i] = mask[i];
+  __syncthreads();
+  const int wid = threadIdx.x >> 5, i = blockIdx.x * WARPS_PER_BLOCK + wid;
+  if (i >= n) return;
+  const SubpixItem it = items[i];
+  float x = it.x, y = it.y;
+  subpix_point(GroupWarp(), sm[wid], pyr_tab[it.pyr].lv[0], smask, 20, 0.001 * 0.001, x, y);
+  if ((threadIdx.x & 31) == 0) {
+    out_xy[2 * i] = x;
+    out_xy[2 * i + 1] = y;
+    if (out_xy_dev) {
+      out_xy_dev[2 * i] = x;
+      out_xy_dev[2 * i + 1] = y;
+    }
+  }
+}
+
+cudaError_t launch_subpix(cudaStream_t st, const SubpixItem *items, int n, const PyrDesc *pyr_tab, const float *mask_dev,
+                          float *out_xy, float *out_xy_dev) {
+  if (n <= 0) return cudaSuccess;
+  k_subpix<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, mask_dev, out_xy,
+                                                                                      out_xy_dev);
+  return cudaGetLastError();
+}
+
+cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st) {
+  // the Gaussian weights are evaluated with the host's expf, as the CPU tracker does (App. A.5)
+  float m[SP_N];
+  for (int i = 0; i < SP_W; i++) {
+    float y = (float)(i - SP_WIN) / SP_WIN;
+    float vy = expf(-y * y);
+    for (int j = 0; j < SP_W; j++) {
+      float x = (float)(j - SP_WIN) / SP_WIN;
+      m[i * SP_W + j] = (float)(vy * expf(-x * x));
+    }
+  }
+  cudaError_t e = cudaMemcpyAsync(mask_dev, m, sizeof(m), cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return e;
+  return cudaStreamSynchronize(st);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// pyramidal LK: one warp per feature, all levels inside the kernel
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
+                                                             const float *init_from_dev, int max_count, double eps_sq,
+                                                             LkOut *out_host, uint8_t *status_host, LkOut *out_dev,
+                                                             uint8_t *status_dev) {
+  __shared__ LkSmem sm[WARPS_PER_BLOCK];
+  const int wid = threadIdx.x >> 5, i = blockIdx.x * WARPS_PER_BLOCK + wid;
+  if (i >= n) return;
+  const LkItem it = items[i];
+  float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
+  if (init_from_dev) {
+    px = nx = init_from_dev[2 * i];
+    py = ny = init_from_dev[2 * i + 1];
+  }
+  const PyrDesc &P0 = pyr_tab[it.prev_pyr], &P1 = pyr_tab[it.next_pyr];
+  LkParams prm;
+  prm.max_level = P0.nlv - 1;
+  prm.max_count = max_count;
+  prm.eps_sq = eps_sq;
+  prm.min_eig = 1e-4;
+  uint8_t status;
+  lk_track_point(GroupWarp(), sm[wid], P0.lv, P1.lv, prm, px, py, nx, ny, status);
+  if ((threadIdx.x & 31) == 0) {
+    LkOut o{nx, ny};
+    out_host[i] = o;
+    status_host[i] = status;
+    out_dev[i] = o;
+    status_dev[i] = status;
+  }
+}
+
+cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
+                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev) {
+  if (n <= 0) return cudaSuccess;
+  k_lk<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, init_from_dev, max_count,
+                                                                                  eps * eps, out_host, status_host, out_dev,
+                                                                                  status_dev);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// undistort + fundamental-matrix RANSAC: one block per (rig, camera)
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int RANSAC_THREADS = 128;
+
+__global__ void __launch_bounds__(RANSAC_THREADS) k_ransac(const RansacJob *jobs, const LkItem *items, const LkOut *lk,
+                                                           const uint8_t *status, const CamModel *cams, float *p0n, float *p1n,
+                                                           float *p1n_host, uint8_t *mask_host, uint8_t *mask_dev) {
+  extern __shared__ float dyn[];
+  __shared__ RansacSmem s;
+  const RansacJob job = jobs[blockIdx.x];
+  const int n = job.n;
+  const CamModel c0 = cams[job.cam0], c1 = cams[job.cam1];
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int k = job.off + i;
+    float a, b;
+    undistort_point(c0, items[k].px, items[k].py, a, b);
+    p0n[2 * k] = a;
+    p0n[2 * k + 1] = b;
+    const LkOut o = lk[k];
+    undistort_point(c1, o.x, o.y, a, b);
+    p1n[2 * k] = a;
+    p1n[2 * k + 1] = b;
+    p1n_host[2 * k] = a;
+    p1n_host[2 * k + 1] = b;
+  }
+  __syncthreads();
+  const bool run = job.run && n >= 7;
+  if (run) {
+    s.x0 = dyn;
+    s.y0 = dyn + n;
+    s.x1 = dyn + 2 * n;
+    s.y1 = dyn + 3 * n;
+    __syncthreads();
+    ransac_job(GroupBlock(), s, p0n + 2 * job.off, p1n + 2 * job.off, n, job.thr, 0.999, 1000, mask_dev + job.off);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x)
+    mask_host[job.off + i] = run ? (uint8_t)(status[job.off + i] && mask_dev[job.off + i]) : (uint8_t)0;
+}
+
+cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk_dev,
+                          const uint8_t *status_dev, const CamModel *cams_dev, float *p0n_dev, float *p1n_dev, float *p1n_host,
+                          uint8_t *mask_host, uint8_t *mask_dev) {
+  if (njobs <= 0) return cudaSuccess;
+  size_t dyn = (size_t)4 * max_n * sizeof(float);
+  static size_t configured = 0;
+  if (dyn > configured && dyn + sizeof(RansacSmem) > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(k_ransac, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    if (e != cudaSuccess) return e;
+    configured = dyn;
+  }
+  k_ransac<<<njobs, RANSAC_THREADS, dyn, st>>>(jobs, items, lk_dev, status_dev, cams_dev, p0n_dev, p1n_dev, p1n_host, mask_host,
+                                               mask_dev);
+  return cudaGetLastError();
+}
+
+}  // namespace uvio

@@ -1,0 +1,68 @@
+// Host-callable launch wrappers of the sm_100a kernels (implemented in kernels.cu).  Plain C++ types only.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "fast_body.h"
+#include "ransac_body.h"
+#include "simt.h"
+
+namespace uvio {
+
+constexpr int MAX_LEVELS = 8;          // pyramid levels per image (level 0 included)
+constexpr int HIST_BANDS = 16;         // row bands (thread blocks) per image in the histogram / LUT passes
+constexpr int CLAHE_TILES = 8;         // TrackKLT.cpp:62 (8x8 tiles)
+
+struct PyrDesc {                       // one image pyramid resident in HBM
+  ImgView lv[MAX_LEVELS];
+  int nlv;                             // levels built (max_level + 1)
+};
+
+struct PreJob {                        // one image to pre-process this frame
+  int raw;                             // index into the raw-image table (uploaded frame)
+  int pyr;                             // destination pyramid
+  int method;                          // 0 none, 1 equalizeHist, 2 CLAHE   (TrackBase::HistogramMethod)
+};
+
+struct SubpixItem { float x, y; int pyr; int pad; };
+struct LkItem { float px, py, nx, ny; int prev_pyr, next_pyr; };
+struct LkOut { float x, y; };
+
+struct RansacJob {
+  int off, n;                          // slice of the LK item / output arrays (the points of one camera of one rig)
+  int cam0, cam1;                      // camera models used to undistort the old / new points
+  double thr;                          // 2.0 / max focal length (TrackKLT.cpp:870-873)
+  int run;                             // 0: fewer than 10 points -> mask stays zero (TrackKLT.cpp:848-852), only undistort
+};
+
+struct Workspace;                      // device-side scratch owned by the engine (hist, LUTs, tickets)
+
+// ---- image-wide passes ------------------------------------------------------------------------------------------------
+// equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels
+cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const ImgView *raw_tab_dev,
+                              const PyrDesc *pyr_tab_dev, unsigned *hist_dev /*njobs*256, zero*/, unsigned *ticket_dev,
+                              uint8_t *lut_dev /*njobs*256*/, uint8_t *clahe_lut_dev /*njobs*64*256*/, int max_w, int max_h,
+                              int any_hist, int any_clahe, int max_levels);
+
+// ---- detection ----------------------------------------------------------------------------------------------------------
+// FAST + NMS on grid cells; compacts each job's corner list into out_host (mapped pinned) and writes its count.
+cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max_cell_w, int max_cell_h, const PyrDesc *pyr_tab_dev,
+                        int threshold_unused, const int *thresholds /*per job*/, uint32_t *out_dev, unsigned *count_dev,
+                        unsigned *ticket_dev, uint32_t *out_host, unsigned *count_host);
+
+cudaError_t launch_subpix(cudaStream_t st, const SubpixItem *items, int n, const PyrDesc *pyr_tab_dev, const float *mask_dev,
+                          float *out_xy /*2n*/, float *out_xy_dev /*2n, may be null*/);
+
+// ---- tracking -----------------------------------------------------------------------------------------------------------
+// If init_from_dev != null, item i takes (px,py,nx,ny) from init_from_dev[2*i..] (used to chain subpix -> stereo LK).
+cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc *pyr_tab_dev, const float *init_from_dev,
+                      int max_count, double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev);
+
+// undistort old/new points of every job and run the fundamental-matrix RANSAC; mask = klt_status && inlier
+cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk_dev,
+                          const uint8_t *status_dev, const CamModel *cams_dev, float *p0n_dev, float *p1n_dev,
+                          float *p1n_host, uint8_t *mask_host, uint8_t *mask_dev);
+
+cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st);
+
+}  // namespace uvio

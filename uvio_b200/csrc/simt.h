@@ -1,0 +1,117 @@
+// Execution-group abstraction shared by every kernel body in this directory.
+//
+// Kernel bodies are written once as "phase" code: loops of the form
+//     for (int i = g.lane(); i < n; i += g.size()) { ... }   separated by   g.sync();
+// On the device `g` is a warp (GroupWarp) or a thread block (GroupBlock).  tests/hostsim compiles the very same bodies
+// with g++ and runs them with GroupSeq (one lane, sync = no-op) so the arithmetic can be checked against OpenCV on a
+// machine without a GPU.  GroupSeq is test scaffolding only: the product library (libuvio_klt.so) is built by nvcc,
+// contains device code only, and refuses to load without a CUDA device.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define UVIO_HD __host__ __device__ __forceinline__
+#else
+#define UVIO_HD inline
+#endif
+
+namespace uvio {
+
+struct GroupSeq {
+  UVIO_HD int lane() const { return 0; }
+  UVIO_HD int size() const { return 1; }
+  UVIO_HD void sync() const {}
+};
+
+#ifdef __CUDACC__
+struct GroupWarp {
+  __device__ __forceinline__ int lane() const { return threadIdx.x & 31; }
+  __device__ __forceinline__ int size() const { return 32; }
+  __device__ __forceinline__ void sync() const { __syncwarp(); }
+};
+struct GroupBlock {
+  __device__ __forceinline__ int lane() const { return threadIdx.x; }
+  __device__ __forceinline__ int size() const { return blockDim.x; }
+  __device__ __forceinline__ void sync() const { __syncthreads(); }
+};
+#endif
+
+// cvRound: round half to even, float -> int.
+UVIO_HD int round_f2i(float v) {
+#ifdef __CUDA_ARCH__
+  return __float2int_rn(v);
+#else
+  return (int)lrintf(v);
+#endif
+}
+UVIO_HD int round_d2i(double v) {
+#ifdef __CUDA_ARCH__
+  return __double2int_rn(v);
+#else
+  return (int)lrint(v);
+#endif
+}
+UVIO_HD int floor_f2i(float v) { return (int)floorf(v); }
+UVIO_HD uint8_t sat_u8(int v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+UVIO_HD int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// Non-contracted fp32 arithmetic: the OpenCV baseline build the oracle pins (SSE3, no FMA) never fuses a*b+c.
+// The .cu files are also compiled with -fmad=false; these helpers make the intent explicit where it matters.
+UVIO_HD float fmul(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __fmul_rn(a, b);
+#else
+  return a * b;
+#endif
+}
+UVIO_HD float fadd(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __fadd_rn(a, b);
+#else
+  return a + b;
+#endif
+}
+UVIO_HD float fsub(float a, float b) {
+#ifdef __CUDA_ARCH__
+  return __fsub_rn(a, b);
+#else
+  return a - b;
+#endif
+}
+UVIO_HD double dmul(double a, double b) {
+#ifdef __CUDA_ARCH__
+  return __dmul_rn(a, b);
+#else
+  return a * b;
+#endif
+}
+UVIO_HD double dadd(double a, double b) {
+#ifdef __CUDA_ARCH__
+  return __dadd_rn(a, b);
+#else
+  return a + b;
+#endif
+}
+UVIO_HD double dsub(double a, double b) {
+#ifdef __CUDA_ARCH__
+  return __dsub_rn(a, b);
+#else
+  return a - b;
+#endif
+}
+
+// BORDER_REFLECT_101 (gfedcb|abcdefgh|gfedcba), any distance.
+UVIO_HD int reflect101(int p, int len) {
+  if (len == 1) return 0;
+  while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+  return p;
+}
+
+// A pitched 8-bit image view (one pyramid level).
+struct ImgView {
+  const uint8_t *p;
+  int w, h, pitch;
+};
+
+}  // namespace uvio
