@@ -1,0 +1,35 @@
+// TEST SCAFFOLDING ONLY. A stand-in for the CUDA runtime so that the *host* logic of the tracker (engine.cpp, abi.cpp)
+// can be exercised by `pytest -m "not gpu"` on a machine without a GPU: device memory becomes heap memory and the
+// launch_* functions are replaced by tests/hostsim/launch_sim.cpp, which runs the same kernel bodies with GroupSeq.
+// The product library is built by nvcc against the real runtime and never sees this file.
+#pragma once
+#include <stdlib.h>
+#include <string.h>
+
+typedef int cudaError_t;
+typedef void *cudaStream_t;
+enum { cudaSuccess = 0, cudaErrorInvalidDevice = 101 };
+enum cudaMemcpyKind { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2 };
+enum { cudaHostAllocMapped = 2, cudaStreamNonBlocking = 1 };
+
+static inline cudaError_t cudaMalloc(void **p, size_t n) { *p = malloc(n ? n : 1); return *p ? 0 : 2; }
+static inline cudaError_t cudaFree(void *p) { free(p); return 0; }
+static inline cudaError_t cudaMemset(void *p, int v, size_t n) { memset(p, v, n); return 0; }
+static inline cudaError_t cudaMemcpy(void *d, const void *s, size_t n, int) { memcpy(d, s, n); return 0; }
+static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, int, cudaStream_t) { memcpy(d, s, n); return 0; }
+static inline cudaError_t cudaMemcpy2D(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, int) {
+  for (size_t y = 0; y < h; y++) memcpy((char *)d + y * dp, (const char *)s + y * sp, w);
+  return 0;
+}
+static inline cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, int k, cudaStream_t) {
+  return cudaMemcpy2D(d, dp, s, sp, w, h, k);
+}
+static inline cudaError_t cudaHostAlloc(void **p, size_t n, unsigned) { *p = calloc(n ? n : 1, 1); return *p ? 0 : 2; }
+static inline cudaError_t cudaFreeHost(void *p) { free(p); return 0; }
+static inline cudaError_t cudaHostGetDevicePointer(void **d, void *h, unsigned) { *d = h; return 0; }
+static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }
+static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned) { *s = (void *)1; return 0; }
+static inline cudaError_t cudaStreamDestroy(cudaStream_t) { return 0; }
+static inline cudaError_t cudaSetDevice(int) { return 0; }
+static inline cudaError_t cudaGetDeviceCount(int *n) { *n = 1; return 0; }
+static inline cudaError_t cudaGetLastError() { return 0; }

@@ -1,0 +1,130 @@
+// TEST SCAFFOLDING ONLY — see tests/hostsim/cuda_runtime.h. CPU stand-ins for the launch_* wrappers of kernels.cu: the
+// same *_body.h code, one lane (GroupSeq), looping over what would be thread blocks / warps.
+#include <vector>
+
+#include "../../uvio_b200/csrc/kernels.h"
+#include "../../uvio_b200/csrc/lk_body.h"
+#include "../../uvio_b200/csrc/subpix_body.h"
+
+namespace uvio {
+
+cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab, unsigned *,
+                              unsigned *, uint8_t *, uint8_t *, int, int, int, int, int) {
+  GroupSeq g;
+  for (int j = 0; j < njobs; j++) {
+    const ImgView I = raw_tab[jobs[j].raw];
+    const PyrDesc &P = pyr_tab[jobs[j].pyr];
+    uint8_t *d0 = (uint8_t *)P.lv[0].p;
+    if (jobs[j].method == 1) {
+      unsigned hist[256] = {0};
+      hist_rows(g, hist, I, 0, I.h);
+      uint8_t lut[256];
+      equalize_lut(hist, I.w * I.h, lut);
+      lut_rows(g, lut, I, d0, P.lv[0].pitch, 0, I.h);
+    } else if (jobs[j].method == 2) {
+      ClaheGeom q = clahe_geom(I.w, I.h, 10.0, CLAHE_TILES, CLAHE_TILES);
+      std::vector<uint8_t> luts(CLAHE_TILES * CLAHE_TILES * 256);
+      for (int t = 0; t < CLAHE_TILES * CLAHE_TILES; t++) {
+        unsigned hist[256] = {0};
+        clahe_tile_hist(g, hist, I, q, t % CLAHE_TILES, t / CLAHE_TILES);
+        clahe_tile_lut(hist, q, luts.data() + t * 256);
+      }
+      for (int y = 0; y < I.h; y++)
+        for (int x = 0; x < I.w; x++) d0[(size_t)y * P.lv[0].pitch + x] = clahe_pixel(luts.data(), q, x, y, I.p[(size_t)y * I.pitch + x]);
+    } else {
+      for (int y = 0; y < I.h; y++) memcpy(d0 + (size_t)y * P.lv[0].pitch, I.p + (size_t)y * I.pitch, I.w);
+    }
+    PyrSmem s;
+    for (int l = 1; l < P.nlv; l++)
+      for (int oy = 0; oy < P.lv[l].h; oy += PD_TH)
+        for (int ox = 0; ox < P.lv[l].w; ox += PD_TW)
+          pyrdown_tile(g, s, P.lv[l - 1], (uint8_t *)P.lv[l].p, P.lv[l].w, P.lv[l].h, P.lv[l].pitch, ox, oy);
+  }
+  return 0;
+}
+
+cudaError_t launch_fast(cudaStream_t, const FastJob *jobs, int njobs, int, int, const PyrDesc *pyr_tab, int, const int *thresholds,
+                        uint32_t *, unsigned *, unsigned *, uint32_t *out_host, unsigned *count_host) {
+  GroupSeq g;
+  FastSmem s;
+  for (int j = 0; j < njobs; j++) {
+    const FastJob job = jobs[j];
+    unsigned count = 0;
+    for (int ty = 0; ty < job.h; ty += FT_H)
+      for (int tx = 0; tx < job.w; tx += FT_W) fast_tile(g, s, pyr_tab[job.img].lv[0], job, tx, ty, thresholds[j], out_host, &count);
+    count_host[j] = count;
+  }
+  return 0;
+}
+
+static float g_mask[SP_N];
+cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t) {
+  for (int i = 0; i < SP_W; i++) {
+    float y = (float)(i - SP_WIN) / SP_WIN;
+    float vy = expf(-y * y);
+    for (int j = 0; j < SP_W; j++) {
+      float x = (float)(j - SP_WIN) / SP_WIN;
+      mask_dev[i * SP_W + j] = (float)(vy * expf(-x * x));
+    }
+  }
+  return 0;
+}
+
+cudaError_t launch_subpix(cudaStream_t, const SubpixItem *items, int n, const PyrDesc *pyr_tab, const float *mask, float *out_xy,
+                          float *out_xy_dev) {
+  GroupSeq g;
+  SubpixSmem s;
+  for (int i = 0; i < n; i++) {
+    float x = items[i].x, y = items[i].y;
+    subpix_point(g, s, pyr_tab[items[i].pyr].lv[0], mask, 20, 0.001 * 0.001, x, y);
+    out_xy[2 * i] = x;
+    out_xy[2 * i + 1] = y;
+    if (out_xy_dev) { out_xy_dev[2 * i] = x; out_xy_dev[2 * i + 1] = y; }
+  }
+  return 0;
+}
+
+cudaError_t launch_lk(cudaStream_t, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
+                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev) {
+  GroupSeq g;
+  LkSmem s;
+  for (int i = 0; i < n; i++) {
+    const LkItem it = items[i];
+    float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
+    if (init_from_dev) { px = nx = init_from_dev[2 * i]; py = ny = init_from_dev[2 * i + 1]; }
+    const PyrDesc &P0 = pyr_tab[it.prev_pyr], &P1 = pyr_tab[it.next_pyr];
+    LkParams prm{P0.nlv - 1, max_count, eps * eps, 1e-4};
+    uint8_t st;
+    lk_track_point(g, s, P0.lv, P1.lv, prm, px, py, nx, ny, st);
+    out_host[i] = out_dev[i] = LkOut{nx, ny};
+    status_host[i] = status_dev[i] = st;
+  }
+  return 0;
+}
+
+cudaError_t launch_ransac(cudaStream_t, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk,
+                          const uint8_t *status, const CamModel *cams, float *p0n, float *p1n, float *p1n_host, uint8_t *mask_host,
+                          uint8_t *mask_dev) {
+  GroupSeq g;
+  std::vector<float> buf((size_t)4 * max_n + 4);
+  for (int j = 0; j < njobs; j++) {
+    const RansacJob job = jobs[j];
+    for (int i = 0; i < job.n; i++) {
+      int k = job.off + i;
+      undistort_point(cams[job.cam0], items[k].px, items[k].py, p0n[2 * k], p0n[2 * k + 1]);
+      undistort_point(cams[job.cam1], lk[k].x, lk[k].y, p1n[2 * k], p1n[2 * k + 1]);
+      p1n_host[2 * k] = p1n[2 * k];
+      p1n_host[2 * k + 1] = p1n[2 * k + 1];
+    }
+    bool run = job.run && job.n >= 7;
+    if (run) {
+      RansacSmem s;
+      s.x0 = buf.data(); s.y0 = s.x0 + job.n; s.x1 = s.y0 + job.n; s.y1 = s.x1 + job.n;
+      ransac_job(g, s, p0n + 2 * job.off, p1n + 2 * job.off, job.n, job.thr, 0.999, 1000, mask_dev + job.off);
+    }
+    for (int i = 0; i < job.n; i++) mask_host[job.off + i] = run ? (uint8_t)(status[job.off + i] && mask_dev[job.off + i]) : 0;
+  }
+  return 0;
+}
+
+}  // namespace uvio

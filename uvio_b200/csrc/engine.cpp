@@ -15,6 +15,8 @@
 #include <memory>
 
 #include "hostlogic.h"
+#include "lk_body.h"
+#include "subpix_body.h"
 
 namespace uvio {
 
@@ -214,3 +216,755 @@ CamState *Rig::find_cam(size_t id) {
   auto it = cam_index.find(id);
   return it == cam_index.end() ? nullptr : &cams[it->second];
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// One "unit" = what the reference tracks as a whole: a stereo pair (feed_stereo) or a single camera (feed_monocular).
+// ---------------------------------------------------------------------------------------------------------------------
+struct Side {                         // one camera of a unit during one feed
+  CamState *cam = nullptr;
+  int msg = -1;                       // index in the message
+  int det_slot = 0;                   // pyramid slot detection runs on (last frame; current frame on the first feed)
+  const uint8_t *det_mask = nullptr;  // mask of that image (null = all zeros)
+  OccState occ;
+  bool detect = false;                // FAST jobs were emitted for this side (left: final; right: speculative)
+  GridGeom geom;
+  std::vector<std::pair<int, int>> cells;              // cells FAST ran on
+  std::vector<int> job_of_cell;                        // job index per cell (-1: cell skipped, Grider_GRID.h:117)
+  std::vector<std::vector<KeyPointLite>> top;          // per cell: top-K in sort order (no mask test yet)
+  std::vector<int> sp_of_cell;                         // first sub-pixel item of each cell
+  std::vector<Pt> pts;                                 // pts_old after detection (input of the temporal LK)
+  std::vector<size_t> ids;
+  int lk_off = 0, lk_n = 0;                            // slice in the temporal LK arrays
+  bool lk_run = false;                                 // >= 10 points (TrackKLT.cpp:848)
+};
+
+struct Unit {
+  Rig *rig = nullptr;
+  FeedRequest *req = nullptr;
+  bool stereo = false, first = false;
+  Side L, R;
+  std::vector<KeyPointLite> selL;     // left corners that passed the mask test, in cell order (sub-pixel items sp0L..)
+  int sp0L = 0, lk0 = 0;              // first sub-pixel item / first stereo-LK item of selL
+  bool failed = false;
+};
+
+static const uint8_t *mask_ptr(CamState &c, int slot) { return c.mask_nonzero[slot] ? c.mask[slot].data() : nullptr; }
+
+// emit FAST jobs for the cells of one side
+static void emit_fast_jobs(Context *ctx, Side &s, int threshold, int &njobs, size_t &nwords) {
+  const int cols = s.cam->w, rows = s.cam->h;
+  s.job_of_cell.assign(s.cells.size(), -1);
+  for (size_t r = 0; r < s.cells.size(); r++) {
+    int x = s.cells[r].first * s.geom.size_x, y = s.cells[r].second * s.geom.size_y;
+    if (x + s.geom.size_x > cols || y + s.geom.size_y > rows) continue;   // Grider_GRID.h:117
+    FastJob j;
+    j.img = s.cam->pyr[s.det_slot];
+    j.x0 = x; j.y0 = y; j.w = s.geom.size_x; j.h = s.geom.size_y;
+    j.out_off = (int)nwords;
+    j.out_cap = ((j.w + 1) / 2) * ((j.h + 1) / 2);
+    ctx->fast_jobs.h[njobs] = j;
+    ctx->fast_thr.h[njobs] = threshold;
+    s.job_of_cell[r] = njobs++;
+    nwords += (size_t)j.out_cap;
+  }
+}
+
+// Phase A: occupancy passes and the list of cells to run FAST on.
+static void phase_a(Unit &u) {
+  const Params &P = u.rig->prm;
+  Side &L = u.L;
+  const int thr = std::min(20, (int)(0.5 * P.num_features));
+  {
+    CamState &c = *L.cam;
+    L.det_slot = u.first ? c.cur : 1 - c.cur;
+    L.det_mask = mask_ptr(c, L.det_slot);
+    occ_init(L.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y);
+    if (!u.first) occ_feed(L.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), L.det_mask, c.paint.data(), nullptr);
+    const int need = P.num_features - (int)L.occ.pts.size();
+    // mono returns when need < thr (TrackKLT.cpp:470); stereo detects when need > thr (:609)
+    L.detect = u.stereo ? (need > thr) : !(need < thr);
+    L.cells.clear();
+    if (L.detect) {
+      valid_cells(L.occ, L.det_mask, P.num_features, L.cells);
+      L.geom = grider_geom(c.w, c.h, P.num_features, P.grid_x, P.grid_y);
+    }
+  }
+  if (u.stereo) {
+    Side &R = u.R;
+    CamState &c = *R.cam;
+    R.det_slot = u.first ? c.cur : 1 - c.cur;
+    R.det_mask = mask_ptr(c, R.det_slot);
+    occ_init(R.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y);
+    // The right pass (:722-780) runs after the left detection appended new stereo points to pts1, but it is a plain
+    // in-order loop: its first |pts_last| steps only see the old points, and the new ids are fresh, so they cannot
+    // change the stereo-id exemption of an old point. Run those steps now; phase C continues the same loop.
+    std::unordered_set<size_t> stereo_ids(L.occ.ids.begin(), L.occ.ids.end());
+    if (!u.first) occ_feed(R.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), R.det_mask, c.paint.data(), &stereo_ids);
+    // Cells: new points only raise counts and lower the need, so the cells valid now are a superset of the cells the
+    // reference will extract from; FAST + top-K + sub-pixel run on the superset, phase C keeps the right subset.
+    const int need = P.num_features - (int)R.occ.pts.size();
+    R.detect = need > thr;
+    R.cells.clear();
+    if (R.detect) {
+      valid_cells(R.occ, R.det_mask, P.num_features, R.cells);
+      R.geom = grider_geom(c.w, c.h, P.num_features, P.grid_x, P.grid_y);
+    }
+  }
+}
+
+// Phase B: per-cell top-K (reference sort order), left mask test, sub-pixel / stereo-LK items.
+static void phase_b(Context *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint32_t> &tmp, std::vector<KeyPointLite> &kps) {
+  for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+    Side &s = side ? u.R : u.L;
+    s.top.assign(s.cells.size(), {});
+    if (!s.detect) continue;
+    for (size_t r = 0; r < s.cells.size(); r++) {
+      int j = s.job_of_cell[r];
+      if (j < 0) continue;
+      const FastJob &job = ctx->fast_jobs.h[j];
+      cell_top_k(ctx->fast_out.h + job.out_off, ctx->fast_cnt.h[j], job.x0, job.y0, s.geom.per_cell, tmp, kps, s.top[r]);
+    }
+  }
+  // left: mask test against mask_updated = mask | painted boxes (Grider_GRID.h:142-148), then sub-pixel
+  Side &L = u.L;
+  u.selL.clear();
+  u.sp0L = nsp;
+  if (L.detect) {
+    const int cols = L.cam->w, rows = L.cam->h;
+    const uint8_t *paint = L.cam->paint.data();
+    for (auto &cell : L.top)
+      for (auto &k : cell) {
+        int x = (int)k.x, y = (int)k.y;
+        if (x < 0 || x > cols || y < 0 || y > rows) continue;
+        size_t at = (size_t)y * cols + x;
+        if ((L.det_mask && L.det_mask[at] > 127) || paint[at] > 127) continue;
+        u.selL.push_back(k);
+      }
+  }
+  occ_unpaint(L.occ, L.cam->paint.data());
+  for (auto &k : u.selL) ctx->sp_items.h[nsp++] = SubpixItem{k.x, k.y, L.cam->pyr[L.det_slot], 0};
+  u.lk0 = nlk;
+  if (u.stereo) {
+    // left -> right LK of every selected left corner, chained on the sub-pixel output (item i <-> sub-pixel item i)
+    for (size_t i = 0; i < u.selL.size(); i++)
+      ctx->lk_items.h[nlk++] = LkItem{0, 0, 0, 0, L.cam->pyr[L.det_slot], u.R.cam->pyr[u.R.det_slot]};
+  }
+}
+
+static void phase_b_right(Context *ctx, Unit &u, int &nsp) {
+  Side &R = u.R;
+  R.sp_of_cell.assign(R.cells.size(), -1);
+  if (!R.detect) return;
+  for (size_t r = 0; r < R.cells.size(); r++) {
+    R.sp_of_cell[r] = nsp;
+    for (auto &k : R.top[r]) ctx->sp_items.h[nsp++] = SubpixItem{k.x, k.y, R.cam->pyr[R.det_slot], 0};
+  }
+}
+
+// Phase C: finish the detection with the refined corners (min-distance reject, ids, right side), then either store the
+// first-frame result or emit the temporal LK / RANSAC work.
+static int phase_c_detect(Context *ctx, Unit &u) {
+  const Params &P = u.rig->prm;
+  Side &L = u.L;
+  const int thr = std::min(20, (int)(0.5 * P.num_features));
+  std::vector<Pt> refined(u.selL.size());
+  for (size_t i = 0; i < u.selL.size(); i++) refined[i] = Pt{ctx->sp_out.h[2 * (u.sp0L + i)], ctx->sp_out.h[2 * (u.sp0L + i) + 1]};
+  std::vector<int> keep;
+  close_reject(L.occ, refined.data(), refined.size(), keep);       // TrackKLT.cpp:497-512 / :635-650
+  std::vector<Pt> new_r;
+  std::vector<size_t> new_r_ids;
+  if (!u.stereo) {
+    for (int i : keep) {                                            // :519-527
+      L.occ.pts.push_back(refined[i]);
+      L.occ.ids.push_back(++u.rig->currid);
+    }
+  } else {
+    Side &R = u.R;
+    const int cols0 = L.cam->w, rows0 = L.cam->h, cols1 = R.cam->w, rows1 = R.cam->h;
+    for (int i : keep) {                                            // :675-708
+      const Pt p0 = refined[i];
+      const LkOut o = ctx->lk_out.h[u.lk0 + i];
+      const bool oob_left = (int)p0.x < 0 || (int)p0.x >= cols0 || (int)p0.y < 0 || (int)p0.y >= rows0;
+      const bool oob_right = (int)o.x < 0 || (int)o.x >= cols1 || (int)o.y < 0 || (int)o.y >= rows1;
+      if (!oob_left && !oob_right && ctx->lk_status.h[u.lk0 + i] == 1) {
+        size_t id = ++u.rig->currid;
+        L.occ.pts.push_back(p0);
+        L.occ.ids.push_back(id);
+        new_r.push_back(Pt{o.x, o.y});
+        new_r_ids.push_back(id);
+      } else if (!oob_left) {
+        L.occ.pts.push_back(p0);
+        L.occ.ids.push_back(++u.rig->currid);
+      }
+    }
+    // right: continue the occupancy loop over the appended stereo points (:722-780), then the right top-up (:784-826)
+    std::unordered_set<size_t> stereo_ids(L.occ.ids.begin(), L.occ.ids.end());
+    occ_feed(R.occ, new_r.data(), new_r_ids.data(), new_r.size(), R.det_mask, R.cam->paint.data(), &stereo_ids);
+    const int need = P.num_features - (int)R.occ.pts.size();
+    if (need > thr) {
+      std::vector<std::pair<int, int>> cells;
+      valid_cells(R.occ, R.det_mask, P.num_features, cells);
+      std::vector<Pt> ext;
+      const uint8_t *paint = R.cam->paint.data();
+      const uint8_t *mask0 = (cols0 == cols1 && rows0 == rows1) ? L.det_mask : nullptr;   // :721 clones mask0 (sic)
+      for (auto &cell : cells) {
+        size_t r = 0;
+        while (r < R.cells.size() && R.cells[r] != cell) r++;
+        if (r == R.cells.size() || !R.detect) return E_ARG;   // cannot happen: R.cells is a superset (phase_a)
+        for (size_t k = 0; k < R.top[r].size(); k++) {
+          const KeyPointLite &kp = R.top[r][k];
+          int x = (int)kp.x, y = (int)kp.y;
+          if (x < 0 || x > cols1 || y < 0 || y > rows1) continue;
+          size_t at = (size_t)y * cols1 + x;
+          if ((mask0 && mask0[at] > 127) || paint[at] > 127) continue;
+          int sp = R.sp_of_cell[r] + (int)k;
+          ext.push_back(Pt{ctx->sp_out.h[2 * sp], ctx->sp_out.h[2 * sp + 1]});
+        }
+      }
+      close_reject(R.occ, ext.data(), ext.size(), keep);            // :811-825
+      for (int i : keep) {
+        R.occ.pts.push_back(ext[i]);
+        R.occ.ids.push_back(++u.rig->currid);
+      }
+    }
+    occ_unpaint(R.occ, R.cam->paint.data());
+    R.pts.swap(R.occ.pts);
+    R.ids.swap(R.occ.ids);
+  }
+  L.pts.swap(L.occ.pts);
+  L.ids.swap(L.occ.ids);
+  return OK;
+}
+
+static void store_last(Side &s, std::vector<Pt> &pts, std::vector<size_t> &ids) {
+  s.cam->pts_last.swap(pts);
+  s.cam->ids_last.swap(ids);
+  s.cam->have_last = true;
+}
+
+static void emit_temporal(Context *ctx, Unit &u, int &nlk, int &nrs) {
+  for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+    Side &s = side ? u.R : u.L;
+    CamState &c = *s.cam;
+    s.lk_off = nlk;
+    s.lk_n = 0;
+    s.lk_run = s.pts.size() >= 10;                                  // TrackKLT.cpp:848-852
+    if (!s.lk_run) continue;
+    s.lk_n = (int)s.pts.size();
+    for (auto &p : s.pts) ctx->lk_items.h[nlk++] = LkItem{p.x, p.y, p.x, p.y, c.pyr[1 - c.cur], c.pyr[c.cur]};
+    RansacJob j;
+    j.off = s.lk_off;
+    j.n = s.lk_n;
+    j.cam0 = j.cam1 = c.cam_model_idx;
+    j.thr = 2.0 / c.max_focal;                                      // :870-873 (id0 == id1 for the temporal match)
+    j.run = 1;
+    ctx->rs_jobs.h[nrs++] = j;
+  }
+}
+
+// Phase D: merge / filter the matches and produce the feature-database observations (TrackKLT.cpp:143-189, :285-381).
+static void phase_d(Context *ctx, Unit &u) {
+  Rig &rig = *u.rig;
+  Side &L = u.L, &R = u.R;
+  auto new_pt = [&](Side &s, size_t i) { const LkOut o = ctx->lk_out.h[s.lk_off + i]; return Pt{o.x, o.y}; };
+  auto ok = [&](Side &s, size_t i) { return s.lk_run && ctx->rs_mask.h[s.lk_off + i]; };
+  auto add_obs = [&](Side &s, size_t i, size_t id, Pt p) {
+    rig.obs.push_back(Obs{id, s.cam->cam_id, p.x, p.y, ctx->p1n.h[2 * (s.lk_off + i)], ctx->p1n.h[2 * (s.lk_off + i) + 1]});
+  };
+  std::vector<Pt> good_l, good_r;
+  std::vector<size_t> ids_l, ids_r;
+  if (!u.stereo) {
+    CamState &c = *L.cam;
+    if (L.pts.empty()) {                                            // :143-152 (mask_ll empty)
+      store_last(L, good_l, ids_l);
+      return;
+    }
+    const uint8_t *mask = mask_ptr(c, c.cur);                       // :166 tests the current message mask
+    for (size_t i = 0; i < L.pts.size(); i++) {                     // :159-173
+      if (!L.lk_run) break;
+      Pt p = new_pt(L, i);
+      if (p.x < 0 || p.y < 0 || (int)p.x >= c.w || (int)p.y >= c.h) continue;
+      if (mask && mask[(size_t)(int)p.y * c.w + (int)p.x] > 127) continue;
+      if (ok(L, i)) {
+        good_l.push_back(p);
+        ids_l.push_back(L.ids[i]);
+        add_obs(L, i, L.ids[i], p);
+      }
+    }
+    store_last(L, good_l, ids_l);
+    return;
+  }
+  if (L.pts.empty() && R.pts.empty()) {                             // :285-299
+    store_last(L, good_l, ids_l);
+    store_last(R, good_r, ids_r);
+    return;
+  }
+  const int cols_l = L.cam->w, rows_l = L.cam->h, cols_r = R.cam->w, rows_r = R.cam->h;
+  std::unordered_map<size_t, size_t> first_right;                   // id -> first index in ids_right_old (:314-320)
+  for (size_t i = R.ids.size(); i-- > 0;) first_right[R.ids[i]] = i;
+  std::vector<size_t> obs_l_idx, obs_r_idx;
+  if (L.lk_run)
+    for (size_t i = 0; i < L.pts.size(); i++) {                     // :306-338
+      Pt p = new_pt(L, i);
+      if (p.x < 0 || p.y < 0 || (int)p.x > cols_l || (int)p.y > rows_l) continue;   // '>' on the left (:308-309)
+      auto it = first_right.find(L.ids[i]);
+      const bool found_right = it != first_right.end();
+      if (ok(L, i) && found_right && ok(R, it->second)) {
+        Pt q = new_pt(R, it->second);
+        if (q.x < 0 || q.y < 0 || (int)q.x >= cols_r || (int)q.y >= rows_r) continue;
+        good_l.push_back(p);
+        ids_l.push_back(L.ids[i]);
+        obs_l_idx.push_back(i);
+        good_r.push_back(q);
+        ids_r.push_back(R.ids[it->second]);
+        obs_r_idx.push_back(it->second);
+      } else if (ok(L, i)) {
+        good_l.push_back(p);
+        ids_l.push_back(L.ids[i]);
+        obs_l_idx.push_back(i);
+      }
+    }
+  if (R.lk_run) {
+    std::unordered_set<size_t> added(ids_r.begin(), ids_r.end());
+    for (size_t i = 0; i < R.pts.size(); i++) {                     // :341-354
+      Pt q = new_pt(R, i);
+      if (q.x < 0 || q.y < 0 || (int)q.x >= cols_r || (int)q.y >= rows_r) continue;
+      if (ok(R, i) && !added.count(R.ids[i])) {
+        good_r.push_back(q);
+        ids_r.push_back(R.ids[i]);
+        obs_r_idx.push_back(i);
+        added.insert(R.ids[i]);
+      }
+    }
+  }
+  for (size_t k = 0; k < good_l.size(); k++) add_obs(L, obs_l_idx[k], ids_l[k], good_l[k]);   // :357-366 left, then right
+  for (size_t k = 0; k < good_r.size(); k++) add_obs(R, obs_r_idx[k], ids_r[k], good_r[k]);
+  store_last(L, good_l, ids_l);
+  store_last(R, good_r, ids_r);
+}
+
+static double now_us() {
+  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// copy a caller mask into the camera's host slot; returns whether any pixel is non-zero
+static bool copy_mask(const HostImage &m, std::vector<uint8_t> &dst, int w, int h) {
+  if (!m.p) {
+    return false;
+  }
+  bool nz = false;
+  for (int y = 0; y < h; y++) {
+    const uint8_t *r = m.p + (size_t)y * m.stride;
+    uint8_t *d = dst.data() + (size_t)y * w;
+    memcpy(d, r, (size_t)w);
+    if (!nz) {
+      int x = 0;
+      for (; x + 8 <= w && !nz; x += 8) {
+        uint64_t v;
+        memcpy(&v, d + x, 8);
+        nz = v != 0;
+      }
+      for (; x < w && !nz; x++) nz = d[x] != 0;
+    }
+  }
+  return nz;
+}
+
+int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  const double t0 = now_us();
+  std::vector<Unit> units;
+  int worst = OK;
+  auto fail = [&](FeedRequest &r, int code) {
+    r.status = code;
+    r.rig->last_error = code;
+    if (code > worst) worst = code;
+  };
+  // ---- validate, allocate, upload ------------------------------------------------------------------------------------
+  int nimg = 0, max_w = 0, max_h = 0, max_lv = 1, any_hist = 0, any_clahe = 0;
+  for (int i = 0; i < n; i++) nimg += reqs[i].n > 0 ? reqs[i].n : 0;
+  CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
+  int npre = 0;
+  for (int i = 0; i < n; i++) {
+    FeedRequest &rq = reqs[i];
+    Rig &rig = *rq.rig;
+    rq.status = OK;
+    rig.obs.clear();
+    const Params &P = rig.prm;
+    if (rq.n <= 0 || !rq.sensor_ids || !rq.images || !rq.masks) { fail(rq, E_BADMSG); continue; }   // TrackKLT.cpp:37-43
+    if (P.use_stereo && rq.n > 2) { fail(rq, E_BADMSG); continue; }                                   // :90-93
+    if (P.win_size != LK_WIN) { fail(rq, E_ARG); continue; }
+    bool bad = false;
+    for (int k = 0; k < rq.n && !bad; k++) {
+      CamState *c = rig.find_cam(rq.sensor_ids[k]);
+      if (!c) { fail(rq, E_CAMID); bad = true; break; }                                               // :53-54 (.at throws)
+      const HostImage &im = rq.images[k];
+      if (!im.p || im.w <= 0 || im.h <= 0 || im.w > 4095 || im.h > 4095) { fail(rq, E_BADMSG); bad = true; break; }
+      if (rq.masks[k].p && (rq.masks[k].w != im.w || rq.masks[k].h != im.h)) { fail(rq, E_BADMSG); bad = true; break; }
+      for (int q = 0; q < k; q++) if (rq.sensor_ids[q] == rq.sensor_ids[k]) { fail(rq, E_BADMSG); bad = true; }
+      if (bad) break;
+      if (c->raw < 0) {
+        int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size);
+        if (e != OK) { fail(rq, e); bad = true; break; }
+      } else if (c->w != im.w || c->h != im.h) { fail(rq, E_SIZE); bad = true; break; }
+    }
+    if (bad) continue;
+    for (int k = 0; k < rq.n; k++) {
+      CamState &c = *rig.find_cam(rq.sensor_ids[k]);
+      const HostImage &im = rq.images[k];
+      c.cur ^= 1;
+      const ImgView &raw = ctx->raw_tab[c.raw];
+      CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyHostToDevice,
+                               ctx->stream));
+      c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
+      ctx->pre_jobs.h[npre++] = PreJob{c.raw, c.pyr[c.cur], P.histogram_method};
+      max_w = std::max(max_w, im.w);
+      max_h = std::max(max_h, im.h);
+      max_lv = std::max(max_lv, ctx->pyr_tab[c.pyr[c.cur]].nlv);
+      any_hist |= P.histogram_method == 1;
+      any_clahe |= P.histogram_method == 2;
+    }
+    // units (TrackKLT.cpp:80-93)
+    auto make_side = [&](Side &s, int k) { s.cam = rig.find_cam(rq.sensor_ids[k]); s.msg = k; };
+    if (rq.n == 2 && P.use_stereo) {
+      Unit u;
+      u.rig = &rig; u.req = &rq; u.stereo = true;
+      make_side(u.L, 0);
+      make_side(u.R, 1);
+      u.first = u.L.cam->pts_last.empty() && u.R.cam->pts_last.empty();                               // :221
+      if (!u.first && (!u.L.cam->have_last || !u.R.cam->have_last)) { fail(rq, E_BADMSG); continue; }
+      units.push_back(std::move(u));
+    } else {
+      for (int k = 0; k < rq.n; k++) {
+        Unit u;
+        u.rig = &rig; u.req = &rq; u.stereo = false;
+        make_side(u.L, k);
+        u.first = u.L.cam->pts_last.empty();                                                          // :110
+        units.push_back(std::move(u));
+      }
+    }
+  }
+  // ---- round 1: pre-process + FAST -----------------------------------------------------------------------------------
+  CU_TRY(ctx->hist.reserve((size_t)npre * 256, true));
+  CU_TRY(ctx->hist_ticket.reserve((size_t)npre, true));
+  CU_TRY(ctx->lut.reserve((size_t)npre * 256));
+  if (any_clahe) CU_TRY(ctx->clahe_lut.reserve((size_t)npre * CLAHE_TILES * CLAHE_TILES * 256));
+  if (!ctx->sp_mask_ready) {
+    CU_TRY(ctx->sp_mask.reserve(SP_N));
+    CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
+    ctx->sp_mask_ready = true;
+  }
+  if (ctx->upload_tables() != OK) return E_CUDA;
+  CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, ctx->raw_dev.d, ctx->pyr_dev.d, ctx->hist.d, ctx->hist_ticket.d,
+                           ctx->lut.d, ctx->clahe_lut.d, max_w, max_h, any_hist, any_clahe, max_lv));
+  size_t ncells = 0, nwords = 0;
+  int max_cw = 1, max_ch = 1;
+  for (auto &u : units) {
+    phase_a(u);
+    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+      Side &s = side ? u.R : u.L;
+      if (!s.detect) continue;
+      ncells += s.cells.size();
+      nwords += s.cells.size() * (size_t)(((s.geom.size_x + 1) / 2) * ((s.geom.size_y + 1) / 2));
+      max_cw = std::max(max_cw, s.geom.size_x);
+      max_ch = std::max(max_ch, s.geom.size_y);
+    }
+  }
+  CU_TRY(ctx->fast_jobs.reserve(ncells));
+  CU_TRY(ctx->fast_thr.reserve(ncells));
+  CU_TRY(ctx->fast_cnt.reserve(ncells));
+  CU_TRY(ctx->fast_out.reserve(nwords));
+  CU_TRY(ctx->fast_out_dev.reserve(nwords));
+  CU_TRY(ctx->fast_cnt_dev.reserve(ncells, true));
+  CU_TRY(ctx->fast_ticket.reserve(ncells, true));
+  int njobs = 0;
+  nwords = 0;
+  for (auto &u : units)
+    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+      Side &s = side ? u.R : u.L;
+      if (s.detect) emit_fast_jobs(ctx, s, u.rig->prm.fast_threshold, njobs, nwords);
+    }
+  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, ctx->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
+                     ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  if (ctx->sync() != OK) return E_CUDA;
+  const double t1 = now_us();
+  // ---- round 2: sub-pixel + stereo LK --------------------------------------------------------------------------------
+  size_t sp_bound = 0;
+  for (auto &u : units)
+    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+      Side &s = side ? u.R : u.L;
+      if (s.detect) sp_bound += s.cells.size() * (size_t)s.geom.per_cell;
+    }
+  CU_TRY(ctx->sp_items.reserve(sp_bound));
+  CU_TRY(ctx->sp_out.reserve(2 * sp_bound));
+  CU_TRY(ctx->sp_out_dev.reserve(2 * sp_bound));
+  CU_TRY(ctx->lk_items.reserve(sp_bound));
+  CU_TRY(ctx->lk_out.reserve(sp_bound));
+  CU_TRY(ctx->lk_status.reserve(sp_bound));
+  CU_TRY(ctx->lk_out_dev.reserve(sp_bound));
+  CU_TRY(ctx->lk_status_dev.reserve(sp_bound));
+  int nsp = 0, nlk = 0;
+  {
+    // sub-pixel items: all left selections first (so that stereo-LK item i chains on sub-pixel item i), then the right
+    std::vector<uint32_t> tmp;
+    std::vector<KeyPointLite> kps;
+    for (auto &u : units) phase_b(ctx, u, nsp, nlk, tmp, kps);
+    // a unit's lk0 must equal its sp0L for the chaining: true when only stereo units select points; mono units add
+    // sub-pixel items without LK items, so stereo units are given explicit coordinates below instead
+    for (auto &u : units)
+      if (u.stereo) phase_b_right(ctx, u, nsp);
+  }
+  CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, nsp, ctx->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, ctx->sp_out_dev.d));
+  // stereo LK items read their start point from the sub-pixel output: build the index map
+  bool chained = true;
+  for (auto &u : units) chained &= (!u.stereo || u.lk0 == u.sp0L);
+  if (nlk > 0) {
+    if (!chained) {
+      // mixed batch: wait for the refined corners and fill the LK items on the host
+      if (ctx->sync() != OK) return E_CUDA;
+      for (auto &u : units)
+        if (u.stereo)
+          for (size_t i = 0; i < u.selL.size(); i++) {
+            LkItem &it = ctx->lk_items.h[u.lk0 + i];
+            it.px = it.nx = ctx->sp_out.h[2 * (u.sp0L + i)];
+            it.py = it.ny = ctx->sp_out.h[2 * (u.sp0L + i) + 1];
+          }
+    }
+    CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, ctx->pyr_dev.d, chained ? ctx->sp_out_dev.d : nullptr, 30, 0.01,
+                     ctx->lk_out.d, ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
+  }
+  if (ctx->sync() != OK) return E_CUDA;
+  // ---- host: finish detection; round 3: temporal LK + RANSAC -----------------------------------------------------------
+  size_t lk_bound = 0;
+  for (auto &u : units) {
+    int e = phase_c_detect(ctx, u);
+    if (e != OK) { fail(*u.req, e); u.failed = true; continue; }
+    if (u.first) {                                                   // TrackKLT.cpp:110-123 / :221-240: store, no DB update
+      store_last(u.L, u.L.pts, u.L.ids);
+      if (u.stereo) store_last(u.R, u.R.pts, u.R.ids);
+      continue;
+    }
+    lk_bound += u.L.pts.size() + (u.stereo ? u.R.pts.size() : 0);
+  }
+  const double t2 = now_us();
+  CU_TRY(ctx->lk_items.reserve(lk_bound));
+  CU_TRY(ctx->lk_out.reserve(lk_bound));
+  CU_TRY(ctx->lk_status.reserve(lk_bound));
+  CU_TRY(ctx->lk_out_dev.reserve(lk_bound));
+  CU_TRY(ctx->lk_status_dev.reserve(lk_bound));
+  CU_TRY(ctx->rs_jobs.reserve(2 * units.size()));
+  CU_TRY(ctx->p0n_dev.reserve(2 * lk_bound));
+  CU_TRY(ctx->p1n_dev.reserve(2 * lk_bound));
+  CU_TRY(ctx->p1n.reserve(2 * lk_bound));
+  CU_TRY(ctx->rs_mask.reserve(lk_bound));
+  CU_TRY(ctx->rs_mask_dev.reserve(lk_bound));
+  nlk = 0;
+  int nrs = 0, max_n = 1;
+  for (auto &u : units) {
+    if (u.first || u.failed) continue;
+    emit_temporal(ctx, u, nlk, nrs);
+    max_n = std::max(max_n, std::max(u.L.lk_n, u.R.lk_n));
+  }
+  CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, ctx->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,
+                   ctx->lk_out_dev.d, ctx->lk_status_dev.d));
+  CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, nrs, max_n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d,
+                       ctx->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
+  if (ctx->sync() != OK) return E_CUDA;
+  const double t3 = now_us();
+  for (auto &u : units)
+    if (!u.first && !u.failed) phase_d(ctx, u);
+  const double t4 = now_us();
+  for (int i = 0; i < n; i++) {
+    float *s = reqs[i].rig->stage_us;
+    s[0] = (float)(t1 - t0);   // upload + equalise + pyramid (+ FAST of round 1)
+    s[1] = (float)(t2 - t1);   // detection (top-K, sub-pixel, id assignment)
+    s[2] = (float)(t3 - t2);   // temporal KLT + RANSAC
+    s[3] = 0.f;                // stereo KLT is part of the detection round here
+    s[4] = (float)(t4 - t3);   // merge + observations
+  }
+  return worst;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Stage entry points: run one kernel on the pyramids a rig already holds (parity tests and micro-benchmarks).
+// slot: 0 = the frame fed last ("curr"), 1 = the one before it ("last").
+// ---------------------------------------------------------------------------------------------------------------------
+static int slot_pyr(Rig *rig, size_t cam_id, int slot, CamState **out) {
+  CamState *c = rig->find_cam(cam_id);
+  if (!c || c->raw < 0) return -1;
+  *out = c;
+  return c->pyr[slot ? 1 - c->cur : c->cur];
+}
+
+int stage_get_level(Rig *rig, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *h, int *nlv) {
+  Context *ctx = rig->ctx;
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  CamState *c;
+  int p = slot_pyr(rig, cam_id, slot, &c);
+  if (p < 0) return E_CAMID;
+  const PyrDesc &d = ctx->pyr_tab[p];
+  if (nlv) *nlv = d.nlv;
+  if (level < 0 || level >= d.nlv) return E_ARG;
+  if (w) *w = d.lv[level].w;
+  if (h) *h = d.lv[level].h;
+  if (out) {
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+    CU_TRY(cudaMemcpy2D(out, out_stride, d.lv[level].p, d.lv[level].pitch, d.lv[level].w, d.lv[level].h, cudaMemcpyDeviceToHost));
+  }
+  return OK;
+}
+
+int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch, int threshold, int *xy, float *resp, int cap,
+               int *n_out) {
+  Context *ctx = rig->ctx;
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  CamState *c;
+  int p = slot_pyr(rig, cam_id, slot, &c);
+  if (p < 0) return E_CAMID;
+  if (x0 < 0 || y0 < 0 || cw <= 0 || ch <= 0 || x0 + cw > c->w || y0 + ch > c->h) return E_ARG;
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  if (ctx->upload_tables() != OK) return E_CUDA;
+  size_t words = (size_t)((cw + 1) / 2) * ((ch + 1) / 2);
+  CU_TRY(ctx->fast_jobs.reserve(1));
+  CU_TRY(ctx->fast_thr.reserve(1));
+  CU_TRY(ctx->fast_cnt.reserve(1));
+  CU_TRY(ctx->fast_out.reserve(words));
+  CU_TRY(ctx->fast_out_dev.reserve(words));
+  CU_TRY(ctx->fast_cnt_dev.reserve(1, true));
+  CU_TRY(ctx->fast_ticket.reserve(1, true));
+  ctx->fast_jobs.h[0] = FastJob{p, x0, y0, cw, ch, 0, (int)words};
+  ctx->fast_thr.h[0] = threshold;
+  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, ctx->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
+                     ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  if (ctx->sync() != OK) return E_CUDA;
+  unsigned cnt = ctx->fast_cnt.h[0];
+  std::vector<uint32_t> v(ctx->fast_out.h, ctx->fast_out.h + cnt);
+  std::sort(v.begin(), v.end(), [](uint32_t a, uint32_t b) { return (a & 0xFFFFFFu) < (b & 0xFFFFFFu); });
+  for (unsigned i = 0; i < cnt && (int)i < cap; i++) {
+    xy[2 * i] = (int)(v[i] & 4095u);
+    xy[2 * i + 1] = (int)((v[i] >> 12) & 4095u);
+    resp[i] = (float)(v[i] >> 24);
+  }
+  *n_out = (int)cnt;
+  return OK;
+}
+
+int stage_subpix(Rig *rig, size_t cam_id, int slot, const float *pts, int n, float *out) {
+  Context *ctx = rig->ctx;
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  CamState *c;
+  int p = slot_pyr(rig, cam_id, slot, &c);
+  if (p < 0) return E_CAMID;
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  if (ctx->upload_tables() != OK) return E_CUDA;
+  if (!ctx->sp_mask_ready) {
+    CU_TRY(ctx->sp_mask.reserve(SP_N));
+    CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
+    ctx->sp_mask_ready = true;
+  }
+  CU_TRY(ctx->sp_items.reserve(n));
+  CU_TRY(ctx->sp_out.reserve(2 * (size_t)n));
+  for (int i = 0; i < n; i++) ctx->sp_items.h[i] = SubpixItem{pts[2 * i], pts[2 * i + 1], p, 0};
+  CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, n, ctx->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, nullptr));
+  if (ctx->sync() != OK) return E_CUDA;
+  memcpy(out, ctx->sp_out.h, sizeof(float) * 2 * (size_t)n);
+  return OK;
+}
+
+// LK from (cam0, slot0) to (cam1, slot1); optionally followed by undistort + RANSAC on the result (mask/p1n may be null)
+int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const float *pts0, const float *pts1_init, int n,
+             float *out, uint8_t *status, uint8_t *mask, float *p1n) {
+  Context *ctx = rig->ctx;
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  CamState *c0, *c1;
+  int p0 = slot_pyr(rig, cam0, slot0, &c0), p1 = slot_pyr(rig, cam1, slot1, &c1);
+  if (p0 < 0 || p1 < 0) return E_CAMID;
+  if (ctx->pyr_tab[p0].nlv != ctx->pyr_tab[p1].nlv || c0->w != c1->w || c0->h != c1->h) return E_SIZE;
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  if (ctx->upload_tables() != OK) return E_CUDA;
+  size_t N = (size_t)n;
+  CU_TRY(ctx->lk_items.reserve(N));
+  CU_TRY(ctx->lk_out.reserve(N));
+  CU_TRY(ctx->lk_status.reserve(N));
+  CU_TRY(ctx->lk_out_dev.reserve(N));
+  CU_TRY(ctx->lk_status_dev.reserve(N));
+  for (int i = 0; i < n; i++)
+    ctx->lk_items.h[i] = LkItem{pts0[2 * i], pts0[2 * i + 1], pts1_init[2 * i], pts1_init[2 * i + 1], p0, p1};
+  CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, n, ctx->pyr_dev.d, nullptr, rig->prm.lk_max_iters, rig->prm.lk_eps, ctx->lk_out.d,
+                   ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
+  if (mask) {
+    CU_TRY(ctx->rs_jobs.reserve(1));
+    CU_TRY(ctx->p0n_dev.reserve(2 * N));
+    CU_TRY(ctx->p1n_dev.reserve(2 * N));
+    CU_TRY(ctx->p1n.reserve(2 * N));
+    CU_TRY(ctx->rs_mask.reserve(N));
+    CU_TRY(ctx->rs_mask_dev.reserve(N));
+    RansacJob j;
+    j.off = 0;
+    j.n = n;
+    j.cam0 = c0->cam_model_idx;
+    j.cam1 = c1->cam_model_idx;
+    j.thr = 2.0 / std::max(c0->max_focal, c1->max_focal);
+    j.run = n >= 10;
+    ctx->rs_jobs.h[0] = j;
+    CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, ctx->cam_dev.d,
+                         ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
+  }
+  if (ctx->sync() != OK) return E_CUDA;
+  for (int i = 0; i < n; i++) {
+    out[2 * i] = ctx->lk_out.h[i].x;
+    out[2 * i + 1] = ctx->lk_out.h[i].y;
+    status[i] = ctx->lk_status.h[i];
+  }
+  if (mask) {
+    memcpy(mask, ctx->rs_mask.h, N);
+    if (p1n) memcpy(p1n, ctx->p1n.h, sizeof(float) * 2 * N);
+  }
+  return OK;
+}
+
+// undistort + RANSAC on caller-supplied pixel correspondences (no LK): mask = inliers, p0n/p1n = normalised points
+int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const float *pts1, int n, uint8_t *mask, float *p0n,
+                 float *p1n) {
+  Context *ctx = rig->ctx;
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  CamState *c0 = rig->find_cam(cam0), *c1 = rig->find_cam(cam1);
+  if (!c0 || !c1) return E_CAMID;
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  if (ctx->upload_tables() != OK) return E_CUDA;
+  size_t N = (size_t)n;
+  CU_TRY(ctx->lk_items.reserve(N));
+  CU_TRY(ctx->lk_out_dev.reserve(N));
+  CU_TRY(ctx->lk_status_dev.reserve(N));
+  CU_TRY(ctx->rs_jobs.reserve(1));
+  CU_TRY(ctx->p0n_dev.reserve(2 * N));
+  CU_TRY(ctx->p1n_dev.reserve(2 * N));
+  CU_TRY(ctx->p1n.reserve(2 * N));
+  CU_TRY(ctx->rs_mask.reserve(N));
+  CU_TRY(ctx->rs_mask_dev.reserve(N));
+  std::vector<uint8_t> ones(N, 1);
+  for (int i = 0; i < n; i++) ctx->lk_items.h[i] = LkItem{pts0[2 * i], pts0[2 * i + 1], 0, 0, 0, 0};
+  CU_TRY(cudaMemcpyAsync(ctx->lk_out_dev.d, pts1, sizeof(float) * 2 * N, cudaMemcpyHostToDevice, ctx->stream));
+  CU_TRY(cudaMemcpyAsync(ctx->lk_status_dev.d, ones.data(), N, cudaMemcpyHostToDevice, ctx->stream));
+  RansacJob j;
+  j.off = 0;
+  j.n = n;
+  j.cam0 = c0->cam_model_idx;
+  j.cam1 = c1->cam_model_idx;
+  j.thr = 2.0 / std::max(c0->max_focal, c1->max_focal);
+  j.run = n >= 10;
+  ctx->rs_jobs.h[0] = j;
+  CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, ctx->cam_dev.d,
+                       ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
+  if (ctx->sync() != OK) return E_CUDA;
+  memcpy(mask, ctx->rs_mask.h, N);
+  if (p1n) memcpy(p1n, ctx->p1n.h, sizeof(float) * 2 * N);
+  if (p0n) CU_TRY(cudaMemcpy(p0n, ctx->p0n_dev.d, sizeof(float) * 2 * N, cudaMemcpyDeviceToHost));
+  return OK;
+}
+
+int context_cuda_error(Context *ctx) { return ctx->cuda_err; }
+
+}  // namespace uvio

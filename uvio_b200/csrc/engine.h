@@ -101,5 +101,16 @@ struct FeedRequest {            // one feed_new_camera call (utils/sensor_data.h
 int feed_batch(Context *ctx, FeedRequest *reqs, int n);
 
 Context *context_for_device(int device, int *err);
+int context_cuda_error(Context *ctx);
+
+// stage entry points (see engine.cpp); slot 0 = frame fed last, 1 = the one before
+int stage_get_level(Rig *rig, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *h, int *nlv);
+int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch, int threshold, int *xy, float *resp, int cap,
+               int *n_out);
+int stage_subpix(Rig *rig, size_t cam_id, int slot, const float *pts, int n, float *out);
+int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const float *pts0, const float *pts1_init, int n, float *out,
+             uint8_t *status, uint8_t *mask, float *p1n);
+int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const float *pts1, int n, uint8_t *mask, float *p0n,
+                 float *p1n);
 
 }  // namespace uvio
