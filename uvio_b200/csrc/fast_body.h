@@ -9,6 +9,11 @@
 #pragma once
 #include "image_body.h"
 #include "simt.h"
+#ifndef __CUDACC__
+#include <algorithm>
+using std::max;
+using std::min;
+#endif
 
 namespace uvio {
 
@@ -52,18 +57,30 @@ UVIO_HD int fast_score(const uint8_t *p, int pitch, int threshold) {
   r1 &= r1 >> 4; r2 &= r2 >> 4;
   r1 &= m1 >> 8; r2 &= m2 >> 8;
   if (!((r1 | r2) & 0xFFFFu)) return 0;
+  // Arc minima by doubling (m2 over d[k..k+1], m4 over 4, m8 over 8, then the ninth element), once for d = centre - ring
+  // and once for e = ring - centre. Written without negating a min/max result: ptxas 12.9 for sm_100a drops the negation
+  // when it fuses max(x, -max(..)) into VIMNMX3 (seen on B200: scores came out as max(d) instead of the arc minimum).
+  int e[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) e[k] = (int)p[fast_ring_off(k, pitch)] - v;
   int best = -1000;
+  {
+    int m2[16], m4[16];
 #pragma unroll
-  for (int k = 0; k < 16; k++) {
-    int mn = d[k], mx = d[k];
+    for (int k = 0; k < 16; k++) m2[k] = min(d[k], d[(k + 1) & 15]);
 #pragma unroll
-    for (int j = 1; j < 9; j++) {
-      int e = d[(k + j) & 15];
-      mn = e < mn ? e : mn;
-      mx = e > mx ? e : mx;
-    }
-    best = mn > best ? mn : best;
-    best = -mx > best ? -mx : best;
+    for (int k = 0; k < 16; k++) m4[k] = min(m2[k], m2[(k + 2) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; k++) best = max(best, min(min(m4[k], m4[(k + 4) & 15]), d[(k + 8) & 15]));
+  }
+  {
+    int m2[16], m4[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) m2[k] = min(e[k], e[(k + 1) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; k++) m4[k] = min(m2[k], m2[(k + 2) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; k++) best = max(best, min(min(m4[k], m4[(k + 4) & 15]), e[(k + 8) & 15]));
   }
   return best > threshold ? best - 1 : 0;
 }
