@@ -111,6 +111,14 @@ int uvio_klt_last_error(uvio_klt *h);
 int uvio_klt_cuda_error(uvio_klt *h); /* last cudaError_t seen on this tracker's device context */
 const char *uvio_klt_version(void);
 
+/* ---- measurement helpers (no reference counterpart; the reference stamps wall-clock rT1..rT7, TrackBase.h:195) ------
+ * Counters of the device context since its creation: [0] frames fed, [1] kernels launched, [2] image bytes uploaded,
+ * [3] bytes the GPU wrote to host memory (corner lists, refined / tracked points, status, masks), [4] feed_batch calls. */
+int uvio_klt_device_stats(int cuda_device, unsigned long long out[8]);
+/* CUDA-event stopwatch recorded on the stream all kernels of that device's trackers are launched on. */
+int uvio_klt_timer_start(int cuda_device);
+int uvio_klt_timer_stop(int cuda_device, float *ms);
+
 /* ---- stage entry points: one kernel on the pyramids the tracker already holds (parity tests, micro-benchmarks) ------
  * slot 0 = the frame fed last (img_pyramid_last after the feed returns), slot 1 = the frame before it. */
 /* level `level` of cv::buildOpticalFlowPyramid's output (after equalisation, TrackKLT.cpp:58-71); out may be NULL */

@@ -200,6 +200,26 @@ int uvio_klt_last_error(uvio_klt *h) { return h ? h->rig->last_error : UVIO_E_AR
 int uvio_klt_cuda_error(uvio_klt *h) { return h ? context_cuda_error(h->rig->ctx) : 0; }
 const char *uvio_klt_version(void) { return "uvio_klt 0.1 (sm_100a)"; }
 
+int uvio_klt_device_stats(int cuda_device, unsigned long long out[8]) {
+  if (!out) return UVIO_E_ARG;
+  int err = 0;
+  Context *ctx = context_for_device(cuda_device, &err);
+  if (!ctx) return UVIO_E_CUDA;
+  context_stats(ctx, out);
+  return UVIO_OK;
+}
+int uvio_klt_timer_start(int cuda_device) {
+  int err = 0;
+  Context *ctx = context_for_device(cuda_device, &err);
+  return ctx ? context_timer(ctx, 0, nullptr) : UVIO_E_CUDA;
+}
+int uvio_klt_timer_stop(int cuda_device, float *ms) {
+  if (!ms) return UVIO_E_ARG;
+  int err = 0;
+  Context *ctx = context_for_device(cuda_device, &err);
+  return ctx ? context_timer(ctx, 1, ms) : UVIO_E_CUDA;
+}
+
 int uvio_klt_stage_get_level(uvio_klt *h, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *hgt,
                              int *n_levels) {
   GUARD_BEGIN

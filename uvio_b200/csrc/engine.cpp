@@ -71,6 +71,10 @@ class Context {
   cudaStream_t stream = nullptr;
   int cuda_err = 0;
   std::mutex mtx;
+  // counters since creation: [0] feeds (frames), [1] kernel launches, [2] bytes uploaded, [3] bytes the GPU wrote to host memory,
+  // [4] feed_batch calls
+  unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
   // tables (host copy + device copy, re-uploaded when dirty)
   std::vector<PyrDesc> pyr_tab;
   std::vector<ImgView> raw_tab;
@@ -615,8 +619,9 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
       const HostImage &im = rq.images[k];
       c.cur ^= 1;
       const ImgView &raw = ctx->raw_tab[c.raw];
-      CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyHostToDevice,
-                               ctx->stream));
+      CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
+                               ctx->stream));   // host (pageable or pinned) or device memory
+      ctx->stats[2] += (unsigned long long)im.w * im.h;
       c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
       ctx->pre_jobs.h[npre++] = PreJob{c.raw, c.pyr[c.cur], P.histogram_method};
       max_w = std::max(max_w, im.w);
@@ -658,6 +663,7 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   if (ctx->upload_tables() != OK) return E_CUDA;
   CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, ctx->raw_dev.d, ctx->pyr_dev.d, ctx->hist.d, ctx->hist_ticket.d,
                            ctx->lut.d, ctx->clahe_lut.d, max_w, max_h, any_hist, any_clahe, max_lv));
+  ctx->stats[1] += (npre > 0) ? (unsigned)(any_hist + 1 + 2 * any_clahe + (max_lv - 1)) : 0u;
   size_t ncells = 0, nwords = 0;
   int max_cw = 1, max_ch = 1;
   for (auto &u : units) {
@@ -688,6 +694,8 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, ctx->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   if (ctx->sync() != OK) return E_CUDA;
+  ctx->stats[1] += njobs > 0;
+  for (int j = 0; j < njobs; j++) ctx->stats[3] += 4ull * ctx->fast_cnt.h[j] + 4ull;
   const double t1 = now_us();
   // ---- round 2: sub-pixel + stereo LK --------------------------------------------------------------------------------
   size_t sp_bound = 0;
@@ -735,6 +743,8 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
                      ctx->lk_out.d, ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   }
   if (ctx->sync() != OK) return E_CUDA;
+  ctx->stats[1] += (nsp > 0) + (nlk > 0);
+  ctx->stats[3] += 8ull * nsp + 9ull * nlk;
   // ---- host: finish detection; round 3: temporal LK + RANSAC -----------------------------------------------------------
   size_t lk_bound = 0;
   for (auto &u : units) {
@@ -771,6 +781,10 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, nrs, max_n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d,
                        ctx->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
   if (ctx->sync() != OK) return E_CUDA;
+  ctx->stats[1] += (nlk > 0) + (nrs > 0);
+  ctx->stats[3] += 9ull * nlk + (nrs > 0 ? 9ull * nlk : 0ull);
+  ctx->stats[0] += (unsigned long long)n;
+  ctx->stats[4] += 1;
   const double t3 = now_us();
   for (auto &u : units)
     if (!u.first && !u.failed) phase_d(ctx, u);
@@ -966,5 +980,24 @@ int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const fl
 }
 
 int context_cuda_error(Context *ctx) { return ctx->cuda_err; }
+
+void context_stats(Context *ctx, unsigned long long out[8]) {
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  memcpy(out, ctx->stats, sizeof(ctx->stats));
+}
+
+// CUDA-event stopwatch on the context's stream (the stream every kernel of this device's trackers is launched on)
+int context_timer(Context *ctx, int stop, float *ms) {
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  for (int i = 0; i < 2; i++)
+    if (!ctx->ev[i]) CU_TRY(cudaEventCreate(&ctx->ev[i]));
+  CU_TRY(cudaEventRecord(ctx->ev[stop ? 1 : 0], ctx->stream));
+  if (stop) {
+    CU_TRY(cudaEventSynchronize(ctx->ev[1]));
+    CU_TRY(cudaEventElapsedTime(ms, ctx->ev[0], ctx->ev[1]));
+  }
+  return OK;
+}
 
 }  // namespace uvio
