@@ -113,11 +113,26 @@ const char *uvio_klt_version(void);
 
 /* ---- measurement helpers (no reference counterpart; the reference stamps wall-clock rT1..rT7, TrackBase.h:195) ------
  * Counters of the device context since its creation: [0] frames fed, [1] kernels launched, [2] image bytes uploaded,
- * [3] bytes the GPU wrote to host memory (corner lists, refined / tracked points, status, masks), [4] feed_batch calls. */
+ * [3] bytes the GPU wrote to host memory (corner lists, refined / tracked points, status, masks), [4] feed_batch calls,
+ * [5] pixels scanned by FAST, [6] LK point-levels (templates staged), [7] LK iterations. */
 int uvio_klt_device_stats(int cuda_device, unsigned long long out[8]);
 /* CUDA-event stopwatch recorded on the stream all kernels of that device's trackers are launched on. */
 int uvio_klt_timer_start(int cuda_device);
 int uvio_klt_timer_stop(int cuda_device, float *ms);
+/* Per-kernel CUDA-event timing on that stream. enable: 1 = reset and start, 0 = stop, -1 = leave as is. ms / launches (16
+ * entries each, may be NULL) receive the sums accumulated so far, indexed by UVIO_K_*. */
+#define UVIO_K_HIST 0
+#define UVIO_K_LUT_APPLY 1
+#define UVIO_K_CLAHE_TILES 2
+#define UVIO_K_CLAHE_APPLY 3
+#define UVIO_K_PYRDOWN 4
+#define UVIO_K_FAST 5
+#define UVIO_K_SUBPIX 6
+#define UVIO_K_LK 7
+#define UVIO_K_RANSAC 8
+int uvio_klt_profile(int cuda_device, int enable, double ms[16], unsigned long long launches[16]);
+/* uvio_klt_get_new_observations for n trackers at once: tracker i writes at out + i*cap_each, counts[i] = its count */
+int uvio_klt_get_new_observations_batch(uvio_klt *const *h, int n, UvioObs *out, int cap_each, int *counts);
 
 /* ---- stage entry points: one kernel on the pyramids the tracker already holds (parity tests, micro-benchmarks) ------
  * slot 0 = the frame fed last (img_pyramid_last after the feed returns), slot 1 = the frame before it. */

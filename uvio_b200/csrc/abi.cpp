@@ -220,6 +220,29 @@ int uvio_klt_timer_stop(int cuda_device, float *ms) {
   return ctx ? context_timer(ctx, 1, ms) : UVIO_E_CUDA;
 }
 
+int uvio_klt_profile(int cuda_device, int enable, double ms[16], unsigned long long launches[16]) {
+  int err = 0;
+  Context *ctx = context_for_device(cuda_device, &err);
+  if (!ctx) return UVIO_E_CUDA;
+  double m[K_COUNT];
+  unsigned long long l[K_COUNT];
+  int rc = context_profile(ctx, enable, m, l);
+  for (int i = 0; i < 16; i++) {
+    if (ms) ms[i] = i < K_COUNT ? m[i] : 0.0;
+    if (launches) launches[i] = i < K_COUNT ? l[i] : 0ull;
+  }
+  return rc;
+}
+
+int uvio_klt_get_new_observations_batch(uvio_klt *const *hs, int n, UvioObs *out, int cap_each, int *counts) {
+  if (!hs || n <= 0 || !out || !counts || cap_each < 0) return UVIO_E_ARG;
+  for (int i = 0; i < n; i++) {
+    int rc = uvio_klt_get_new_observations(hs[i], out + (size_t)i * cap_each, cap_each, &counts[i]);
+    if (rc != UVIO_OK) return rc;
+  }
+  return UVIO_OK;
+}
+
 int uvio_klt_stage_get_level(uvio_klt *h, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *hgt,
                              int *n_levels) {
   GUARD_BEGIN

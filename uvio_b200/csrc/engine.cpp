@@ -20,6 +20,8 @@
 
 namespace uvio {
 
+KernelProf *g_prof = nullptr;
+
 #define CU_TRY(expr)                                          \
   do {                                                        \
     cudaError_t e__ = (expr);                                 \
@@ -75,6 +77,42 @@ class Context {
   // [4] feed_batch calls
   unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   cudaEvent_t ev[2] = {nullptr, nullptr};
+  // per-kernel CUDA-event timing (off by default)
+  KernelProf prof;
+  bool prof_on = false;
+  double prof_ms[K_COUNT] = {0};
+  unsigned long long prof_launches[K_COUNT] = {0};
+  void prof_begin() {
+    if (!prof_on) return;
+    if (!prof.ready) {
+      for (int i = 0; i < KernelProf::MAX_MARKS; i++) cudaEventCreate(&prof.ev[i]);
+      prof.ready = true;
+    }
+    prof.n = 0;
+    g_prof = &prof;
+  }
+  // call after the stream was synchronised: close the last interval and accumulate
+  void prof_end() {
+    if (!prof_on || g_prof != &prof) return;
+    g_prof = nullptr;
+  }
+  void prof_close_round() {   // one more mark after the last kernel of a round, then (after sync) fold the intervals
+    if (!prof_on || g_prof != &prof || prof.n == 0 || prof.n >= KernelProf::MAX_MARKS) return;
+    cudaEventRecord(prof.ev[prof.n], stream);
+    prof.id[prof.n++] = -1;
+  }
+  void prof_fold() {
+    if (!prof_on || g_prof != &prof) return;
+    for (int i = 0; i + 1 < prof.n; i++) {
+      if (prof.id[i] < 0) continue;
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, prof.ev[i], prof.ev[i + 1]) == cudaSuccess) {
+        prof_ms[prof.id[i]] += ms;
+        prof_launches[prof.id[i]] += 1;
+      }
+    }
+    prof.n = 0;
+  }
   // tables (host copy + device copy, re-uploaded when dirty)
   std::vector<PyrDesc> pyr_tab;
   std::vector<ImgView> raw_tab;
@@ -578,6 +616,8 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
   const double t0 = now_us();
+  ctx->prof_begin();
+  struct ProfGuard { Context *c; ~ProfGuard() { c->prof_end(); } } prof_guard{ctx};
   std::vector<Unit> units;
   int worst = OK;
   auto fail = [&](FeedRequest &r, int code) {
@@ -693,8 +733,11 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     }
   CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, ctx->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  ctx->prof_close_round();
   if (ctx->sync() != OK) return E_CUDA;
+  ctx->prof_fold();
   ctx->stats[1] += njobs > 0;
+  for (int j = 0; j < njobs; j++) ctx->stats[5] += (unsigned long long)ctx->fast_jobs.h[j].w * ctx->fast_jobs.h[j].h;
   for (int j = 0; j < njobs; j++) ctx->stats[3] += 4ull * ctx->fast_cnt.h[j] + 4ull;
   const double t1 = now_us();
   // ---- round 2: sub-pixel + stereo LK --------------------------------------------------------------------------------
@@ -742,7 +785,9 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, ctx->pyr_dev.d, chained ? ctx->sp_out_dev.d : nullptr, 30, 0.01,
                      ctx->lk_out.d, ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   }
+  ctx->prof_close_round();
   if (ctx->sync() != OK) return E_CUDA;
+  ctx->prof_fold();
   ctx->stats[1] += (nsp > 0) + (nlk > 0);
   ctx->stats[3] += 8ull * nsp + 9ull * nlk;
   // ---- host: finish detection; round 3: temporal LK + RANSAC -----------------------------------------------------------
@@ -780,7 +825,9 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
                    ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, nrs, max_n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d,
                        ctx->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
+  ctx->prof_close_round();
   if (ctx->sync() != OK) return E_CUDA;
+  ctx->prof_fold();
   ctx->stats[1] += (nlk > 0) + (nrs > 0);
   ctx->stats[3] += 9ull * nlk + (nrs > 0 ? 9ull * nlk : 0ull);
   ctx->stats[0] += (unsigned long long)n;
@@ -981,9 +1028,29 @@ int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const fl
 
 int context_cuda_error(Context *ctx) { return ctx->cuda_err; }
 
+int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long long launches[K_COUNT]) {
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  if (ms) memcpy(ms, ctx->prof_ms, sizeof(ctx->prof_ms));
+  if (launches) memcpy(launches, ctx->prof_launches, sizeof(ctx->prof_launches));
+  if (enable >= 0) {
+    ctx->prof_on = enable != 0;
+    if (enable) {
+      memset(ctx->prof_ms, 0, sizeof(ctx->prof_ms));
+      memset(ctx->prof_launches, 0, sizeof(ctx->prof_launches));
+    }
+  }
+  return OK;
+}
+
 void context_stats(Context *ctx, unsigned long long out[8]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
   memcpy(out, ctx->stats, sizeof(ctx->stats));
+  unsigned long long w[3] = {0, 0, 0};
+  if (cudaSetDevice(ctx->device) == cudaSuccess && read_lk_work(w, 0) == cudaSuccess) {
+    out[6] = w[0];   // LK point-levels
+    out[7] = w[1];   // LK iterations
+  }
 }
 
 // CUDA-event stopwatch on the context's stream (the stream every kernel of this device's trackers is launched on)

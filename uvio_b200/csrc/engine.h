@@ -104,6 +104,7 @@ Context *context_for_device(int device, int *err);
 int context_cuda_error(Context *ctx);
 void context_stats(Context *ctx, unsigned long long out[8]);
 int context_timer(Context *ctx, int stop, float *ms);
+int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long long launches[K_COUNT]);
 
 // stage entry points (see engine.cpp); slot 0 = frame fed last, 1 = the one before
 int stage_get_level(Rig *rig, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *h, int *nlv);

@@ -123,16 +123,21 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
                               unsigned *hist, unsigned *ticket, uint8_t *lut, uint8_t *clahe_lut, int max_w, int max_h,
                               int any_hist, int any_clahe, int max_levels) {
   if (njobs <= 0) return cudaSuccess;
+  if (any_hist) prof_mark(st, K_HIST);
   if (any_hist) k_hist<<<dim3(HIST_BANDS, njobs), 256, 0, st>>>(jobs, raw_tab, hist, ticket, lut);
+  prof_mark(st, K_LUT_APPLY);
   k_lut_apply<<<dim3(HIST_BANDS, njobs), 256, 0, st>>>(jobs, raw_tab, pyr_tab, lut);
   if (any_clahe) {
+    prof_mark(st, K_CLAHE_TILES);
     k_clahe_tiles<<<dim3(CLAHE_TILES * CLAHE_TILES, njobs), 256, 0, st>>>(jobs, raw_tab, clahe_lut);
+    prof_mark(st, K_CLAHE_APPLY);
     k_clahe_apply<<<dim3(HIST_BANDS * 2, njobs), 256, 0, st>>>(jobs, raw_tab, pyr_tab, clahe_lut);
   }
   int w = max_w, h = max_h;
   for (int l = 1; l < max_levels; l++) {
     w = (w + 1) / 2;
     h = (h + 1) / 2;
+    prof_mark(st, K_PYRDOWN);
     k_pyrdown<<<dim3((w + PD_TW - 1) / PD_TW, (h + PD_TH - 1) / PD_TH, njobs), 256, 0, st>>>(jobs, pyr_tab, l);
   }
   return cudaGetLastError();
@@ -174,6 +179,7 @@ cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max
                         uint32_t *out_host, unsigned *count_host) {
   if (njobs <= 0) return cudaSuccess;
   int tiles = ((max_cell_w + FT_W - 1) / FT_W) * ((max_cell_h + FT_H - 1) / FT_H);
+  prof_mark(st, K_FAST);
   k_fast<<<dim3(tiles, njobs), 256, 0, st>>>(jobs, thresholds, pyr_tab, out_dev, count_dev, ticket_dev, out_host, count_host);
   return cudaGetLastError();
 }
@@ -207,6 +213,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_subpix(const SubpixIte
 cudaError_t launch_subpix(cudaStream_t st, const SubpixItem *items, int n, const PyrDesc *pyr_tab, const float *mask_dev,
                           float *out_xy, float *out_xy_dev) {
   if (n <= 0) return cudaSuccess;
+  prof_mark(st, K_SUBPIX);
   k_subpix<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, mask_dev, out_xy,
                                                                                       out_xy_dev);
   return cudaGetLastError();
@@ -231,6 +238,9 @@ cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------------------------------
 // pyramidal LK: one warp per feature, all levels inside the kernel
 // ---------------------------------------------------------------------------------------------------------------------
+// work counters for the roofline arithmetic: [0] templates staged (point-levels), [1] iterations, [2] points
+__device__ unsigned long long g_lk_work[3];
+
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
                                                              const float *init_from_dev, int max_count, double eps_sq,
                                                              LkOut *out_host, uint8_t *status_host, LkOut *out_dev,
@@ -251,8 +261,12 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items
   prm.eps_sq = eps_sq;
   prm.min_eig = 1e-4;
   uint8_t status;
-  lk_track_point(GroupWarp(), sm[wid], P0.lv, P1.lv, prm, px, py, nx, ny, status);
+  int work[2] = {0, 0};
+  lk_track_point(GroupWarp(), sm[wid], P0.lv, P1.lv, prm, px, py, nx, ny, status, work);
   if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&g_lk_work[0], (unsigned long long)work[0]);
+    atomicAdd(&g_lk_work[1], (unsigned long long)work[1]);
+    atomicAdd(&g_lk_work[2], 1ull);
     LkOut o{nx, ny};
     out_host[i] = o;
     status_host[i] = status;
@@ -261,9 +275,19 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items
   }
 }
 
+cudaError_t read_lk_work(unsigned long long out[3], int reset) {
+  cudaError_t e = cudaMemcpyFromSymbol(out, g_lk_work, sizeof(unsigned long long) * 3);
+  if (e == cudaSuccess && reset) {
+    unsigned long long z[3] = {0, 0, 0};
+    e = cudaMemcpyToSymbol(g_lk_work, z, sizeof(z));
+  }
+  return e;
+}
+
 cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
                       double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev) {
   if (n <= 0) return cudaSuccess;
+  prof_mark(st, K_LK);
   k_lk<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, init_from_dev, max_count,
                                                                                   eps * eps, out_host, status_host, out_dev,
                                                                                   status_dev);
@@ -322,6 +346,7 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
     if (e != cudaSuccess) return e;
     configured = dyn;
   }
+  prof_mark(st, K_RANSAC);
   k_ransac<<<njobs, RANSAC_THREADS, dyn, st>>>(jobs, items, lk_dev, status_dev, cams_dev, p0n_dev, p1n_dev, p1n_host, mask_host,
                                                mask_dev);
   return cudaGetLastError();

@@ -35,7 +35,23 @@ struct RansacJob {
   int run;                             // 0: fewer than 10 points -> mask stays zero (TrackKLT.cpp:848-852), only undistort
 };
 
-struct Workspace;                      // device-side scratch owned by the engine (hist, LUTs, tickets)
+// Optional per-kernel timing: when g_prof is set, every launch wrapper records a CUDA event before each kernel it launches
+// (and the engine one after the last), on the launching stream.
+enum KernelId { K_HIST = 0, K_LUT_APPLY, K_CLAHE_TILES, K_CLAHE_APPLY, K_PYRDOWN, K_FAST, K_SUBPIX, K_LK, K_RANSAC, K_COUNT };
+struct KernelProf {
+  static constexpr int MAX_MARKS = 48;
+  cudaEvent_t ev[MAX_MARKS];
+  int id[MAX_MARKS];
+  int n = 0;
+  bool ready = false;
+};
+extern KernelProf *g_prof;   // defined in engine.cpp; guarded by the context mutex
+inline void prof_mark(cudaStream_t st, int kernel_id) {
+  KernelProf *p = g_prof;
+  if (!p || p->n >= KernelProf::MAX_MARKS) return;
+  cudaEventRecord(p->ev[p->n], st);
+  p->id[p->n++] = kernel_id;
+}
 
 // ---- image-wide passes ------------------------------------------------------------------------------------------------
 // equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels
@@ -64,5 +80,7 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
                           float *p1n_host, uint8_t *mask_host, uint8_t *mask_dev);
 
 cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st);
+// LK work counters since the last reset: [0] point-levels (templates staged), [1] iterations, [2] points
+cudaError_t read_lk_work(unsigned long long out[3], int reset);
 
 }  // namespace uvio

@@ -159,7 +159,7 @@ UVIO_HD void lk_weights(float a, float b, int &iw00, int &iw01, int &iw10, int &
 // prev/next: arrays of max_level+1 level views. (nx, ny) holds the initial guess on entry and the result on return.
 template <class G>
 UVIO_HD void lk_track_point(G g, LkSmem &s, const ImgView *prev, const ImgView *next, const LkParams &P, float px,
-                            float py, float &nx, float &ny, uint8_t &status) {
+                            float py, float &nx, float &ny, uint8_t &status, int *work = nullptr) {
   const float FLT_SCALE = 1.f / (1 << 20);
   const float half = (LK_WIN - 1) * 0.5f;
   status = 1;
@@ -188,6 +188,7 @@ UVIO_HD void lk_track_point(G g, LkSmem &s, const ImgView *prev, const ImgView *
     int iw00, iw01, iw10, iw11;
     lk_weights(fsub(ppx, (float)ipx), fsub(ppy, (float)ipy), iw00, iw01, iw10, iw11);
     lk_stage_template(g, s, I, ipx, ipy, iw00, iw01, iw10, iw11);
+    if (work) work[0]++;   // levels whose template was staged
     lk_accumulate_gram(g, s);
     float A11 = fmul(lk_fold(s.red + 0), FLT_SCALE);
     float A12 = fmul(lk_fold(s.red + 5), FLT_SCALE);
@@ -212,6 +213,7 @@ UVIO_HD void lk_track_point(G g, LkSmem &s, const ImgView *prev, const ImgView *
       }
       lk_weights(fsub(npx, (float)inx), fsub(npy, (float)iny), iw00, iw01, iw10, iw11);
       lk_stage_diff(g, s, J, inx, iny, iw00, iw01, iw10, iw11);
+      if (work) work[1]++;   // iterations (J footprints staged)
       lk_accumulate_mismatch(g, s);
       float b1 = fmul(lk_fold(s.red + 0), FLT_SCALE);
       float b2 = fmul(lk_fold(s.red + 5), FLT_SCALE);

@@ -88,6 +88,11 @@ def lib():
         L.uvio_klt_stage_subpix.argtypes = [vp, sz, ci, vp, ci, vp]
         L.uvio_klt_stage_lk.argtypes = [vp, sz, ci, sz, ci, vp, vp, ci, vp, vp, vp, vp]
         L.uvio_klt_stage_ransac.argtypes = [vp, sz, sz, vp, vp, ci, vp, vp, vp]
+        L.uvio_klt_device_stats.argtypes = [ci, C.POINTER(C.c_ulonglong)]
+        L.uvio_klt_timer_start.argtypes = [ci]
+        L.uvio_klt_timer_stop.argtypes = [ci, C.POINTER(C.c_float)]
+        L.uvio_klt_profile.argtypes = [ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
+        L.uvio_klt_get_new_observations_batch.argtypes = [C.POINTER(vp), ci, vp, ci, C.POINTER(ci)]
         _lib = L
     return _lib
 
@@ -370,3 +375,25 @@ def make_tracker(cfg, device: int = 0, **over) -> TrackKLT:
               pyr_levels=cfg.pyr_levels, device=device)
     kw.update(over)
     return TrackKLT({i: c for i, c in enumerate(cfg.cams)}, **kw)
+
+
+KERNEL_NAMES = ["k_hist", "k_lut_apply", "k_clahe_tiles", "k_clahe_apply", "k_pyrdown", "k_fast", "k_subpix", "k_lk", "k_ransac"]
+
+
+def device_stats(device: int = 0) -> dict:
+    out = (C.c_ulonglong * 8)()
+    rc = lib().uvio_klt_device_stats(device, out)
+    if rc != UVIO_OK:
+        raise UvioError(rc, "uvio_klt_device_stats")
+    return {"frames": out[0], "launches": out[1], "h2d_bytes": out[2], "d2h_bytes": out[3], "feed_calls": out[4],
+            "fast_pixels": out[5], "lk_point_levels": out[6], "lk_iterations": out[7]}
+
+
+def profile(device: int = 0, enable: int = -1) -> dict:
+    """Per-kernel CUDA-event sums since profiling was last enabled: name -> (ms, launches)."""
+    ms = (C.c_double * 16)()
+    ln = (C.c_ulonglong * 16)()
+    rc = lib().uvio_klt_profile(device, enable, ms, ln)
+    if rc != UVIO_OK:
+        raise UvioError(rc, "uvio_klt_profile")
+    return {k: (ms[i], int(ln[i])) for i, k in enumerate(KERNEL_NAMES)}
