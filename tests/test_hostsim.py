@@ -1,0 +1,111 @@
+"""CPU: (1) the kernel bodies of uvio_b200/csrc/*_body.h, compiled with g++ and run one-lane (tests/hostsim/hostsim.cpp),
+against the stage goldens; (2) the host logic of the tracker (engine.cpp + abi.cpp over a stand-in CUDA runtime,
+tests/hostsim/launch_sim.cpp) against the golden sequences.  Test scaffolding only: the product library is never replaced;
+the simulation build is loaded explicitly here and nowhere else."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from uvio_b200 import configs, track
+from uvio_b200.synth import frames_checksum
+
+from golden_util import GOLDEN, check_tracker_against_golden
+from util import frames_for
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+SIM = os.path.join(HERE, "hostsim")
+FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno-unknown-pragmas"]
+
+
+def _build(out, srcs, extra=()):
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    deps = srcs + [os.path.join(ROOT, "uvio_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "uvio_b200", "csrc"))]
+    if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
+        subprocess.check_call(["g++"] + FLAGS + list(extra) + ["-o", out] + srcs + ["-lpthread"])
+    return out
+
+
+@pytest.fixture(scope="module")
+def bodies():
+    return ctypes.CDLL(_build(os.path.join(SIM, "_sim", "libbodies.so"), [os.path.join(SIM, "hostsim.cpp")]))
+
+
+@pytest.fixture()
+def sim_tracker(monkeypatch):
+    csrc = os.path.join(ROOT, "uvio_b200", "csrc")
+    lib = _build(os.path.join(SIM, "_sim", "libuvio_klt_sim.so"),
+                 [os.path.join(csrc, "engine.cpp"), os.path.join(csrc, "abi.cpp"), os.path.join(SIM, "launch_sim.cpp")], ["-I", SIM])
+    monkeypatch.setattr(track, "LIB_PATH", lib)
+    monkeypatch.setattr(track, "_lib", None)
+    yield lambda cfg: track.make_tracker(cfg)
+    monkeypatch.setattr(track, "_lib", None)
+
+
+def _p(a):
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+def test_kernel_bodies_against_stage_goldens(bodies):
+    L = bodies
+    g = np.load(os.path.join(GOLDEN, "stages_euroc.npz"))
+    cfg = configs.EUROC_MAV
+    frames = frames_for(cfg, 2, events=False, start=7)
+    w, h = cfg.width, cfg.height
+    eq = []
+    for fr in frames:
+        o = np.empty_like(fr[0])
+        L.hs_equalize(_p(fr[0]), w, h, w, _p(o), w)
+        eq.append(o)
+    cl = np.empty_like(frames[0][0])
+    L.hs_clahe(_p(frames[0][0]), w, h, w, _p(cl), w, ctypes.c_double(10.0), 8, 8)
+    assert frames_checksum([cl]) == int(g["clahe_sum"])
+    pyr = [[e] for e in eq]
+    for k in range(2):
+        for _ in range(4):
+            a = pyr[k][-1]
+            d = np.empty(((a.shape[0] + 1) // 2, (a.shape[1] + 1) // 2), np.uint8)
+            L.hs_pyrdown(_p(a), a.shape[1], a.shape[0], a.shape[1], _p(d), d.shape[1])
+            pyr[k].append(d)
+    for lv in range(5):
+        assert frames_checksum([pyr[0][lv]]) == int(g[f"pyr_sum_{lv}"])
+    sx, sy = w // cfg.grid_x, h // cfg.grid_y
+    for (gx, gy) in ((0, 0), (2, 3), (4, 4)):
+        xy = np.empty((4096, 2), np.int32)
+        r = np.empty(4096, np.float32)
+        n = L.hs_fast(_p(eq[0]), w, h, w, gx * sx, gy * sy, sx, sy, cfg.fast_threshold, _p(xy), _p(r), 4096)
+        assert np.array_equal(xy[:n], g[f"fast_xy_{gx}_{gy}"].astype(np.int32)) and np.array_equal(r[:n], g[f"fast_resp_{gx}_{gy}"].astype(np.float32))
+    sp = g["subpix_in"].copy()
+    L.hs_subpix(_p(eq[0]), w, h, w, _p(sp), len(sp), 20, ctypes.c_double(0.001))
+    assert np.array_equal(sp, g["subpix_out"])
+    vp = ctypes.c_void_p
+    PP = (vp * 5)(*[a.ctypes.data for a in pyr[0]])
+    NN = (vp * 5)(*[a.ctypes.data for a in pyr[1]])
+    lw = np.array([a.shape[1] for a in pyr[0]], np.int32)
+    lh = np.array([a.shape[0] for a in pyr[0]], np.int32)
+    p0 = g["lk_in"].copy()
+    p1 = p0.copy()
+    st = np.zeros(len(p0), np.uint8)
+    L.hs_lk(PP, NN, _p(lw), _p(lh), _p(lw), 4, _p(p0), _p(p1), _p(st), len(p0), 30, ctypes.c_double(0.01))
+    assert np.array_equal(st, g["lk_status"]) and np.array_equal(p1[st == 1], g["lk_out"][st == 1])
+    c = cfg.cams[0]
+    K, D = np.array(c.intrinsics, np.float64), np.array(c.dist, np.float64)
+    uin = np.ascontiguousarray(g["undist_in_radtan"])           # keep the arrays alive while C reads them
+    un = np.empty_like(uin)
+    L.hs_undistort(_p(uin), len(un), 0, _p(K), _p(D), _p(un))
+    assert np.array_equal(un, g["undist_out_radtan"])
+    rp0, rp1 = np.ascontiguousarray(g["ransac_p0"]), np.ascontiguousarray(g["ransac_p1"])
+    a_n, b_n = np.empty_like(rp0), np.empty_like(rp1)
+    L.hs_undistort(_p(rp0), len(a_n), 0, _p(K), _p(D), _p(a_n))
+    L.hs_undistort(_p(rp1), len(b_n), 0, _p(K), _p(D), _p(b_n))
+    mask = np.zeros(len(a_n), np.uint8)
+    L.hs_ransac(_p(a_n), _p(b_n), len(a_n), ctypes.c_double(2.0 / max(c.intrinsics[0], c.intrinsics[1])), ctypes.c_double(0.999), 1000, _p(mask))
+    assert np.array_equal(mask, g["ransac_mask"])
+
+
+@pytest.mark.parametrize("name,n", [("euroc_mav", 8), ("tum_vi", 6), ("rs_d455", 4), ("euroc_mono", 6)])
+def test_host_logic_against_golden_sequences(sim_tracker, name, n):
+    assert check_tracker_against_golden(name, sim_tracker, n=n) > 300
