@@ -1,0 +1,169 @@
+// TrackKLTGpu — the reference-facing side of the drop-in: a TrackBase subclass that forwards to the C ABI
+// (include/uvio_klt.h) and replays the returned observations into the tracker-owned FeatureDatabase in the reference's
+// order (TrackKLT.cpp:357-366: all left, then all right), so every consumer of ov_core::TrackBase keeps working:
+//
+//     // ov_msckf/src/core/VioManager.cpp:133-135
+//     trackFEATS = std::shared_ptr<TrackBase>(new TrackKLTGpu(state->_cam_intrinsics_cameras, init_max_features,
+//                      state->_options.max_aruco_features, params.use_stereo, params.histogram_method,
+//                      params.fast_threshold, params.grid_x, params.grid_y, params.min_px_dist));
+//
+// Compiled against ov_core_mirror.h here (no OpenCV / Eigen / Boost in this container).  With the real ov_core headers
+// (-DUVIO_USE_REAL_OV_CORE) the same class derives from the real ov_core::TrackBase: cv::Mat gives
+// data/step/cols/rows, CamBase gives is_fisheye()/get_value().
+#pragma once
+#include <cstdio>
+#include <cstdlib>
+#include <stdexcept>
+#include <vector>
+
+#include "../../include/uvio_klt.h"
+
+#ifdef UVIO_USE_REAL_OV_CORE
+#include "cam/CamBase.h"
+#include "cam/CamEqui.h"
+#include "feat/FeatureDatabase.h"
+#include "track/TrackBase.h"
+#else
+#include "ov_core_mirror.h"
+#endif
+
+namespace ov_core {
+
+class TrackKLTGpu : public TrackBase {
+public:
+#ifdef UVIO_USE_REAL_OV_CORE
+  typedef std::unordered_map<size_t, std::shared_ptr<CamBase>> CamMap;
+  typedef cv::KeyPoint KeyPointT;
+#else
+  typedef std::unordered_map<size_t, std::shared_ptr<CamCalibMirror>> CamMap;
+  typedef KeyPointMirror KeyPointT;
+#endif
+
+  // same argument list as TrackKLT::TrackKLT (TrackKLT.h:54-57); cuda_device is the only addition
+  explicit TrackKLTGpu(CamMap cameras, int numfeats, int numaruco, bool stereo, HistogramMethod histmethod, int fast_threshold,
+                       int gridx, int gridy, int minpxdist, int cuda_device = 0)
+      : TrackBase(cameras, numfeats, numaruco, stereo, histmethod) {
+    UvioKltParams p;
+    uvio_klt_default_params(&p);
+    p.num_features = numfeats;
+    p.num_aruco = numaruco;
+    p.use_stereo = stereo ? 1 : 0;
+    p.histogram_method = (int)histmethod;          // NONE, HISTOGRAM, CLAHE = 0, 1, 2 on both sides
+    p.fast_threshold = fast_threshold;
+    p.grid_x = gridx;
+    p.grid_y = gridy;
+    p.min_px_dist = minpxdist;
+    std::vector<UvioCamCalib> cc;
+    for (auto const &kv : cameras) {
+      UvioCamCalib c;
+      c.cam_id = kv.first;
+#ifdef UVIO_USE_REAL_OV_CORE
+      c.model = std::dynamic_pointer_cast<CamEqui>(kv.second) ? UVIO_CAM_EQUI : UVIO_CAM_RADTAN;
+      Eigen::MatrixXd v = kv.second->get_value();
+      for (int i = 0; i < 4; i++) { c.intrinsics[i] = v(i); c.distortion[i] = v(4 + i); }
+#else
+      c.model = kv.second->is_fisheye ? UVIO_CAM_EQUI : UVIO_CAM_RADTAN;
+      for (int i = 0; i < 4; i++) { c.intrinsics[i] = kv.second->values[i]; c.distortion[i] = kv.second->values[4 + i]; }
+#endif
+      cc.push_back(c);
+    }
+    int rc = uvio_klt_create(&p, cc.data(), (int)cc.size(), cuda_device, &handle);
+    if (rc != UVIO_OK) throw std::runtime_error("TrackKLTGpu: uvio_klt_create failed (no CUDA device? there is no CPU fallback)");
+  }
+  ~TrackKLTGpu() override { uvio_klt_destroy(handle); }
+
+  // TrackKLT::feed_new_camera (TrackKLT.cpp:34-94)
+  void feed_new_camera(const CameraData &message) override {
+    const size_t n = message.images.size();
+    if (message.sensor_ids.empty() || message.sensor_ids.size() != n || n != message.masks.size()) {
+      std::fprintf(stderr, "[ERROR]: MESSAGE DATA SIZES DO NOT MATCH OR EMPTY!!!\n");   // TrackKLT.cpp:37-43
+      std::exit(EXIT_FAILURE);
+    }
+    std::vector<size_t> ids(n), istep(n), mstep(n);
+    std::vector<const uint8_t *> img(n), msk(n);
+    std::vector<int> w(n), h(n);
+    for (size_t i = 0; i < n; i++) {
+      ids[i] = (size_t)message.sensor_ids[i];
+      img[i] = message.images[i].data;
+      istep[i] = (size_t)message.images[i].step;
+      msk[i] = message.masks[i].data;
+      mstep[i] = (size_t)message.masks[i].step;
+      w[i] = message.images[i].cols;
+      h[i] = message.images[i].rows;
+    }
+    UvioFrame f;
+    f.timestamp = message.timestamp;
+    f.n_img = (int)n;
+    f.sensor_ids = ids.data();
+    f.img = img.data();
+    f.img_stride = istep.data();
+    f.mask = msk.data();
+    f.mask_stride = mstep.data();
+    f.width = w.data();
+    f.height = h.data();
+    f.status = 0;
+    int rc = uvio_klt_feed(handle, &f);
+    if (rc == UVIO_E_BADMSG) {                                                        // TrackKLT.cpp:90-93
+      std::fprintf(stderr, "[ERROR]: invalid number of images passed %zu, we only support mono or stereo tracking\n", n);
+      std::exit(EXIT_FAILURE);
+    }
+    if (rc == UVIO_E_CAMID) throw std::out_of_range("TrackKLTGpu: unknown camera id");   // .at() in the reference (:53-54)
+    if (rc != UVIO_OK) throw std::runtime_error("TrackKLTGpu: uvio_klt_feed failed");
+    replay_observations(message.timestamp);
+  }
+
+  // TrackBase::get_last_obs / get_last_ids (TrackBase.h:134-146)
+  std::unordered_map<size_t, std::vector<KeyPointT>> get_last_obs() override {
+    std::unordered_map<size_t, std::vector<KeyPointT>> out;
+    for (auto const &kv : camera_calib) {
+      std::vector<size_t> ids;
+      std::vector<float> uv;
+      last_of(kv.first, ids, uv);
+      std::vector<KeyPointT> kps(ids.size());
+      for (size_t i = 0; i < ids.size(); i++) { kps[i].pt.x = uv[2 * i]; kps[i].pt.y = uv[2 * i + 1]; }
+      out[kv.first] = kps;
+    }
+    return out;
+  }
+  std::unordered_map<size_t, std::vector<size_t>> get_last_ids() override {
+    std::unordered_map<size_t, std::vector<size_t>> out;
+    for (auto const &kv : camera_calib) {
+      std::vector<float> uv;
+      last_of(kv.first, out[kv.first], uv);
+    }
+    return out;
+  }
+  void set_num_features(int _num_features) override {   // TrackBase.h:152
+    num_features = _num_features;
+    uvio_klt_set_num_features(handle, _num_features);
+  }
+  // TrackBase.cpp:230-248, including its quirk: get_internal_data() returns the map by value, so only featid changes
+  void change_feat_id(size_t id_old, size_t id_new) override {
+    auto data = database->get_internal_data();
+    auto it = data.find(id_old);
+    if (it != data.end()) it->second->featid = id_new;
+    uvio_klt_change_feat_id(handle, id_old, id_new);
+  }
+  uvio_klt *native_handle() { return handle; }
+
+protected:
+  void replay_observations(double timestamp) {
+    int n = 0;
+    uvio_klt_get_new_observations(handle, nullptr, 0, &n);
+    obs.resize((size_t)n);
+    if (n) uvio_klt_get_new_observations(handle, obs.data(), n, &n);
+    for (int i = 0; i < n; i++)
+      database->update_feature(obs[i].id, timestamp, obs[i].cam_id, obs[i].u, obs[i].v, obs[i].un, obs[i].vn);
+  }
+  void last_of(size_t cam, std::vector<size_t> &ids, std::vector<float> &uv) {
+    int n = 0;
+    uvio_klt_get_last(handle, cam, nullptr, nullptr, 0, &n);
+    ids.resize((size_t)n);
+    uv.resize((size_t)2 * n);
+    if (n) uvio_klt_get_last(handle, cam, ids.data(), uv.data(), n, &n);
+  }
+  uvio_klt *handle = nullptr;
+  std::vector<UvioObs> obs;
+};
+
+}  // namespace ov_core
