@@ -39,3 +39,4 @@ static inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return 0;
 static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return 0; }
 static inline cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return 0; }
 static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return 0; }
+static inline cudaError_t cudaDeviceSynchronize() { return 0; }

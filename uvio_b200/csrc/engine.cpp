@@ -10,9 +10,14 @@
 
 #include <stdio.h>
 
+#include <stdlib.h>
+
 #include <chrono>
+#include <condition_variable>
+#include <functional>
 #include <map>
 #include <memory>
+#include <thread>
 
 #include "hostlogic.h"
 #include "lk_body.h"
@@ -20,7 +25,7 @@
 
 namespace uvio {
 
-KernelProf *g_prof = nullptr;
+thread_local KernelProf *g_prof = nullptr;
 
 #define CU_TRY(expr)                                          \
   do {                                                        \
@@ -67,16 +72,16 @@ struct DevVec {
   ~DevVec() { if (d) cudaFree(d); }
 };
 
-class Context {
- public:
-  int device = 0;
+class Context;
+
+// One lane = one CUDA stream with its own job / result buffers.  A feed_batch call splits its trackers over the lanes and
+// runs them on separate host threads, so the host bookkeeping of one group overlaps the GPU rounds of the others.
+struct Lane {
+  Context *dev = nullptr;
+  int index = 0;
   cudaStream_t stream = nullptr;
   int cuda_err = 0;
-  std::mutex mtx;
-  // counters since creation: [0] feeds (frames), [1] kernel launches, [2] bytes uploaded, [3] bytes the GPU wrote to host memory,
-  // [4] feed_batch calls
-  unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  cudaEvent_t ev[2] = {nullptr, nullptr};
+  unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // accumulated into the context after every feed
   // per-kernel CUDA-event timing (off by default)
   KernelProf prof;
   bool prof_on = false;
@@ -91,17 +96,10 @@ class Context {
     prof.n = 0;
     g_prof = &prof;
   }
-  // call after the stream was synchronised: close the last interval and accumulate
   void prof_end() {
-    if (!prof_on || g_prof != &prof) return;
-    g_prof = nullptr;
+    if (g_prof == &prof) g_prof = nullptr;
   }
-  void prof_close_round() {   // one more mark after the last kernel of a round, then (after sync) fold the intervals
-    if (!prof_on || g_prof != &prof || prof.n == 0 || prof.n >= KernelProf::MAX_MARKS) return;
-    cudaEventRecord(prof.ev[prof.n], stream);
-    prof.id[prof.n++] = -1;
-  }
-  void prof_fold() {
+  void prof_fold() {   // after the stream was synchronised: every (kernel mark, next mark) interval is one kernel's duration
     if (!prof_on || g_prof != &prof) return;
     for (int i = 0; i + 1 < prof.n; i++) {
       if (prof.id[i] < 0) continue;
@@ -113,15 +111,6 @@ class Context {
     }
     prof.n = 0;
   }
-  // tables (host copy + device copy, re-uploaded when dirty)
-  std::vector<PyrDesc> pyr_tab;
-  std::vector<ImgView> raw_tab;
-  std::vector<CamModel> cam_tab;
-  DevVec<PyrDesc> pyr_dev;
-  DevVec<ImgView> raw_dev;
-  DevVec<CamModel> cam_dev;
-  bool tables_dirty = true;
-  std::vector<void *> allocs;   // image memory of all cameras
   // round 1
   MappedVec<PreJob> pre_jobs;
   DevVec<unsigned> hist, hist_ticket;
@@ -154,10 +143,38 @@ class Context {
     if (e != cudaSuccess) { cuda_err = (int)e; return E_CUDA; }
     return OK;
   }
+  ~Lane() {
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+class Pool;
+
+class Context {
+ public:
+  int device = 0;
+  int cuda_err = 0;
+  std::mutex mtx;
+  // counters since creation: [0] frames fed, [1] kernel launches, [2] bytes uploaded, [3] bytes the GPU wrote to host memory,
+  // [4] feed_batch calls, [5] pixels scanned by FAST
+  unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  std::vector<std::unique_ptr<Lane>> lanes;
+  Pool *pool = nullptr;
+  // tables (host copy + device copy, re-uploaded when dirty; read-only while lanes run)
+  std::vector<PyrDesc> pyr_tab;
+  std::vector<ImgView> raw_tab;
+  std::vector<CamModel> cam_tab;
+  DevVec<PyrDesc> pyr_dev;
+  DevVec<ImgView> raw_dev;
+  DevVec<CamModel> cam_dev;
+  bool tables_dirty = true;
+  std::vector<void *> allocs;   // image memory of all cameras
+
   int upload_tables() {
     Context *ctx = this;
     if (!tables_dirty) return OK;
-    CU_TRY(cudaStreamSynchronize(stream));
+    CU_TRY(cudaDeviceSynchronize());
     CU_TRY(pyr_dev.reserve(pyr_tab.size()));
     CU_TRY(raw_dev.reserve(raw_tab.size()));
     CU_TRY(cam_dev.reserve(cam_tab.size()));
@@ -210,11 +227,88 @@ class Context {
     tables_dirty = true;
     return OK;
   }
-  ~Context() {
-    for (void *p : allocs) cudaFree(p);
-    if (stream) cudaStreamDestroy(stream);
-  }
+  ~Context();
 };
+
+// Minimal persistent worker pool: run(n, fn) executes fn(0) on the caller and fn(1..n-1) on workers, then joins.
+class Pool {
+ public:
+  explicit Pool(int workers) {
+    for (int i = 0; i < workers; i++) threads.emplace_back([this, i] { loop(i); });
+  }
+  ~Pool() {
+    {
+      std::lock_guard<std::mutex> lk(m);
+      quit = true;
+    }
+    cv.notify_all();
+    for (auto &t : threads) t.join();
+  }
+  void run(int n, const std::function<void(int)> &fn) {
+    if (n <= 1 || threads.empty()) {
+      for (int i = 0; i < n; i++) fn(i);
+      return;
+    }
+    {
+      std::lock_guard<std::mutex> lk(m);
+      job = &fn;
+      next = 1;
+      total = n;
+      pending = n - 1;
+      generation++;
+    }
+    cv.notify_all();
+    fn(0);
+    std::unique_lock<std::mutex> lk(m);
+    done.wait(lk, [this] { return pending == 0; });
+    job = nullptr;
+  }
+
+ private:
+  void loop(int) {
+    while (true) {
+      int mine = -1;
+      const std::function<void(int)> *fn = nullptr;
+      {
+        std::unique_lock<std::mutex> lk(m);
+        cv.wait(lk, [&] { return quit || (job && next < total); });
+        if (quit) return;
+        mine = next++;
+        fn = job;
+      }
+      (*fn)(mine);
+      {
+        std::lock_guard<std::mutex> lk(m);
+        if (--pending == 0) done.notify_all();
+      }
+    }
+  }
+  std::vector<std::thread> threads;
+  std::mutex m;
+  std::condition_variable cv, done;
+  const std::function<void(int)> *job = nullptr;
+  int next = 0, total = 0, pending = 0;
+  unsigned long long generation = 0;
+  bool quit = false;
+};
+
+Context::~Context() {
+  delete pool;
+  lanes.clear();
+  for (void *p : allocs) cudaFree(p);
+}
+
+static int default_lanes() {
+  if (const char *e = getenv("UVIO_KLT_LANES")) {
+    int v = atoi(e);
+    if (v >= 1) return v > 16 ? 16 : v;
+  }
+  int hw = (int)std::thread::hardware_concurrency();
+  int local_world = 1;
+  if (const char *e = getenv("LOCAL_WORLD_SIZE")) local_world = atoi(e) > 0 ? atoi(e) : 1;
+  int v = hw / local_world;   // one process per GPU shares the host cores with its siblings
+  return v < 1 ? 1 : (v > 4 ? 4 : v);
+}
 
 Context *context_for_device(int device, int *err) {
   static std::mutex m;
@@ -230,10 +324,22 @@ Context *context_for_device(int device, int *err) {
   }
   std::unique_ptr<Context> c(new Context);
   c->device = device;
-  if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+  if ((e = cudaSetDevice(device)) != cudaSuccess) {
     if (err) *err = (int)e;
     return nullptr;
   }
+  const int nl = default_lanes();
+  for (int i = 0; i < nl; i++) {
+    std::unique_ptr<Lane> ln(new Lane);
+    ln->dev = c.get();
+    ln->index = i;
+    if ((e = cudaStreamCreateWithFlags(&ln->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+      if (err) *err = (int)e;
+      return nullptr;
+    }
+    c->lanes.push_back(std::move(ln));
+  }
+  c->pool = new Pool(nl - 1);
   Context *p = c.get();
   table[device] = std::move(c);
   return p;
@@ -293,7 +399,7 @@ struct Unit {
 static const uint8_t *mask_ptr(CamState &c, int slot) { return c.mask_nonzero[slot] ? c.mask[slot].data() : nullptr; }
 
 // emit FAST jobs for the cells of one side
-static void emit_fast_jobs(Context *ctx, Side &s, int threshold, int &njobs, size_t &nwords) {
+static void emit_fast_jobs(Lane *ctx, Side &s, int threshold, int &njobs, size_t &nwords) {
   const int cols = s.cam->w, rows = s.cam->h;
   s.job_of_cell.assign(s.cells.size(), -1);
   for (size_t r = 0; r < s.cells.size(); r++) {
@@ -321,7 +427,7 @@ static void phase_a(Unit &u) {
     L.det_slot = u.first ? c.cur : 1 - c.cur;
     L.det_mask = mask_ptr(c, L.det_slot);
     occ_init(L.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y);
-    if (!u.first) occ_feed(L.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), L.det_mask, c.paint.data(), nullptr);
+    if (!u.first) occ_feed(L.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), L.det_mask, nullptr);
     const int need = P.num_features - (int)L.occ.pts.size();
     // mono returns when need < thr (TrackKLT.cpp:470); stereo detects when need > thr (:609)
     L.detect = u.stereo ? (need > thr) : !(need < thr);
@@ -341,7 +447,7 @@ static void phase_a(Unit &u) {
     // in-order loop: its first |pts_last| steps only see the old points, and the new ids are fresh, so they cannot
     // change the stereo-id exemption of an old point. Run those steps now; phase C continues the same loop.
     std::unordered_set<size_t> stereo_ids(L.occ.ids.begin(), L.occ.ids.end());
-    if (!u.first) occ_feed(R.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), R.det_mask, c.paint.data(), &stereo_ids);
+    if (!u.first) occ_feed(R.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), R.det_mask, &stereo_ids);
     // Cells: new points only raise counts and lower the need, so the cells valid now are a superset of the cells the
     // reference will extract from; FAST + top-K + sub-pixel run on the superset, phase C keeps the right subset.
     const int need = P.num_features - (int)R.occ.pts.size();
@@ -355,7 +461,7 @@ static void phase_a(Unit &u) {
 }
 
 // Phase B: per-cell top-K (reference sort order), left mask test, sub-pixel / stereo-LK items.
-static void phase_b(Context *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint32_t> &tmp, std::vector<KeyPointLite> &kps) {
+static void phase_b(Lane *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint32_t> &tmp, std::vector<KeyPointLite> &kps) {
   for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
     Side &s = side ? u.R : u.L;
     s.top.assign(s.cells.size(), {});
@@ -373,6 +479,7 @@ static void phase_b(Context *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint3
   u.sp0L = nsp;
   if (L.detect) {
     const int cols = L.cam->w, rows = L.cam->h;
+    occ_paint(L.occ, L.cam->paint.data());
     const uint8_t *paint = L.cam->paint.data();
     for (auto &cell : L.top)
       for (auto &k : cell) {
@@ -393,7 +500,7 @@ static void phase_b(Context *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint3
   }
 }
 
-static void phase_b_right(Context *ctx, Unit &u, int &nsp) {
+static void phase_b_right(Lane *ctx, Unit &u, int &nsp) {
   Side &R = u.R;
   R.sp_of_cell.assign(R.cells.size(), -1);
   if (!R.detect) return;
@@ -405,7 +512,7 @@ static void phase_b_right(Context *ctx, Unit &u, int &nsp) {
 
 // Phase C: finish the detection with the refined corners (min-distance reject, ids, right side), then either store the
 // first-frame result or emit the temporal LK / RANSAC work.
-static int phase_c_detect(Context *ctx, Unit &u) {
+static int phase_c_detect(Lane *ctx, Unit &u) {
   const Params &P = u.rig->prm;
   Side &L = u.L;
   const int thr = std::min(20, (int)(0.5 * P.num_features));
@@ -441,12 +548,13 @@ static int phase_c_detect(Context *ctx, Unit &u) {
     }
     // right: continue the occupancy loop over the appended stereo points (:722-780), then the right top-up (:784-826)
     std::unordered_set<size_t> stereo_ids(L.occ.ids.begin(), L.occ.ids.end());
-    occ_feed(R.occ, new_r.data(), new_r_ids.data(), new_r.size(), R.det_mask, R.cam->paint.data(), &stereo_ids);
+    occ_feed(R.occ, new_r.data(), new_r_ids.data(), new_r.size(), R.det_mask, &stereo_ids);
     const int need = P.num_features - (int)R.occ.pts.size();
     if (need > thr) {
       std::vector<std::pair<int, int>> cells;
       valid_cells(R.occ, R.det_mask, P.num_features, cells);
       std::vector<Pt> ext;
+      occ_paint(R.occ, R.cam->paint.data());
       const uint8_t *paint = R.cam->paint.data();
       const uint8_t *mask0 = (cols0 == cols1 && rows0 == rows1) ? L.det_mask : nullptr;   // :721 clones mask0 (sic)
       for (auto &cell : cells) {
@@ -484,7 +592,7 @@ static void store_last(Side &s, std::vector<Pt> &pts, std::vector<size_t> &ids) 
   s.cam->have_last = true;
 }
 
-static void emit_temporal(Context *ctx, Unit &u, int &nlk, int &nrs) {
+static void emit_temporal(Lane *ctx, Unit &u, int &nlk, int &nrs) {
   for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
     Side &s = side ? u.R : u.L;
     CamState &c = *s.cam;
@@ -505,7 +613,7 @@ static void emit_temporal(Context *ctx, Unit &u, int &nlk, int &nrs) {
 }
 
 // Phase D: merge / filter the matches and produce the feature-database observations (TrackKLT.cpp:143-189, :285-381).
-static void phase_d(Context *ctx, Unit &u) {
+static void phase_d(Lane *ctx, Unit &u) {
   Rig &rig = *u.rig;
   Side &L = u.L, &R = u.R;
   auto new_pt = [&](Side &s, size_t i) { const LkOut o = ctx->lk_out.h[s.lk_off + i]; return Pt{o.x, o.y}; };
@@ -612,12 +720,13 @@ static bool copy_mask(const HostImage &m, std::vector<uint8_t> &dst, int w, int 
   return nz;
 }
 
-int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
-  std::lock_guard<std::mutex> guard(ctx->mtx);
-  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+// Everything one lane does for its share of a feed_batch call: upload, the three GPU rounds and the host phases between.
+static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
+  Context *dev = ctx->dev;
+  if (cudaSetDevice(dev->device) != cudaSuccess) return E_CUDA;
   const double t0 = now_us();
   ctx->prof_begin();
-  struct ProfGuard { Context *c; ~ProfGuard() { c->prof_end(); } } prof_guard{ctx};
+  struct ProfGuard { Lane *c; ~ProfGuard() { c->prof_end(); } } prof_guard{ctx};
   std::vector<Unit> units;
   int worst = OK;
   auto fail = [&](FeedRequest &r, int code) {
@@ -625,40 +734,20 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     r.rig->last_error = code;
     if (code > worst) worst = code;
   };
-  // ---- validate, allocate, upload ------------------------------------------------------------------------------------
+  // ---- upload + pre-processing jobs + units -----------------------------------------------------------------------------
   int nimg = 0, max_w = 0, max_h = 0, max_lv = 1, any_hist = 0, any_clahe = 0;
-  for (int i = 0; i < n; i++) nimg += reqs[i].n > 0 ? reqs[i].n : 0;
+  for (int i = 0; i < n; i++) nimg += reqs[i]->n;
   CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
   int npre = 0;
   for (int i = 0; i < n; i++) {
-    FeedRequest &rq = reqs[i];
+    FeedRequest &rq = *reqs[i];
     Rig &rig = *rq.rig;
-    rq.status = OK;
-    rig.obs.clear();
     const Params &P = rig.prm;
-    if (rq.n <= 0 || !rq.sensor_ids || !rq.images || !rq.masks) { fail(rq, E_BADMSG); continue; }   // TrackKLT.cpp:37-43
-    if (P.use_stereo && rq.n > 2) { fail(rq, E_BADMSG); continue; }                                   // :90-93
-    if (P.win_size != LK_WIN) { fail(rq, E_ARG); continue; }
-    bool bad = false;
-    for (int k = 0; k < rq.n && !bad; k++) {
-      CamState *c = rig.find_cam(rq.sensor_ids[k]);
-      if (!c) { fail(rq, E_CAMID); bad = true; break; }                                               // :53-54 (.at throws)
-      const HostImage &im = rq.images[k];
-      if (!im.p || im.w <= 0 || im.h <= 0 || im.w > 4095 || im.h > 4095) { fail(rq, E_BADMSG); bad = true; break; }
-      if (rq.masks[k].p && (rq.masks[k].w != im.w || rq.masks[k].h != im.h)) { fail(rq, E_BADMSG); bad = true; break; }
-      for (int q = 0; q < k; q++) if (rq.sensor_ids[q] == rq.sensor_ids[k]) { fail(rq, E_BADMSG); bad = true; }
-      if (bad) break;
-      if (c->raw < 0) {
-        int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size);
-        if (e != OK) { fail(rq, e); bad = true; break; }
-      } else if (c->w != im.w || c->h != im.h) { fail(rq, E_SIZE); bad = true; break; }
-    }
-    if (bad) continue;
     for (int k = 0; k < rq.n; k++) {
       CamState &c = *rig.find_cam(rq.sensor_ids[k]);
       const HostImage &im = rq.images[k];
       c.cur ^= 1;
-      const ImgView &raw = ctx->raw_tab[c.raw];
+      const ImgView &raw = dev->raw_tab[c.raw];
       CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
                                ctx->stream));   // host (pageable or pinned) or device memory
       ctx->stats[2] += (unsigned long long)im.w * im.h;
@@ -666,7 +755,7 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
       ctx->pre_jobs.h[npre++] = PreJob{c.raw, c.pyr[c.cur], P.histogram_method};
       max_w = std::max(max_w, im.w);
       max_h = std::max(max_h, im.h);
-      max_lv = std::max(max_lv, ctx->pyr_tab[c.pyr[c.cur]].nlv);
+      max_lv = std::max(max_lv, dev->pyr_tab[c.pyr[c.cur]].nlv);
       any_hist |= P.histogram_method == 1;
       any_clahe |= P.histogram_method == 2;
     }
@@ -700,8 +789,7 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
     ctx->sp_mask_ready = true;
   }
-  if (ctx->upload_tables() != OK) return E_CUDA;
-  CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, ctx->raw_dev.d, ctx->pyr_dev.d, ctx->hist.d, ctx->hist_ticket.d,
+  CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, dev->raw_dev.d, dev->pyr_dev.d, ctx->hist.d, ctx->hist_ticket.d,
                            ctx->lut.d, ctx->clahe_lut.d, max_w, max_h, any_hist, any_clahe, max_lv));
   ctx->stats[1] += (npre > 0) ? (unsigned)(any_hist + 1 + 2 * any_clahe + (max_lv - 1)) : 0u;
   size_t ncells = 0, nwords = 0;
@@ -731,9 +819,8 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
       Side &s = side ? u.R : u.L;
       if (s.detect) emit_fast_jobs(ctx, s, u.rig->prm.fast_threshold, njobs, nwords);
     }
-  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, ctx->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
+  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
-  ctx->prof_close_round();
   if (ctx->sync() != OK) return E_CUDA;
   ctx->prof_fold();
   ctx->stats[1] += njobs > 0;
@@ -766,7 +853,7 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     for (auto &u : units)
       if (u.stereo) phase_b_right(ctx, u, nsp);
   }
-  CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, nsp, ctx->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, ctx->sp_out_dev.d));
+  CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, nsp, dev->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, ctx->sp_out_dev.d));
   // stereo LK items read their start point from the sub-pixel output: build the index map
   bool chained = true;
   for (auto &u : units) chained &= (!u.stereo || u.lk0 == u.sp0L);
@@ -782,10 +869,9 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
             it.py = it.ny = ctx->sp_out.h[2 * (u.sp0L + i) + 1];
           }
     }
-    CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, ctx->pyr_dev.d, chained ? ctx->sp_out_dev.d : nullptr, 30, 0.01,
+    CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, chained ? ctx->sp_out_dev.d : nullptr, 30, 0.01,
                      ctx->lk_out.d, ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   }
-  ctx->prof_close_round();
   if (ctx->sync() != OK) return E_CUDA;
   ctx->prof_fold();
   ctx->stats[1] += (nsp > 0) + (nlk > 0);
@@ -821,23 +907,21 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     emit_temporal(ctx, u, nlk, nrs);
     max_n = std::max(max_n, std::max(u.L.lk_n, u.R.lk_n));
   }
-  CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, ctx->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,
+  CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,
                    ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, nrs, max_n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d,
-                       ctx->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
-  ctx->prof_close_round();
+                       dev->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
   if (ctx->sync() != OK) return E_CUDA;
   ctx->prof_fold();
   ctx->stats[1] += (nlk > 0) + (nrs > 0);
   ctx->stats[3] += 9ull * nlk + (nrs > 0 ? 9ull * nlk : 0ull);
   ctx->stats[0] += (unsigned long long)n;
-  ctx->stats[4] += 1;
   const double t3 = now_us();
   for (auto &u : units)
     if (!u.first && !u.failed) phase_d(ctx, u);
   const double t4 = now_us();
   for (int i = 0; i < n; i++) {
-    float *s = reqs[i].rig->stage_us;
+    float *s = reqs[i]->rig->stage_us;
     s[0] = (float)(t1 - t0);   // upload + equalise + pyramid (+ FAST of round 1)
     s[1] = (float)(t2 - t1);   // detection (top-K, sub-pixel, id assignment)
     s[2] = (float)(t3 - t2);   // temporal KLT + RANSAC
@@ -847,6 +931,62 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   return worst;
 }
 
+int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  int worst = OK;
+  auto fail = [&](FeedRequest &r, int code) {
+    r.status = code;
+    r.rig->last_error = code;
+    if (code > worst) worst = code;
+  };
+  // ---- validate every message and give new cameras their device memory (serial: it edits the shared tables) ----------------
+  std::vector<FeedRequest *> good;
+  for (int i = 0; i < n; i++) {
+    FeedRequest &rq = reqs[i];
+    Rig &rig = *rq.rig;
+    rq.status = OK;
+    rig.obs.clear();
+    const Params &P = rig.prm;
+    if (rq.n <= 0 || !rq.sensor_ids || !rq.images || !rq.masks) { fail(rq, E_BADMSG); continue; }   // TrackKLT.cpp:37-43
+    if (P.use_stereo && rq.n > 2) { fail(rq, E_BADMSG); continue; }                                   // :90-93
+    if (P.win_size != LK_WIN) { fail(rq, E_ARG); continue; }
+    bool bad = false;
+    for (int k = 0; k < rq.n && !bad; k++) {
+      CamState *c = rig.find_cam(rq.sensor_ids[k]);
+      if (!c) { fail(rq, E_CAMID); bad = true; break; }                                               // :53-54 (.at throws)
+      const HostImage &im = rq.images[k];
+      if (!im.p || im.w <= 0 || im.h <= 0 || im.w > 4095 || im.h > 4095) { fail(rq, E_BADMSG); bad = true; break; }
+      if (rq.masks[k].p && (rq.masks[k].w != im.w || rq.masks[k].h != im.h)) { fail(rq, E_BADMSG); bad = true; break; }
+      for (int q = 0; q < k; q++) if (rq.sensor_ids[q] == rq.sensor_ids[k]) { fail(rq, E_BADMSG); bad = true; }
+      if (bad) break;
+      if (c->raw < 0) {
+        int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size);
+        if (e != OK) { fail(rq, e); bad = true; break; }
+      } else if (c->w != im.w || c->h != im.h) { fail(rq, E_SIZE); bad = true; break; }
+    }
+    if (!bad) good.push_back(&rq);
+  }
+  if (ctx->upload_tables() != OK) return E_CUDA;
+  // ---- split the trackers over the lanes (contiguous shares) and run the lanes concurrently ---------------------------------
+  const int nl = std::max(1, std::min((int)ctx->lanes.size(), (int)good.size()));
+  std::vector<int> rc(nl, OK);
+  ctx->pool->run(nl, [&](int l) {
+    size_t b = good.size() * (size_t)l / nl, e = good.size() * (size_t)(l + 1) / nl;
+    rc[l] = e > b ? lane_feed(ctx->lanes[l].get(), good.data() + b, (int)(e - b)) : OK;
+  });
+  for (int l = 0; l < nl; l++) {
+    Lane &ln = *ctx->lanes[l];
+    for (int k = 0; k < 8; k++) {
+      ctx->stats[k] += ln.stats[k];
+      ln.stats[k] = 0;
+    }
+    if (ln.cuda_err) ctx->cuda_err = ln.cuda_err;
+    if (rc[l] > worst) worst = rc[l];
+  }
+  ctx->stats[4] += 1;
+  return worst;
+}
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Stage entry points: run one kernel on the pyramids a rig already holds (parity tests and micro-benchmarks).
@@ -860,18 +1000,19 @@ static int slot_pyr(Rig *rig, size_t cam_id, int slot, CamState **out) {
 }
 
 int stage_get_level(Rig *rig, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *h, int *nlv) {
-  Context *ctx = rig->ctx;
-  std::lock_guard<std::mutex> guard(ctx->mtx);
+  Context *dev = rig->ctx;
+  std::lock_guard<std::mutex> guard(dev->mtx);
+  Lane *ctx = dev->lanes[0].get();
   CamState *c;
   int p = slot_pyr(rig, cam_id, slot, &c);
   if (p < 0) return E_CAMID;
-  const PyrDesc &d = ctx->pyr_tab[p];
+  const PyrDesc &d = dev->pyr_tab[p];
   if (nlv) *nlv = d.nlv;
   if (level < 0 || level >= d.nlv) return E_ARG;
   if (w) *w = d.lv[level].w;
   if (h) *h = d.lv[level].h;
   if (out) {
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+    if (cudaSetDevice(dev->device) != cudaSuccess) return E_CUDA;
     CU_TRY(cudaMemcpy2D(out, out_stride, d.lv[level].p, d.lv[level].pitch, d.lv[level].w, d.lv[level].h, cudaMemcpyDeviceToHost));
   }
   return OK;
@@ -879,14 +1020,15 @@ int stage_get_level(Rig *rig, size_t cam_id, int slot, int level, uint8_t *out, 
 
 int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch, int threshold, int *xy, float *resp, int cap,
                int *n_out) {
-  Context *ctx = rig->ctx;
-  std::lock_guard<std::mutex> guard(ctx->mtx);
+  Context *dev = rig->ctx;
+  std::lock_guard<std::mutex> guard(dev->mtx);
+  Lane *ctx = dev->lanes[0].get();
   CamState *c;
   int p = slot_pyr(rig, cam_id, slot, &c);
   if (p < 0) return E_CAMID;
   if (x0 < 0 || y0 < 0 || cw <= 0 || ch <= 0 || x0 + cw > c->w || y0 + ch > c->h) return E_ARG;
-  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
-  if (ctx->upload_tables() != OK) return E_CUDA;
+  if (cudaSetDevice(dev->device) != cudaSuccess) return E_CUDA;
+  if (dev->upload_tables() != OK) return E_CUDA;
   size_t words = (size_t)((cw + 1) / 2) * ((ch + 1) / 2);
   CU_TRY(ctx->fast_jobs.reserve(1));
   CU_TRY(ctx->fast_thr.reserve(1));
@@ -897,7 +1039,7 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
   CU_TRY(ctx->fast_ticket.reserve(1, true));
   ctx->fast_jobs.h[0] = FastJob{p, x0, y0, cw, ch, 0, (int)words};
   ctx->fast_thr.h[0] = threshold;
-  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, ctx->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
+  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, dev->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   if (ctx->sync() != OK) return E_CUDA;
   unsigned cnt = ctx->fast_cnt.h[0];
@@ -913,13 +1055,14 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
 }
 
 int stage_subpix(Rig *rig, size_t cam_id, int slot, const float *pts, int n, float *out) {
-  Context *ctx = rig->ctx;
-  std::lock_guard<std::mutex> guard(ctx->mtx);
+  Context *dev = rig->ctx;
+  std::lock_guard<std::mutex> guard(dev->mtx);
+  Lane *ctx = dev->lanes[0].get();
   CamState *c;
   int p = slot_pyr(rig, cam_id, slot, &c);
   if (p < 0) return E_CAMID;
-  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
-  if (ctx->upload_tables() != OK) return E_CUDA;
+  if (cudaSetDevice(dev->device) != cudaSuccess) return E_CUDA;
+  if (dev->upload_tables() != OK) return E_CUDA;
   if (!ctx->sp_mask_ready) {
     CU_TRY(ctx->sp_mask.reserve(SP_N));
     CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
@@ -928,7 +1071,7 @@ int stage_subpix(Rig *rig, size_t cam_id, int slot, const float *pts, int n, flo
   CU_TRY(ctx->sp_items.reserve(n));
   CU_TRY(ctx->sp_out.reserve(2 * (size_t)n));
   for (int i = 0; i < n; i++) ctx->sp_items.h[i] = SubpixItem{pts[2 * i], pts[2 * i + 1], p, 0};
-  CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, n, ctx->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, nullptr));
+  CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, n, dev->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, nullptr));
   if (ctx->sync() != OK) return E_CUDA;
   memcpy(out, ctx->sp_out.h, sizeof(float) * 2 * (size_t)n);
   return OK;
@@ -937,14 +1080,15 @@ int stage_subpix(Rig *rig, size_t cam_id, int slot, const float *pts, int n, flo
 // LK from (cam0, slot0) to (cam1, slot1); optionally followed by undistort + RANSAC on the result (mask/p1n may be null)
 int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const float *pts0, const float *pts1_init, int n,
              float *out, uint8_t *status, uint8_t *mask, float *p1n) {
-  Context *ctx = rig->ctx;
-  std::lock_guard<std::mutex> guard(ctx->mtx);
+  Context *dev = rig->ctx;
+  std::lock_guard<std::mutex> guard(dev->mtx);
+  Lane *ctx = dev->lanes[0].get();
   CamState *c0, *c1;
   int p0 = slot_pyr(rig, cam0, slot0, &c0), p1 = slot_pyr(rig, cam1, slot1, &c1);
   if (p0 < 0 || p1 < 0) return E_CAMID;
-  if (ctx->pyr_tab[p0].nlv != ctx->pyr_tab[p1].nlv || c0->w != c1->w || c0->h != c1->h) return E_SIZE;
-  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
-  if (ctx->upload_tables() != OK) return E_CUDA;
+  if (dev->pyr_tab[p0].nlv != dev->pyr_tab[p1].nlv || c0->w != c1->w || c0->h != c1->h) return E_SIZE;
+  if (cudaSetDevice(dev->device) != cudaSuccess) return E_CUDA;
+  if (dev->upload_tables() != OK) return E_CUDA;
   size_t N = (size_t)n;
   CU_TRY(ctx->lk_items.reserve(N));
   CU_TRY(ctx->lk_out.reserve(N));
@@ -953,7 +1097,7 @@ int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const flo
   CU_TRY(ctx->lk_status_dev.reserve(N));
   for (int i = 0; i < n; i++)
     ctx->lk_items.h[i] = LkItem{pts0[2 * i], pts0[2 * i + 1], pts1_init[2 * i], pts1_init[2 * i + 1], p0, p1};
-  CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, n, ctx->pyr_dev.d, nullptr, rig->prm.lk_max_iters, rig->prm.lk_eps, ctx->lk_out.d,
+  CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, n, dev->pyr_dev.d, nullptr, rig->prm.lk_max_iters, rig->prm.lk_eps, ctx->lk_out.d,
                    ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   if (mask) {
     CU_TRY(ctx->rs_jobs.reserve(1));
@@ -970,7 +1114,7 @@ int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const flo
     j.thr = 2.0 / std::max(c0->max_focal, c1->max_focal);
     j.run = n >= 10;
     ctx->rs_jobs.h[0] = j;
-    CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, ctx->cam_dev.d,
+    CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, dev->cam_dev.d,
                          ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
   }
   if (ctx->sync() != OK) return E_CUDA;
@@ -989,12 +1133,13 @@ int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const flo
 // undistort + RANSAC on caller-supplied pixel correspondences (no LK): mask = inliers, p0n/p1n = normalised points
 int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const float *pts1, int n, uint8_t *mask, float *p0n,
                  float *p1n) {
-  Context *ctx = rig->ctx;
-  std::lock_guard<std::mutex> guard(ctx->mtx);
+  Context *dev = rig->ctx;
+  std::lock_guard<std::mutex> guard(dev->mtx);
+  Lane *ctx = dev->lanes[0].get();
   CamState *c0 = rig->find_cam(cam0), *c1 = rig->find_cam(cam1);
   if (!c0 || !c1) return E_CAMID;
-  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
-  if (ctx->upload_tables() != OK) return E_CUDA;
+  if (cudaSetDevice(dev->device) != cudaSuccess) return E_CUDA;
+  if (dev->upload_tables() != OK) return E_CUDA;
   size_t N = (size_t)n;
   CU_TRY(ctx->lk_items.reserve(N));
   CU_TRY(ctx->lk_out_dev.reserve(N));
@@ -1017,7 +1162,7 @@ int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const fl
   j.thr = 2.0 / std::max(c0->max_focal, c1->max_focal);
   j.run = n >= 10;
   ctx->rs_jobs.h[0] = j;
-  CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, ctx->cam_dev.d,
+  CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, dev->cam_dev.d,
                        ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
   if (ctx->sync() != OK) return E_CUDA;
   memcpy(mask, ctx->rs_mask.h, N);
@@ -1031,13 +1176,21 @@ int context_cuda_error(Context *ctx) { return ctx->cuda_err; }
 int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long long launches[K_COUNT]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
-  if (ms) memcpy(ms, ctx->prof_ms, sizeof(ctx->prof_ms));
-  if (launches) memcpy(launches, ctx->prof_launches, sizeof(ctx->prof_launches));
-  if (enable >= 0) {
-    ctx->prof_on = enable != 0;
-    if (enable) {
-      memset(ctx->prof_ms, 0, sizeof(ctx->prof_ms));
-      memset(ctx->prof_launches, 0, sizeof(ctx->prof_launches));
+  for (int k = 0; k < K_COUNT; k++) {
+    if (ms) ms[k] = 0;
+    if (launches) launches[k] = 0;
+  }
+  for (auto &ln : ctx->lanes) {
+    for (int k = 0; k < K_COUNT; k++) {
+      if (ms) ms[k] += ln->prof_ms[k];
+      if (launches) launches[k] += ln->prof_launches[k];
+    }
+    if (enable >= 0) {
+      ln->prof_on = enable != 0;
+      if (enable) {
+        memset(ln->prof_ms, 0, sizeof(ln->prof_ms));
+        memset(ln->prof_launches, 0, sizeof(ln->prof_launches));
+      }
     }
   }
   return OK;
@@ -1053,13 +1206,14 @@ void context_stats(Context *ctx, unsigned long long out[8]) {
   }
 }
 
-// CUDA-event stopwatch on the context's stream (the stream every kernel of this device's trackers is launched on)
+// CUDA-event stopwatch. The events are recorded on lane 0's stream; every feed is host-synchronous on all lanes, so the
+// interval between the two records spans exactly the device work (and host gaps) of the feeds issued in between.
 int context_timer(Context *ctx, int stop, float *ms) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
   for (int i = 0; i < 2; i++)
     if (!ctx->ev[i]) CU_TRY(cudaEventCreate(&ctx->ev[i]));
-  CU_TRY(cudaEventRecord(ctx->ev[stop ? 1 : 0], ctx->stream));
+  CU_TRY(cudaEventRecord(ctx->ev[stop ? 1 : 0], ctx->lanes[0]->stream));
   if (stop) {
     CU_TRY(cudaEventSynchronize(ctx->ev[1]));
     CU_TRY(cudaEventElapsedTime(ms, ctx->ev[0], ctx->ev[1]));

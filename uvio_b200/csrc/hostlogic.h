@@ -25,7 +25,8 @@ struct OccState {
   std::vector<uint8_t> close, grid;
   std::vector<Pt> pts;                // kept points, in order
   std::vector<size_t> ids;
-  std::vector<std::pair<int, int>> painted;   // centres of the boxes painted into `paint`
+  std::vector<std::pair<int, int>> boxes;     // centres of the (2*mpd+1)^2 boxes of mask_updated (:457-461)
+  size_t painted = 0;                         // how many of them are currently painted into the scratch image
 };
 
 inline void occ_init(OccState &o, int cols, int rows, int mpd, int gx, int gy) {
@@ -38,13 +39,15 @@ inline void occ_init(OccState &o, int cols, int rows, int mpd, int gx, int gy) {
   o.grid.assign((size_t)gx * gy, 0);
   o.pts.clear();
   o.ids.clear();
-  o.painted.clear();
+  o.boxes.clear();
+  o.painted = 0;
 }
 
 // Runs the erase-while-iterating loop over n more points (kept ones are appended to o.pts / o.ids).
-// mask: the image mask tested at :446/:762 (null = all zeros).  paint: scratch image receiving the 255-boxes of
-// mask_updated (:457-461).  stereo_ids: right pass only, ids exempt from the closeness erase (:754-759).
-inline void occ_feed(OccState &o, const Pt *pts, const size_t *ids, size_t n, const uint8_t *mask, uint8_t *paint,
+// mask: the image mask tested at :446/:762 (null = all zeros).  The 255-boxes of mask_updated (:457-461) are only recorded
+// here; occ_paint() rasterises them when a detection actually needs mask_updated (most frames need none).
+// stereo_ids: right pass only, ids exempt from the closeness erase (:754-759).
+inline void occ_feed(OccState &o, const Pt *pts, const size_t *ids, size_t n, const uint8_t *mask,
                      const std::unordered_set<size_t> *stereo_ids) {
   const int cols = o.cols, rows = o.rows, mpd = o.mpd;
   for (size_t i = 0; i < n; i++) {
@@ -66,20 +69,25 @@ inline void occ_feed(OccState &o, const Pt *pts, const size_t *ids, size_t n, co
     o.close[(size_t)y_close * o.cw + x_close] = 255;
     uint8_t &g = o.grid[(size_t)y_grid * o.gx + x_grid];
     if (g < 255) g += 1;
-    if (x - mpd >= 0 && x + mpd < cols && y - mpd >= 0 && y + mpd < rows) {
-      for (int yy = y - mpd; yy <= y + mpd; yy++) memset(paint + (size_t)yy * cols + (x - mpd), 255, (size_t)(2 * mpd + 1));
-      o.painted.emplace_back(x, y);
-    }
+    if (x - mpd >= 0 && x + mpd < cols && y - mpd >= 0 && y + mpd < rows) o.boxes.emplace_back(x, y);
     o.pts.push_back(pts[i]);
     o.ids.push_back(ids[i]);
   }
 }
 
+inline void occ_fill(OccState &o, uint8_t *paint, size_t from, size_t to, int value) {
+  for (size_t i = from; i < to; i++)
+    for (int yy = o.boxes[i].second - o.mpd; yy <= o.boxes[i].second + o.mpd; yy++)
+      memset(paint + (size_t)yy * o.cols + (o.boxes[i].first - o.mpd), value, (size_t)(2 * o.mpd + 1));
+}
+// paint = (mask_updated minus the original mask): all recorded boxes set to 255 in the (otherwise zero) scratch image
+inline void occ_paint(OccState &o, uint8_t *paint) {
+  occ_fill(o, paint, o.painted, o.boxes.size(), 255);
+  o.painted = o.boxes.size();
+}
 inline void occ_unpaint(OccState &o, uint8_t *paint) {
-  for (auto &c : o.painted)
-    for (int yy = c.second - o.mpd; yy <= c.second + o.mpd; yy++)
-      memset(paint + (size_t)yy * o.cols + (c.first - o.mpd), 0, (size_t)(2 * o.mpd + 1));
-  o.painted.clear();
+  occ_fill(o, paint, 0, o.painted, 0);
+  o.painted = 0;
 }
 
 // cv::resize(mask, mask_grid, Size(gx,gy), 0, 0, INTER_NEAREST) sample position along one axis

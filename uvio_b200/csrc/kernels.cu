@@ -140,6 +140,7 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
     prof_mark(st, K_PYRDOWN);
     k_pyrdown<<<dim3((w + PD_TW - 1) / PD_TW, (h + PD_TH - 1) / PD_TH, njobs), 256, 0, st>>>(jobs, pyr_tab, l);
   }
+  prof_mark(st, -1);
   return cudaGetLastError();
 }
 
@@ -181,6 +182,7 @@ cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max
   int tiles = ((max_cell_w + FT_W - 1) / FT_W) * ((max_cell_h + FT_H - 1) / FT_H);
   prof_mark(st, K_FAST);
   k_fast<<<dim3(tiles, njobs), 256, 0, st>>>(jobs, thresholds, pyr_tab, out_dev, count_dev, ticket_dev, out_host, count_host);
+  prof_mark(st, -1);
   return cudaGetLastError();
 }
 
@@ -216,6 +218,7 @@ cudaError_t launch_subpix(cudaStream_t st, const SubpixItem *items, int n, const
   prof_mark(st, K_SUBPIX);
   k_subpix<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, mask_dev, out_xy,
                                                                                       out_xy_dev);
+  prof_mark(st, -1);
   return cudaGetLastError();
 }
 
@@ -291,6 +294,7 @@ cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc
   k_lk<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, init_from_dev, max_count,
                                                                                   eps * eps, out_host, status_host, out_dev,
                                                                                   status_dev);
+  prof_mark(st, -1);
   return cudaGetLastError();
 }
 
@@ -349,6 +353,7 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
   prof_mark(st, K_RANSAC);
   k_ransac<<<njobs, RANSAC_THREADS, dyn, st>>>(jobs, items, lk_dev, status_dev, cams_dev, p0n_dev, p1n_dev, p1n_host, mask_host,
                                                mask_dev);
+  prof_mark(st, -1);
   return cudaGetLastError();
 }
 

@@ -45,7 +45,7 @@ struct KernelProf {
   int n = 0;
   bool ready = false;
 };
-extern KernelProf *g_prof;   // defined in engine.cpp; guarded by the context mutex
+extern thread_local KernelProf *g_prof;   // defined in engine.cpp; set by the lane thread that is launching
 inline void prof_mark(cudaStream_t st, int kernel_id) {
   KernelProf *p = g_prof;
   if (!p || p->n >= KernelProf::MAX_MARKS) return;
