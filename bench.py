@@ -170,6 +170,7 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
     if dist is not None:
         dist.barrier()
     track.profile(device, enable=1)
+    track.host_profile(device, reset=True)
     s0 = track.device_stats(device)
     clocks = ClockSampler(device) if sample_clocks else None
     L.uvio_klt_timer_start(device)
@@ -182,6 +183,7 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
     wall = time.perf_counter() - t_wall
     clk = clocks.stop() if clocks else None
     prof = track.profile(device, enable=0)
+    hostp = track.host_profile(device, reset=True)
     s1 = track.device_stats(device)
     sec = ms.value / 1e3
     if dist is not None:
@@ -190,6 +192,9 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
         sec = float(tt.item())
         dist.barrier()
     delta = {k: s1[k] - s0[k] for k in s0}
+    passes = max(1.0, hostp.pop("lane_passes"))
+    delta["host_us_per_lane_pass"] = {k: round(v / passes, 1) for k, v in hostp.items()}
+    delta["lanes"] = passes / max(1, steps)
     for t in trackers:
         t.close()
     return sec, n_obs, clk, delta, prof, wall
@@ -247,6 +252,8 @@ def run_ours(args):
                 "d2h_bytes_per_step": st2["d2h_bytes"] / K, "ms_per_step": 1e3 * sec2 / K,
                 "note": "uvio_klt_feed_batch + uvio_klt_get_new_observations_batch on pinned host frames and host masks"},
         "gpu_launches": int(st["launches"]),
+        "host": {"lanes": st["lanes"], "resident_us_per_lane_pass": st["host_us_per_lane_pass"],
+                 "e2e_us_per_lane_pass": st2["host_us_per_lane_pass"]},
         "clocks": clk,
     }
     return line, prof, st, K, S, cfg, rank, world, dist

@@ -131,6 +131,10 @@ int uvio_klt_timer_stop(int cuda_device, float *ms);
 #define UVIO_K_LK 7
 #define UVIO_K_RANSAC 8
 int uvio_klt_profile(int cuda_device, int enable, double ms[16], unsigned long long launches[16]);
+/* Host wall-clock of the feed, summed over the lanes of that device's context, in microseconds: [0] upload + round-1 launch
+ * issue, [1] wait for round 1, [2] host selection + round-2 issue, [3] wait for round 2, [4] host detection + round-3 issue,
+ * [5] wait for round 3, [6] host merge + observations, [7] lane passes counted. reset != 0 clears the sums afterwards. */
+int uvio_klt_host_profile(int cuda_device, int reset, double us[8]);
 /* uvio_klt_get_new_observations for n trackers at once: tracker i writes at out + i*cap_each, counts[i] = its count */
 int uvio_klt_get_new_observations_batch(uvio_klt *const *h, int n, UvioObs *out, int cap_each, int *counts);
 

@@ -11,7 +11,7 @@ typedef void *cudaStream_t;
 enum { cudaSuccess = 0, cudaErrorInvalidDevice = 101 };
 enum cudaMemcpyKind { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2, cudaMemcpyDefault = 4 };
 typedef void *cudaEvent_t;
-enum { cudaHostAllocMapped = 2, cudaStreamNonBlocking = 1 };
+enum { cudaHostAllocDefault = 0, cudaHostAllocMapped = 2, cudaStreamNonBlocking = 1 };
 
 static inline cudaError_t cudaMalloc(void **p, size_t n) { *p = malloc(n ? n : 1); return *p ? 0 : 2; }
 static inline cudaError_t cudaFree(void *p) { free(p); return 0; }

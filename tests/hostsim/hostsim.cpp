@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../uvio_b200/csrc/fast_body.h"
+#include "../../uvio_b200/csrc/hostlogic.h"
 #include "../../uvio_b200/csrc/image_body.h"
 #include "../../uvio_b200/csrc/lk_body.h"
 #include "../../uvio_b200/csrc/ransac_body.h"
@@ -46,10 +47,9 @@ void hs_pyrdown(const uint8_t *src, int w, int h, int pitch, uint8_t *dst, int d
   GroupSeq g;
   ImgView I{src, w, h, pitch};
   int dw = (w + 1) / 2, dh = (h + 1) / 2;
-  PyrSmem *s = new PyrSmem;
-  for (int oy = 0; oy < dh; oy += PD_TH)
-    for (int ox = 0; ox < dw; ox += PD_TW) pyrdown_tile(g, *s, I, dst, dw, dh, dpitch, ox, oy);
-  delete s;
+  (void)g;
+  for (int oy = 0; oy < dh; oy += PD_ROWS)
+    for (int ox = 0; ox < dw; ox += PD_COLS) pyrdown_strip(I, dst, dw, dh, dpitch, ox, oy);
 }
 
 int hs_pyr_max_level(int w, int h, int req, int win) { return pyr_max_level(w, h, req, win); }
@@ -129,4 +129,16 @@ int hs_ransac(const float *p0, const float *p1, int n, double thr, double conf, 
   return ok;
 }
 
+// per-cell top-K of the host logic: packed words (x | y<<12 | score<<24, any order) -> K keypoints (x, y, response)
+int hs_cell_top_k(const uint32_t *words, int count, int cw, int ch, int K, float *out) {
+  std::vector<uint32_t> tmp, tmp2;
+  std::vector<KeyPointLite> top;
+  cell_top_k(words, (unsigned)count, cw, ch, 0, 0, K, tmp, tmp2, top);
+  for (size_t i = 0; i < top.size(); i++) {
+    out[3 * i] = top[i].x;
+    out[3 * i + 1] = top[i].y;
+    out[3 * i + 2] = top[i].response;
+  }
+  return (int)top.size();
+}
 }  // extern "C"

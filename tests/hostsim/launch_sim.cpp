@@ -34,11 +34,10 @@ cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const
     } else {
       for (int y = 0; y < I.h; y++) memcpy(d0 + (size_t)y * P.lv[0].pitch, I.p + (size_t)y * I.pitch, I.w);
     }
-    PyrSmem s;
     for (int l = 1; l < P.nlv; l++)
-      for (int oy = 0; oy < P.lv[l].h; oy += PD_TH)
-        for (int ox = 0; ox < P.lv[l].w; ox += PD_TW)
-          pyrdown_tile(g, s, P.lv[l - 1], (uint8_t *)P.lv[l].p, P.lv[l].w, P.lv[l].h, P.lv[l].pitch, ox, oy);
+      for (int oy = 0; oy < P.lv[l].h; oy += PD_ROWS)
+        for (int ox = 0; ox < P.lv[l].w; ox += PD_COLS)
+          pyrdown_strip(P.lv[l - 1], (uint8_t *)P.lv[l].p, P.lv[l].w, P.lv[l].h, P.lv[l].pitch, ox, oy);
   }
   return 0;
 }

@@ -31,7 +31,7 @@ def _build(out, srcs, extra=()):
 
 @pytest.fixture(scope="module")
 def bodies():
-    return ctypes.CDLL(_build(os.path.join(SIM, "_sim", "libbodies.so"), [os.path.join(SIM, "hostsim.cpp")]))
+    return ctypes.CDLL(_build(os.path.join(SIM, "_sim", "libbodies.so"), [os.path.join(SIM, "hostsim.cpp")], ["-I", SIM]))
 
 
 @pytest.fixture()
@@ -47,6 +47,34 @@ def sim_tracker(monkeypatch):
 
 def _p(a):
     return ctypes.c_void_p(a.ctypes.data)
+
+
+def test_cell_top_k_matches_real_std_sort(bodies):
+    """The host's per-cell top-K (radix order by position + prefix-only replica of libstdc++'s introsort) against the
+    oracle's real std::sort with the reference comparator, on cells with many response ties (Grider_GRID.h:125-141)."""
+    from oracle.trackklt_cv2 import std_sort_perm
+    rng = np.random.default_rng(5)
+    L = bodies
+    for trial in range(400):
+        cw, ch = int(rng.integers(8, 120)), int(rng.integers(8, 100))
+        n = int(rng.integers(1, min(cw * ch, 700)))
+        if trial % 7 == 0:
+            n = min(n, 40)                      # the comparison-sort path for small cells
+        K = int(rng.integers(1, 24))
+        pos = rng.choice(cw * ch, size=n, replace=False)
+        nresp = int(rng.integers(1, 40))        # few distinct scores -> many ties
+        score = rng.integers(20, 20 + nresp, size=n).astype(np.uint32)
+        words = (score << 24) | ((pos // cw).astype(np.uint32) << 12) | (pos % cw).astype(np.uint32)
+        words = np.ascontiguousarray(words[rng.permutation(n)], dtype=np.uint32)   # the GPU's append order is arbitrary
+        out = np.zeros((K, 3), np.float32)
+        got = L.hs_cell_top_k(_p(words), n, cw, ch, K, _p(out))
+        order = np.argsort(words & 0xFFFFFF, kind="stable")                        # cv::FAST emits row-major
+        rm = words[order]
+        perm = std_sort_perm((rm >> 24).astype(np.float32))
+        want = rm[perm][:K]
+        assert got == min(K, n)
+        exp = np.stack([(want & 4095), (want >> 12) & 4095, want >> 24], axis=1).astype(np.float32)
+        np.testing.assert_array_equal(out[:got], exp, err_msg=f"trial {trial}: n={n} K={K} cell {cw}x{ch}")
 
 
 def test_kernel_bodies_against_stage_goldens(bodies):

@@ -220,6 +220,14 @@ int uvio_klt_timer_stop(int cuda_device, float *ms) {
   return ctx ? context_timer(ctx, 1, ms) : UVIO_E_CUDA;
 }
 
+int uvio_klt_host_profile(int cuda_device, int reset, double us[8]) {
+  int err = 0;
+  Context *ctx = context_for_device(cuda_device, &err);
+  if (!ctx) return UVIO_E_CUDA;
+  context_host_profile(ctx, reset, us);
+  return UVIO_OK;
+}
+
 int uvio_klt_profile(int cuda_device, int enable, double ms[16], unsigned long long launches[16]) {
   int err = 0;
   Context *ctx = context_for_device(cuda_device, &err);

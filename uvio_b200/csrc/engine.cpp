@@ -17,6 +17,7 @@
 #include <functional>
 #include <map>
 #include <memory>
+#include <atomic>
 #include <thread>
 
 #include "hostlogic.h"
@@ -26,6 +27,39 @@
 namespace uvio {
 
 thread_local KernelProf *g_prof = nullptr;
+
+// Optional host-side scope timers (compile with -DUVIO_HOSTPROF; development aid, prints at exit).
+#ifdef UVIO_HOSTPROF
+struct HostProfTable {
+  const char *name[32];
+  std::atomic<long long> ns[32];
+  std::atomic<long long> calls[32];
+  int n = 0;
+  int slot(const char *nm) {
+    for (int i = 0; i < n; i++) if (name[i] == nm) return i;
+    name[n] = nm;
+    return n++;
+  }
+  ~HostProfTable() {
+    for (int i = 0; i < n; i++)
+      fprintf(stderr, "[hostprof] %-24s %10.1f us total %8lld calls %8.2f us/call\n", name[i], ns[i].load() / 1e3, calls[i].load(),
+              ns[i].load() / 1e3 / (double)std::max(1ll, calls[i].load()));
+  }
+};
+static HostProfTable g_hostprof;
+struct HostProfScope {
+  int slot;
+  std::chrono::steady_clock::time_point t0;
+  explicit HostProfScope(int s) : slot(s), t0(std::chrono::steady_clock::now()) {}
+  ~HostProfScope() {
+    g_hostprof.ns[slot] += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+    g_hostprof.calls[slot] += 1;
+  }
+};
+#define HOSTPROF(id) static const int hp_slot_##id = g_hostprof.slot(#id); HostProfScope hp_scope_##id(hp_slot_##id)
+#else
+#define HOSTPROF(id) do { } while (0)
+#endif
 
 #define CU_TRY(expr)                                          \
   do {                                                        \
@@ -51,6 +85,47 @@ struct MappedVec {   // pinned host memory mapped into the device address space 
     return cudaSuccess;
   }
   ~MappedVec() { if (h) cudaFreeHost(h); }
+};
+
+// A job list written by the host and read by one kernel.  Two transports: "copy" (default) keeps the list in pinned host
+// memory and sends the used part to a device buffer with one asynchronous copy ahead of the kernel, so that the kernel's
+// blocks read it from L2/HBM; "mapped" (UVIO_KLT_JOBS=mapped) lets the kernel read the pinned host memory across PCIe.
+static bool jobs_mapped() {
+  static const bool v = [] {
+    const char *e = getenv("UVIO_KLT_JOBS");
+    return e && strcmp(e, "mapped") == 0;
+  }();
+  return v;
+}
+template <class T>
+struct JobVec {
+  T *h = nullptr, *d = nullptr;
+  size_t cap = 0;
+  bool mapped = false;
+  cudaError_t reserve(size_t want) {   // contents are not preserved; call only while the stream is idle
+    if (want <= cap) return cudaSuccess;
+    size_t ncap = want + want / 2 + 64;
+    release();
+    mapped = jobs_mapped();
+    cudaError_t e = cudaHostAlloc((void **)&h, ncap * sizeof(T), mapped ? cudaHostAllocMapped : cudaHostAllocDefault);
+    if (e != cudaSuccess) return e;
+    if (mapped) e = cudaHostGetDevicePointer((void **)&d, h, 0);
+    else e = cudaMalloc((void **)&d, ncap * sizeof(T));
+    if (e != cudaSuccess) return e;
+    cap = ncap;
+    return cudaSuccess;
+  }
+  cudaError_t upload(cudaStream_t st, size_t n) {
+    if (mapped || n == 0) return cudaSuccess;
+    return cudaMemcpyAsync(d, h, n * sizeof(T), cudaMemcpyHostToDevice, st);
+  }
+  void release() {
+    if (h) cudaFreeHost(h);
+    if (d && !mapped) cudaFree(d);
+    h = d = nullptr;
+    cap = 0;
+  }
+  ~JobVec() { release(); }
 };
 
 template <class T>
@@ -82,6 +157,8 @@ struct Lane {
   cudaStream_t stream = nullptr;
   int cuda_err = 0;
   unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // accumulated into the context after every feed
+  // host wall-clock per segment of lane_feed (us): issue r1, wait r1, host+issue r2, wait r2, host+issue r3, wait r3, host D, calls
+  double seg_us[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   // per-kernel CUDA-event timing (off by default)
   KernelProf prof;
   bool prof_on = false;
@@ -112,11 +189,11 @@ struct Lane {
     prof.n = 0;
   }
   // round 1
-  MappedVec<PreJob> pre_jobs;
+  JobVec<PreJob> pre_jobs;
   DevVec<unsigned> hist, hist_ticket;
   DevVec<uint8_t> lut, clahe_lut;
-  MappedVec<FastJob> fast_jobs;
-  MappedVec<int> fast_thr;
+  JobVec<FastJob> fast_jobs;
+  JobVec<int> fast_thr;
   DevVec<uint32_t> fast_out_dev;
   DevVec<unsigned> fast_cnt_dev, fast_ticket;
   MappedVec<uint32_t> fast_out;
@@ -124,15 +201,15 @@ struct Lane {
   // round 2 / 3
   DevVec<float> sp_mask;
   bool sp_mask_ready = false;
-  MappedVec<SubpixItem> sp_items;
+  JobVec<SubpixItem> sp_items;
   MappedVec<float> sp_out;
   DevVec<float> sp_out_dev;
-  MappedVec<LkItem> lk_items;
+  JobVec<LkItem> lk_items;
   MappedVec<LkOut> lk_out;
   MappedVec<uint8_t> lk_status;
   DevVec<LkOut> lk_out_dev;
   DevVec<uint8_t> lk_status_dev;
-  MappedVec<RansacJob> rs_jobs;
+  JobVec<RansacJob> rs_jobs;
   DevVec<float> p0n_dev, p1n_dev;
   MappedVec<float> p1n;
   MappedVec<uint8_t> rs_mask;
@@ -158,8 +235,10 @@ class Context {
   // counters since creation: [0] frames fed, [1] kernel launches, [2] bytes uploaded, [3] bytes the GPU wrote to host memory,
   // [4] feed_batch calls, [5] pixels scanned by FAST
   unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  double seg_us[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // sum over lanes of Lane::seg_us
   cudaEvent_t ev[2] = {nullptr, nullptr};
-  std::vector<std::unique_ptr<Lane>> lanes;
+  std::vector<std::unique_ptr<Lane>> lanes;   // threads * depth of them
+  int threads = 1;                            // host threads a feed_batch call uses (caller included)
   Pool *pool = nullptr;
   // tables (host copy + device copy, re-uploaded when dirty; read-only while lanes run)
   std::vector<PyrDesc> pyr_tab;
@@ -190,7 +269,9 @@ class Context {
     const int L = pyr_max_level(w, h, pyr_levels, win);
     if (L + 1 > MAX_LEVELS) return E_ARG;
     auto pitch_of = [](int ww) { return (ww + 127) / 128 * 128; };
-    size_t raw_bytes = (size_t)pitch_of(w) * h, pyr_bytes = 0;
+    // the upload buffer keeps the rows as tight as 16-byte loads allow, so that a tightly packed host frame is one 1-D copy
+    const int raw_pitch = (w + 15) / 16 * 16;
+    size_t raw_bytes = ((size_t)raw_pitch * h + 255) / 256 * 256, pyr_bytes = 0;
     int lw = w, lh = h;
     for (int l = 0; l <= L; l++) {
       pyr_bytes += (size_t)pitch_of(lw) * lh;
@@ -204,7 +285,7 @@ class Context {
     c.w = w;
     c.h = h;
     c.raw = (int)raw_tab.size();
-    raw_tab.push_back(ImgView{base, w, h, pitch_of(w)});
+    raw_tab.push_back(ImgView{base, w, h, raw_pitch});
     uint8_t *p = base + raw_bytes;
     for (int s = 0; s < 2; s++) {
       PyrDesc d;
@@ -223,23 +304,24 @@ class Context {
       c.mask[s].assign((size_t)w * h, 0);
       c.mask_nonzero[s] = false;
     }
-    c.paint.assign((size_t)w * h, 0);
     tables_dirty = true;
     return OK;
   }
   ~Context();
 };
 
-// Minimal persistent worker pool: run(n, fn) executes fn(0) on the caller and fn(1..n-1) on workers, then joins.
+// Minimal persistent worker pool: run(n, fn) executes fn(0) on the caller and fn(1..n-1) on workers, then joins.  Workers
+// spin briefly for the next job before they sleep (feed_batch calls arrive back to back when a pipeline is busy), and the
+// caller spins for the join: both waits are far shorter than a futex round trip.
 class Pool {
  public:
   explicit Pool(int workers) {
-    for (int i = 0; i < workers; i++) threads.emplace_back([this, i] { loop(i); });
+    for (int i = 0; i < workers; i++) threads.emplace_back([this] { loop(); });
   }
   ~Pool() {
     {
       std::lock_guard<std::mutex> lk(m);
-      quit = true;
+      quit.store(true);
     }
     cv.notify_all();
     for (auto &t : threads) t.join();
@@ -252,44 +334,68 @@ class Pool {
     {
       std::lock_guard<std::mutex> lk(m);
       job = &fn;
-      next = 1;
       total = n;
-      pending = n - 1;
-      generation++;
+      pending.store(n - 1);
+      const unsigned long long g = generation.load() + 1;
+      next.store((g << 32) | 1ull);   // claims carry the generation, so a straggler of an older run can never take one
+      generation.store(g, std::memory_order_release);
     }
-    cv.notify_all();
+    if (sleepers.load() > 0) cv.notify_all();
     fn(0);
-    std::unique_lock<std::mutex> lk(m);
-    done.wait(lk, [this] { return pending == 0; });
+    drain(generation.load(), fn, n);   // help with whatever is left, then wait for the stragglers
+    while (pending.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+    std::lock_guard<std::mutex> lk(m);
     job = nullptr;
   }
 
  private:
-  void loop(int) {
+  void loop() {
+    unsigned long long seen = 0;
     while (true) {
-      int mine = -1;
-      const std::function<void(int)> *fn = nullptr;
-      {
-        std::unique_lock<std::mutex> lk(m);
-        cv.wait(lk, [&] { return quit || (job && next < total); });
-        if (quit) return;
-        mine = next++;
-        fn = job;
+      const auto spin_until = std::chrono::steady_clock::now() + std::chrono::microseconds(300);
+      while (generation.load(std::memory_order_acquire) == seen && !quit.load(std::memory_order_relaxed) &&
+             std::chrono::steady_clock::now() < spin_until) {
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
       }
-      (*fn)(mine);
+      if (generation.load(std::memory_order_acquire) == seen) {
+        std::unique_lock<std::mutex> lk(m);
+        sleepers.fetch_add(1);
+        cv.wait(lk, [&] { return quit.load() || generation.load() != seen; });
+        sleepers.fetch_sub(1);
+      }
+      if (quit.load()) return;
+      const std::function<void(int)> *fn;
+      int n;
       {
-        std::lock_guard<std::mutex> lk(m);
-        if (--pending == 0) done.notify_all();
+        std::lock_guard<std::mutex> lk(m);   // pairs with run(): job/total are published under the mutex
+        seen = generation.load();
+        fn = job;
+        n = total;
+      }
+      if (!fn) continue;
+      drain(seen, *fn, n);
+    }
+  }
+  void drain(unsigned long long gen, const std::function<void(int)> &fn, int n) {
+    unsigned long long cur = next.load();
+    while ((cur >> 32) == (gen & 0xffffffffull) && (int)(cur & 0xffffffffull) < n) {
+      if (next.compare_exchange_weak(cur, cur + 1)) {
+        fn((int)(cur & 0xffffffffull));
+        pending.fetch_sub(1, std::memory_order_release);
+        cur = next.load();
       }
     }
   }
   std::vector<std::thread> threads;
   std::mutex m;
-  std::condition_variable cv, done;
+  std::condition_variable cv;
   const std::function<void(int)> *job = nullptr;
-  int next = 0, total = 0, pending = 0;
-  unsigned long long generation = 0;
-  bool quit = false;
+  int total = 0;
+  std::atomic<int> pending{0}, sleepers{0};
+  std::atomic<unsigned long long> next{0}, generation{0};
+  std::atomic<bool> quit{false};
 };
 
 Context::~Context() {
@@ -298,7 +404,9 @@ Context::~Context() {
   for (void *p : allocs) cudaFree(p);
 }
 
-static int default_lanes() {
+// Host threads per device context: UVIO_KLT_LANES, else the process's share of the cores (one process per GPU shares the
+// host with its siblings), at most 8.  Every thread drives UVIO_KLT_DEPTH lanes (default 2) alternately.
+static int default_threads() {
   if (const char *e = getenv("UVIO_KLT_LANES")) {
     int v = atoi(e);
     if (v >= 1) return v > 16 ? 16 : v;
@@ -306,8 +414,15 @@ static int default_lanes() {
   int hw = (int)std::thread::hardware_concurrency();
   int local_world = 1;
   if (const char *e = getenv("LOCAL_WORLD_SIZE")) local_world = atoi(e) > 0 ? atoi(e) : 1;
-  int v = hw / local_world;   // one process per GPU shares the host cores with its siblings
-  return v < 1 ? 1 : (v > 4 ? 4 : v);
+  int v = hw / local_world / 2;
+  return v < 1 ? 1 : (v > 8 ? 8 : v);
+}
+static int default_depth() {
+  if (const char *e = getenv("UVIO_KLT_DEPTH")) {
+    int v = atoi(e);
+    if (v >= 1) return v > 4 ? 4 : v;
+  }
+  return 2;
 }
 
 Context *context_for_device(int device, int *err) {
@@ -328,7 +443,8 @@ Context *context_for_device(int device, int *err) {
     if (err) *err = (int)e;
     return nullptr;
   }
-  const int nl = default_lanes();
+  c->threads = default_threads();
+  const int nl = c->threads * default_depth();
   for (int i = 0; i < nl; i++) {
     std::unique_ptr<Lane> ln(new Lane);
     ln->dev = c.get();
@@ -339,7 +455,7 @@ Context *context_for_device(int device, int *err) {
     }
     c->lanes.push_back(std::move(ln));
   }
-  c->pool = new Pool(nl - 1);
+  c->pool = new Pool(c->threads - 1);
   Context *p = c.get();
   table[device] = std::move(c);
   return p;
@@ -359,7 +475,6 @@ Rig::Rig(Context *c, const Params &p, const CamCalib *cc, int n_cams) : ctx(c), 
   }
   c->tables_dirty = true;
 }
-Rig::~Rig() {}
 CamState *Rig::find_cam(size_t id) {
   auto it = cam_index.find(id);
   return it == cam_index.end() ? nullptr : &cams[it->second];
@@ -394,12 +509,44 @@ struct Unit {
   std::vector<KeyPointLite> selL;     // left corners that passed the mask test, in cell order (sub-pixel items sp0L..)
   int sp0L = 0, lk0 = 0;              // first sub-pixel item / first stereo-LK item of selL
   bool failed = false;
+  // scratch that keeps its capacity from feed to feed
+  std::vector<Pt> good_l, good_r, refined, new_r, ext;
+  std::vector<size_t> ids_l, ids_r, obs_l_idx, obs_r_idx, new_r_ids;
+  std::vector<int> keep;
+  IdTable tab_a, tab_b;
+};
+
+Rig::~Rig() {
+  for (Unit *u : unit_pool) delete u;
+}
+Unit *Rig::unit_at(size_t i) {
+  while (unit_pool.size() <= i) unit_pool.push_back(new Unit);
+  Unit *u = unit_pool[i];
+  u->rig = this;
+  u->failed = false;
+  return u;
+}
+
+// the units of one pass: pointers into the rigs' pools, iterated as references
+struct UnitList {
+  std::vector<Unit *> v;
+  struct It {
+    Unit *const *p;
+    Unit &operator*() const { return **p; }
+    It &operator++() { ++p; return *this; }
+    bool operator!=(const It &o) const { return p != o.p; }
+  };
+  It begin() const { return It{v.data()}; }
+  It end() const { return It{v.data() + v.size()}; }
+  size_t size() const { return v.size(); }
+  void push_back(Unit *u) { v.push_back(u); }
 };
 
 static const uint8_t *mask_ptr(CamState &c, int slot) { return c.mask_nonzero[slot] ? c.mask[slot].data() : nullptr; }
 
 // emit FAST jobs for the cells of one side
 static void emit_fast_jobs(Lane *ctx, Side &s, int threshold, int &njobs, size_t &nwords) {
+  HOSTPROF(emit_fast_jobs);
   const int cols = s.cam->w, rows = s.cam->h;
   s.job_of_cell.assign(s.cells.size(), -1);
   for (size_t r = 0; r < s.cells.size(); r++) {
@@ -419,6 +566,7 @@ static void emit_fast_jobs(Lane *ctx, Side &s, int threshold, int &njobs, size_t
 
 // Phase A: occupancy passes and the list of cells to run FAST on.
 static void phase_a(Unit &u) {
+  HOSTPROF(phase_a);
   const Params &P = u.rig->prm;
   Side &L = u.L;
   const int thr = std::min(20, (int)(0.5 * P.num_features));
@@ -426,7 +574,8 @@ static void phase_a(Unit &u) {
     CamState &c = *L.cam;
     L.det_slot = u.first ? c.cur : 1 - c.cur;
     L.det_mask = mask_ptr(c, L.det_slot);
-    occ_init(L.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y);
+    { HOSTPROF(a_occ_init); occ_init(L.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y); }
+    HOSTPROF(a_left_rest);
     if (!u.first) occ_feed(L.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), L.det_mask, nullptr);
     const int need = P.num_features - (int)L.occ.pts.size();
     // mono returns when need < thr (TrackKLT.cpp:470); stereo detects when need > thr (:609)
@@ -446,7 +595,9 @@ static void phase_a(Unit &u) {
     // The right pass (:722-780) runs after the left detection appended new stereo points to pts1, but it is a plain
     // in-order loop: its first |pts_last| steps only see the old points, and the new ids are fresh, so they cannot
     // change the stereo-id exemption of an old point. Run those steps now; phase C continues the same loop.
-    std::unordered_set<size_t> stereo_ids(L.occ.ids.begin(), L.occ.ids.end());
+    IdTable &stereo_ids = u.tab_a;
+    { HOSTPROF(a_idtable); stereo_ids.fill(L.occ.ids.data(), L.occ.ids.size()); }
+    HOSTPROF(a_right_feed);
     if (!u.first) occ_feed(R.occ, c.pts_last.data(), c.ids_last.data(), c.pts_last.size(), R.det_mask, &stereo_ids);
     // Cells: new points only raise counts and lower the need, so the cells valid now are a superset of the cells the
     // reference will extract from; FAST + top-K + sub-pixel run on the superset, phase C keeps the right subset.
@@ -461,16 +612,22 @@ static void phase_a(Unit &u) {
 }
 
 // Phase B: per-cell top-K (reference sort order), left mask test, sub-pixel / stereo-LK items.
-static void phase_b(Lane *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint32_t> &tmp, std::vector<KeyPointLite> &kps) {
+static void phase_b(Lane *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint32_t> &tmp, std::vector<uint32_t> &grid) {
+  HOSTPROF(phase_b);
   for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
     Side &s = side ? u.R : u.L;
-    s.top.assign(s.cells.size(), {});
+    if (s.top.size() < s.cells.size()) s.top.resize(s.cells.size());   // entries beyond cells.size() are stale scratch
+    for (size_t r = 0; r < s.cells.size(); r++) s.top[r].clear();
     if (!s.detect) continue;
+    HOSTPROF(b_topk);
     for (size_t r = 0; r < s.cells.size(); r++) {
       int j = s.job_of_cell[r];
       if (j < 0) continue;
       const FastJob &job = ctx->fast_jobs.h[j];
-      cell_top_k(ctx->fast_out.h + job.out_off, ctx->fast_cnt.h[j], job.x0, job.y0, s.geom.per_cell, tmp, kps, s.top[r]);
+#ifdef UVIO_HOSTPROF
+      { static long long cells = 0, corners = 0; cells++; corners += ctx->fast_cnt.h[j]; if ((cells & 255) == 0) fprintf(stderr, "[hostprof] cells %lld corners %lld\n", cells, corners); }
+#endif
+      cell_top_k(ctx->fast_out.h + job.out_off, ctx->fast_cnt.h[j], job.w, job.h, job.x0, job.y0, s.geom.per_cell, tmp, grid, s.top[r]);
     }
   }
   // left: mask test against mask_updated = mask | painted boxes (Grider_GRID.h:142-148), then sub-pixel
@@ -478,19 +635,17 @@ static void phase_b(Lane *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint32_t
   u.selL.clear();
   u.sp0L = nsp;
   if (L.detect) {
+    HOSTPROF(b_masktest);
     const int cols = L.cam->w, rows = L.cam->h;
-    occ_paint(L.occ, L.cam->paint.data());
-    const uint8_t *paint = L.cam->paint.data();
-    for (auto &cell : L.top)
-      for (auto &k : cell) {
+    for (size_t r = 0; r < L.cells.size(); r++)
+      for (auto &k : L.top[r]) {
         int x = (int)k.x, y = (int)k.y;
         if (x < 0 || x > cols || y < 0 || y > rows) continue;
         size_t at = (size_t)y * cols + x;
-        if ((L.det_mask && L.det_mask[at] > 127) || paint[at] > 127) continue;
+        if ((L.det_mask && L.det_mask[at] > 127) || occ_boxed(L.occ, at)) continue;
         u.selL.push_back(k);
       }
   }
-  occ_unpaint(L.occ, L.cam->paint.data());
   for (auto &k : u.selL) ctx->sp_items.h[nsp++] = SubpixItem{k.x, k.y, L.cam->pyr[L.det_slot], 0};
   u.lk0 = nlk;
   if (u.stereo) {
@@ -501,6 +656,7 @@ static void phase_b(Lane *ctx, Unit &u, int &nsp, int &nlk, std::vector<uint32_t
 }
 
 static void phase_b_right(Lane *ctx, Unit &u, int &nsp) {
+  HOSTPROF(phase_b_right);
   Side &R = u.R;
   R.sp_of_cell.assign(R.cells.size(), -1);
   if (!R.detect) return;
@@ -513,15 +669,19 @@ static void phase_b_right(Lane *ctx, Unit &u, int &nsp) {
 // Phase C: finish the detection with the refined corners (min-distance reject, ids, right side), then either store the
 // first-frame result or emit the temporal LK / RANSAC work.
 static int phase_c_detect(Lane *ctx, Unit &u) {
+  HOSTPROF(phase_c_detect);
   const Params &P = u.rig->prm;
   Side &L = u.L;
   const int thr = std::min(20, (int)(0.5 * P.num_features));
-  std::vector<Pt> refined(u.selL.size());
+  std::vector<Pt> &refined = u.refined;
+  refined.resize(u.selL.size());
   for (size_t i = 0; i < u.selL.size(); i++) refined[i] = Pt{ctx->sp_out.h[2 * (u.sp0L + i)], ctx->sp_out.h[2 * (u.sp0L + i) + 1]};
-  std::vector<int> keep;
+  std::vector<int> &keep = u.keep;
   close_reject(L.occ, refined.data(), refined.size(), keep);       // TrackKLT.cpp:497-512 / :635-650
-  std::vector<Pt> new_r;
-  std::vector<size_t> new_r_ids;
+  std::vector<Pt> &new_r = u.new_r;
+  std::vector<size_t> &new_r_ids = u.new_r_ids;
+  new_r.clear();
+  new_r_ids.clear();
   if (!u.stereo) {
     for (int i : keep) {                                            // :519-527
       L.occ.pts.push_back(refined[i]);
@@ -547,15 +707,15 @@ static int phase_c_detect(Lane *ctx, Unit &u) {
       }
     }
     // right: continue the occupancy loop over the appended stereo points (:722-780), then the right top-up (:784-826)
-    std::unordered_set<size_t> stereo_ids(L.occ.ids.begin(), L.occ.ids.end());
+    IdTable &stereo_ids = u.tab_a;
+    stereo_ids.fill(L.occ.ids.data(), L.occ.ids.size());
     occ_feed(R.occ, new_r.data(), new_r_ids.data(), new_r.size(), R.det_mask, &stereo_ids);
     const int need = P.num_features - (int)R.occ.pts.size();
     if (need > thr) {
       std::vector<std::pair<int, int>> cells;
       valid_cells(R.occ, R.det_mask, P.num_features, cells);
-      std::vector<Pt> ext;
-      occ_paint(R.occ, R.cam->paint.data());
-      const uint8_t *paint = R.cam->paint.data();
+      std::vector<Pt> &ext = u.ext;
+      ext.clear();
       const uint8_t *mask0 = (cols0 == cols1 && rows0 == rows1) ? L.det_mask : nullptr;   // :721 clones mask0 (sic)
       for (auto &cell : cells) {
         size_t r = 0;
@@ -566,7 +726,7 @@ static int phase_c_detect(Lane *ctx, Unit &u) {
           int x = (int)kp.x, y = (int)kp.y;
           if (x < 0 || x > cols1 || y < 0 || y > rows1) continue;
           size_t at = (size_t)y * cols1 + x;
-          if ((mask0 && mask0[at] > 127) || paint[at] > 127) continue;
+          if ((mask0 && mask0[at] > 127) || occ_boxed(R.occ, at)) continue;
           int sp = R.sp_of_cell[r] + (int)k;
           ext.push_back(Pt{ctx->sp_out.h[2 * sp], ctx->sp_out.h[2 * sp + 1]});
         }
@@ -577,7 +737,6 @@ static int phase_c_detect(Lane *ctx, Unit &u) {
         R.occ.ids.push_back(++u.rig->currid);
       }
     }
-    occ_unpaint(R.occ, R.cam->paint.data());
     R.pts.swap(R.occ.pts);
     R.ids.swap(R.occ.ids);
   }
@@ -593,6 +752,7 @@ static void store_last(Side &s, std::vector<Pt> &pts, std::vector<size_t> &ids) 
 }
 
 static void emit_temporal(Lane *ctx, Unit &u, int &nlk, int &nrs) {
+  HOSTPROF(emit_temporal);
   for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
     Side &s = side ? u.R : u.L;
     CamState &c = *s.cam;
@@ -614,6 +774,7 @@ static void emit_temporal(Lane *ctx, Unit &u, int &nlk, int &nrs) {
 
 // Phase D: merge / filter the matches and produce the feature-database observations (TrackKLT.cpp:143-189, :285-381).
 static void phase_d(Lane *ctx, Unit &u) {
+  HOSTPROF(phase_d);
   Rig &rig = *u.rig;
   Side &L = u.L, &R = u.R;
   auto new_pt = [&](Side &s, size_t i) { const LkOut o = ctx->lk_out.h[s.lk_off + i]; return Pt{o.x, o.y}; };
@@ -621,8 +782,12 @@ static void phase_d(Lane *ctx, Unit &u) {
   auto add_obs = [&](Side &s, size_t i, size_t id, Pt p) {
     rig.obs.push_back(Obs{id, s.cam->cam_id, p.x, p.y, ctx->p1n.h[2 * (s.lk_off + i)], ctx->p1n.h[2 * (s.lk_off + i) + 1]});
   };
-  std::vector<Pt> good_l, good_r;
-  std::vector<size_t> ids_l, ids_r;
+  std::vector<Pt> &good_l = u.good_l, &good_r = u.good_r;   // scratch kept in the unit; swapped into pts_last at the end
+  std::vector<size_t> &ids_l = u.ids_l, &ids_r = u.ids_r;
+  good_l.clear(); good_r.clear(); ids_l.clear(); ids_r.clear();
+  good_l.reserve(L.pts.size()); ids_l.reserve(L.pts.size());
+  good_r.reserve(R.pts.size()); ids_r.reserve(R.pts.size());
+  rig.obs.reserve(L.pts.size() + R.pts.size());
   if (!u.stereo) {
     CamState &c = *L.cam;
     if (L.pts.empty()) {                                            // :143-152 (mask_ll empty)
@@ -650,24 +815,26 @@ static void phase_d(Lane *ctx, Unit &u) {
     return;
   }
   const int cols_l = L.cam->w, rows_l = L.cam->h, cols_r = R.cam->w, rows_r = R.cam->h;
-  std::unordered_map<size_t, size_t> first_right;                   // id -> first index in ids_right_old (:314-320)
-  for (size_t i = R.ids.size(); i-- > 0;) first_right[R.ids[i]] = i;
-  std::vector<size_t> obs_l_idx, obs_r_idx;
+  IdTable &first_right = u.tab_a;                                   // id -> first index in ids_right_old (:314-320)
+  first_right.fill(R.ids.data(), R.ids.size());
+  std::vector<size_t> &obs_l_idx = u.obs_l_idx, &obs_r_idx = u.obs_r_idx;
+  obs_l_idx.clear(); obs_r_idx.clear();
+  obs_l_idx.reserve(L.pts.size()); obs_r_idx.reserve(R.pts.size());
   if (L.lk_run)
     for (size_t i = 0; i < L.pts.size(); i++) {                     // :306-338
       Pt p = new_pt(L, i);
       if (p.x < 0 || p.y < 0 || (int)p.x > cols_l || (int)p.y > rows_l) continue;   // '>' on the left (:308-309)
-      auto it = first_right.find(L.ids[i]);
-      const bool found_right = it != first_right.end();
-      if (ok(L, i) && found_right && ok(R, it->second)) {
-        Pt q = new_pt(R, it->second);
+      const int ir = first_right.find(L.ids[i]);
+      const bool found_right = ir >= 0;
+      if (ok(L, i) && found_right && ok(R, (size_t)ir)) {
+        Pt q = new_pt(R, (size_t)ir);
         if (q.x < 0 || q.y < 0 || (int)q.x >= cols_r || (int)q.y >= rows_r) continue;
         good_l.push_back(p);
         ids_l.push_back(L.ids[i]);
         obs_l_idx.push_back(i);
         good_r.push_back(q);
-        ids_r.push_back(R.ids[it->second]);
-        obs_r_idx.push_back(it->second);
+        ids_r.push_back(R.ids[ir]);
+        obs_r_idx.push_back((size_t)ir);
       } else if (ok(L, i)) {
         good_l.push_back(p);
         ids_l.push_back(L.ids[i]);
@@ -675,15 +842,17 @@ static void phase_d(Lane *ctx, Unit &u) {
       }
     }
   if (R.lk_run) {
-    std::unordered_set<size_t> added(ids_r.begin(), ids_r.end());
+    IdTable &added = u.tab_b;
+    added.reset(ids_r.size() + R.pts.size());
+    for (size_t k = 0; k < ids_r.size(); k++) added.insert(ids_r[k], (int)k);
     for (size_t i = 0; i < R.pts.size(); i++) {                     // :341-354
       Pt q = new_pt(R, i);
       if (q.x < 0 || q.y < 0 || (int)q.x >= cols_r || (int)q.y >= rows_r) continue;
-      if (ok(R, i) && !added.count(R.ids[i])) {
+      if (ok(R, i) && added.find(R.ids[i]) < 0) {
         good_r.push_back(q);
         ids_r.push_back(R.ids[i]);
         obs_r_idx.push_back(i);
-        added.insert(R.ids[i]);
+        added.insert(R.ids[i], (int)i);
       }
     }
   }
@@ -697,48 +866,93 @@ static double now_us() {
   return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-// copy a caller mask into the camera's host slot; returns whether any pixel is non-zero
+// keep a caller mask for the detection of the next feed (TrackKLT.cpp:129,245 detect on img_mask_last); returns whether any
+// pixel is non-zero.  An all-zero mask (the usual case) is only scanned, not copied.
 static bool copy_mask(const HostImage &m, std::vector<uint8_t> &dst, int w, int h) {
-  if (!m.p) {
-    return false;
-  }
+  HOSTPROF(copy_mask);
+  if (!m.p) return false;
   bool nz = false;
-  for (int y = 0; y < h; y++) {
+  for (int y = 0; y < h && !nz; y++) {
     const uint8_t *r = m.p + (size_t)y * m.stride;
-    uint8_t *d = dst.data() + (size_t)y * w;
-    memcpy(d, r, (size_t)w);
-    if (!nz) {
-      int x = 0;
-      for (; x + 8 <= w && !nz; x += 8) {
-        uint64_t v;
-        memcpy(&v, d + x, 8);
-        nz = v != 0;
-      }
-      for (; x < w && !nz; x++) nz = d[x] != 0;
+    uint64_t acc = 0;
+    int x = 0;
+    for (; x + 32 <= w; x += 32) {
+      uint64_t a, b, c, d;
+      memcpy(&a, r + x, 8);
+      memcpy(&b, r + x + 8, 8);
+      memcpy(&c, r + x + 16, 8);
+      memcpy(&d, r + x + 24, 8);
+      acc |= (a | b) | (c | d);
     }
+    for (; x < w; x++) acc |= r[x];
+    nz = acc != 0;
   }
-  return nz;
+  if (!nz) return false;
+  for (int y = 0; y < h; y++) memcpy(dst.data() + (size_t)y * w, m.p + (size_t)y * m.stride, (size_t)w);
+  return true;
 }
 
-// Everything one lane does for its share of a feed_batch call: upload, the three GPU rounds and the host phases between.
-static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
-  Context *dev = ctx->dev;
-  if (cudaSetDevice(dev->device) != cudaSuccess) return E_CUDA;
-  const double t0 = now_us();
-  ctx->prof_begin();
-  struct ProfGuard { Lane *c; ~ProfGuard() { c->prof_end(); } } prof_guard{ctx};
-  std::vector<Unit> units;
+// Everything one lane does for its share of a feed_batch call, cut at the three stream synchronisations into four stages so
+// that one host thread can drive two lanes alternately: while it does the host bookkeeping of one lane, the GPU works on the
+// rounds the other lane has already issued.
+struct Pass {
+  Lane *ctx = nullptr;
+  FeedRequest **reqs = nullptr;
+  int n = 0;
+  UnitList units;
   int worst = OK;
-  auto fail = [&](FeedRequest &r, int code) {
+  int rc = OK;          // E_CUDA once a stage failed; later stages are skipped
+  int stage = 0;
+  int npre = 0, njobs = 0, nsp = 0, nlk = 0, nrs = 0;
+  double t0 = 0, t1 = 0, t2 = 0, t3 = 0, tmark = 0;
+
+  void fail(FeedRequest &r, int code) {
     r.status = code;
     r.rig->last_error = code;
     if (code > worst) worst = code;
-  };
+  }
+  void seg(int k) {   // close host-profile segment k at the current time
+    double t = now_us();
+    ctx->seg_us[k] += t - tmark;
+    tmark = t;
+  }
+  int stage0();
+  int stage1();
+  int stage2();
+  int stage3();
+  // run the next stage (synchronising the lane's stream first when the stage consumes GPU results)
+  void step() {
+    if (rc == OK && n > 0) {
+      cudaSetDevice(ctx->dev->device);
+      g_prof = ctx->prof_on ? &ctx->prof : nullptr;
+      if (stage > 0) {
+        if (ctx->sync() != OK) rc = E_CUDA;
+        else {
+          seg(2 * stage - 1);
+          ctx->prof_fold();
+        }
+      }
+      if (rc == OK) {
+        int e = stage == 0 ? stage0() : stage == 1 ? stage1() : stage == 2 ? stage2() : stage3();
+        if (e != OK) rc = e;
+      }
+      g_prof = nullptr;
+    }
+    stage++;
+  }
+  int result() const { return rc != OK ? rc : worst; }
+};
+
+int Pass::stage0() {
+  Context *dev = ctx->dev;
+  t0 = tmark = now_us();
+  ctx->prof_begin();
+  g_prof = ctx->prof_on ? &ctx->prof : nullptr;
   // ---- upload + pre-processing jobs + units -----------------------------------------------------------------------------
   int nimg = 0, max_w = 0, max_h = 0, max_lv = 1, any_hist = 0, any_clahe = 0;
   for (int i = 0; i < n; i++) nimg += reqs[i]->n;
   CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
-  int npre = 0;
+  npre = 0;
   for (int i = 0; i < n; i++) {
     FeedRequest &rq = *reqs[i];
     Rig &rig = *rq.rig;
@@ -748,8 +962,12 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
       const HostImage &im = rq.images[k];
       c.cur ^= 1;
       const ImgView &raw = dev->raw_tab[c.raw];
-      CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
-                               ctx->stream));   // host (pageable or pinned) or device memory
+      // host (pageable or pinned) or device memory
+      if ((size_t)raw.pitch == im.stride)
+        CU_TRY(cudaMemcpyAsync((void *)raw.p, im.p, (size_t)raw.pitch * (im.h - 1) + im.w, cudaMemcpyDefault, ctx->stream));
+      else
+        CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
+                                 ctx->stream));
       ctx->stats[2] += (unsigned long long)im.w * im.h;
       c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
       ctx->pre_jobs.h[npre++] = PreJob{c.raw, c.pyr[c.cur], P.histogram_method};
@@ -762,20 +980,20 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
     // units (TrackKLT.cpp:80-93)
     auto make_side = [&](Side &s, int k) { s.cam = rig.find_cam(rq.sensor_ids[k]); s.msg = k; };
     if (rq.n == 2 && P.use_stereo) {
-      Unit u;
-      u.rig = &rig; u.req = &rq; u.stereo = true;
+      Unit &u = *rig.unit_at(0);
+      u.req = &rq; u.stereo = true;
       make_side(u.L, 0);
       make_side(u.R, 1);
       u.first = u.L.cam->pts_last.empty() && u.R.cam->pts_last.empty();                               // :221
       if (!u.first && (!u.L.cam->have_last || !u.R.cam->have_last)) { fail(rq, E_BADMSG); continue; }
-      units.push_back(std::move(u));
+      units.push_back(&u);
     } else {
       for (int k = 0; k < rq.n; k++) {
-        Unit u;
-        u.rig = &rig; u.req = &rq; u.stereo = false;
+        Unit &u = *rig.unit_at((size_t)k);
+        u.req = &rq; u.stereo = false;
         make_side(u.L, k);
         u.first = u.L.cam->pts_last.empty();                                                          // :110
-        units.push_back(std::move(u));
+        units.push_back(&u);
       }
     }
   }
@@ -789,6 +1007,7 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
     CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
     ctx->sp_mask_ready = true;
   }
+  CU_TRY(ctx->pre_jobs.upload(ctx->stream, (size_t)npre));
   CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, dev->raw_dev.d, dev->pyr_dev.d, ctx->hist.d, ctx->hist_ticket.d,
                            ctx->lut.d, ctx->clahe_lut.d, max_w, max_h, any_hist, any_clahe, max_lv));
   ctx->stats[1] += (npre > 0) ? (unsigned)(any_hist + 1 + 2 * any_clahe + (max_lv - 1)) : 0u;
@@ -812,21 +1031,27 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
   CU_TRY(ctx->fast_out_dev.reserve(nwords));
   CU_TRY(ctx->fast_cnt_dev.reserve(ncells, true));
   CU_TRY(ctx->fast_ticket.reserve(ncells, true));
-  int njobs = 0;
+  njobs = 0;
   nwords = 0;
   for (auto &u : units)
     for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
       Side &s = side ? u.R : u.L;
       if (s.detect) emit_fast_jobs(ctx, s, u.rig->prm.fast_threshold, njobs, nwords);
     }
+  CU_TRY(ctx->fast_jobs.upload(ctx->stream, (size_t)njobs));
+  CU_TRY(ctx->fast_thr.upload(ctx->stream, (size_t)njobs));
   CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
-  if (ctx->sync() != OK) return E_CUDA;
-  ctx->prof_fold();
+  seg(0);
+  return OK;
+}
+
+int Pass::stage1() {
+  Context *dev = ctx->dev;
   ctx->stats[1] += njobs > 0;
   for (int j = 0; j < njobs; j++) ctx->stats[5] += (unsigned long long)ctx->fast_jobs.h[j].w * ctx->fast_jobs.h[j].h;
   for (int j = 0; j < njobs; j++) ctx->stats[3] += 4ull * ctx->fast_cnt.h[j] + 4ull;
-  const double t1 = now_us();
+  t1 = now_us();
   // ---- round 2: sub-pixel + stereo LK --------------------------------------------------------------------------------
   size_t sp_bound = 0;
   for (auto &u : units)
@@ -842,17 +1067,19 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
   CU_TRY(ctx->lk_status.reserve(sp_bound));
   CU_TRY(ctx->lk_out_dev.reserve(sp_bound));
   CU_TRY(ctx->lk_status_dev.reserve(sp_bound));
-  int nsp = 0, nlk = 0;
+  nsp = 0;
+  nlk = 0;
   {
     // sub-pixel items: all left selections first (so that stereo-LK item i chains on sub-pixel item i), then the right
     std::vector<uint32_t> tmp;
-    std::vector<KeyPointLite> kps;
-    for (auto &u : units) phase_b(ctx, u, nsp, nlk, tmp, kps);
+    std::vector<uint32_t> grid;
+    for (auto &u : units) phase_b(ctx, u, nsp, nlk, tmp, grid);
     // a unit's lk0 must equal its sp0L for the chaining: true when only stereo units select points; mono units add
     // sub-pixel items without LK items, so stereo units are given explicit coordinates below instead
     for (auto &u : units)
       if (u.stereo) phase_b_right(ctx, u, nsp);
   }
+  CU_TRY(ctx->sp_items.upload(ctx->stream, (size_t)nsp));
   CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, nsp, dev->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, ctx->sp_out_dev.d));
   // stereo LK items read their start point from the sub-pixel output: build the index map
   bool chained = true;
@@ -869,11 +1096,16 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
             it.py = it.ny = ctx->sp_out.h[2 * (u.sp0L + i) + 1];
           }
     }
+    CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)nlk));
     CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, chained ? ctx->sp_out_dev.d : nullptr, 30, 0.01,
                      ctx->lk_out.d, ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   }
-  if (ctx->sync() != OK) return E_CUDA;
-  ctx->prof_fold();
+  seg(2);
+  return OK;
+}
+
+int Pass::stage2() {
+  Context *dev = ctx->dev;
   ctx->stats[1] += (nsp > 0) + (nlk > 0);
   ctx->stats[3] += 8ull * nsp + 9ull * nlk;
   // ---- host: finish detection; round 3: temporal LK + RANSAC -----------------------------------------------------------
@@ -888,7 +1120,7 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
     }
     lk_bound += u.L.pts.size() + (u.stereo ? u.R.pts.size() : 0);
   }
-  const double t2 = now_us();
+  t2 = now_us();
   CU_TRY(ctx->lk_items.reserve(lk_bound));
   CU_TRY(ctx->lk_out.reserve(lk_bound));
   CU_TRY(ctx->lk_status.reserve(lk_bound));
@@ -901,25 +1133,34 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
   CU_TRY(ctx->rs_mask.reserve(lk_bound));
   CU_TRY(ctx->rs_mask_dev.reserve(lk_bound));
   nlk = 0;
-  int nrs = 0, max_n = 1;
+  nrs = 0;
+  int max_n = 1;
   for (auto &u : units) {
     if (u.first || u.failed) continue;
     emit_temporal(ctx, u, nlk, nrs);
     max_n = std::max(max_n, std::max(u.L.lk_n, u.R.lk_n));
   }
+  CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)nlk));
+  CU_TRY(ctx->rs_jobs.upload(ctx->stream, (size_t)nrs));
   CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,
                    ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, nrs, max_n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d,
                        dev->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
-  if (ctx->sync() != OK) return E_CUDA;
-  ctx->prof_fold();
+  seg(4);
+  return OK;
+}
+
+int Pass::stage3() {
   ctx->stats[1] += (nlk > 0) + (nrs > 0);
   ctx->stats[3] += 9ull * nlk + (nrs > 0 ? 9ull * nlk : 0ull);
   ctx->stats[0] += (unsigned long long)n;
-  const double t3 = now_us();
+  t3 = now_us();
   for (auto &u : units)
     if (!u.first && !u.failed) phase_d(ctx, u);
   const double t4 = now_us();
+  seg(6);
+  ctx->seg_us[7] += 1;
+  ctx->prof_end();
   for (int i = 0; i < n; i++) {
     float *s = reqs[i]->rig->stage_us;
     s[0] = (float)(t1 - t0);   // upload + equalise + pyramid (+ FAST of round 1)
@@ -928,7 +1169,7 @@ static int lane_feed(Lane *ctx, FeedRequest **reqs, int n) {
     s[3] = 0.f;                // stereo KLT is part of the detection round here
     s[4] = (float)(t4 - t3);   // merge + observations
   }
-  return worst;
+  return OK;
 }
 
 int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
@@ -968,18 +1209,29 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     if (!bad) good.push_back(&rq);
   }
   if (ctx->upload_tables() != OK) return E_CUDA;
-  // ---- split the trackers over the lanes (contiguous shares) and run the lanes concurrently ---------------------------------
+  // ---- split the trackers over the lanes (contiguous shares); every host thread drives `depth` lanes stage by stage ---------
   const int nl = std::max(1, std::min((int)ctx->lanes.size(), (int)good.size()));
-  std::vector<int> rc(nl, OK);
-  ctx->pool->run(nl, [&](int l) {
+  const int nthreads = std::max(1, std::min(ctx->threads, nl));
+  std::vector<Pass> passes(nl);
+  for (int l = 0; l < nl; l++) {
     size_t b = good.size() * (size_t)l / nl, e = good.size() * (size_t)(l + 1) / nl;
-    rc[l] = e > b ? lane_feed(ctx->lanes[l].get(), good.data() + b, (int)(e - b)) : OK;
+    passes[l].ctx = ctx->lanes[l].get();
+    passes[l].reqs = good.data() + b;
+    passes[l].n = (int)(e - b);
+  }
+  ctx->pool->run(nthreads, [&](int t) {
+    for (int stage = 0; stage < 4; stage++)
+      for (int l = t; l < nl; l += nthreads) passes[l].step();
   });
+  std::vector<int> rc(nl, OK);
+  for (int l = 0; l < nl; l++) rc[l] = passes[l].result();
   for (int l = 0; l < nl; l++) {
     Lane &ln = *ctx->lanes[l];
     for (int k = 0; k < 8; k++) {
       ctx->stats[k] += ln.stats[k];
       ln.stats[k] = 0;
+      ctx->seg_us[k] += ln.seg_us[k];
+      ln.seg_us[k] = 0;
     }
     if (ln.cuda_err) ctx->cuda_err = ln.cuda_err;
     if (rc[l] > worst) worst = rc[l];
@@ -1039,6 +1291,8 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
   CU_TRY(ctx->fast_ticket.reserve(1, true));
   ctx->fast_jobs.h[0] = FastJob{p, x0, y0, cw, ch, 0, (int)words};
   ctx->fast_thr.h[0] = threshold;
+  CU_TRY(ctx->fast_jobs.upload(ctx->stream, 1));
+  CU_TRY(ctx->fast_thr.upload(ctx->stream, 1));
   CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, dev->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   if (ctx->sync() != OK) return E_CUDA;
@@ -1071,6 +1325,7 @@ int stage_subpix(Rig *rig, size_t cam_id, int slot, const float *pts, int n, flo
   CU_TRY(ctx->sp_items.reserve(n));
   CU_TRY(ctx->sp_out.reserve(2 * (size_t)n));
   for (int i = 0; i < n; i++) ctx->sp_items.h[i] = SubpixItem{pts[2 * i], pts[2 * i + 1], p, 0};
+  CU_TRY(ctx->sp_items.upload(ctx->stream, (size_t)n));
   CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, n, dev->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, nullptr));
   if (ctx->sync() != OK) return E_CUDA;
   memcpy(out, ctx->sp_out.h, sizeof(float) * 2 * (size_t)n);
@@ -1097,6 +1352,7 @@ int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const flo
   CU_TRY(ctx->lk_status_dev.reserve(N));
   for (int i = 0; i < n; i++)
     ctx->lk_items.h[i] = LkItem{pts0[2 * i], pts0[2 * i + 1], pts1_init[2 * i], pts1_init[2 * i + 1], p0, p1};
+  CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)n));
   CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, n, dev->pyr_dev.d, nullptr, rig->prm.lk_max_iters, rig->prm.lk_eps, ctx->lk_out.d,
                    ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   if (mask) {
@@ -1114,6 +1370,7 @@ int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const flo
     j.thr = 2.0 / std::max(c0->max_focal, c1->max_focal);
     j.run = n >= 10;
     ctx->rs_jobs.h[0] = j;
+    CU_TRY(ctx->rs_jobs.upload(ctx->stream, 1));
     CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, dev->cam_dev.d,
                          ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
   }
@@ -1162,6 +1419,8 @@ int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const fl
   j.thr = 2.0 / std::max(c0->max_focal, c1->max_focal);
   j.run = n >= 10;
   ctx->rs_jobs.h[0] = j;
+  CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)n));
+  CU_TRY(ctx->rs_jobs.upload(ctx->stream, 1));
   CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, 1, n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, dev->cam_dev.d,
                        ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
   if (ctx->sync() != OK) return E_CUDA;
@@ -1208,6 +1467,14 @@ void context_stats(Context *ctx, unsigned long long out[8]) {
 
 // CUDA-event stopwatch. The events are recorded on lane 0's stream; every feed is host-synchronous on all lanes, so the
 // interval between the two records spans exactly the device work (and host gaps) of the feeds issued in between.
+void context_host_profile(Context *ctx, int reset, double us[8]) {
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  for (int k = 0; k < 8; k++) {
+    if (us) us[k] = ctx->seg_us[k];
+    if (reset) ctx->seg_us[k] = 0;
+  }
+}
+
 int context_timer(Context *ctx, int stop, float *ms) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;

@@ -62,13 +62,12 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   std::vector<size_t> ids_last;
   std::vector<uint8_t> mask[2]; // host copies of the masks, indexed like pyr[]
   bool mask_nonzero[2] = {false, false};
-  std::vector<uint8_t> paint;   // scratch for mask_updated = mask | painted boxes (always restored to zero)
 };
 
 enum Status { OK = 0, E_BADMSG = 1, E_CAMID = 2, E_CUDA = 3, E_ARG = 4, E_SIZE = 5 };
 
 class Context;
-struct FeedWork;                // per-feed scratch (engine.cpp)
+struct Unit;                    // per-feed scratch of one stereo pair / mono camera (engine.cpp)
 
 class Rig {                     // one tracker = one TrackKLT instance
  public:
@@ -85,6 +84,8 @@ class Rig {                     // one tracker = one TrackKLT instance
   int cuda_error = 0;
   std::mutex mtx;                                   // serialises feed / getters on this handle
   CamState *find_cam(size_t id);
+  std::vector<Unit *> unit_pool;                    // scratch reused from feed to feed (keeps its vectors' capacity)
+  Unit *unit_at(size_t i);
 };
 
 struct FeedRequest {            // one feed_new_camera call (utils/sensor_data.h:55-80 CameraData)
@@ -104,6 +105,7 @@ Context *context_for_device(int device, int *err);
 int context_cuda_error(Context *ctx);
 void context_stats(Context *ctx, unsigned long long out[8]);
 int context_timer(Context *ctx, int stop, float *ms);
+void context_host_profile(Context *ctx, int reset, double us[8]);
 int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long long launches[K_COUNT]);
 
 // stage entry points (see engine.cpp); slot 0 = frame fed last, 1 = the one before

@@ -6,6 +6,8 @@
 //
 // All three are HBM-bound byte passes; bodies are written per thread block (GroupBlock on the device).
 #pragma once
+#include <string.h>
+
 #include "simt.h"
 
 namespace uvio {
@@ -19,19 +21,45 @@ inline unsigned gmem_add(unsigned *p, unsigned v) { unsigned o = *p; *p += v; re
 #endif
 
 // ---- histogram of rows [row0,row1) of one image into a block-private histogram ---------------------------------------
+// sh holds `nsub` (a power of two) histograms of 256 bins; warp k of the group counts into copy k % nsub, which keeps the
+// shared-memory atomics of different warps apart.  Rows are read as 16-byte vectors when the layout allows it.
+struct Vec16 { uint32_t x, y, z, w; };
+
+UVIO_HD void hist_word(unsigned *sh, uint32_t v) {
+  smem_inc(&sh[v & 255]);
+  smem_inc(&sh[(v >> 8) & 255]);
+  smem_inc(&sh[(v >> 16) & 255]);
+  smem_inc(&sh[v >> 24]);
+}
+
+#ifdef __CUDA_ARCH__
+__device__ __forceinline__ Vec16 load_vec16(const uint8_t *p) {
+  uint4 v = *(const uint4 *)p;
+  return Vec16{v.x, v.y, v.z, v.w};
+}
+__device__ __forceinline__ void store_vec16(uint8_t *p, const Vec16 &v) { *(uint4 *)p = make_uint4(v.x, v.y, v.z, v.w); }
+#else
+inline Vec16 load_vec16(const uint8_t *p) { Vec16 v; memcpy(&v, p, 16); return v; }
+inline void store_vec16(uint8_t *p, const Vec16 &v) { memcpy(p, &v, 16); }
+#endif
+
 template <class G>
-UVIO_HD void hist_rows(G g, unsigned *sh /*256, zeroed*/, const ImgView &I, int row0, int row1) {
-  const int w4 = I.w >> 2;   // pitch is a multiple of 16, base 16-byte aligned: rows can be read as 32-bit words
-  for (int y = row0; y < row1; y++) {
-    const uint32_t *r = (const uint32_t *)(I.p + (size_t)y * I.pitch);
-    for (int x = g.lane(); x < w4; x += g.size()) {
-      uint32_t v = r[x];
-      smem_inc(&sh[v & 255]);
-      smem_inc(&sh[(v >> 8) & 255]);
-      smem_inc(&sh[(v >> 16) & 255]);
-      smem_inc(&sh[v >> 24]);
-    }
-    for (int x = (w4 << 2) + g.lane(); x < I.w; x += g.size()) smem_inc(&sh[I.p[(size_t)y * I.pitch + x]]);
+UVIO_HD void hist_rows(G g, unsigned *sh /*nsub*256, zeroed*/, const ImgView &I, int row0, int row1, int nsub = 1) {
+  unsigned *mine = sh + ((g.lane() >> 5) & (nsub - 1)) * 256;
+  const bool vec = ((I.pitch & 15) == 0) && ((((size_t)I.p) & 15) == 0);
+  const int w16 = vec ? (I.w >> 4) : 0, rows = row1 - row0;
+  for (int i = g.lane(); i < rows * w16; i += g.size()) {
+    int y = i / w16, x = i - y * w16;
+    Vec16 v = load_vec16(I.p + (size_t)(row0 + y) * I.pitch + 16 * x);
+    hist_word(mine, v.x);
+    hist_word(mine, v.y);
+    hist_word(mine, v.z);
+    hist_word(mine, v.w);
+  }
+  const int x0 = w16 << 4, rem = I.w - x0;   // columns the vectors did not cover
+  for (int i = g.lane(); i < rows * rem; i += g.size()) {
+    int y = i / rem, x = i - y * rem;
+    smem_inc(&mine[I.p[(size_t)(row0 + y) * I.pitch + x0 + x]]);
   }
 }
 
@@ -53,18 +81,28 @@ UVIO_HD void equalize_lut(const unsigned *hist, int total, uint8_t *lut) {
 }
 
 // ---- apply a 256-entry LUT to rows [row0,row1) ------------------------------------------------------------------------
+UVIO_HD uint32_t lut_word(const uint8_t *lut, uint32_t v) {
+  return (uint32_t)lut[v & 255] | ((uint32_t)lut[(v >> 8) & 255] << 8) | ((uint32_t)lut[(v >> 16) & 255] << 16) |
+         ((uint32_t)lut[v >> 24] << 24);
+}
+
 template <class G>
 UVIO_HD void lut_rows(G g, const uint8_t *lut /*shared*/, const ImgView &I, uint8_t *dst, int dpitch, int row0, int row1) {
-  const int w4 = I.w >> 2;
-  for (int y = row0; y < row1; y++) {
-    const uint32_t *r = (const uint32_t *)(I.p + (size_t)y * I.pitch);
-    uint32_t *d = (uint32_t *)(dst + (size_t)y * dpitch);
-    for (int x = g.lane(); x < w4; x += g.size()) {
-      uint32_t v = r[x];
-      d[x] = (uint32_t)lut[v & 255] | ((uint32_t)lut[(v >> 8) & 255] << 8) | ((uint32_t)lut[(v >> 16) & 255] << 16) |
-             ((uint32_t)lut[v >> 24] << 24);
-    }
-    for (int x = (w4 << 2) + g.lane(); x < I.w; x += g.size()) dst[(size_t)y * dpitch + x] = lut[I.p[(size_t)y * I.pitch + x]];
+  const bool vec = ((I.pitch & 15) == 0) && ((((size_t)I.p) & 15) == 0) && ((dpitch & 15) == 0) && ((((size_t)dst) & 15) == 0);
+  const int w16 = vec ? (I.w >> 4) : 0, rows = row1 - row0;
+  for (int i = g.lane(); i < rows * w16; i += g.size()) {
+    int y = i / w16, x = i - y * w16;
+    Vec16 v = load_vec16(I.p + (size_t)(row0 + y) * I.pitch + 16 * x);
+    v.x = lut_word(lut, v.x);
+    v.y = lut_word(lut, v.y);
+    v.z = lut_word(lut, v.z);
+    v.w = lut_word(lut, v.w);
+    store_vec16(dst + (size_t)(row0 + y) * dpitch + 16 * x, v);
+  }
+  const int x0 = w16 << 4, rem = I.w - x0;
+  for (int i = g.lane(); i < rows * rem; i += g.size()) {
+    int y = i / rem, x = i - y * rem;
+    dst[(size_t)(row0 + y) * dpitch + x0 + x] = lut[I.p[(size_t)(row0 + y) * I.pitch + x0 + x]];
   }
 }
 
@@ -152,40 +190,81 @@ UVIO_HD uint8_t clahe_pixel(const uint8_t *luts, const ClaheGeom &q, int x, int 
   return sat_u8(round_f2i(res));
 }
 
-// ---- pyrDown: one block computes a PD_TW x PD_TH tile of the output level --------------------------------------------
-constexpr int PD_TW = 64, PD_TH = 8;
-constexpr int PD_SW = 2 * PD_TW + 3, PD_SH = 2 * PD_TH + 3;   // staged source footprint 131 x 19
-constexpr int PD_SP = PD_SW + 1;                              // staging pitch
+// ---- pyrDown: one lane computes a PD_COLS x PD_ROWS strip of the output level ----------------------------------------
+constexpr int PD_COLS = 4;    // output columns per lane (one 32-bit store)
+constexpr int PD_ROWS = 4;    // output rows per lane: 2*PD_ROWS+3 source rows, all fetched before the arithmetic starts
 
-struct PyrSmem {
-  uint8_t src[PD_SH * PD_SP];
-  unsigned short hsum[PD_SH * PD_TW];   // horizontal [1 4 6 4 1] sums (<= 4080)
-};
+// one aligned source word, REFLECT_101 at the frame border
+UVIO_HD uint32_t pyr_src_word(const uint8_t *row, int X0, int w, bool aligned) {
+  if (aligned && X0 >= 0 && X0 + 3 < w) return *(const uint32_t *)(row + X0);
+  return (uint32_t)row[reflect101(X0, w)] | ((uint32_t)row[reflect101(X0 + 1, w)] << 8) |
+         ((uint32_t)row[reflect101(X0 + 2, w)] << 16) | ((uint32_t)row[reflect101(X0 + 3, w)] << 24);
+}
 
-template <class G>
-UVIO_HD void pyrdown_tile(G g, PyrSmem &s, const ImgView &I, uint8_t *dst, int dw, int dh, int dpitch, int ox0, int oy0) {
-  int sx0 = 2 * ox0 - 2, sy0 = 2 * oy0 - 2;
-  for (int i = g.lane(); i < PD_SH * PD_SW; i += g.size()) {
-    int yy = i / PD_SW, xx = i - yy * PD_SW;
-    int X = reflect101(sx0 + xx, I.w), Y = reflect101(sy0 + yy, I.h);
-    s.src[yy * PD_SP + xx] = I.p[(size_t)Y * I.pitch + X];
-  }
-  g.sync();
-  for (int i = g.lane(); i < PD_SH * PD_TW; i += g.size()) {
-    int yy = i / PD_TW, ox = i - yy * PD_TW;
-    const uint8_t *r = s.src + yy * PD_SP + 2 * ox;
-    s.hsum[i] = (unsigned short)(r[0] + 4 * r[1] + 6 * r[2] + 4 * r[3] + r[4]);
-  }
-  g.sync();
-  for (int i = g.lane(); i < PD_TH * PD_TW; i += g.size()) {
-    int oy = i / PD_TW, ox = i - oy * PD_TW;
-    if (ox0 + ox < dw && oy0 + oy < dh) {
-      const unsigned short *c = s.hsum + (2 * oy) * PD_TW + ox;
-      int v = c[0] + 4 * c[PD_TW] + 6 * c[2 * PD_TW] + 4 * c[3 * PD_TW] + c[4 * PD_TW];
-      dst[(size_t)(oy0 + oy) * dpitch + ox0 + ox] = (uint8_t)((v + 128) >> 8);
+// horizontal [1 4 6 4 1] sums for output columns ox0..ox0+3 from the four words around them, packed as 16-bit pairs
+// (each <= 4080).  b(k) = source pixel 2*ox0 + k, k = -2 .. 8.
+UVIO_HD void pyr_hsum(uint32_t wm, uint32_t w0, uint32_t w1, uint32_t wp, uint32_t &h01, uint32_t &h23) {
+  uint32_t bm2 = (wm >> 16) & 255, bm1 = wm >> 24;
+  uint32_t b0 = w0 & 255, b1 = (w0 >> 8) & 255, b2 = (w0 >> 16) & 255, b3 = w0 >> 24;
+  uint32_t b4 = w1 & 255, b5 = (w1 >> 8) & 255, b6 = (w1 >> 16) & 255, b7 = w1 >> 24;
+  uint32_t b8 = wp & 255;
+  uint32_t h0 = bm2 + b2 + 4 * (bm1 + b1) + 6 * b0;
+  uint32_t h1 = b0 + b4 + 4 * (b1 + b3) + 6 * b2;
+  uint32_t h2 = b2 + b6 + 4 * (b3 + b5) + 6 * b4;
+  uint32_t h3 = b4 + b8 + 4 * (b5 + b7) + 6 * b6;
+  h01 = h0 | (h1 << 16);
+  h23 = h2 | (h3 << 16);
+}
+
+// vertical [1 4 6 4 1] on packed pairs: each 16-bit lane <= 16*4080 = 65280, no carry between the lanes
+UVIO_HD uint32_t pyr_vsum(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t a4) {
+  return a0 + a4 + 4 * (a1 + a3) + 6 * a2;
+}
+
+// One lane's share of cv::pyrDown (App. A.3): output columns ox0..ox0+3 (ox0 a multiple of 4), rows oy0..oy0+PD_ROWS-1.
+// Every source byte is fetched as part of an aligned word; there is no shared-memory staging and no barrier.  INTERIOR:
+// the lane's source columns 2*ox0 .. 2*ox0+11 lie inside the frame and rows are word-aligned, so the loads carry no
+// branches and the compiler can issue all of them up front (the two reflected pixels left of column 0 are taken from
+// the first word in registers).  Only the lanes at the right border of the frame take the general path.
+template <bool INTERIOR>
+UVIO_HD void pyrdown_strip_t(const ImgView &I, uint8_t *UVIO_RESTRICT dst, int dw, int dh, int dpitch, int ox0, int oy0) {
+  constexpr int NR = 2 * PD_ROWS + 3;
+  const int sx = 2 * ox0, sy = 2 * oy0 - 2;
+  uint32_t a[NR], c[NR];   // columns (0,1) in a, (2,3) in c
+#pragma unroll
+  for (int r = 0; r < NR; r++) {
+    const uint8_t *UVIO_RESTRICT row = I.p + (size_t)(INTERIOR ? reflect101_once(sy + r, I.h) : reflect101(sy + r, I.h)) * I.pitch;
+    uint32_t wm, w0, w1, wp;
+    if (INTERIOR) {
+      const uint32_t *q = (const uint32_t *)(row + sx);
+      w0 = q[0]; w1 = q[1]; wp = q[2];
+      wm = sx ? q[-1] : ((w0 & 0x00ff0000u) | ((w0 & 0x0000ff00u) << 16));   // pixels -2,-1 mirror pixels 2,1
+    } else {
+      const bool al = ((I.pitch & 3) == 0) && ((((size_t)I.p) & 3) == 0);
+      wm = pyr_src_word(row, sx - 4, I.w, al); w0 = pyr_src_word(row, sx, I.w, al);
+      w1 = pyr_src_word(row, sx + 4, I.w, al); wp = pyr_src_word(row, sx + 8, I.w, al);
     }
+    pyr_hsum(wm, w0, w1, wp, a[r], c[r]);
   }
-  g.sync();
+  const bool dst_word = ((dpitch & 3) == 0) && ((((size_t)dst) & 3) == 0) && ox0 + 3 < dw;
+#pragma unroll
+  for (int o = 0; o < PD_ROWS; o++) {
+    if (oy0 + o >= dh) break;
+    uint32_t v01 = pyr_vsum(a[2 * o], a[2 * o + 1], a[2 * o + 2], a[2 * o + 3], a[2 * o + 4]) + 0x00800080u;   // +128 per lane
+    uint32_t v23 = pyr_vsum(c[2 * o], c[2 * o + 1], c[2 * o + 2], c[2 * o + 3], c[2 * o + 4]) + 0x00800080u;
+    uint32_t out = ((v01 >> 8) & 255) | ((v01 >> 24) << 8) | (((v23 >> 8) & 255) << 16) | ((v23 >> 24) << 24);
+    uint8_t *d = dst + (size_t)(oy0 + o) * dpitch + ox0;
+    if (dst_word) *(uint32_t *)d = out;
+    else
+      for (int k = 0; k < 4 && ox0 + k < dw; k++) d[k] = (uint8_t)(out >> (8 * k));
+  }
+}
+
+UVIO_HD void pyrdown_strip(const ImgView &I, uint8_t *dst, int dw, int dh, int dpitch, int ox0, int oy0) {
+  if (ox0 >= dw || oy0 >= dh) return;
+  const bool aligned = ((I.pitch & 3) == 0) && ((((size_t)I.p) & 3) == 0);
+  if (aligned && 2 * ox0 + 12 <= I.w && I.h >= 4) pyrdown_strip_t<true>(I, dst, dw, dh, dpitch, ox0, oy0);
+  else pyrdown_strip_t<false>(I, dst, dw, dh, dpitch, ox0, oy0);
 }
 
 // Last pyramid level cv::buildOpticalFlowPyramid creates: it stops before a level that is <= the LK window.

@@ -4,6 +4,7 @@
 #include "kernels.h"
 
 #include <math.h>
+#include <string.h>
 
 #include "fast_body.h"
 #include "image_body.h"
@@ -20,18 +21,23 @@ __global__ void __launch_bounds__(256) k_hist(const PreJob *jobs, const ImgView 
                                               uint8_t *lut_out) {
   const PreJob job = jobs[blockIdx.y];
   if (job.method != 1) return;
-  __shared__ unsigned sh[256];
+  constexpr int NSUB = 8;   // one private histogram per warp
+  __shared__ unsigned sh[NSUB * 256];
   __shared__ unsigned cdf[256];
   __shared__ int s_first, s_last;
   const ImgView I = raw_tab[job.raw];
   GroupBlock g;
-  sh[threadIdx.x] = 0;
+#pragma unroll
+  for (int k = 0; k < NSUB; k++) sh[k * 256 + threadIdx.x] = 0;
   __syncthreads();
   int r0 = (int)((long long)I.h * blockIdx.x / gridDim.x), r1 = (int)((long long)I.h * (blockIdx.x + 1) / gridDim.x);
-  hist_rows(g, sh, I, r0, r1);
+  hist_rows(g, sh, I, r0, r1, NSUB);
   __syncthreads();
   unsigned *gh = hist + (size_t)blockIdx.y * 256;
-  if (sh[threadIdx.x]) atomicAdd(&gh[threadIdx.x], sh[threadIdx.x]);
+  unsigned mine = 0;
+#pragma unroll
+  for (int k = 0; k < NSUB; k++) mine += sh[k * 256 + threadIdx.x];
+  if (mine) atomicAdd(&gh[threadIdx.x], mine);
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) s_last = (atomicAdd(&ticket[blockIdx.y], 1u) == gridDim.x - 1);
@@ -109,14 +115,14 @@ __global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const I
 // ---------------------------------------------------------------------------------------------------------------------
 // pyramid: level l-1 -> level l for every image of the launch
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_pyrdown(const PreJob *jobs, const PyrDesc *pyr_tab, int level) {
+constexpr int PD_BLOCK_Y = 4;   // strips per block: a block covers 128 x 32 output pixels
+
+__global__ void __launch_bounds__(32 * PD_BLOCK_Y) k_pyrdown(const PreJob *jobs, const PyrDesc *pyr_tab, int level) {
   const PyrDesc &P = pyr_tab[jobs[blockIdx.z].pyr];
   if (level >= P.nlv) return;
   const ImgView S = P.lv[level - 1], D = P.lv[level];
-  int ox0 = blockIdx.x * PD_TW, oy0 = blockIdx.y * PD_TH;
-  if (ox0 >= D.w || oy0 >= D.h) return;
-  __shared__ PyrSmem s;
-  pyrdown_tile(GroupBlock(), s, S, (uint8_t *)D.p, D.w, D.h, D.pitch, ox0, oy0);
+  const int ox0 = (blockIdx.x * 32 + threadIdx.x) * PD_COLS, oy0 = (blockIdx.y * PD_BLOCK_Y + threadIdx.y) * PD_ROWS;
+  pyrdown_strip(S, (uint8_t *)D.p, D.w, D.h, D.pitch, ox0, oy0);
 }
 
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
@@ -138,7 +144,8 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
     w = (w + 1) / 2;
     h = (h + 1) / 2;
     prof_mark(st, K_PYRDOWN);
-    k_pyrdown<<<dim3((w + PD_TW - 1) / PD_TW, (h + PD_TH - 1) / PD_TH, njobs), 256, 0, st>>>(jobs, pyr_tab, l);
+    k_pyrdown<<<dim3((w + 32 * PD_COLS - 1) / (32 * PD_COLS), (h + PD_BLOCK_Y * PD_ROWS - 1) / (PD_BLOCK_Y * PD_ROWS), njobs),
+                dim3(32, PD_BLOCK_Y), 0, st>>>(jobs, pyr_tab, l);
   }
   prof_mark(st, -1);
   return cudaGetLastError();
@@ -242,7 +249,8 @@ cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st) {
 // pyramidal LK: one warp per feature, all levels inside the kernel
 // ---------------------------------------------------------------------------------------------------------------------
 // work counters for the roofline arithmetic: [0] templates staged (point-levels), [1] iterations, [2] points
-__device__ unsigned long long g_lk_work[3];
+constexpr int LK_WORK_SLOTS = 64;   // the counters are spread over slots so that the atomics of one launch do not queue up
+__device__ unsigned long long g_lk_work[LK_WORK_SLOTS][4];
 
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
                                                              const float *init_from_dev, int max_count, double eps_sq,
@@ -267,9 +275,10 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items
   int work[2] = {0, 0};
   lk_track_point(GroupWarp(), sm[wid], P0.lv, P1.lv, prm, px, py, nx, ny, status, work);
   if ((threadIdx.x & 31) == 0) {
-    atomicAdd(&g_lk_work[0], (unsigned long long)work[0]);
-    atomicAdd(&g_lk_work[1], (unsigned long long)work[1]);
-    atomicAdd(&g_lk_work[2], 1ull);
+    unsigned long long *wk = g_lk_work[blockIdx.x % LK_WORK_SLOTS];
+    atomicAdd(&wk[0], (unsigned long long)work[0]);
+    atomicAdd(&wk[1], (unsigned long long)work[1]);
+    atomicAdd(&wk[2], 1ull);
     LkOut o{nx, ny};
     out_host[i] = o;
     status_host[i] = status;
@@ -279,10 +288,14 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items
 }
 
 cudaError_t read_lk_work(unsigned long long out[3], int reset) {
-  cudaError_t e = cudaMemcpyFromSymbol(out, g_lk_work, sizeof(unsigned long long) * 3);
+  unsigned long long h[LK_WORK_SLOTS][4];
+  cudaError_t e = cudaMemcpyFromSymbol(h, g_lk_work, sizeof(h));
+  out[0] = out[1] = out[2] = 0;
+  for (int s = 0; s < LK_WORK_SLOTS; s++)
+    for (int k = 0; k < 3; k++) out[k] += h[s][k];
   if (e == cudaSuccess && reset) {
-    unsigned long long z[3] = {0, 0, 0};
-    e = cudaMemcpyToSymbol(g_lk_work, z, sizeof(z));
+    memset(h, 0, sizeof(h));
+    e = cudaMemcpyToSymbol(g_lk_work, h, sizeof(h));
   }
   return e;
 }

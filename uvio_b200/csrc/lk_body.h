@@ -20,16 +20,37 @@ namespace uvio {
 constexpr int LK_WIN = 15;                 // TrackKLT.h:144 (win_size 15x15, not configurable in the reference)
 constexpr int LK_NPIX = LK_WIN * LK_WIN;   // 225
 constexpr int LK_FP = 18;                  // template footprint rows/cols (16 + 1-px Scharr halo each side)
-constexpr int LK_FPP = 20;                 // footprint pitch
-constexpr int LK_JP = 16;                  // J footprint rows/cols
+constexpr int LK_FPW = 6;                  // 32-bit words staged per footprint row (24 bytes cover 18 + alignment slack)
+constexpr int LK_JW = 32;                  // rows/cols of the J window staged per level (search range +-8 px around the guess)
+constexpr int LK_JWW = 10;                 // words per staged J row (40 bytes cover 32 + alignment slack)
 
-struct LkSmem {
-  uint8_t foot[LK_FP * LK_FPP];            // I(ip-1 .. ip+16), REFLECT_101
-  uint8_t jfoot[LK_JP * LK_JP];            // J(in .. in+15), REFLECT_101
-  short dI[16 * 16 * 2];                   // Scharr (dx,dy) at ip .. ip+15, zero outside the frame
-  short Iw[LK_NPIX];                       // template, intensity * 32
-  short dIw[LK_NPIX * 2];                  // blended derivative patch
-  short diff[LK_NPIX];                     // J patch - I patch of the current iteration
+constexpr int LK_TAIL = 7 * LK_WIN;         // 105 window pixels in columns 8..14: the scalar tail of every row
+constexpr int LK_TAILP = 108;               // padded to whole 16-byte vectors
+
+struct Short2 { short x, y; };
+struct Float4 { float x, y, z, w; };
+
+// Shared memory of one feature.  Arrays of the ordered sums are laid out the way the chains walk them: columns 0..7 of
+// every row ("simd", 8 or 4 entries per row) and columns 8..14 ("tail", 7 per row, contiguous so that the one lane that
+// owns the scalar chain reads four values per load).
+struct alignas(16) LkSmem {
+  uint32_t footw[LK_FP * LK_FPW];          // I rows (ip-1 .. ip+16), REFLECT_101, as aligned words
+  union {
+    uint32_t jwin[LK_JW * LK_JWW];         // J window rows, REFLECT_101, as aligned words (after the template is built)
+    Short2 dI[16 * 16];                    // Scharr (dx,dy) at ip .. ip+15, zero outside the frame (while it is built)
+  };
+  Short2 dIw[LK_NPIX + 3];                 // blended derivative patch
+  short Iw[LK_NPIX + 7];                   // template, intensity * 32
+  union {
+    struct {
+      float gsimd[3][LK_WIN * 8];          // fp32(Ix*Ix), fp32(Ix*Iy), fp32(Iy*Iy), columns 0..7
+      float gtail[3][LK_TAILP];            // the same, columns 8..14
+    };
+    struct {
+      float psimd[2][LK_WIN * 4];          // per iteration: fp32(diff*Ix (col k) + diff*Ix (col k+4)), k = 0..3; same for Iy
+      float ptail[2][LK_TAILP];            // fp32(diff*Ix), fp32(diff*Iy), columns 8..14
+    };
+  };
   float red[16];                           // results of the ordered accumulation chains
 };
 
@@ -40,41 +61,102 @@ struct LkParams {
   double min_eig;     // 1e-4
 };
 
+#ifdef __CUDA_ARCH__
+__device__ __forceinline__ Float4 load_float4(const float *p) {
+  float4 v = *(const float4 *)p;
+  return Float4{v.x, v.y, v.z, v.w};
+}
+#else
+inline Float4 load_float4(const float *p) { return Float4{p[0], p[1], p[2], p[3]}; }
+#endif
+
+// Stage ROWS image rows starting at (x_aligned, y0) as WORDS aligned 32-bit words each.  A window that lies inside the
+// frame is fetched with plain aligned loads; otherwise words that touch the border are assembled bytewise (REFLECT_101).
+template <int ROWS, int WORDS, class G>
+UVIO_HD void lk_stage_rows(G g, uint32_t *dst, const ImgView &I, int x_aligned, int y0) {
+  const bool aligned = ((I.pitch & 3) == 0) && ((((size_t)I.p) & 3) == 0);
+  constexpr int N = ROWS * WORDS;
+  if (aligned && x_aligned >= 0 && x_aligned + 4 * WORDS <= I.w && y0 >= 0 && y0 + ROWS <= I.h) {
+    const uint8_t *base = I.p + (size_t)y0 * I.pitch + x_aligned;
+    for (int i = g.lane(); i < N; i += g.size()) {
+      int r = i / WORDS, k = i - r * WORDS;
+      dst[i] = *(const uint32_t *)(base + (size_t)r * I.pitch + 4 * k);
+    }
+    return;
+  }
+  for (int i = g.lane(); i < N; i += g.size()) {
+    int r = i / WORDS, k = i - r * WORDS;
+    int X0 = x_aligned + 4 * k;
+    const uint8_t *row = I.p + (size_t)reflect101(y0 + r, I.h) * I.pitch;
+    uint32_t v;
+    if (aligned && X0 >= 0 && X0 + 3 < I.w) {
+      v = *(const uint32_t *)(row + X0);
+    } else {
+      v = (uint32_t)row[reflect101(X0, I.w)] | ((uint32_t)row[reflect101(X0 + 1, I.w)] << 8) |
+          ((uint32_t)row[reflect101(X0 + 2, I.w)] << 16) | ((uint32_t)row[reflect101(X0 + 3, I.w)] << 24);
+    }
+    dst[i] = v;
+  }
+}
+
 template <class G>
 UVIO_HD void lk_stage_template(G g, LkSmem &s, const ImgView &I, int ipx, int ipy, int iw00, int iw01, int iw10, int iw11) {
-  for (int i = g.lane(); i < LK_FP * LK_FP; i += g.size()) {
-    int yy = i / LK_FP, xx = i - yy * LK_FP;
-    int X = reflect101(ipx - 1 + xx, I.w), Y = reflect101(ipy - 1 + yy, I.h);
-    s.foot[yy * LK_FPP + xx] = I.p[(size_t)Y * I.pitch + X];
-  }
+  const int xa = (ipx - 1) & ~3;
+  lk_stage_rows<LK_FP, LK_FPW>(g, s.footw, I, xa, ipy - 1);
   g.sync();
+  const uint8_t *foot = (const uint8_t *)s.footw + ((ipx - 1) - xa);   // foot[yy*24 + xx] = I(ip-1+xx, ip-1+yy)
+  constexpr int FPP = LK_FPW * 4;
+  const bool inside = ipx >= 0 && ipx + 16 <= I.w && ipy >= 0 && ipy + 16 <= I.h;   // no derivative sample falls outside
   for (int i = g.lane(); i < 256; i += g.size()) {
     int y = i >> 4, x = i & 15;
-    int X = ipx + x, Y = ipy + y;
     int dx = 0, dy = 0;
-    if (X >= 0 && X < I.w && Y >= 0 && Y < I.h) {
-      const uint8_t *c = s.foot + (y + 1) * LK_FPP + (x + 1);
-      int tl = c[-LK_FPP - 1], tc = c[-LK_FPP], tr = c[-LK_FPP + 1], ml = c[-1], mr = c[1];
-      int bl = c[LK_FPP - 1], bc = c[LK_FPP], br = c[LK_FPP + 1];
+    if (inside || (ipx + x >= 0 && ipx + x < I.w && ipy + y >= 0 && ipy + y < I.h)) {
+      const uint8_t *c = foot + (y + 1) * FPP + (x + 1);
+      int tl = c[-FPP - 1], tc = c[-FPP], tr = c[-FPP + 1], ml = c[-1], mr = c[1];
+      int bl = c[FPP - 1], bc = c[FPP], br = c[FPP + 1];
       dx = 3 * (tr - tl) + 10 * (mr - ml) + 3 * (br - bl);
       dy = 3 * (bl - tl) + 10 * (bc - tc) + 3 * (br - tr);
     }
-    s.dI[2 * i] = (short)dx;
-    s.dI[2 * i + 1] = (short)dy;
+    s.dI[i] = Short2{(short)dx, (short)dy};
   }
   g.sync();
   for (int i = g.lane(); i < LK_NPIX; i += g.size()) {
     int y = i / LK_WIN, x = i - y * LK_WIN;
-    const uint8_t *c = s.foot + (y + 1) * LK_FPP + (x + 1);
-    int ival = (c[0] * iw00 + c[1] * iw01 + c[LK_FPP] * iw10 + c[LK_FPP + 1] * iw11 + (1 << 8)) >> 9;
-    const short *d = s.dI + 2 * (y * 16 + x);
-    int ix = (d[0] * iw00 + d[2] * iw01 + d[32] * iw10 + d[34] * iw11 + (1 << 13)) >> 14;
-    int iy = (d[1] * iw00 + d[3] * iw01 + d[33] * iw10 + d[35] * iw11 + (1 << 13)) >> 14;
+    const uint8_t *c = foot + (y + 1) * FPP + (x + 1);
+    int ival = (c[0] * iw00 + c[1] * iw01 + c[FPP] * iw10 + c[FPP + 1] * iw11 + (1 << 8)) >> 9;
+    const Short2 *d = s.dI + (y * 16 + x);
+    Short2 d00 = d[0], d01 = d[1], d10 = d[16], d11 = d[17];
+    int ix = (d00.x * iw00 + d01.x * iw01 + d10.x * iw10 + d11.x * iw11 + (1 << 13)) >> 14;
+    int iy = (d00.y * iw00 + d01.y * iw01 + d10.y * iw10 + d11.y * iw11 + (1 << 13)) >> 14;
     s.Iw[i] = (short)ival;
-    s.dIw[2 * i] = (short)ix;
-    s.dIw[2 * i + 1] = (short)iy;
+    s.dIw[i] = Short2{(short)ix, (short)iy};
+    // |ix|,|iy| < 2^15: the int products are exact and (float) rounds them once, as the CPU's float multiply does
+    float xx = (float)(ix * ix), xy = (float)(ix * iy), yy = (float)(iy * iy);
+    if (x < 8) {
+      s.gsimd[0][y * 8 + x] = xx;
+      s.gsimd[1][y * 8 + x] = xy;
+      s.gsimd[2][y * 8 + x] = yy;
+    } else {
+      s.gtail[0][y * 7 + x - 8] = xx;
+      s.gtail[1][y * 7 + x - 8] = xy;
+      s.gtail[2][y * 7 + x - 8] = yy;
+    }
   }
   g.sync();
+}
+
+// the scalar tail of an ordered sum: 105 values added one after the other, fetched four at a time
+UVIO_HD float lk_tail_chain(const float *v) {
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < LK_TAIL / 4; j++) {
+    Float4 f = load_float4(v + 4 * j);
+    q = fadd(q, f.x);
+    q = fadd(q, f.y);
+    q = fadd(q, f.z);
+    q = fadd(q, f.w);
+  }
+  return fadd(q, v[LK_TAIL - 1]);
 }
 
 // 15 ordered chains -> red[0..14]; chain = acc*5 + k, acc in {A11, A12, A22}, k = 0..3 SIMD lane, 4 = scalar tail.
@@ -82,19 +164,16 @@ template <class G>
 UVIO_HD void lk_accumulate_gram(G g, LkSmem &s) {
   for (int c = g.lane(); c < 15; c += g.size()) {
     int acc = c / 5, k = c - acc * 5;
-    int oa = acc == 2 ? 1 : 0, ob = acc == 0 ? 0 : 1;     // A11: ix*ix, A12: ix*iy, A22: iy*iy
     float q = 0.f;
     if (k < 4) {
+      const float *v = s.gsimd[acc] + k;
+#pragma unroll
       for (int y = 0; y < LK_WIN; y++) {
-        const short *r = s.dIw + 2 * (y * LK_WIN);
-        q = fadd(fmul((float)r[2 * k + oa], (float)r[2 * k + ob]), q);
-        q = fadd(fmul((float)r[2 * (k + 4) + oa], (float)r[2 * (k + 4) + ob]), q);
+        q = fadd(v[y * 8], q);
+        q = fadd(v[y * 8 + 4], q);
       }
     } else {
-      for (int y = 0; y < LK_WIN; y++) {
-        const short *r = s.dIw + 2 * (y * LK_WIN);
-        for (int x = 8; x < LK_WIN; x++) q = fadd(q, (float)((int)r[2 * x + oa] * (int)r[2 * x + ob]));
-      }
+      q = lk_tail_chain(s.gtail[acc]);
     }
     s.red[c] = q;
   }
@@ -108,18 +187,11 @@ UVIO_HD void lk_accumulate_mismatch(G g, LkSmem &s) {
     int acc = c / 5, k = c - acc * 5;
     float q = 0.f;
     if (k < 4) {
-      for (int y = 0; y < LK_WIN; y++) {
-        const short *d = s.diff + y * LK_WIN;
-        const short *r = s.dIw + 2 * (y * LK_WIN) + acc;
-        int pair = (int)d[k] * (int)r[2 * k] + (int)d[k + 4] * (int)r[2 * (k + 4)];
-        q = fadd(q, (float)pair);
-      }
+      const float *v = s.psimd[acc] + k;
+#pragma unroll
+      for (int y = 0; y < LK_WIN; y++) q = fadd(q, v[y * 4]);
     } else {
-      for (int y = 0; y < LK_WIN; y++) {
-        const short *d = s.diff + y * LK_WIN;
-        const short *r = s.dIw + 2 * (y * LK_WIN) + acc;
-        for (int x = 8; x < LK_WIN; x++) q = fadd(q, (float)((int)d[x] * (int)r[2 * x]));
-      }
+      q = lk_tail_chain(s.ptail[acc]);
     }
     s.red[c] = q;
   }
@@ -130,19 +202,38 @@ UVIO_HD float lk_fold(const float *r) {   // scalar tail += (l0+l2)+(l1+l3)
   return fadd(r[4], fadd(fadd(r[0], r[2]), fadd(r[1], r[3])));
 }
 
+// J window of the level: rows jy0 .. jy0+31, columns from the aligned x <= jx0
 template <class G>
-UVIO_HD void lk_stage_diff(G g, LkSmem &s, const ImgView &J, int inx, int iny, int iw00, int iw01, int iw10, int iw11) {
-  for (int i = g.lane(); i < LK_JP * LK_JP; i += g.size()) {
-    int yy = i >> 4, xx = i & 15;
-    int X = reflect101(inx + xx, J.w), Y = reflect101(iny + yy, J.h);
-    s.jfoot[i] = J.p[(size_t)Y * J.pitch + X];
-  }
+UVIO_HD void lk_stage_window(G g, LkSmem &s, const ImgView &J, int jx0, int jy0) {
+  lk_stage_rows<LK_JW, LK_JWW>(g, s.jwin, J, jx0 & ~3, jy0);
   g.sync();
-  for (int i = g.lane(); i < LK_NPIX; i += g.size()) {
-    int y = i / LK_WIN, x = i - y * LK_WIN;
-    const uint8_t *c = s.jfoot + y * LK_JP + x;
-    int jv = (c[0] * iw00 + c[1] * iw01 + c[LK_JP] * iw10 + c[LK_JP + 1] * iw11 + (1 << 8)) >> 9;
-    s.diff[i] = (short)(jv - s.Iw[i]);
+}
+
+UVIO_HD int lk_bilinear(const uint8_t *c, int pitch, int iw00, int iw01, int iw10, int iw11) {
+  return (c[0] * iw00 + c[1] * iw01 + c[pitch] * iw10 + c[pitch + 1] * iw11 + (1 << 8)) >> 9;
+}
+
+// diff = J patch - I patch at integer offset (ox, oy) of the staged window, and the mismatch products.  One lane handles
+// either the two pixels (y,k), (y,k+4) that meet in SIMD lane k of the CPU code, or one pixel of the scalar tail.
+template <class G>
+UVIO_HD void lk_diff_from_window(G g, LkSmem &s, int jx0, int ox, int oy, int iw00, int iw01, int iw10, int iw11) {
+  constexpr int JP = LK_JWW * 4;
+  const uint8_t *win = (const uint8_t *)s.jwin + (jx0 - (jx0 & ~3)) + oy * JP + ox;
+  for (int i = g.lane(); i < LK_WIN * 4; i += g.size()) {
+    int y = i >> 2, k = i & 3, e = y * LK_WIN + k;
+    const uint8_t *c = win + y * JP + k;
+    int d0 = lk_bilinear(c, JP, iw00, iw01, iw10, iw11) - s.Iw[e];
+    int d1 = lk_bilinear(c + 4, JP, iw00, iw01, iw10, iw11) - s.Iw[e + 4];
+    Short2 g0 = s.dIw[e], g1 = s.dIw[e + 4];
+    s.psimd[0][i] = (float)(d0 * g0.x + d1 * g1.x);
+    s.psimd[1][i] = (float)(d0 * g0.y + d1 * g1.y);
+  }
+  for (int t = g.lane(); t < LK_TAIL; t += g.size()) {
+    int y = t / 7, x = 8 + t - 7 * y, e = y * LK_WIN + x;
+    int d = lk_bilinear(win + y * JP + x, JP, iw00, iw01, iw10, iw11) - s.Iw[e];
+    Short2 gd = s.dIw[e];
+    s.ptail[0][t] = (float)(d * gd.x);
+    s.ptail[1][t] = (float)(d * gd.y);
   }
   g.sync();
 }
@@ -205,6 +296,8 @@ UVIO_HD void lk_track_point(G g, LkSmem &s, const ImgView *prev, const ImgView *
     npx = fsub(npx, half);
     npy = fsub(npy, half);
     float pdx = 0.f, pdy = 0.f;
+    int jx0 = 0, jy0 = 0;
+    bool have_window = false;
     for (int j = 0; j < P.max_count; j++) {
       int inx = floor_f2i(npx), iny = floor_f2i(npy);
       if (inx < -LK_WIN || inx >= J.w || iny < -LK_WIN || iny >= J.h) {
@@ -212,8 +305,14 @@ UVIO_HD void lk_track_point(G g, LkSmem &s, const ImgView *prev, const ImgView *
         break;
       }
       lk_weights(fsub(npx, (float)inx), fsub(npy, (float)iny), iw00, iw01, iw10, iw11);
-      lk_stage_diff(g, s, J, inx, iny, iw00, iw01, iw10, iw11);
-      if (work) work[1]++;   // iterations (J footprints staged)
+      if (!have_window || inx < jx0 || inx > jx0 + (LK_JW - 16) || iny < jy0 || iny > jy0 + (LK_JW - 16)) {
+        jx0 = inx - (LK_JW - 16) / 2;   // (re)centre the staged window on the current estimate
+        jy0 = iny - (LK_JW - 16) / 2;
+        lk_stage_window(g, s, J, jx0, jy0);
+        have_window = true;
+      }
+      lk_diff_from_window(g, s, jx0, inx - jx0, iny - jy0, iw00, iw01, iw10, iw11);
+      if (work) work[1]++;   // iterations
       lk_accumulate_mismatch(g, s);
       float b1 = fmul(lk_fold(s.red + 0), FLT_SCALE);
       float b2 = fmul(lk_fold(s.red + 5), FLT_SCALE);

@@ -16,6 +16,8 @@
 #define UVIO_HD inline
 #endif
 
+#define UVIO_RESTRICT __restrict__
+
 namespace uvio {
 
 struct GroupSeq {
@@ -106,6 +108,13 @@ UVIO_HD int reflect101(int p, int len) {
   if (len == 1) return 0;
   while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
   return p;
+}
+
+// The same without branches, for -len < p < 2*len - 1 (a single reflection) and len >= 2.
+UVIO_HD int reflect101_once(int p, int len) {
+  p = p < 0 ? -p : p;
+  int q = 2 * (len - 1) - p;
+  return p < q ? p : q;
 }
 
 // A pitched 8-bit image view (one pyramid level).

@@ -92,6 +92,7 @@ def lib():
         L.uvio_klt_timer_start.argtypes = [ci]
         L.uvio_klt_timer_stop.argtypes = [ci, C.POINTER(C.c_float)]
         L.uvio_klt_profile.argtypes = [ci, ci, C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
+        L.uvio_klt_host_profile.argtypes = [ci, ci, C.POINTER(C.c_double)]
         L.uvio_klt_get_new_observations_batch.argtypes = [C.POINTER(vp), ci, vp, ci, C.POINTER(ci)]
         _lib = L
     return _lib
@@ -397,3 +398,15 @@ def profile(device: int = 0, enable: int = -1) -> dict:
     if rc != UVIO_OK:
         raise UvioError(rc, "uvio_klt_profile")
     return {k: (ms[i], int(ln[i])) for i, k in enumerate(KERNEL_NAMES)}
+
+
+HOST_SEGMENTS = ("issue_r1", "wait_r1", "host_r2", "wait_r2", "host_r3", "wait_r3", "host_merge", "lane_passes")
+
+
+def host_profile(device: int = 0, reset: bool = False) -> dict:
+    """Host wall-clock (us) the lanes of `device` spent in each segment of the feed, summed over lanes."""
+    us = (C.c_double * 8)()
+    rc = lib().uvio_klt_host_profile(device, 1 if reset else 0, us)
+    if rc != UVIO_OK:
+        raise UvioError(rc, "uvio_klt_host_profile")
+    return {k: us[i] for i, k in enumerate(HOST_SEGMENTS)}
