@@ -119,8 +119,10 @@ int uvio_klt_device_stats(int cuda_device, unsigned long long out[8]);
 /* CUDA-event stopwatch recorded on the stream all kernels of that device's trackers are launched on. */
 int uvio_klt_timer_start(int cuda_device);
 int uvio_klt_timer_stop(int cuda_device, float *ms);
-/* Per-kernel CUDA-event timing on that stream. enable: 1 = reset and start, 0 = stop, -1 = leave as is. ms / launches (16
- * entries each, may be NULL) receive the sums accumulated so far, indexed by UVIO_K_*. */
+/* Per-kernel CUDA-event timing on that stream. enable: 1 = reset and start (all kernels), 1 | (mask << 1) = reset and start
+ * for the kernels whose UVIO_K_* bit is set in mask only (two event records per timed launch, none for the others),
+ * 0 = stop, -1 = leave as is. ms / launches (16 entries each, may be NULL) receive the sums accumulated so far, indexed by
+ * UVIO_K_*. */
 #define UVIO_K_HIST 0
 #define UVIO_K_LUT_APPLY 1
 #define UVIO_K_CLAHE_TILES 2
@@ -130,6 +132,7 @@ int uvio_klt_timer_stop(int cuda_device, float *ms);
 #define UVIO_K_SUBPIX 6
 #define UVIO_K_LK 7
 #define UVIO_K_RANSAC 8
+#define UVIO_K_PREPROCESS 9 /* equalizeHist + pyramid, one cluster launch (ids 0, 1, 4 are the retired separate passes) */
 int uvio_klt_profile(int cuda_device, int enable, double ms[16], unsigned long long launches[16]);
 /* Host wall-clock of the feed, summed over the lanes of that device's context, in microseconds: [0] upload + round-1 launch
  * issue, [1] wait for round 1, [2] host selection + round-2 issue, [3] wait for round 2, [4] host detection + round-3 issue,

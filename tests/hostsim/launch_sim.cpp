@@ -8,8 +8,8 @@
 
 namespace uvio {
 
-cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab, unsigned *,
-                              unsigned *, uint8_t *, uint8_t *, int, int, int, int, int) {
+cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab, uint8_t *,
+                              int) {
   GroupSeq g;
   for (int j = 0; j < njobs; j++) {
     const ImgView I = raw_tab[jobs[j].raw];
@@ -42,7 +42,7 @@ cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const
   return 0;
 }
 
-cudaError_t launch_fast(cudaStream_t, const FastJob *jobs, int njobs, int, int, const PyrDesc *pyr_tab, int, const int *thresholds,
+cudaError_t launch_fast(cudaStream_t, const FastJob *jobs, int njobs, int, int, const PyrDesc *pyr_tab,
                         uint32_t *, unsigned *, unsigned *, uint32_t *out_host, unsigned *count_host) {
   GroupSeq g;
   FastSmem s;
@@ -50,7 +50,7 @@ cudaError_t launch_fast(cudaStream_t, const FastJob *jobs, int njobs, int, int, 
     const FastJob job = jobs[j];
     unsigned count = 0;
     for (int ty = 0; ty < job.h; ty += FT_H)
-      for (int tx = 0; tx < job.w; tx += FT_W) fast_tile(g, s, pyr_tab[job.img].lv[0], job, tx, ty, thresholds[j], out_host, &count);
+      for (int tx = 0; tx < job.w; tx += FT_W) fast_tile(g, s, pyr_tab[job.img].lv[0], job, tx, ty, job.threshold, out_host, &count);
     count_host[j] = count;
   }
   return 0;

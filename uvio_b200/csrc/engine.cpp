@@ -35,7 +35,9 @@ struct HostProfTable {
   std::atomic<long long> ns[32];
   std::atomic<long long> calls[32];
   int n = 0;
+  std::mutex m;
   int slot(const char *nm) {
+    std::lock_guard<std::mutex> lk(m);
     for (int i = 0; i < n; i++) if (name[i] == nm) return i;
     name[n] = nm;
     return n++;
@@ -171,6 +173,7 @@ struct Lane {
       prof.ready = true;
     }
     prof.n = 0;
+    prof.open = false;
     g_prof = &prof;
   }
   void prof_end() {
@@ -190,10 +193,8 @@ struct Lane {
   }
   // round 1
   JobVec<PreJob> pre_jobs;
-  DevVec<unsigned> hist, hist_ticket;
-  DevVec<uint8_t> lut, clahe_lut;
+  DevVec<uint8_t> clahe_lut;
   JobVec<FastJob> fast_jobs;
-  JobVec<int> fast_thr;
   DevVec<uint32_t> fast_out_dev;
   DevVec<unsigned> fast_cnt_dev, fast_ticket;
   MappedVec<uint32_t> fast_out;
@@ -404,8 +405,9 @@ Context::~Context() {
   for (void *p : allocs) cudaFree(p);
 }
 
-// Host threads per device context: UVIO_KLT_LANES, else the process's share of the cores (one process per GPU shares the
-// host with its siblings), at most 8.  Every thread drives UVIO_KLT_DEPTH lanes (default 2) alternately.
+// Host threads per device context: UVIO_KLT_LANES, else a quarter of the process's share of the logical cores (one
+// process per GPU shares the host with its siblings), at most 8.  Every thread drives UVIO_KLT_DEPTH lanes (default 2)
+// alternately.  Measured on a 16-thread host with one B200: 4 x 2 and 8 x 1 are level, more lanes only shrink the launches.
 static int default_threads() {
   if (const char *e = getenv("UVIO_KLT_LANES")) {
     int v = atoi(e);
@@ -414,7 +416,7 @@ static int default_threads() {
   int hw = (int)std::thread::hardware_concurrency();
   int local_world = 1;
   if (const char *e = getenv("LOCAL_WORLD_SIZE")) local_world = atoi(e) > 0 ? atoi(e) : 1;
-  int v = hw / local_world / 2;
+  int v = hw / local_world / 4;
   return v < 1 ? 1 : (v > 8 ? 8 : v);
 }
 static int default_depth() {
@@ -557,8 +559,8 @@ static void emit_fast_jobs(Lane *ctx, Side &s, int threshold, int &njobs, size_t
     j.x0 = x; j.y0 = y; j.w = s.geom.size_x; j.h = s.geom.size_y;
     j.out_off = (int)nwords;
     j.out_cap = ((j.w + 1) / 2) * ((j.h + 1) / 2);
+    j.threshold = threshold;
     ctx->fast_jobs.h[njobs] = j;
-    ctx->fast_thr.h[njobs] = threshold;
     s.job_of_cell[r] = njobs++;
     nwords += (size_t)j.out_cap;
   }
@@ -949,7 +951,7 @@ int Pass::stage0() {
   ctx->prof_begin();
   g_prof = ctx->prof_on ? &ctx->prof : nullptr;
   // ---- upload + pre-processing jobs + units -----------------------------------------------------------------------------
-  int nimg = 0, max_w = 0, max_h = 0, max_lv = 1, any_hist = 0, any_clahe = 0;
+  int nimg = 0, any_clahe = 0;
   for (int i = 0; i < n; i++) nimg += reqs[i]->n;
   CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
   npre = 0;
@@ -962,19 +964,18 @@ int Pass::stage0() {
       const HostImage &im = rq.images[k];
       c.cur ^= 1;
       const ImgView &raw = dev->raw_tab[c.raw];
+      {
+      HOSTPROF(s0_memcpy);
       // host (pageable or pinned) or device memory
       if ((size_t)raw.pitch == im.stride)
         CU_TRY(cudaMemcpyAsync((void *)raw.p, im.p, (size_t)raw.pitch * (im.h - 1) + im.w, cudaMemcpyDefault, ctx->stream));
       else
         CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
                                  ctx->stream));
+      }
       ctx->stats[2] += (unsigned long long)im.w * im.h;
       c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
       ctx->pre_jobs.h[npre++] = PreJob{c.raw, c.pyr[c.cur], P.histogram_method};
-      max_w = std::max(max_w, im.w);
-      max_h = std::max(max_h, im.h);
-      max_lv = std::max(max_lv, dev->pyr_tab[c.pyr[c.cur]].nlv);
-      any_hist |= P.histogram_method == 1;
       any_clahe |= P.histogram_method == 2;
     }
     // units (TrackKLT.cpp:80-93)
@@ -998,19 +999,18 @@ int Pass::stage0() {
     }
   }
   // ---- round 1: pre-process + FAST -----------------------------------------------------------------------------------
-  CU_TRY(ctx->hist.reserve((size_t)npre * 256, true));
-  CU_TRY(ctx->hist_ticket.reserve((size_t)npre, true));
-  CU_TRY(ctx->lut.reserve((size_t)npre * 256));
   if (any_clahe) CU_TRY(ctx->clahe_lut.reserve((size_t)npre * CLAHE_TILES * CLAHE_TILES * 256));
   if (!ctx->sp_mask_ready) {
     CU_TRY(ctx->sp_mask.reserve(SP_N));
     CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
     ctx->sp_mask_ready = true;
   }
-  CU_TRY(ctx->pre_jobs.upload(ctx->stream, (size_t)npre));
-  CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, dev->raw_dev.d, dev->pyr_dev.d, ctx->hist.d, ctx->hist_ticket.d,
-                           ctx->lut.d, ctx->clahe_lut.d, max_w, max_h, any_hist, any_clahe, max_lv));
-  ctx->stats[1] += (npre > 0) ? (unsigned)(any_hist + 1 + 2 * any_clahe + (max_lv - 1)) : 0u;
+  { HOSTPROF(s0_prejobs_upload); CU_TRY(ctx->pre_jobs.upload(ctx->stream, (size_t)npre)); }
+  HOSTPROF(s0_after_upload);
+  { HOSTPROF(s0_launch_preprocess);
+  CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, dev->raw_dev.d, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe));
+  }
+  ctx->stats[1] += (npre > 0) ? (unsigned)(1 + 2 * any_clahe) : 0u;
   size_t ncells = 0, nwords = 0;
   int max_cw = 1, max_ch = 1;
   for (auto &u : units) {
@@ -1025,7 +1025,6 @@ int Pass::stage0() {
     }
   }
   CU_TRY(ctx->fast_jobs.reserve(ncells));
-  CU_TRY(ctx->fast_thr.reserve(ncells));
   CU_TRY(ctx->fast_cnt.reserve(ncells));
   CU_TRY(ctx->fast_out.reserve(nwords));
   CU_TRY(ctx->fast_out_dev.reserve(nwords));
@@ -1038,9 +1037,9 @@ int Pass::stage0() {
       Side &s = side ? u.R : u.L;
       if (s.detect) emit_fast_jobs(ctx, s, u.rig->prm.fast_threshold, njobs, nwords);
     }
+  HOSTPROF(s0_fast_upload_launch);
   CU_TRY(ctx->fast_jobs.upload(ctx->stream, (size_t)njobs));
-  CU_TRY(ctx->fast_thr.upload(ctx->stream, (size_t)njobs));
-  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
+  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   seg(0);
   return OK;
@@ -1079,6 +1078,7 @@ int Pass::stage1() {
     for (auto &u : units)
       if (u.stereo) phase_b_right(ctx, u, nsp);
   }
+  HOSTPROF(s1_launches);
   CU_TRY(ctx->sp_items.upload(ctx->stream, (size_t)nsp));
   CU_TRY(launch_subpix(ctx->stream, ctx->sp_items.d, nsp, dev->pyr_dev.d, ctx->sp_mask.d, ctx->sp_out.d, ctx->sp_out_dev.d));
   // stereo LK items read their start point from the sub-pixel output: build the index map
@@ -1140,6 +1140,7 @@ int Pass::stage2() {
     emit_temporal(ctx, u, nlk, nrs);
     max_n = std::max(max_n, std::max(u.L.lk_n, u.R.lk_n));
   }
+  HOSTPROF(s2_launches);
   CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)nlk));
   CU_TRY(ctx->rs_jobs.upload(ctx->stream, (size_t)nrs));
   CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,
@@ -1283,17 +1284,14 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
   if (dev->upload_tables() != OK) return E_CUDA;
   size_t words = (size_t)((cw + 1) / 2) * ((ch + 1) / 2);
   CU_TRY(ctx->fast_jobs.reserve(1));
-  CU_TRY(ctx->fast_thr.reserve(1));
   CU_TRY(ctx->fast_cnt.reserve(1));
   CU_TRY(ctx->fast_out.reserve(words));
   CU_TRY(ctx->fast_out_dev.reserve(words));
   CU_TRY(ctx->fast_cnt_dev.reserve(1, true));
   CU_TRY(ctx->fast_ticket.reserve(1, true));
-  ctx->fast_jobs.h[0] = FastJob{p, x0, y0, cw, ch, 0, (int)words};
-  ctx->fast_thr.h[0] = threshold;
+  ctx->fast_jobs.h[0] = FastJob{p, x0, y0, cw, ch, 0, (int)words, threshold};
   CU_TRY(ctx->fast_jobs.upload(ctx->stream, 1));
-  CU_TRY(ctx->fast_thr.upload(ctx->stream, 1));
-  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, dev->pyr_dev.d, 0, ctx->fast_thr.d, ctx->fast_out_dev.d,
+  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, dev->pyr_dev.d, ctx->fast_out_dev.d,
                      ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   if (ctx->sync() != OK) return E_CUDA;
   unsigned cnt = ctx->fast_cnt.h[0];
@@ -1446,6 +1444,7 @@ int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long 
     }
     if (enable >= 0) {
       ln->prof_on = enable != 0;
+      ln->prof.mask = enable > 1 ? (unsigned)(enable >> 1) : ~0u;   // enable = 1: all kernels; 1 | mask<<1: only those
       if (enable) {
         memset(ln->prof_ms, 0, sizeof(ln->prof_ms));
         memset(ln->prof_launches, 0, sizeof(ln->prof_launches));

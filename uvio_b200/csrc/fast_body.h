@@ -31,6 +31,7 @@ struct FastJob {          // one grid cell of one image
   int x0, y0, w, h;       // cell rectangle (Grider_GRID.h:113-114, integer-division cell size)
   int out_off;            // first word of this job's list in the output buffer
   int out_cap;            // capacity in words (sized to the NMS worst case, ceil(w/2)*ceil(h/2): cannot overflow)
+  int threshold;          // cv::FAST threshold of this cell's tracker
 };
 
 UVIO_HD int fast_ring_off(int k, int pitch) {

@@ -3,6 +3,7 @@
 // launch geometry.  Built with -fmad=false: the CPU tracker's OpenCV build does not fuse multiply-adds.
 #include "kernels.h"
 
+#include <cooperative_groups.h>
 #include <math.h>
 #include <string.h>
 
@@ -12,74 +13,92 @@
 #include "ransac_body.h"
 #include "subpix_body.h"
 
+namespace cg = cooperative_groups;
+
 namespace uvio {
 
 // ---------------------------------------------------------------------------------------------------------------------
-// equalizeHist: histogram (+ LUT by the last band to finish) -> apply
+// Pre-processing of one uploaded frame by one thread-block cluster: equalizeHist (histogram -> LUT -> apply) and every
+// level of the optical-flow pyramid in a single launch.  The eight blocks of a cluster share an image; the steps that
+// need the whole image (histogram complete before the LUT, level l-1 complete before level l) are separated by cluster
+// barriers instead of kernel boundaries, and the partial histograms are combined through distributed shared memory.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_hist(const PreJob *jobs, const ImgView *raw_tab, unsigned *hist, unsigned *ticket,
-                                              uint8_t *lut_out) {
-  const PreJob job = jobs[blockIdx.y];
-  if (job.method != 1) return;
-  constexpr int NSUB = 8;   // one private histogram per warp
-  __shared__ unsigned sh[NSUB * 256];
-  __shared__ unsigned cdf[256];
-  __shared__ int s_first, s_last;
-  const ImgView I = raw_tab[job.raw];
-  GroupBlock g;
-#pragma unroll
-  for (int k = 0; k < NSUB; k++) sh[k * 256 + threadIdx.x] = 0;
-  __syncthreads();
-  int r0 = (int)((long long)I.h * blockIdx.x / gridDim.x), r1 = (int)((long long)I.h * (blockIdx.x + 1) / gridDim.x);
-  hist_rows(g, sh, I, r0, r1, NSUB);
-  __syncthreads();
-  unsigned *gh = hist + (size_t)blockIdx.y * 256;
-  unsigned mine = 0;
-#pragma unroll
-  for (int k = 0; k < NSUB; k++) mine += sh[k * 256 + threadIdx.x];
-  if (mine) atomicAdd(&gh[threadIdx.x], mine);
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(&ticket[blockIdx.y], 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (!s_last) return;
-  // last band of this image: LUT from the complete histogram (App. A.1), then reset the scratch for the next frame
-  __threadfence();
-  unsigned hv = __ldcg(&gh[threadIdx.x]);
-  gh[threadIdx.x] = 0;
-  if (threadIdx.x == 0) { ticket[blockIdx.y] = 0; s_first = 256; }
-  cdf[threadIdx.x] = hv;
-  __syncthreads();
-  if (hv) atomicMin(&s_first, (int)threadIdx.x);
-  for (int d = 1; d < 256; d <<= 1) {   // inclusive scan
-    unsigned v = threadIdx.x >= d ? cdf[threadIdx.x - d] : 0;
-    __syncthreads();
-    cdf[threadIdx.x] += v;
-    __syncthreads();
-  }
-  const int i0 = s_first, total = I.w * I.h;
-  const int h0 = (int)(cdf[i0] - (i0 ? cdf[i0 - 1] : 0));
-  uint8_t out;
-  if (h0 == total) out = (uint8_t)i0;
-  else if ((int)threadIdx.x <= i0) out = 0;
-  else {
-    float scale = 255.f / (float)(total - h0);
-    out = sat_u8(round_f2i(fmul((float)(int)(cdf[threadIdx.x] - cdf[i0]), scale)));
-  }
-  lut_out[(size_t)blockIdx.y * 256 + threadIdx.x] = out;
-}
+constexpr int PRE_CLUSTER = 8;      // blocks per image (portable maximum)
+constexpr int PRE_THREADS = 512;
+constexpr int PRE_NSUB = 8;         // private histograms per block (two warps share one)
 
-__global__ void __launch_bounds__(256) k_lut_apply(const PreJob *jobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
-                                                   const uint8_t *lut_in) {
+__global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREADS, 2)
+    k_preprocess(const PreJob *jobs, const ImgView *raw_tab, const PyrDesc *pyr_tab) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank();
   const PreJob job = jobs[blockIdx.y];
-  if (job.method == 2) return;
-  __shared__ uint8_t lut[256];
   const ImgView I = raw_tab[job.raw];
-  const ImgView D = pyr_tab[job.pyr].lv[0];
-  lut[threadIdx.x] = job.method == 1 ? lut_in[(size_t)blockIdx.y * 256 + threadIdx.x] : (uint8_t)threadIdx.x;
+  const PyrDesc &P = pyr_tab[job.pyr];
+  const ImgView D0 = P.lv[0];
+  __shared__ unsigned sh[PRE_NSUB * 256];
+  __shared__ unsigned bh[256];      // this block's histogram (read by the whole cluster)
+  __shared__ unsigned cdf[256];
+  __shared__ uint8_t lut[256];
+  __shared__ int s_first;
+  GroupBlock g;
+  const int r0 = (int)((long long)I.h * rank / PRE_CLUSTER), r1 = (int)((long long)I.h * (rank + 1) / PRE_CLUSTER);
+  if (job.method == 1) {   // uniform over the cluster
+    for (int k = threadIdx.x; k < PRE_NSUB * 256; k += PRE_THREADS) sh[k] = 0;
+    __syncthreads();
+    hist_rows(g, sh, I, r0, r1, PRE_NSUB);
+    __syncthreads();
+    if (threadIdx.x < 256) {
+      unsigned v = 0;
+#pragma unroll
+      for (int k = 0; k < PRE_NSUB; k++) v += sh[k * 256 + threadIdx.x];
+      bh[threadIdx.x] = v;
+    }
+    cluster.sync();
+    // every block builds the LUT from the eight partial histograms (App. A.1)
+    if (threadIdx.x < 256) {
+      unsigned hv = 0;
+#pragma unroll
+      for (int r = 0; r < PRE_CLUSTER; r++) hv += cluster.map_shared_rank(bh, r)[threadIdx.x];
+      cdf[threadIdx.x] = hv;
+      if (threadIdx.x == 0) s_first = 256;
+    }
+    __syncthreads();
+    if (threadIdx.x < 256 && cdf[threadIdx.x]) atomicMin(&s_first, (int)threadIdx.x);
+    for (int d = 1; d < 256; d <<= 1) {   // inclusive scan
+      unsigned v = (threadIdx.x < 256 && threadIdx.x >= d) ? cdf[threadIdx.x - d] : 0;
+      __syncthreads();
+      if (threadIdx.x < 256) cdf[threadIdx.x] += v;
+      __syncthreads();
+    }
+    if (threadIdx.x < 256) {
+      const int i0 = s_first, total = I.w * I.h;
+      const int h0 = (int)(cdf[i0] - (i0 ? cdf[i0 - 1] : 0));
+      uint8_t out;
+      if (h0 == total) out = (uint8_t)i0;
+      else if ((int)threadIdx.x <= i0) out = 0;
+      else {
+        float scale = 255.f / (float)(total - h0);
+        out = sat_u8(round_f2i(fmul((float)(int)(cdf[threadIdx.x] - cdf[i0]), scale)));
+      }
+      lut[threadIdx.x] = out;
+    }
+  } else if (threadIdx.x < 256) {
+    lut[threadIdx.x] = (uint8_t)threadIdx.x;
+  }
   __syncthreads();
-  int r0 = (int)((long long)I.h * blockIdx.x / gridDim.x), r1 = (int)((long long)I.h * (blockIdx.x + 1) / gridDim.x);
-  lut_rows(GroupBlock(), lut, I, (uint8_t *)D.p, D.pitch, r0, r1);
+  if (job.method != 2) lut_rows(g, lut, I, (uint8_t *)D0.p, D0.pitch, r0, r1);   // CLAHE wrote level 0 already
+  // pyramid: one lane per 4 x PD_ROWS output strip, the whole cluster per level
+  const int gtid = rank * PRE_THREADS + threadIdx.x;
+  for (int l = 1; l < P.nlv; l++) {
+    cluster.sync();   // level l-1 is complete (also keeps every block alive while its histogram may still be read)
+    const ImgView S = P.lv[l - 1], D = P.lv[l];
+    const int nsx = (D.w + PD_COLS - 1) / PD_COLS, nsy = (D.h + PD_ROWS - 1) / PD_ROWS;
+    for (int sidx = gtid; sidx < nsx * nsy; sidx += PRE_CLUSTER * PRE_THREADS) {
+      int sy = sidx / nsx, sx = sidx - sy * nsx;
+      pyrdown_strip(S, (uint8_t *)D.p, D.w, D.h, D.pitch, sx * PD_COLS, sy * PD_ROWS);
+    }
+  }
+  cluster.sync();
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -112,41 +131,17 @@ __global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const I
       ((uint8_t *)D.p)[(size_t)y * D.pitch + x] = clahe_pixel(L, q, x, y, I.p[(size_t)y * I.pitch + x]);
 }
 
-// ---------------------------------------------------------------------------------------------------------------------
-// pyramid: level l-1 -> level l for every image of the launch
-// ---------------------------------------------------------------------------------------------------------------------
-constexpr int PD_BLOCK_Y = 4;   // strips per block: a block covers 128 x 32 output pixels
-
-__global__ void __launch_bounds__(32 * PD_BLOCK_Y) k_pyrdown(const PreJob *jobs, const PyrDesc *pyr_tab, int level) {
-  const PyrDesc &P = pyr_tab[jobs[blockIdx.z].pyr];
-  if (level >= P.nlv) return;
-  const ImgView S = P.lv[level - 1], D = P.lv[level];
-  const int ox0 = (blockIdx.x * 32 + threadIdx.x) * PD_COLS, oy0 = (blockIdx.y * PD_BLOCK_Y + threadIdx.y) * PD_ROWS;
-  pyrdown_strip(S, (uint8_t *)D.p, D.w, D.h, D.pitch, ox0, oy0);
-}
-
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
-                              unsigned *hist, unsigned *ticket, uint8_t *lut, uint8_t *clahe_lut, int max_w, int max_h,
-                              int any_hist, int any_clahe, int max_levels) {
+                              uint8_t *clahe_lut, int any_clahe) {
   if (njobs <= 0) return cudaSuccess;
-  if (any_hist) prof_mark(st, K_HIST);
-  if (any_hist) k_hist<<<dim3(HIST_BANDS, njobs), 256, 0, st>>>(jobs, raw_tab, hist, ticket, lut);
-  prof_mark(st, K_LUT_APPLY);
-  k_lut_apply<<<dim3(HIST_BANDS, njobs), 256, 0, st>>>(jobs, raw_tab, pyr_tab, lut);
   if (any_clahe) {
     prof_mark(st, K_CLAHE_TILES);
     k_clahe_tiles<<<dim3(CLAHE_TILES * CLAHE_TILES, njobs), 256, 0, st>>>(jobs, raw_tab, clahe_lut);
     prof_mark(st, K_CLAHE_APPLY);
     k_clahe_apply<<<dim3(HIST_BANDS * 2, njobs), 256, 0, st>>>(jobs, raw_tab, pyr_tab, clahe_lut);
   }
-  int w = max_w, h = max_h;
-  for (int l = 1; l < max_levels; l++) {
-    w = (w + 1) / 2;
-    h = (h + 1) / 2;
-    prof_mark(st, K_PYRDOWN);
-    k_pyrdown<<<dim3((w + 32 * PD_COLS - 1) / (32 * PD_COLS), (h + PD_BLOCK_Y * PD_ROWS - 1) / (PD_BLOCK_Y * PD_ROWS), njobs),
-                dim3(32, PD_BLOCK_Y), 0, st>>>(jobs, pyr_tab, l);
-  }
+  prof_mark(st, K_PREPROCESS);
+  k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, 0, st>>>(jobs, raw_tab, pyr_tab);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
@@ -155,7 +150,7 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
 // FAST on grid cells. grid = (max tiles per cell, jobs). The last tile of a job to finish compacts the job's list into
 // mapped host memory, so the host sees exactly `count` words per cell and nothing else crosses PCIe.
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_fast(const FastJob *jobs, const int *thresholds, const PyrDesc *pyr_tab, uint32_t *out_dev,
+__global__ void __launch_bounds__(256) k_fast(const FastJob *jobs, const PyrDesc *pyr_tab, uint32_t *out_dev,
                                               unsigned *count_dev, unsigned *ticket_dev, uint32_t *out_host, unsigned *count_host) {
   const FastJob job = jobs[blockIdx.y];
   const int tiles_x = (job.w + FT_W - 1) / FT_W, tiles_y = (job.h + FT_H - 1) / FT_H;
@@ -164,7 +159,7 @@ __global__ void __launch_bounds__(256) k_fast(const FastJob *jobs, const int *th
   __shared__ FastSmem s;
   __shared__ int s_last;
   const ImgView I = pyr_tab[job.img].lv[0];
-  fast_tile(GroupBlock(), s, I, job, (blockIdx.x % tiles_x) * FT_W, (blockIdx.x / tiles_x) * FT_H, thresholds[blockIdx.y], out_dev,
+  fast_tile(GroupBlock(), s, I, job, (blockIdx.x % tiles_x) * FT_W, (blockIdx.x / tiles_x) * FT_H, job.threshold, out_dev,
             &count_dev[blockIdx.y]);
   __threadfence();
   __syncthreads();
@@ -183,12 +178,12 @@ __global__ void __launch_bounds__(256) k_fast(const FastJob *jobs, const int *th
 }
 
 cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max_cell_w, int max_cell_h, const PyrDesc *pyr_tab,
-                        int, const int *thresholds, uint32_t *out_dev, unsigned *count_dev, unsigned *ticket_dev,
+                        uint32_t *out_dev, unsigned *count_dev, unsigned *ticket_dev,
                         uint32_t *out_host, unsigned *count_host) {
   if (njobs <= 0) return cudaSuccess;
   int tiles = ((max_cell_w + FT_W - 1) / FT_W) * ((max_cell_h + FT_H - 1) / FT_H);
   prof_mark(st, K_FAST);
-  k_fast<<<dim3(tiles, njobs), 256, 0, st>>>(jobs, thresholds, pyr_tab, out_dev, count_dev, ticket_dev, out_host, count_host);
+  k_fast<<<dim3(tiles, njobs), 256, 0, st>>>(jobs, pyr_tab, out_dev, count_dev, ticket_dev, out_host, count_host);
   prof_mark(st, -1);
   return cudaGetLastError();
 }

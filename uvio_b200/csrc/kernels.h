@@ -37,33 +37,36 @@ struct RansacJob {
 
 // Optional per-kernel timing: when g_prof is set, every launch wrapper records a CUDA event before each kernel it launches
 // (and the engine one after the last), on the launching stream.
-enum KernelId { K_HIST = 0, K_LUT_APPLY, K_CLAHE_TILES, K_CLAHE_APPLY, K_PYRDOWN, K_FAST, K_SUBPIX, K_LK, K_RANSAC, K_COUNT };
+enum KernelId { K_HIST = 0, K_LUT_APPLY, K_CLAHE_TILES, K_CLAHE_APPLY, K_PYRDOWN, K_FAST, K_SUBPIX, K_LK, K_RANSAC, K_PREPROCESS, K_COUNT };
 struct KernelProf {
   static constexpr int MAX_MARKS = 48;
   cudaEvent_t ev[MAX_MARKS];
   int id[MAX_MARKS];
   int n = 0;
   bool ready = false;
+  unsigned mask = ~0u;   // kernels to time (bit = KernelId)
+  bool open = false;     // the last mark recorded started a kernel interval
 };
 extern thread_local KernelProf *g_prof;   // defined in engine.cpp; set by the lane thread that is launching
 inline void prof_mark(cudaStream_t st, int kernel_id) {
   KernelProf *p = g_prof;
   if (!p || p->n >= KernelProf::MAX_MARKS) return;
+  const bool wanted = kernel_id >= 0 && ((p->mask >> kernel_id) & 1u);
+  if (!wanted && !p->open) return;   // neither starts a timed kernel nor ends one
   cudaEventRecord(p->ev[p->n], st);
-  p->id[p->n++] = kernel_id;
+  p->id[p->n++] = wanted ? kernel_id : -1;
+  p->open = wanted;
 }
 
 // ---- image-wide passes ------------------------------------------------------------------------------------------------
-// equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels
+// equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels: one cluster launch
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const ImgView *raw_tab_dev,
-                              const PyrDesc *pyr_tab_dev, unsigned *hist_dev /*njobs*256, zero*/, unsigned *ticket_dev,
-                              uint8_t *lut_dev /*njobs*256*/, uint8_t *clahe_lut_dev /*njobs*64*256*/, int max_w, int max_h,
-                              int any_hist, int any_clahe, int max_levels);
+                              const PyrDesc *pyr_tab_dev, uint8_t *clahe_lut_dev /*njobs*64*256, CLAHE only*/, int any_clahe);
 
 // ---- detection ----------------------------------------------------------------------------------------------------------
 // FAST + NMS on grid cells; compacts each job's corner list into out_host (mapped pinned) and writes its count.
 cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max_cell_w, int max_cell_h, const PyrDesc *pyr_tab_dev,
-                        int threshold_unused, const int *thresholds /*per job*/, uint32_t *out_dev, unsigned *count_dev,
+                        uint32_t *out_dev, unsigned *count_dev,
                         unsigned *ticket_dev, uint32_t *out_host, unsigned *count_host);
 
 cudaError_t launch_subpix(cudaStream_t st, const SubpixItem *items, int n, const PyrDesc *pyr_tab_dev, const float *mask_dev,

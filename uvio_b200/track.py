@@ -378,7 +378,8 @@ def make_tracker(cfg, device: int = 0, **over) -> TrackKLT:
     return TrackKLT({i: c for i, c in enumerate(cfg.cams)}, **kw)
 
 
-KERNEL_NAMES = ["k_hist", "k_lut_apply", "k_clahe_tiles", "k_clahe_apply", "k_pyrdown", "k_fast", "k_subpix", "k_lk", "k_ransac"]
+KERNEL_NAMES = ["k_hist", "k_lut_apply", "k_clahe_tiles", "k_clahe_apply", "k_pyrdown", "k_fast", "k_subpix", "k_lk", "k_ransac",
+                "k_preprocess"]
 
 
 def device_stats(device: int = 0) -> dict:
