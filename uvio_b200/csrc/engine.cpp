@@ -89,13 +89,22 @@ struct MappedVec {   // pinned host memory mapped into the device address space 
   ~MappedVec() { if (h) cudaFreeHost(h); }
 };
 
-// A job list written by the host and read by one kernel.  Two transports: "copy" (default) keeps the list in pinned host
-// memory and sends the used part to a device buffer with one asynchronous copy ahead of the kernel, so that the kernel's
-// blocks read it from L2/HBM; "mapped" (UVIO_KLT_JOBS=mapped) lets the kernel read the pinned host memory across PCIe.
+// A job list written by the host and read by one kernel.  Two transports: "copy" keeps the list in pinned host memory and
+// sends the used part to a device buffer with one asynchronous copy ahead of the kernel, so that the kernel's blocks
+// read it from L2/HBM (lists read by many blocks: pre-processing, FAST); "mapped" lets the kernel read the pinned host
+// memory across PCIe (lists read once per warp while the frames still occupy the copy engine: sub-pixel, LK, RANSAC).
+// UVIO_KLT_JOBS=mapped|copy forces one transport for all lists.
 static bool jobs_mapped() {
   static const bool v = [] {
     const char *e = getenv("UVIO_KLT_JOBS");
     return e && strcmp(e, "mapped") == 0;
+  }();
+  return v;
+}
+static bool jobs_copied() {
+  static const bool v = [] {
+    const char *e = getenv("UVIO_KLT_JOBS");
+    return e && strcmp(e, "copy") == 0;
   }();
   return v;
 }
@@ -104,11 +113,12 @@ struct JobVec {
   T *h = nullptr, *d = nullptr;
   size_t cap = 0;
   bool mapped = false;
+  bool prefer_mapped = false;   // lists issued while the frames are still crossing PCIe: a copy would queue behind them
   cudaError_t reserve(size_t want) {   // contents are not preserved; call only while the stream is idle
     if (want <= cap) return cudaSuccess;
     size_t ncap = want + want / 2 + 64;
     release();
-    mapped = jobs_mapped();
+    mapped = jobs_mapped() || (prefer_mapped && !jobs_copied());
     cudaError_t e = cudaHostAlloc((void **)&h, ncap * sizeof(T), mapped ? cudaHostAllocMapped : cudaHostAllocDefault);
     if (e != cudaSuccess) return e;
     if (mapped) e = cudaHostGetDevicePointer((void **)&d, h, 0);
@@ -154,9 +164,14 @@ class Context;
 // One lane = one CUDA stream with its own job / result buffers.  A feed_batch call splits its trackers over the lanes and
 // runs them on separate host threads, so the host bookkeeping of one group overlaps the GPU rounds of the others.
 struct Lane {
+  Lane() { sp_items.prefer_mapped = lk_items.prefer_mapped = rs_jobs.prefer_mapped = true; }
   Context *dev = nullptr;
   int index = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;      // detection and tracking rounds
+  // The new frames travel and are pre-processed on a stream of their own: detection runs on the previous frame's pyramid
+  // (TrackKLT.cpp:129, :245), so only the temporal LK of round 3 has to wait for them (up_done).
+  cudaStream_t up_stream = nullptr;
+  cudaEvent_t up_done = nullptr;
   int cuda_err = 0;
   unsigned long long stats[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // accumulated into the context after every feed
   // host wall-clock per segment of lane_feed (us): issue r1, wait r1, host+issue r2, wait r2, host+issue r3, wait r3, host D, calls
@@ -202,7 +217,7 @@ struct Lane {
   // round 2 / 3
   DevVec<float> sp_mask;
   bool sp_mask_ready = false;
-  JobVec<SubpixItem> sp_items;
+  JobVec<SubpixItem> sp_items;   // prefer_mapped set in Lane()
   MappedVec<float> sp_out;
   DevVec<float> sp_out_dev;
   JobVec<LkItem> lk_items;
@@ -223,6 +238,8 @@ struct Lane {
   }
   ~Lane() {
     if (stream) cudaStreamDestroy(stream);
+    if (up_stream) cudaStreamDestroy(up_stream);
+    if (up_done) cudaEventDestroy(up_done);
   }
 };
 
@@ -451,7 +468,9 @@ Context *context_for_device(int device, int *err) {
     std::unique_ptr<Lane> ln(new Lane);
     ln->dev = c.get();
     ln->index = i;
-    if ((e = cudaStreamCreateWithFlags(&ln->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+    if ((e = cudaStreamCreateWithFlags(&ln->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&ln->up_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&ln->up_done, cudaEventDisableTiming)) != cudaSuccess) {
       if (err) *err = (int)e;
       return nullptr;
     }
@@ -931,7 +950,7 @@ struct Pass {
         if (ctx->sync() != OK) rc = E_CUDA;
         else {
           seg(2 * stage - 1);
-          ctx->prof_fold();
+          if (stage == 3) ctx->prof_fold();   // every stream of the lane is idle now
         }
       }
       if (rc == OK) {
@@ -950,7 +969,7 @@ int Pass::stage0() {
   t0 = tmark = now_us();
   ctx->prof_begin();
   g_prof = ctx->prof_on ? &ctx->prof : nullptr;
-  // ---- upload + pre-processing jobs + units -----------------------------------------------------------------------------
+  // ---- host bookkeeping of the new messages: frame slots, masks, pre-processing jobs, units ---------------------------------
   int nimg = 0, any_clahe = 0;
   for (int i = 0; i < n; i++) nimg += reqs[i]->n;
   CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
@@ -961,19 +980,7 @@ int Pass::stage0() {
     const Params &P = rig.prm;
     for (int k = 0; k < rq.n; k++) {
       CamState &c = *rig.find_cam(rq.sensor_ids[k]);
-      const HostImage &im = rq.images[k];
       c.cur ^= 1;
-      const ImgView &raw = dev->raw_tab[c.raw];
-      {
-      HOSTPROF(s0_memcpy);
-      // host (pageable or pinned) or device memory
-      if ((size_t)raw.pitch == im.stride)
-        CU_TRY(cudaMemcpyAsync((void *)raw.p, im.p, (size_t)raw.pitch * (im.h - 1) + im.w, cudaMemcpyDefault, ctx->stream));
-      else
-        CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
-                                 ctx->stream));
-      }
-      ctx->stats[2] += (unsigned long long)im.w * im.h;
       c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
       ctx->pre_jobs.h[npre++] = PreJob{c.raw, c.pyr[c.cur], P.histogram_method};
       any_clahe |= P.histogram_method == 2;
@@ -998,23 +1005,21 @@ int Pass::stage0() {
       }
     }
   }
-  // ---- round 1: pre-process + FAST -----------------------------------------------------------------------------------
   if (any_clahe) CU_TRY(ctx->clahe_lut.reserve((size_t)npre * CLAHE_TILES * CLAHE_TILES * 256));
   if (!ctx->sp_mask_ready) {
     CU_TRY(ctx->sp_mask.reserve(SP_N));
     CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
     ctx->sp_mask_ready = true;
   }
-  { HOSTPROF(s0_prejobs_upload); CU_TRY(ctx->pre_jobs.upload(ctx->stream, (size_t)npre)); }
-  HOSTPROF(s0_after_upload);
-  { HOSTPROF(s0_launch_preprocess);
-  CU_TRY(launch_preprocess(ctx->stream, ctx->pre_jobs.d, npre, dev->raw_dev.d, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe));
-  }
-  ctx->stats[1] += (npre > 0) ? (unsigned)(1 + 2 * any_clahe) : 0u;
+  // ---- round 1a: FAST.  Detection runs on the previous frame's pyramid, which is already in HBM, so it is issued ahead of
+  // the upload (its job list would otherwise queue behind the images on the copy engine).  First frames detect on the
+  // frame that is being uploaded and wait for it.
   size_t ncells = 0, nwords = 0;
   int max_cw = 1, max_ch = 1;
+  bool any_first = false;
   for (auto &u : units) {
     phase_a(u);
+    any_first |= u.first;
     for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
       Side &s = side ? u.R : u.L;
       if (!s.detect) continue;
@@ -1037,10 +1042,41 @@ int Pass::stage0() {
       Side &s = side ? u.R : u.L;
       if (s.detect) emit_fast_jobs(ctx, s, u.rig->prm.fast_threshold, njobs, nwords);
     }
-  HOSTPROF(s0_fast_upload_launch);
   CU_TRY(ctx->fast_jobs.upload(ctx->stream, (size_t)njobs));
-  CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d,
-                     ctx->fast_cnt_dev.d, ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  if (!any_first) {
+    HOSTPROF(s0_fast_launch);
+    CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d, ctx->fast_cnt_dev.d,
+                       ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  }
+  // ---- round 1b: upload + equalise + pyramid on the upload stream --------------------------------------------------------
+  CU_TRY(ctx->pre_jobs.upload(ctx->up_stream, (size_t)npre));
+  for (int i = 0; i < n; i++) {
+    HOSTPROF(s0_memcpy);
+    FeedRequest &rq = *reqs[i];
+    for (int k = 0; k < rq.n; k++) {
+      CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
+      const HostImage &im = rq.images[k];
+      const ImgView &raw = dev->raw_tab[c.raw];
+      // host (pageable or pinned) or device memory
+      if ((size_t)raw.pitch == im.stride)
+        CU_TRY(cudaMemcpyAsync((void *)raw.p, im.p, (size_t)raw.pitch * (im.h - 1) + im.w, cudaMemcpyDefault, ctx->up_stream));
+      else
+        CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
+                                 ctx->up_stream));
+      ctx->stats[2] += (unsigned long long)im.w * im.h;
+    }
+  }
+  {
+    HOSTPROF(s0_launch_preprocess);
+    CU_TRY(launch_preprocess(ctx->up_stream, ctx->pre_jobs.d, npre, dev->raw_dev.d, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe));
+    CU_TRY(cudaEventRecord(ctx->up_done, ctx->up_stream));
+  }
+  ctx->stats[1] += (npre > 0) ? (unsigned)(1 + 2 * any_clahe) : 0u;
+  if (any_first) {
+    CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->up_done, 0));
+    CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d, ctx->fast_cnt_dev.d,
+                       ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  }
   seg(0);
   return OK;
 }
@@ -1141,6 +1177,7 @@ int Pass::stage2() {
     max_n = std::max(max_n, std::max(u.L.lk_n, u.R.lk_n));
   }
   HOSTPROF(s2_launches);
+  CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->up_done, 0));   // the temporal LK reads the new pyramids
   CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)nlk));
   CU_TRY(ctx->rs_jobs.upload(ctx->stream, (size_t)nrs));
   CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,

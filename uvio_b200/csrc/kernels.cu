@@ -247,12 +247,15 @@ cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st) {
 constexpr int LK_WORK_SLOTS = 64;   // the counters are spread over slots so that the atomics of one launch do not queue up
 __device__ unsigned long long g_lk_work[LK_WORK_SLOTS][4];
 
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
+// one warp per block: features differ a lot in iteration count, and single-warp blocks let the SM refill warp by warp
+constexpr int LK_WARPS_PER_BLOCK = 1;
+
+__global__ void __launch_bounds__(LK_WARPS_PER_BLOCK * 32) k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
                                                              const float *init_from_dev, int max_count, double eps_sq,
                                                              LkOut *out_host, uint8_t *status_host, LkOut *out_dev,
                                                              uint8_t *status_dev) {
-  __shared__ LkSmem sm[WARPS_PER_BLOCK];
-  const int wid = threadIdx.x >> 5, i = blockIdx.x * WARPS_PER_BLOCK + wid;
+  __shared__ LkSmem sm[LK_WARPS_PER_BLOCK];
+  const int wid = threadIdx.x >> 5, i = blockIdx.x * LK_WARPS_PER_BLOCK + wid;
   if (i >= n) return;
   const LkItem it = items[i];
   float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
@@ -299,7 +302,7 @@ cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc
                       double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev) {
   if (n <= 0) return cudaSuccess;
   prof_mark(st, K_LK);
-  k_lk<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, init_from_dev, max_count,
+  k_lk<<<(n + LK_WARPS_PER_BLOCK - 1) / LK_WARPS_PER_BLOCK, LK_WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, init_from_dev, max_count,
                                                                                   eps * eps, out_host, status_host, out_dev,
                                                                                   status_dev);
   prof_mark(st, -1);

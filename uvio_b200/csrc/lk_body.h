@@ -84,17 +84,32 @@ UVIO_HD void lk_stage_rows(G g, uint32_t *dst, const ImgView &I, int x_aligned, 
     }
     return;
   }
+  // The window sticks out of the frame.  When one reflection is enough for every coordinate it can take (always, except
+  // on images smaller than the window's reach) the border handling is branch-free index arithmetic.
+  const bool once = x_aligned > -I.w && x_aligned + 4 * WORDS <= 2 * I.w - 2 && y0 > -I.h && y0 + ROWS <= 2 * I.h - 2 &&
+                    I.w >= 2 && I.h >= 2;
+  if (once) {
+    for (int i = g.lane(); i < N; i += g.size()) {
+      int r = i / WORDS, k = i - r * WORDS;
+      int X0 = x_aligned + 4 * k;
+      const uint8_t *row = I.p + (size_t)reflect101_once(y0 + r, I.h) * I.pitch;
+      uint32_t v;
+      if (aligned && X0 >= 0 && X0 + 3 < I.w) {
+        v = *(const uint32_t *)(row + X0);
+      } else {
+        v = (uint32_t)row[reflect101_once(X0, I.w)] | ((uint32_t)row[reflect101_once(X0 + 1, I.w)] << 8) |
+            ((uint32_t)row[reflect101_once(X0 + 2, I.w)] << 16) | ((uint32_t)row[reflect101_once(X0 + 3, I.w)] << 24);
+      }
+      dst[i] = v;
+    }
+    return;
+  }
   for (int i = g.lane(); i < N; i += g.size()) {
     int r = i / WORDS, k = i - r * WORDS;
     int X0 = x_aligned + 4 * k;
     const uint8_t *row = I.p + (size_t)reflect101(y0 + r, I.h) * I.pitch;
-    uint32_t v;
-    if (aligned && X0 >= 0 && X0 + 3 < I.w) {
-      v = *(const uint32_t *)(row + X0);
-    } else {
-      v = (uint32_t)row[reflect101(X0, I.w)] | ((uint32_t)row[reflect101(X0 + 1, I.w)] << 8) |
-          ((uint32_t)row[reflect101(X0 + 2, I.w)] << 16) | ((uint32_t)row[reflect101(X0 + 3, I.w)] << 24);
-    }
+    uint32_t v = (uint32_t)row[reflect101(X0, I.w)] | ((uint32_t)row[reflect101(X0 + 1, I.w)] << 8) |
+                 ((uint32_t)row[reflect101(X0 + 2, I.w)] << 16) | ((uint32_t)row[reflect101(X0 + 3, I.w)] << 24);
     dst[i] = v;
   }
 }

@@ -76,7 +76,8 @@ UVIO_HD unsigned rng_next(uint64_t &state) {
   return (unsigned)state;
 }
 
-constexpr int RS_H = 32;        // samples per chunk
+constexpr int RS_H = 32;        // most samples per chunk
+constexpr int RS_H_FIRST = 8;   // samples in the first chunk
 constexpr int RS_MAXROOT = 3;
 
 struct RansacSmem {
@@ -87,6 +88,8 @@ struct RansacSmem {
   int nmodels[RS_H];
   double F[RS_H][RS_MAXROOT][9];
   unsigned counts[RS_H * RS_MAXROOT];       // RANSAC: inlier counts
+  uint8_t slots[RS_H * RS_MAXROOT];         // RANSAC: the (sample, root) slots that hold a model
+  int nslots;
   float median[RS_H * RS_MAXROOT];          // LMedS: median error
   double bestF[9];
   // serial state (written by lane 0 only)
@@ -270,12 +273,12 @@ UVIO_HD int ransac_update_iters(double p, double ep, int model_points, int max_i
   return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : round_d2i(num / denom);
 }
 
-// Draw RS_H samples (lane 0; integer work only), then check collinearity one sample per lane.
+// Draw `chunk` (<= RS_H) samples (lane 0; integer work only), then check collinearity one sample per lane.
 template <class G>
-UVIO_HD void ransac_draw_chunk(G g, RansacSmem &s, int N) {
+UVIO_HD void ransac_draw_chunk(G g, RansacSmem &s, int N, int chunk) {
   if (g.lane() == 0) {
     uint64_t st = s.state;
-    for (int h = 0; h < RS_H; h++) {
+    for (int h = 0; h < chunk; h++) {
       int *idx = s.idx[h];
       for (int i = 0; i < 7; ++i) {
         int v;
@@ -291,7 +294,7 @@ UVIO_HD void ransac_draw_chunk(G g, RansacSmem &s, int N) {
     }
   }
   g.sync();
-  for (int h = g.lane(); h < RS_H; h += g.size())
+  for (int h = g.lane(); h < chunk; h += g.size())
     s.ok[h] = !collinear_last(s.x0, s.y0, s.idx[h]) && !collinear_last(s.x1, s.y1, s.idx[h]);
   g.sync();
 }
@@ -335,11 +338,15 @@ UVIO_HD int ransac_job(G g, RansacSmem &s, const float *p0, const float *p1, int
     return ok;
   }
   const float thr_sq = (float)(thr * thr);
+  // Hypotheses are evaluated speculatively, a chunk at a time, and then consumed in order with OpenCV's adaptive
+  // iteration count; whatever the count cuts off was wasted.  The first good model usually drops the count to a handful,
+  // so the first chunk is small and later chunks are sized by what is still allowed.
+  int chunk = RS_H_FIRST;
   while (true) {
-    ransac_draw_chunk(g, s, N);
+    ransac_draw_chunk(g, s, N, chunk);
     // a collinear sample ends the chunk: everything after it was drawn from a generator state OpenCV never reaches
     int nvalid = 0;
-    while (nvalid < RS_H && s.ok[nvalid]) nvalid++;
+    while (nvalid < chunk && s.ok[nvalid]) nvalid++;
     for (int h = g.lane(); h < nvalid; h += g.size()) {
       double x0[7], y0[7], x1[7], y1[7];
       for (int i = 0; i < 7; i++) {
@@ -351,11 +358,19 @@ UVIO_HD int ransac_job(G g, RansacSmem &s, const float *p0, const float *p1, int
     for (int i = g.lane(); i < RS_H * RS_MAXROOT; i += g.size()) s.counts[i] = 0;
     g.sync();
     if (!lmeds) {
-      int total = nvalid * RS_MAXROOT * N;
+      // list the models that exist (1 or 3 per sample) so that no lane scores an empty slot
+      if (g.lane() == 0) {
+        int m = 0;
+        for (int h = 0; h < nvalid; h++)
+          for (int k = 0; k < s.nmodels[h]; k++) s.slots[m++] = (uint8_t)(h * RS_MAXROOT + k);
+        s.nslots = m;
+      }
+      g.sync();
+      int total = s.nslots * N;
       for (int t = g.lane(); t < total; t += g.size()) {
-        int slot = t / N, p = t - slot * N;
-        int h = slot / RS_MAXROOT, k = slot - h * RS_MAXROOT;
-        if (k < s.nmodels[h] && fm_error(s.F[h][k], s.x0[p], s.y0[p], s.x1[p], s.y1[p]) <= thr_sq) smem_inc(&s.counts[slot]);
+        int m = t / N, p = t - m * N;
+        int slot = s.slots[m];
+        if (fm_error(s.F[0][0] + 9 * slot, s.x0[p], s.y0[p], s.x1[p], s.y1[p]) <= thr_sq) smem_inc(&s.counts[slot]);
       }
     } else {
       for (int slot = g.lane(); slot < nvalid * RS_MAXROOT; slot += g.size()) {
@@ -400,17 +415,19 @@ UVIO_HD int ransac_job(G g, RansacSmem &s, const float *p0, const float *p1, int
       }
       if (!s.done) {
         if (s.iter >= s.niters) s.done = 1;
-        else if (nvalid < RS_H) {
+        else if (nvalid < chunk) {
           // sample `nvalid` was rejected: OpenCV redraws it from the generator state right after the rejected draw
           s.state = s.state_after[nvalid];
           if (++s.attempts >= max_attempts) s.done = 1;   // getSubset gave up (iter == 0: no model at all)
         } else {
-          s.state = s.state_after[RS_H - 1];
+          s.state = s.state_after[chunk - 1];
         }
       }
     }
     g.sync();
     if (s.done) break;
+    int left = s.niters - s.iter;
+    chunk = left < 1 ? 1 : (left > RS_H ? RS_H : left);
   }
   int ok = s.have_best;
   if (ok) {
