@@ -200,6 +200,25 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
     return sec, n_obs, clk, delta, prof, wall
 
 
+def _latency_leg(track, L, cfg, device, step_frames, n_frames):
+    """One stream fed frame by frame through uvio_klt_feed (host frames and masks): wall-clock of the synchronous call."""
+    t = track.make_tracker(cfg, device=device)
+    obs = np.zeros((1024,), track.OBS_DTYPE)
+    n = C.c_int()
+    lat = []
+    for k in range(n_frames):
+        t0 = time.perf_counter()
+        rc = L.uvio_klt_feed(t._h, C.byref(step_frames[k][0]))
+        L.uvio_klt_get_new_observations(t._h, obs.ctypes.data, 1024, C.byref(n))
+        lat.append(1e3 * (time.perf_counter() - t0))
+        if rc != 0:
+            raise RuntimeError(f"uvio_klt_feed failed: {rc}")
+    t.close()
+    lat = sorted(lat[5:])
+    return {"p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(0.99 * len(lat)))], "frames": len(lat),
+            "what": "uvio_klt_feed + uvio_klt_get_new_observations, one euroc_mav stereo stream, pinned host frames and masks"}
+
+
 def run_ours(args):
     import torch
     from uvio_b200 import build, track
@@ -242,6 +261,7 @@ def run_ours(args):
     sec, n_obs, clk, st, prof, wall = _run_leg(track, L, cfg, local, S, dev_steps, W, K, dist, obs_buf, counts, True, lk_only)
     sec2, n_obs2, _clk2, st2, _prof2, wall2 = _run_leg(track, L, cfg, local, S, host_steps, W, K, dist, obs_buf, counts, False, lk_only)
     sec3, _n3, _clk3, st3, prof3, _wall3 = _run_leg(track, L, cfg, local, S, dev_steps, W, K, dist, obs_buf, counts, False, 1)
+    lat = _latency_leg(track, L, cfg, local, host_steps, min(T, 60))
     total_frames = world * S * K
     value = total_frames / sec
     e2e = total_frames / sec2
@@ -251,6 +271,7 @@ def run_ours(args):
         "dtype": "u8 images, int32 FAST/LK inner products, fp32 LK normal equations, fp64 cornerSubPix/RANSAC",
         "data": "synthetic (uvio_b200.synth, seeded)",
         "config": config_dict(cfg, S, {"latency_ms_per_batched_step": 1e3 * sec / K,
+                                        "single_stream_frame_latency_ms": lat,
                                         "observations_per_frame": n_obs / max(1, S * K)}),
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": st2["h2d_bytes"] / K,
                 "d2h_bytes_per_step": st2["d2h_bytes"] / K, "ms_per_step": 1e3 * sec2 / K,
@@ -392,6 +413,14 @@ def roofline_entry(profs, stats, K, S, cfg):
     else:
         ach = alg / (ms / 1e3) / 1e9
         entry.update({"achieved": ach, "frac": ach / peak, "algorithmic_bytes_per_launch": alg / max(1, launches)})
+        tpath = os.path.join(ROOT, "profiles", "r1_lk_traffic.json")
+        if name == "k_lk" and os.path.exists(tpath):
+            cap = json.load(open(tpath))
+            per_feature = (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["features_in_launch"]
+            feats = stats["lk_point_levels"] / max(1, len(lv)) / max(1, launches)      # features per launch in this run
+            entry["traffic"] = per_feature * feats
+            entry["traffic_source"] = (f"{cap['capture']}: {per_feature:.0f} DRAM bytes per feature, scaled to this run's "
+                                       f"{feats:.0f} features per launch")
         if name == "k_lk":
             entry["note"] = ("LK is an L2/shared-memory gather + ordered fp32 accumulation, not an HBM stream: algorithmic bytes = 324 B "
                              "per point-level template footprint + 256 B per iteration J footprint (SURVEY 8(d)); the fraction is "

@@ -8,11 +8,11 @@
 
 namespace uvio {
 
-cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab, uint8_t *,
+cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const PyrDesc *pyr_tab, uint8_t *,
                               int) {
   GroupSeq g;
   for (int j = 0; j < njobs; j++) {
-    const ImgView I = raw_tab[jobs[j].raw];
+    const ImgView I = jobs[j].src;
     const PyrDesc &P = pyr_tab[jobs[j].pyr];
     uint8_t *d0 = (uint8_t *)P.lv[0].p;
     if (jobs[j].method == 1) {

@@ -77,6 +77,24 @@ def test_cell_top_k_matches_real_std_sort(bodies):
         np.testing.assert_array_equal(out[:got], exp, err_msg=f"trial {trial}: n={n} K={K} cell {cw}x{ch}")
 
 
+def test_ransac_root_order_on_tie_cases(bodies):
+    """Two models of one 7-point sample with the same best inlier count: the winner is the one cv::run7Point lists first
+    (tests/golden/ransac_ties.npz, masks from cv2; see tests/golden/make_ransac_ties.py)."""
+    L = bodies
+    g = np.load(os.path.join(GOLDEN, "ransac_ties.npz"))
+    K = np.ascontiguousarray(g["intrinsics"], np.float64)
+    D = np.ascontiguousarray(g["dist"], np.float64)
+    for k in ("a", "b"):
+        p0 = np.ascontiguousarray(g[f"p0_{k}"], np.float32)
+        p1 = np.ascontiguousarray(g[f"p1_{k}"], np.float32)
+        a_n, b_n = np.zeros_like(p0), np.zeros_like(p1)
+        L.hs_undistort(_p(p0), len(p0), int(g["model"]), _p(K), _p(D), _p(a_n))
+        L.hs_undistort(_p(p1), len(p1), int(g["model"]), _p(K), _p(D), _p(b_n))
+        mask = np.zeros(len(p0), np.uint8)
+        L.hs_ransac(_p(a_n), _p(b_n), len(p0), ctypes.c_double(2.0 / max(K[0], K[1])), ctypes.c_double(0.999), 1000, _p(mask))
+        assert np.array_equal(mask, g[f"mask_{k}"]), f"case {k}: {np.nonzero(mask != g[f'mask_{k}'])[0]}"
+
+
 def test_kernel_bodies_against_stage_goldens(bodies):
     L = bodies
     g = np.load(os.path.join(GOLDEN, "stages_euroc.npz"))

@@ -263,20 +263,19 @@ class Context {
   std::vector<ImgView> raw_tab;
   std::vector<CamModel> cam_tab;
   DevVec<PyrDesc> pyr_dev;
-  DevVec<ImgView> raw_dev;
   DevVec<CamModel> cam_dev;
   bool tables_dirty = true;
   std::vector<void *> allocs;   // image memory of all cameras
+  uint8_t *raw_arena = nullptr;   // next free byte of the current upload-buffer chunk
+  size_t raw_arena_left = 0;
 
   int upload_tables() {
     Context *ctx = this;
     if (!tables_dirty) return OK;
     CU_TRY(cudaDeviceSynchronize());
     CU_TRY(pyr_dev.reserve(pyr_tab.size()));
-    CU_TRY(raw_dev.reserve(raw_tab.size()));
     CU_TRY(cam_dev.reserve(cam_tab.size()));
     if (!pyr_tab.empty()) CU_TRY(cudaMemcpy(pyr_dev.d, pyr_tab.data(), pyr_tab.size() * sizeof(PyrDesc), cudaMemcpyHostToDevice));
-    if (!raw_tab.empty()) CU_TRY(cudaMemcpy(raw_dev.d, raw_tab.data(), raw_tab.size() * sizeof(ImgView), cudaMemcpyHostToDevice));
     if (!cam_tab.empty()) CU_TRY(cudaMemcpy(cam_dev.d, cam_tab.data(), cam_tab.size() * sizeof(CamModel), cudaMemcpyHostToDevice));
     tables_dirty = false;
     return OK;
@@ -296,15 +295,27 @@ class Context {
       lw = (lw + 1) / 2;
       lh = (lh + 1) / 2;
     }
+    // Upload buffers come from an arena in creation order: cameras created one after the other (the two cameras of a rig,
+    // the rigs of a batch) get adjacent buffers, so frames that are adjacent in host memory go up as one copy.
+    if (raw_arena_left < raw_bytes) {
+      const size_t chunk = std::max<size_t>(raw_bytes, (size_t)64 << 20);
+      CU_TRY(cudaMalloc((void **)&raw_arena, chunk + 256));
+      CU_TRY(cudaMemset(raw_arena, 0, chunk + 256));
+      allocs.push_back(raw_arena);
+      raw_arena_left = chunk;
+    }
+    uint8_t *raw_base = raw_arena;
+    raw_arena += raw_bytes;
+    raw_arena_left -= raw_bytes;
     uint8_t *base = nullptr;
-    CU_TRY(cudaMalloc((void **)&base, raw_bytes + 2 * pyr_bytes + 256));
-    CU_TRY(cudaMemset(base, 0, raw_bytes + 2 * pyr_bytes + 256));
+    CU_TRY(cudaMalloc((void **)&base, 2 * pyr_bytes + 256));
+    CU_TRY(cudaMemset(base, 0, 2 * pyr_bytes + 256));
     allocs.push_back(base);
     c.w = w;
     c.h = h;
     c.raw = (int)raw_tab.size();
-    raw_tab.push_back(ImgView{base, w, h, raw_pitch});
-    uint8_t *p = base + raw_bytes;
+    raw_tab.push_back(ImgView{raw_base, w, h, raw_pitch});
+    uint8_t *p = base;
     for (int s = 0; s < 2; s++) {
       PyrDesc d;
       memset(&d, 0, sizeof(d));
@@ -982,7 +993,7 @@ int Pass::stage0() {
       CamState &c = *rig.find_cam(rq.sensor_ids[k]);
       c.cur ^= 1;
       c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
-      ctx->pre_jobs.h[npre++] = PreJob{c.raw, c.pyr[c.cur], P.histogram_method};
+      ctx->pre_jobs.h[npre++] = PreJob{dev->raw_tab[c.raw], c.pyr[c.cur], P.histogram_method};   // src is settled below
       any_clahe |= P.histogram_method == 2;
     }
     // units (TrackKLT.cpp:80-93)
@@ -1049,26 +1060,62 @@ int Pass::stage0() {
                        ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   }
   // ---- round 1b: upload + equalise + pyramid on the upload stream --------------------------------------------------------
-  CU_TRY(ctx->pre_jobs.upload(ctx->up_stream, (size_t)npre));
-  for (int i = 0; i < n; i++) {
+  {
     HOSTPROF(s0_memcpy);
-    FeedRequest &rq = *reqs[i];
-    for (int k = 0; k < rq.n; k++) {
-      CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
-      const HostImage &im = rq.images[k];
-      const ImgView &raw = dev->raw_tab[c.raw];
-      // host (pageable or pinned) or device memory
-      if ((size_t)raw.pitch == im.stride)
-        CU_TRY(cudaMemcpyAsync((void *)raw.p, im.p, (size_t)raw.pitch * (im.h - 1) + im.w, cudaMemcpyDefault, ctx->up_stream));
-      else
-        CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
-                                 ctx->up_stream));
-      ctx->stats[2] += (unsigned long long)im.w * im.h;
+    // Frames already in device memory are consumed where they lie; host frames go to the upload buffers.  Copies whose
+    // source and destination both continue the previous one are merged (a batch of tightly packed frames is one copy).
+    uint8_t *pend_dst = nullptr;
+    const uint8_t *pend_src = nullptr;
+    size_t pend_bytes = 0;
+    auto flush = [&]() -> cudaError_t {
+      if (!pend_bytes) return cudaSuccess;
+      cudaError_t e = cudaMemcpyAsync(pend_dst, pend_src, pend_bytes, cudaMemcpyHostToDevice, ctx->up_stream);
+      pend_bytes = 0;
+      return e;
+    };
+    int j = 0;
+    for (int i = 0; i < n; i++) {
+      FeedRequest &rq = *reqs[i];
+      for (int k = 0; k < rq.n; k++, j++) {
+        CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
+        const HostImage &im = rq.images[k];
+        const ImgView &raw = dev->raw_tab[c.raw];
+        cudaPointerAttributes attr;
+        const bool on_device = cudaPointerGetAttributes(&attr, im.p) == cudaSuccess &&
+                               (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+        if (on_device) {
+          ctx->pre_jobs.h[j].src = ImgView{im.p, im.w, im.h, (int)im.stride};
+          continue;
+        }
+        cudaGetLastError();   // an unregistered host pointer is not an error
+        ctx->stats[2] += (unsigned long long)im.w * im.h;
+        if ((size_t)raw.pitch == im.stride) {
+          const size_t bytes = (size_t)raw.pitch * (im.h - 1) + im.w, span = (size_t)raw.pitch * im.h;
+          if (pend_bytes && pend_src + pend_bytes == im.p && pend_dst + pend_bytes == raw.p) {
+            pend_bytes += span;
+          } else {
+            CU_TRY(flush());
+            pend_dst = (uint8_t *)raw.p;
+            pend_src = im.p;
+            pend_bytes = span;
+          }
+          if (span != bytes && (size_t)im.w != im.stride) {   // never read past the caller's last row
+            pend_bytes -= span - bytes;
+            CU_TRY(flush());
+          }
+        } else {
+          CU_TRY(flush());
+          CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
+                                   ctx->up_stream));
+        }
+      }
     }
+    CU_TRY(flush());
+    CU_TRY(ctx->pre_jobs.upload(ctx->up_stream, (size_t)npre));
   }
   {
     HOSTPROF(s0_launch_preprocess);
-    CU_TRY(launch_preprocess(ctx->up_stream, ctx->pre_jobs.d, npre, dev->raw_dev.d, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe));
+    CU_TRY(launch_preprocess(ctx->up_stream, ctx->pre_jobs.d, npre, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe));
     CU_TRY(cudaEventRecord(ctx->up_done, ctx->up_stream));
   }
   ctx->stats[1] += (npre > 0) ? (unsigned)(1 + 2 * any_clahe) : 0u;
@@ -1211,6 +1258,7 @@ int Pass::stage3() {
 }
 
 int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
+  HOSTPROF(fb_total);
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
   int worst = OK;
@@ -1257,10 +1305,14 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     passes[l].reqs = good.data() + b;
     passes[l].n = (int)(e - b);
   }
+  {
+  HOSTPROF(fb_pool_run);
   ctx->pool->run(nthreads, [&](int t) {
+    HOSTPROF(fb_thread);
     for (int stage = 0; stage < 4; stage++)
       for (int l = t; l < nl; l += nthreads) passes[l].step();
   });
+  }
   std::vector<int> rc(nl, OK);
   for (int l = 0; l < nl; l++) rc[l] = passes[l].result();
   for (int l = 0; l < nl; l++) {

@@ -28,11 +28,11 @@ constexpr int PRE_THREADS = 512;
 constexpr int PRE_NSUB = 8;         // private histograms per block (two warps share one)
 
 __global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREADS, 2)
-    k_preprocess(const PreJob *jobs, const ImgView *raw_tab, const PyrDesc *pyr_tab) {
+    k_preprocess(const PreJob *jobs, const PyrDesc *pyr_tab) {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
   const PreJob job = jobs[blockIdx.y];
-  const ImgView I = raw_tab[job.raw];
+  const ImgView I = job.src;
   const PyrDesc &P = pyr_tab[job.pyr];
   const ImgView D0 = P.lv[0];
   __shared__ unsigned sh[PRE_NSUB * 256];
@@ -104,11 +104,11 @@ __global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREAD
 // ---------------------------------------------------------------------------------------------------------------------
 // CLAHE: per-tile clipped LUTs -> bilinear apply
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_clahe_tiles(const PreJob *jobs, const ImgView *raw_tab, uint8_t *luts) {
+__global__ void __launch_bounds__(256) k_clahe_tiles(const PreJob *jobs, uint8_t *luts) {
   const PreJob job = jobs[blockIdx.y];
   if (job.method != 2) return;
   __shared__ unsigned sh[256];
-  const ImgView I = raw_tab[job.raw];
+  const ImgView I = job.src;
   const ClaheGeom q = clahe_geom(I.w, I.h, 10.0, CLAHE_TILES, CLAHE_TILES);
   sh[threadIdx.x] = 0;
   __syncthreads();
@@ -117,11 +117,11 @@ __global__ void __launch_bounds__(256) k_clahe_tiles(const PreJob *jobs, const I
   if (threadIdx.x == 0) clahe_tile_lut(sh, q, luts + ((size_t)blockIdx.y * CLAHE_TILES * CLAHE_TILES + blockIdx.x) * 256);
 }
 
-__global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
+__global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const PyrDesc *pyr_tab,
                                                      const uint8_t *luts) {
   const PreJob job = jobs[blockIdx.y];
   if (job.method != 2) return;
-  const ImgView I = raw_tab[job.raw];
+  const ImgView I = job.src;
   const ImgView D = pyr_tab[job.pyr].lv[0];
   const ClaheGeom q = clahe_geom(I.w, I.h, 10.0, CLAHE_TILES, CLAHE_TILES);
   const uint8_t *L = luts + (size_t)blockIdx.y * CLAHE_TILES * CLAHE_TILES * 256;
@@ -131,17 +131,17 @@ __global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const I
       ((uint8_t *)D.p)[(size_t)y * D.pitch + x] = clahe_pixel(L, q, x, y, I.p[(size_t)y * I.pitch + x]);
 }
 
-cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const ImgView *raw_tab, const PyrDesc *pyr_tab,
+cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const PyrDesc *pyr_tab,
                               uint8_t *clahe_lut, int any_clahe) {
   if (njobs <= 0) return cudaSuccess;
   if (any_clahe) {
     prof_mark(st, K_CLAHE_TILES);
-    k_clahe_tiles<<<dim3(CLAHE_TILES * CLAHE_TILES, njobs), 256, 0, st>>>(jobs, raw_tab, clahe_lut);
+    k_clahe_tiles<<<dim3(CLAHE_TILES * CLAHE_TILES, njobs), 256, 0, st>>>(jobs, clahe_lut);
     prof_mark(st, K_CLAHE_APPLY);
-    k_clahe_apply<<<dim3(HIST_BANDS * 2, njobs), 256, 0, st>>>(jobs, raw_tab, pyr_tab, clahe_lut);
+    k_clahe_apply<<<dim3(HIST_BANDS * 2, njobs), 256, 0, st>>>(jobs, pyr_tab, clahe_lut);
   }
   prof_mark(st, K_PREPROCESS);
-  k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, 0, st>>>(jobs, raw_tab, pyr_tab);
+  k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, 0, st>>>(jobs, pyr_tab);
   prof_mark(st, -1);
   return cudaGetLastError();
 }

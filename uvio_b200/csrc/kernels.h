@@ -19,7 +19,7 @@ struct PyrDesc {                       // one image pyramid resident in HBM
 };
 
 struct PreJob {                        // one image to pre-process this frame
-  int raw;                             // index into the raw-image table (uploaded frame)
+  ImgView src;                         // the frame in device-visible memory: the upload buffer, or the caller's own device memory
   int pyr;                             // destination pyramid
   int method;                          // 0 none, 1 equalizeHist, 2 CLAHE   (TrackBase::HistogramMethod)
 };
@@ -60,8 +60,7 @@ inline void prof_mark(cudaStream_t st, int kernel_id) {
 
 // ---- image-wide passes ------------------------------------------------------------------------------------------------
 // equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels: one cluster launch
-cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const ImgView *raw_tab_dev,
-                              const PyrDesc *pyr_tab_dev, uint8_t *clahe_lut_dev /*njobs*64*256, CLAHE only*/, int any_clahe);
+cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const PyrDesc *pyr_tab_dev, uint8_t *clahe_lut_dev /*njobs*64*256, CLAHE only*/, int any_clahe);
 
 // ---- detection ----------------------------------------------------------------------------------------------------------
 // FAST + NMS on grid cells; compacts each job's corner list into out_host (mapped pinned) and writes its count.

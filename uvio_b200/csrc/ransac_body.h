@@ -5,9 +5,12 @@
 //
 // SURVEY.md App. A.7 / A.8.  One thread block per (rig, camera) job.  The sample stream is OpenCV's: a multiply-with-
 // carry generator seeded with 2^64-1 on every call, seven distinct indices per sample, collinearity-rejected, so the
-// hypotheses tested are the ones the CPU tracker tests, in the same order.  Samples are drawn RS_H at a time by one
-// lane, solved one per lane (7-point: 2-D null space + cubic), scored lane-parallel over all points, and a serial scan
-// applies the adaptive iteration cut-off in order.  N < 15 points switches to least-median (as OpenCV does silently).
+// hypotheses tested are the ones the CPU tracker tests, in the same order.  Samples are drawn a chunk at a time by one
+// lane, solved one per lane, scored lane-parallel over all points, and a serial scan applies the adaptive iteration
+// cut-off in order.  The 7-point solver follows cv::run7Point as of OpenCV 4.13: Hartley-normalised points, the two
+// null-space vectors OpenCV's Jacobi SVD produces (see seven_point), cv::solveCubic.  The solutions do not depend on
+// those choices but their ORDER does, and RANSAC keeps the first of two equally good models (tests/golden/
+// ransac_ties.npz).  N < 15 points switches to least-median (as OpenCV does silently).
 #pragma once
 #include <float.h>
 
@@ -77,7 +80,11 @@ UVIO_HD unsigned rng_next(uint64_t &state) {
 }
 
 constexpr int RS_H = 32;        // most samples per chunk
+#ifdef RS_H_FIRST_OVERRIDE
+constexpr int RS_H_FIRST = RS_H_FIRST_OVERRIDE;
+#else
 constexpr int RS_H_FIRST = 8;   // samples in the first chunk
+#endif
 constexpr int RS_MAXROOT = 3;
 
 struct RansacSmem {
@@ -164,7 +171,28 @@ UVIO_HD int solve_cubic(const double *c, double *r) {
 }
 
 // 7-point algorithm on sample points (x0,y0) <-> (x1,y1). Writes up to 3 matrices (row-major 3x3); returns the count.
-UVIO_HD int seven_point(const double *x0, const double *y0, const double *x1, const double *y1, double (*Fout)[9]) {
+UVIO_HD int seven_point(const double *x0r, const double *y0r, const double *x1r, const double *y1r, double (*Fout)[9]) {
+  // Hartley normalisation of the seven points, as cv::run7Point does (centre at the origin, mean distance sqrt(2)).  It does
+  // not change the solutions, but the cubic is solved in the normalised system and its root order is the order of the models.
+  double c0x = 0, c0y = 0, c1x = 0, c1y = 0;
+  for (int i = 0; i < 7; i++) { c0x += x0r[i]; c0y += y0r[i]; c1x += x1r[i]; c1y += y1r[i]; }
+  const double t7 = 1. / 7;
+  c0x *= t7; c0y *= t7; c1x *= t7; c1y *= t7;
+  double scale0 = 0, scale1 = 0;
+  for (int i = 0; i < 7; i++) {
+    scale0 += sqrt((x0r[i] - c0x) * (x0r[i] - c0x) + (y0r[i] - c0y) * (y0r[i] - c0y));
+    scale1 += sqrt((x1r[i] - c1x) * (x1r[i] - c1x) + (y1r[i] - c1y) * (y1r[i] - c1y));
+  }
+  scale0 *= t7;
+  scale1 *= t7;
+  if (scale0 < FLT_EPSILON || scale1 < FLT_EPSILON) return 0;
+  scale0 = sqrt(2.) / scale0;
+  scale1 = sqrt(2.) / scale1;
+  double x0[7], y0[7], x1[7], y1[7];
+  for (int i = 0; i < 7; i++) {
+    x0[i] = (x0r[i] - c0x) * scale0; y0[i] = (y0r[i] - c0y) * scale0;
+    x1[i] = (x1r[i] - c1x) * scale1; y1[i] = (y1r[i] - c1y) * scale1;
+  }
   double A[7][9];
   int perm[9];
   for (int j = 0; j < 9; j++) perm[j] = j;
@@ -207,6 +235,32 @@ UVIO_HD int seven_point(const double *x0, const double *y0, const double *x1, co
   for (int i = 0; i < 9; i++) { f2[i] -= dot * f1[i]; n2 += f2[i] * f2[i]; }
   n2 = 1.0 / sqrt(n2);
   for (int i = 0; i < 9; i++) f2[i] *= n2;
+  // (f1, f2) is now an orthonormal basis of the null space.  Which basis is used does not change the three solutions, but
+  // it decides the ORDER solveCubic returns them in, and RANSAC keeps the first of two equally good models.  OpenCV takes
+  // rows 7 and 8 of V from SVD::compute(FULL_UV); for a 7x9 system that is its own Jacobi SVD (below the LAPACK size
+  // threshold), which completes V by projecting two fixed pseudo-random sign vectors (cv::RNG(0x12345678), +-1/9) off the
+  // rows already found and normalising (JacobiSVDImpl_, modules/core/src/lapack.cpp).  Those two vectors are therefore the
+  // projections of the fixed sign vectors onto the null space, whatever basis it was found in:
+  {
+    const double sg1[9] = {-1, -1, 1, -1, -1, -1, -1, 1, 1}, sg2[9] = {1, -1, 1, 1, 1, 1, 1, -1, 1};
+    double a1 = 0, a2 = 0, b1 = 0, b2 = 0;
+    for (int i = 0; i < 9; i++) {
+      a1 += sg1[i] * f1[i]; a2 += sg1[i] * f2[i];
+      b1 += sg2[i] * f1[i]; b2 += sg2[i] * f2[i];
+    }
+    double g1[9], g2[9], m1 = 0, m2 = 0, d = 0;
+    for (int i = 0; i < 9; i++) { g1[i] = a1 * f1[i] + a2 * f2[i]; m1 += g1[i] * g1[i]; }
+    if (m1 > 1e-24) {   // (OpenCV would draw another vector if the projection vanished; that needs a 1e-12 coincidence)
+      m1 = 1.0 / sqrt(m1);
+      for (int i = 0; i < 9; i++) { g1[i] *= m1; g2[i] = b1 * f1[i] + b2 * f2[i]; }
+      for (int i = 0; i < 9; i++) d += g1[i] * g2[i];
+      for (int i = 0; i < 9; i++) { g2[i] -= d * g1[i]; m2 += g2[i] * g2[i]; }
+      if (m2 > 1e-24) {
+        m2 = 1.0 / sqrt(m2);
+        for (int i = 0; i < 9; i++) { f1[i] = g1[i]; f2[i] = g2[i] * m2; }
+      }
+    }
+  }
   // F = lambda*f1 + (1-lambda)*f2 ; det F = 0 is a cubic in lambda
   for (int i = 0; i < 9; i++) f1[i] -= f2[i];
   double c[4], t0, t1, t2;
@@ -241,6 +295,22 @@ UVIO_HD int seven_point(const double *x0, const double *y0, const double *x1, co
       F[8] = 0.;
     }
     for (int i = 0; i < 8; i++) F[i] = f1[i] * lambda + f2[i] * mu;
+    // back to the caller's coordinates: F <- T1^T F T0 with T = [s 0 -s*cx; 0 s -s*cy; 0 0 1], then F(3,3) = 1
+    double G[9];
+    for (int r = 0; r < 3; r++) {   // G = F * T0
+      G[3 * r + 0] = F[3 * r + 0] * scale0;
+      G[3 * r + 1] = F[3 * r + 1] * scale0;
+      G[3 * r + 2] = F[3 * r + 2] - (F[3 * r + 0] * c0x + F[3 * r + 1] * c0y) * scale0;
+    }
+    for (int c = 0; c < 3; c++) {   // F = T1^T * G
+      F[0 + c] = G[0 + c] * scale1;
+      F[3 + c] = G[3 + c] * scale1;
+      F[6 + c] = G[6 + c] - (G[0 + c] * c1x + G[3 + c] * c1y) * scale1;
+    }
+    if (fabs(F[8]) > FLT_EPSILON) {
+      double inv = 1. / F[8];
+      for (int i = 0; i < 9; i++) F[i] *= inv;
+    }
   }
   return n;
 }

@@ -156,7 +156,31 @@ class FeatureDatabase:
                 if not any(t and t[-1] > timestamp for t in f.timestamps.values())]
 
 
-def _as_u8(a: np.ndarray) -> np.ndarray:
+class DeviceImage:
+    """A CV_8UC1 image that already lives in device memory (consumed in place by the tracker, no copy): raw pointer, size
+    and row stride in bytes.  ``DeviceImage.of(x)`` wraps anything with ``__cuda_array_interface__`` (a torch CUDA tensor)."""
+
+    def __init__(self, ptr: int, height: int, width: int, stride: int, owner=None):
+        self.ptr, self.shape, self.strides, self.owner = int(ptr), (int(height), int(width)), (int(stride), 1), owner
+        self.ctypes = type("_P", (), {"data": int(ptr)})()
+
+    @staticmethod
+    def of(x) -> "DeviceImage":
+        ai = x.__cuda_array_interface__
+        if ai["typestr"] not in ("|u1", "<u1") or len(ai["shape"]) != 2:
+            raise TypeError("device images must be 2-D uint8")
+        h, w = ai["shape"]
+        st = ai.get("strides") or (w, 1)
+        if st[1] != 1:
+            raise TypeError("device images must have unit pixel stride")
+        return DeviceImage(ai["data"][0], h, w, st[0], owner=x)
+
+
+def _as_u8(a):
+    if isinstance(a, DeviceImage):
+        return a
+    if hasattr(a, "__cuda_array_interface__"):
+        return DeviceImage.of(a)
     if a.dtype != np.uint8 or a.ndim != 2:
         raise TypeError("images / masks must be 2-D uint8 arrays (CV_8UC1)")
     if a.strides[1] != 1:
