@@ -981,7 +981,7 @@ int Pass::stage0() {
   ctx->prof_begin();
   g_prof = ctx->prof_on ? &ctx->prof : nullptr;
   // ---- host bookkeeping of the new messages: frame slots, masks, pre-processing jobs, units ---------------------------------
-  int nimg = 0, any_clahe = 0;
+  int nimg = 0, any_clahe = 0, max_band = 0;
   for (int i = 0; i < n; i++) nimg += reqs[i]->n;
   CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
   npre = 0;
@@ -994,6 +994,7 @@ int Pass::stage0() {
       c.cur ^= 1;
       c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
       ctx->pre_jobs.h[npre++] = PreJob{dev->raw_tab[c.raw], c.pyr[c.cur], P.histogram_method};   // src is settled below
+      max_band = std::max(max_band, ((c.h + 7) / 8 + 1) * c.w);
       any_clahe |= P.histogram_method == 2;
     }
     // units (TrackKLT.cpp:80-93)
@@ -1115,7 +1116,7 @@ int Pass::stage0() {
   }
   {
     HOSTPROF(s0_launch_preprocess);
-    CU_TRY(launch_preprocess(ctx->up_stream, ctx->pre_jobs.d, npre, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe));
+    CU_TRY(launch_preprocess(ctx->up_stream, ctx->pre_jobs.d, npre, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe, max_band));
     CU_TRY(cudaEventRecord(ctx->up_done, ctx->up_stream));
   }
   ctx->stats[1] += (npre > 0) ? (unsigned)(1 + 2 * any_clahe) : 0u;

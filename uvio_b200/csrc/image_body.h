@@ -226,19 +226,28 @@ UVIO_HD uint32_t pyr_vsum(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, ui
 // the lane's source columns 2*ox0 .. 2*ox0+11 lie inside the frame and rows are word-aligned, so the loads carry no
 // branches and the compiler can issue all of them up front (the two reflected pixels left of column 0 are taken from
 // the first word in registers).  Only the lanes at the right border of the frame take the general path.
-template <bool INTERIOR>
+template <bool INTERIOR, bool ONCE>
 UVIO_HD void pyrdown_strip_t(const ImgView &I, uint8_t *UVIO_RESTRICT dst, int dw, int dh, int dpitch, int ox0, int oy0) {
   constexpr int NR = 2 * PD_ROWS + 3;
   const int sx = 2 * ox0, sy = 2 * oy0 - 2;
   uint32_t a[NR], c[NR];   // columns (0,1) in a, (2,3) in c
 #pragma unroll
   for (int r = 0; r < NR; r++) {
-    const uint8_t *UVIO_RESTRICT row = I.p + (size_t)(INTERIOR ? reflect101_once(sy + r, I.h) : reflect101(sy + r, I.h)) * I.pitch;
+    const uint8_t *UVIO_RESTRICT row = I.p + (size_t)((INTERIOR || ONCE) ? reflect101_once(sy + r, I.h) : reflect101(sy + r, I.h)) * I.pitch;
     uint32_t wm, w0, w1, wp;
     if (INTERIOR) {
       const uint32_t *q = (const uint32_t *)(row + sx);
       w0 = q[0]; w1 = q[1]; wp = q[2];
       wm = sx ? q[-1] : ((w0 & 0x00ff0000u) | ((w0 & 0x0000ff00u) << 16));   // pixels -2,-1 mirror pixels 2,1
+    } else if (ONCE) {
+      // right border (or an unaligned image): the 11 source pixels one by one, reflected without branches
+      uint32_t px[11];
+#pragma unroll
+      for (int k = 0; k < 11; k++) px[k] = row[reflect101_once(sx - 2 + k, I.w)];
+      wm = (px[0] << 16) | (px[1] << 24);
+      w0 = px[2] | (px[3] << 8) | (px[4] << 16) | (px[5] << 24);
+      w1 = px[6] | (px[7] << 8) | (px[8] << 16) | (px[9] << 24);
+      wp = px[10];
     } else {
       const bool al = ((I.pitch & 3) == 0) && ((((size_t)I.p) & 3) == 0);
       wm = pyr_src_word(row, sx - 4, I.w, al); w0 = pyr_src_word(row, sx, I.w, al);
@@ -263,8 +272,12 @@ UVIO_HD void pyrdown_strip_t(const ImgView &I, uint8_t *UVIO_RESTRICT dst, int d
 UVIO_HD void pyrdown_strip(const ImgView &I, uint8_t *dst, int dw, int dh, int dpitch, int ox0, int oy0) {
   if (ox0 >= dw || oy0 >= dh) return;
   const bool aligned = ((I.pitch & 3) == 0) && ((((size_t)I.p) & 3) == 0);
-  if (aligned && 2 * ox0 + 12 <= I.w && I.h >= 4) pyrdown_strip_t<true>(I, dst, dw, dh, dpitch, ox0, oy0);
-  else pyrdown_strip_t<false>(I, dst, dw, dh, dpitch, ox0, oy0);
+  // a strip reads source rows 2*oy0-2 .. 2*oy0+2*PD_ROWS and columns 2*ox0-2 .. 2*ox0+8 whether or not all of its outputs exist:
+  // one reflection covers them when the image is at least 2*PD_ROWS+8 = 16 high / wide (every pyramid source level is)
+  constexpr int MIN_ONCE = 2 * PD_ROWS + 8;
+  if (aligned && 2 * ox0 + 12 <= I.w && I.h >= MIN_ONCE) pyrdown_strip_t<true, false>(I, dst, dw, dh, dpitch, ox0, oy0);
+  else if (I.w >= MIN_ONCE && I.h >= MIN_ONCE) pyrdown_strip_t<false, true>(I, dst, dw, dh, dpitch, ox0, oy0);
+  else pyrdown_strip_t<false, false>(I, dst, dw, dh, dpitch, ox0, oy0);
 }
 
 // Last pyramid level cv::buildOpticalFlowPyramid creates: it stops before a level that is <= the LK window.

@@ -24,24 +24,82 @@ namespace uvio {
 // barriers instead of kernel boundaries, and the partial histograms are combined through distributed shared memory.
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int PRE_CLUSTER = 8;      // blocks per image (portable maximum)
-constexpr int PRE_THREADS = 512;
+#ifndef UVIO_PRE_THREADS
+#define UVIO_PRE_THREADS 512
+#endif
+constexpr int PRE_THREADS = UVIO_PRE_THREADS;
 constexpr int PRE_NSUB = 8;         // private histograms per block (two warps share one)
+constexpr int PRE_MAX_BAND_BYTES = 96 * 1024;   // largest band of rows a block stages in shared memory (2 blocks/SM stay resident)
 
-__global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREADS, 2)
-    k_preprocess(const PreJob *jobs, const PyrDesc *pyr_tab) {
+// ---- TMA (bulk asynchronous copy) helpers: global -> shared, completion counted in bytes on an mbarrier ----------------
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // make the initialised barrier visible to the async proxy
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src_gmem, unsigned bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE_%=;\n"
+      "bra WAIT_LOOP_%=;\n"
+      "WAIT_DONE_%=:\n"
+      "}\n" ::"r"(smem_addr(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+__global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS)
+    k_preprocess(const PreJob *jobs, const PyrDesc *pyr_tab, int band_bytes) {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
   const PreJob job = jobs[blockIdx.y];
-  const ImgView I = job.src;
+  ImgView I = job.src;
   const PyrDesc &P = pyr_tab[job.pyr];
   const ImgView D0 = P.lv[0];
+  extern __shared__ __align__(128) uint8_t band[];   // this block's rows of the frame, staged by TMA (band_bytes of them)
+  __shared__ __align__(8) uint64_t band_bar;
   __shared__ unsigned sh[PRE_NSUB * 256];
   __shared__ unsigned bh[256];      // this block's histogram (read by the whole cluster)
   __shared__ unsigned cdf[256];
   __shared__ uint8_t lut[256];
   __shared__ int s_first;
   GroupBlock g;
-  const int r0 = (int)((long long)I.h * rank / PRE_CLUSTER), r1 = (int)((long long)I.h * (rank + 1) / PRE_CLUSTER);
+  int r0 = (int)((long long)I.h * rank / PRE_CLUSTER), r1 = (int)((long long)I.h * (rank + 1) / PRE_CLUSTER);
+  uint8_t *dst0 = (uint8_t *)D0.p;
+  // Stage the band in shared memory with bulk asynchronous copies (one per row, or one for the whole band when the rows are
+  // contiguous): the frame is then read from global memory once for both the histogram and the LUT pass.
+  const bool staged = job.method != 2 && (I.w & 15) == 0 && (I.pitch & 15) == 0 && ((((size_t)I.p) & 15) == 0) &&
+                      (size_t)(r1 - r0) * I.w <= (size_t)band_bytes && r1 > r0;
+  if (staged) {
+    const int rows = r1 - r0;
+    if (threadIdx.x == 0) mbar_init(&band_bar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) mbar_expect_tx(&band_bar, (unsigned)(rows * I.w));
+    __syncthreads();
+    if (I.pitch == I.w) {
+      if (threadIdx.x == 0) tma_load_1d(band, I.p + (size_t)r0 * I.pitch, (unsigned)(rows * I.w), &band_bar);
+    } else {
+      for (int r = threadIdx.x; r < rows; r += PRE_THREADS)
+        tma_load_1d(band + (size_t)r * I.w, I.p + (size_t)(r0 + r) * I.pitch, (unsigned)I.w, &band_bar);
+    }
+    mbar_wait(&band_bar, 0);
+    I = ImgView{band, I.w, rows, I.w};   // from here on "the image" of this block is its staged band
+    dst0 += (size_t)r0 * D0.pitch;
+    r1 = rows;
+    r0 = 0;
+  }
+  const int total_px = job.src.w * job.src.h;
   if (job.method == 1) {   // uniform over the cluster
     for (int k = threadIdx.x; k < PRE_NSUB * 256; k += PRE_THREADS) sh[k] = 0;
     __syncthreads();
@@ -71,7 +129,7 @@ __global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREAD
       __syncthreads();
     }
     if (threadIdx.x < 256) {
-      const int i0 = s_first, total = I.w * I.h;
+      const int i0 = s_first, total = total_px;
       const int h0 = (int)(cdf[i0] - (i0 ? cdf[i0 - 1] : 0));
       uint8_t out;
       if (h0 == total) out = (uint8_t)i0;
@@ -86,7 +144,7 @@ __global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREAD
     lut[threadIdx.x] = (uint8_t)threadIdx.x;
   }
   __syncthreads();
-  if (job.method != 2) lut_rows(g, lut, I, (uint8_t *)D0.p, D0.pitch, r0, r1);   // CLAHE wrote level 0 already
+  if (job.method != 2) lut_rows(g, lut, I, dst0, D0.pitch, r0, r1);   // CLAHE wrote level 0 already
   // pyramid: one lane per 4 x PD_ROWS output strip, the whole cluster per level
   const int gtid = rank * PRE_THREADS + threadIdx.x;
   for (int l = 1; l < P.nlv; l++) {
@@ -132,8 +190,18 @@ __global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const P
 }
 
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const PyrDesc *pyr_tab,
-                              uint8_t *clahe_lut, int any_clahe) {
+                              uint8_t *clahe_lut, int any_clahe, int max_band_bytes) {
   if (njobs <= 0) return cudaSuccess;
+  // dynamic shared memory for the staged band of rows (0 = bands too large: the kernel reads global memory directly)
+  int band_bytes = max_band_bytes <= PRE_MAX_BAND_BYTES ? (max_band_bytes + 127) / 128 * 128 : 0;
+  static thread_local int attr_set_for_device = -1;
+  int device = 0;
+  cudaGetDevice(&device);
+  if (attr_set_for_device != device) {
+    cudaError_t e = cudaFuncSetAttribute(k_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_MAX_BAND_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set_for_device = device;
+  }
   if (any_clahe) {
     prof_mark(st, K_CLAHE_TILES);
     k_clahe_tiles<<<dim3(CLAHE_TILES * CLAHE_TILES, njobs), 256, 0, st>>>(jobs, clahe_lut);
@@ -141,7 +209,7 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
     k_clahe_apply<<<dim3(HIST_BANDS * 2, njobs), 256, 0, st>>>(jobs, pyr_tab, clahe_lut);
   }
   prof_mark(st, K_PREPROCESS);
-  k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, 0, st>>>(jobs, pyr_tab);
+  k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, band_bytes, st>>>(jobs, pyr_tab, band_bytes);
   prof_mark(st, -1);
   return cudaGetLastError();
 }

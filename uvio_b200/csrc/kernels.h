@@ -60,7 +60,8 @@ inline void prof_mark(cudaStream_t st, int kernel_id) {
 
 // ---- image-wide passes ------------------------------------------------------------------------------------------------
 // equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels: one cluster launch
-cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const PyrDesc *pyr_tab_dev, uint8_t *clahe_lut_dev /*njobs*64*256, CLAHE only*/, int any_clahe);
+cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const PyrDesc *pyr_tab_dev, uint8_t *clahe_lut_dev /*njobs*64*256, CLAHE only*/, int any_clahe,
+                              int max_band_bytes /* max over the jobs of (ceil(h/8)+1) * w: the rows one block stages by TMA */);
 
 // ---- detection ----------------------------------------------------------------------------------------------------------
 // FAST + NMS on grid cells; compacts each job's corner list into out_host (mapped pinned) and writes its count.

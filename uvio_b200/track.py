@@ -19,7 +19,7 @@ from typing import Dict, List, Sequence, Tuple
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libuvio_klt.so")
+LIB_PATH = os.environ.get("UVIO_KLT_LIB") or os.path.join(_HERE, "libuvio_klt.so")   # the override is for A/B builds of the same library
 
 UVIO_OK, UVIO_E_BADMSG, UVIO_E_CAMID, UVIO_E_CUDA, UVIO_E_ARG, UVIO_E_SIZE = range(6)
 ERR_NAMES = {0: "UVIO_OK", 1: "UVIO_E_BADMSG", 2: "UVIO_E_CAMID", 3: "UVIO_E_CUDA", 4: "UVIO_E_ARG", 5: "UVIO_E_SIZE"}
