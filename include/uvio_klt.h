@@ -114,8 +114,9 @@ const char *uvio_klt_version(void);
 /* ---- measurement helpers (no reference counterpart; the reference stamps wall-clock rT1..rT7, TrackBase.h:195) ------
  * Counters of the device context since its creation: [0] frames fed, [1] kernels launched, [2] image bytes uploaded,
  * [3] bytes the GPU wrote to host memory (corner lists, refined / tracked points, status, masks), [4] feed_batch calls,
- * [5] pixels scanned by FAST, [6] LK point-levels (templates staged), [7] LK iterations. */
-int uvio_klt_device_stats(int cuda_device, unsigned long long out[8]);
+ * [5] pixels scanned by FAST, [6] LK point-levels (templates staged), [7] LK iterations, [8] LK iterations whose mismatch
+ * sums needed the ordered fp32 chains (the others were exact integer reductions), [9..11] reserved (0). */
+int uvio_klt_device_stats(int cuda_device, unsigned long long out[12]);
 /* CUDA-event stopwatch recorded on the stream all kernels of that device's trackers are launched on. */
 int uvio_klt_timer_start(int cuda_device);
 int uvio_klt_timer_stop(int cuda_device, float *ms);

@@ -101,7 +101,7 @@ cudaError_t launch_lk(cudaStream_t, const LkItem *items, int n, const PyrDesc *p
   return 0;
 }
 
-cudaError_t read_lk_work(unsigned long long out[3], int) { out[0] = out[1] = out[2] = 0; return 0; }
+cudaError_t read_lk_work(unsigned long long out[4], int) { out[0] = out[1] = out[2] = out[3] = 0; return 0; }
 
 cudaError_t launch_ransac(cudaStream_t, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk,
                           const uint8_t *status, const CamModel *cams, float *p0n, float *p1n, float *p1n_host, uint8_t *mask_host,

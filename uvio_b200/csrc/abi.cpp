@@ -200,7 +200,7 @@ int uvio_klt_last_error(uvio_klt *h) { return h ? h->rig->last_error : UVIO_E_AR
 int uvio_klt_cuda_error(uvio_klt *h) { return h ? context_cuda_error(h->rig->ctx) : 0; }
 const char *uvio_klt_version(void) { return "uvio_klt 0.1 (sm_100a)"; }
 
-int uvio_klt_device_stats(int cuda_device, unsigned long long out[8]) {
+int uvio_klt_device_stats(int cuda_device, unsigned long long out[12]) {
   if (!out) return UVIO_E_ARG;
   int err = 0;
   Context *ctx = context_for_device(cuda_device, &err);

@@ -1544,13 +1544,15 @@ int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long 
   return OK;
 }
 
-void context_stats(Context *ctx, unsigned long long out[8]) {
+void context_stats(Context *ctx, unsigned long long out[12]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
   memcpy(out, ctx->stats, sizeof(ctx->stats));
-  unsigned long long w[3] = {0, 0, 0};
+  out[8] = out[9] = out[10] = out[11] = 0;
+  unsigned long long w[4] = {0, 0, 0, 0};
   if (cudaSetDevice(ctx->device) == cudaSuccess && read_lk_work(w, 0) == cudaSuccess) {
     out[6] = w[0];   // LK point-levels
     out[7] = w[1];   // LK iterations
+    out[8] = w[3];   // ... of which ran the ordered fp32 chains
   }
 }
 

@@ -103,7 +103,7 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n);
 
 Context *context_for_device(int device, int *err);
 int context_cuda_error(Context *ctx);
-void context_stats(Context *ctx, unsigned long long out[8]);
+void context_stats(Context *ctx, unsigned long long out[12]);
 int context_timer(Context *ctx, int stop, float *ms);
 void context_host_profile(Context *ctx, int reset, double us[8]);
 int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long long launches[K_COUNT]);

@@ -311,14 +311,20 @@ cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------------------------------
 // pyramidal LK: one warp per feature, all levels inside the kernel
 // ---------------------------------------------------------------------------------------------------------------------
-// work counters for the roofline arithmetic: [0] templates staged (point-levels), [1] iterations, [2] points
+// work counters for the roofline arithmetic: [0] templates staged (point-levels), [1] iterations, [2] points,
+// [3] iterations whose mismatch sums ran as ordered fp32 chains (the others took the exact integer reduction)
 constexpr int LK_WORK_SLOTS = 64;   // the counters are spread over slots so that the atomics of one launch do not queue up
 __device__ unsigned long long g_lk_work[LK_WORK_SLOTS][4];
 
 // one warp per block: features differ a lot in iteration count, and single-warp blocks let the SM refill warp by warp
 constexpr int LK_WARPS_PER_BLOCK = 1;
 
-__global__ void __launch_bounds__(LK_WARPS_PER_BLOCK * 32) k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
+#ifdef UVIO_LK_MIN_BLOCKS
+#define LK_BOUNDS __launch_bounds__(LK_WARPS_PER_BLOCK * 32, UVIO_LK_MIN_BLOCKS)
+#else
+#define LK_BOUNDS __launch_bounds__(LK_WARPS_PER_BLOCK * 32)
+#endif
+__global__ void LK_BOUNDS k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
                                                              const float *init_from_dev, int max_count, double eps_sq,
                                                              LkOut *out_host, uint8_t *status_host, LkOut *out_dev,
                                                              uint8_t *status_dev) {
@@ -338,13 +344,14 @@ __global__ void __launch_bounds__(LK_WARPS_PER_BLOCK * 32) k_lk(const LkItem *it
   prm.eps_sq = eps_sq;
   prm.min_eig = 1e-4;
   uint8_t status;
-  int work[2] = {0, 0};
+  int work[3] = {0, 0, 0};
   lk_track_point(GroupWarp(), sm[wid], P0.lv, P1.lv, prm, px, py, nx, ny, status, work);
   if ((threadIdx.x & 31) == 0) {
     unsigned long long *wk = g_lk_work[blockIdx.x % LK_WORK_SLOTS];
     atomicAdd(&wk[0], (unsigned long long)work[0]);
     atomicAdd(&wk[1], (unsigned long long)work[1]);
     atomicAdd(&wk[2], 1ull);
+    if (work[2]) atomicAdd(&wk[3], (unsigned long long)work[2]);
     LkOut o{nx, ny};
     out_host[i] = o;
     status_host[i] = status;
@@ -353,12 +360,12 @@ __global__ void __launch_bounds__(LK_WARPS_PER_BLOCK * 32) k_lk(const LkItem *it
   }
 }
 
-cudaError_t read_lk_work(unsigned long long out[3], int reset) {
+cudaError_t read_lk_work(unsigned long long out[4], int reset) {
   unsigned long long h[LK_WORK_SLOTS][4];
   cudaError_t e = cudaMemcpyFromSymbol(h, g_lk_work, sizeof(h));
-  out[0] = out[1] = out[2] = 0;
+  out[0] = out[1] = out[2] = out[3] = 0;
   for (int s = 0; s < LK_WORK_SLOTS; s++)
-    for (int k = 0; k < 3; k++) out[k] += h[s][k];
+    for (int k = 0; k < 4; k++) out[k] += h[s][k];
   if (e == cudaSuccess && reset) {
     memset(h, 0, sizeof(h));
     e = cudaMemcpyToSymbol(g_lk_work, h, sizeof(h));

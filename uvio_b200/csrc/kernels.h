@@ -84,6 +84,6 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
 
 cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st);
 // LK work counters since the last reset: [0] point-levels (templates staged), [1] iterations, [2] points
-cudaError_t read_lk_work(unsigned long long out[3], int reset);
+cudaError_t read_lk_work(unsigned long long out[4], int reset);
 
 }  // namespace uvio

@@ -230,27 +230,90 @@ UVIO_HD int lk_bilinear(const uint8_t *c, int pitch, int iw00, int iw01, int iw1
 
 // diff = J patch - I patch at integer offset (ox, oy) of the staged window, and the mismatch products.  One lane handles
 // either the two pixels (y,k), (y,k+4) that meet in SIMD lane k of the CPU code, or one pixel of the scalar tail.
+//
+// The products are integers, so the CPU's ordered fp32 sums are EXACT (and therefore order-independent) whenever no
+// partial sum can reach 2^24: every partial sum of a subset of the terms lies in [-NEG, POS] (NEG / POS = the sums of the
+// negative / positive terms).  With max(POS, NEG) < 2^24 the result is fp32(integer sum), which a warp reduction
+// delivers; this holds for ~90 % of the iterations.  Otherwise the products go to shared memory and the ordered chains of
+// lk_accumulate_mismatch run.  Returns true when (b1, b2) (unscaled) were produced here.
 template <class G>
-UVIO_HD void lk_diff_from_window(G g, LkSmem &s, int jx0, int ox, int oy, int iw00, int iw01, int iw10, int iw11) {
+UVIO_HD bool lk_mismatch_products(G g, LkSmem &s, int jx0, int ox, int oy, int iw00, int iw01, int iw10, int iw11, float &b1,
+                                  float &b2) {
   constexpr int JP = LK_JWW * 4;
+  constexpr int NPAIR = LK_WIN * 4;
+  constexpr int RP = (NPAIR + G::SIZE - 1) / G::SIZE, RT = (LK_TAIL + G::SIZE - 1) / G::SIZE;
+  typedef typename G::acc_t acc_t;
   const uint8_t *win = (const uint8_t *)s.jwin + (jx0 - (jx0 & ~3)) + oy * JP + ox;
-  for (int i = g.lane(); i < LK_WIN * 4; i += g.size()) {
-    int y = i >> 2, k = i & 3, e = y * LK_WIN + k;
-    const uint8_t *c = win + y * JP + k;
-    int d0 = lk_bilinear(c, JP, iw00, iw01, iw10, iw11) - s.Iw[e];
-    int d1 = lk_bilinear(c + 4, JP, iw00, iw01, iw10, iw11) - s.Iw[e + 4];
-    Short2 g0 = s.dIw[e], g1 = s.dIw[e + 4];
-    s.psimd[0][i] = (float)(d0 * g0.x + d1 * g1.x);
-    s.psimd[1][i] = (float)(d0 * g0.y + d1 * g1.y);
+  int pa[RP], pb[RP], ta[RT], tb[RT];
+  acc_t sum1 = 0, pos1 = 0, sum2 = 0, pos2 = 0;
+#pragma unroll
+  for (int r = 0; r < RP; r++) {
+    int i = g.lane() + r * G::SIZE;
+    int a = 0, b = 0;
+    if (i < NPAIR) {
+      int y = i >> 2, k = i & 3, e = y * LK_WIN + k;
+      const uint8_t *c = win + y * JP + k;
+      int d0 = lk_bilinear(c, JP, iw00, iw01, iw10, iw11) - s.Iw[e];
+      int d1 = lk_bilinear(c + 4, JP, iw00, iw01, iw10, iw11) - s.Iw[e + 4];
+      Short2 g0 = s.dIw[e], g1 = s.dIw[e + 4];
+      a = d0 * g0.x + d1 * g1.x;
+      b = d0 * g0.y + d1 * g1.y;
+    }
+    pa[r] = a;
+    pb[r] = b;
+    sum1 += a;
+    pos1 += a > 0 ? a : 0;
+    sum2 += b;
+    pos2 += b > 0 ? b : 0;
   }
-  for (int t = g.lane(); t < LK_TAIL; t += g.size()) {
-    int y = t / 7, x = 8 + t - 7 * y, e = y * LK_WIN + x;
-    int d = lk_bilinear(win + y * JP + x, JP, iw00, iw01, iw10, iw11) - s.Iw[e];
-    Short2 gd = s.dIw[e];
-    s.ptail[0][t] = (float)(d * gd.x);
-    s.ptail[1][t] = (float)(d * gd.y);
+#pragma unroll
+  for (int r = 0; r < RT; r++) {
+    int t = g.lane() + r * G::SIZE;
+    int a = 0, b = 0;
+    if (t < LK_TAIL) {
+      int y = t / 7, x = 8 + t - 7 * y, e = y * LK_WIN + x;
+      int d = lk_bilinear(win + y * JP + x, JP, iw00, iw01, iw10, iw11) - s.Iw[e];
+      Short2 gd = s.dIw[e];
+      a = d * gd.x;
+      b = d * gd.y;
+    }
+    ta[r] = a;
+    tb[r] = b;
+    sum1 += a;
+    pos1 += a > 0 ? a : 0;
+    sum2 += b;
+    pos2 += b > 0 ? b : 0;
+  }
+  // |term| <= 2 * 8160 * 4080 and a lane of a warp owns at most 6 terms: the int accumulators cannot overflow
+  const acc_t LIM = (acc_t)1 << 24;
+  acc_t neg1 = pos1 - sum1, neg2 = pos2 - sum2;
+  unsigned P1 = g.reduce_add((unsigned)(pos1 < LIM ? pos1 : LIM)), N1 = g.reduce_add((unsigned)(neg1 < LIM ? neg1 : LIM));
+  unsigned P2 = g.reduce_add((unsigned)(pos2 < LIM ? pos2 : LIM)), N2 = g.reduce_add((unsigned)(neg2 < LIM ? neg2 : LIM));
+  unsigned worst = P1 > N1 ? P1 : N1, w2 = P2 > N2 ? P2 : N2;
+  worst = worst > w2 ? worst : w2;
+  if (worst < (unsigned)LIM) {
+    b1 = (float)((int)P1 - (int)N1);
+    b2 = (float)((int)P2 - (int)N2);
+    return true;
+  }
+#pragma unroll
+  for (int r = 0; r < RP; r++) {
+    int i = g.lane() + r * G::SIZE;
+    if (i < NPAIR) {
+      s.psimd[0][i] = (float)pa[r];
+      s.psimd[1][i] = (float)pb[r];
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < RT; r++) {
+    int t = g.lane() + r * G::SIZE;
+    if (t < LK_TAIL) {
+      s.ptail[0][t] = (float)ta[r];
+      s.ptail[1][t] = (float)tb[r];
+    }
   }
   g.sync();
+  return false;
 }
 
 UVIO_HD void lk_weights(float a, float b, int &iw00, int &iw01, int &iw10, int &iw11) {
@@ -326,12 +389,17 @@ UVIO_HD void lk_track_point(G g, LkSmem &s, const ImgView *prev, const ImgView *
         lk_stage_window(g, s, J, jx0, jy0);
         have_window = true;
       }
-      lk_diff_from_window(g, s, jx0, inx - jx0, iny - jy0, iw00, iw01, iw10, iw11);
+      float b1, b2;
       if (work) work[1]++;   // iterations
-      lk_accumulate_mismatch(g, s);
-      float b1 = fmul(lk_fold(s.red + 0), FLT_SCALE);
-      float b2 = fmul(lk_fold(s.red + 5), FLT_SCALE);
-      g.sync();
+      if (!lk_mismatch_products(g, s, jx0, inx - jx0, iny - jy0, iw00, iw01, iw10, iw11, b1, b2)) {
+        if (work) work[2]++;   // iterations that needed the ordered chains
+        lk_accumulate_mismatch(g, s);
+        b1 = lk_fold(s.red + 0);
+        b2 = lk_fold(s.red + 5);
+        g.sync();
+      }
+      b1 = fmul(b1, FLT_SCALE);
+      b2 = fmul(b2, FLT_SCALE);
       float dx = fmul(fsub(fmul(A12, b2), fmul(A22, b1)), D);
       float dy = fmul(fsub(fmul(A12, b1), fmul(A11, b2)), D);
       npx = fadd(npx, dx);

@@ -24,6 +24,9 @@ struct GroupSeq {
   UVIO_HD int lane() const { return 0; }
   UVIO_HD int size() const { return 1; }
   UVIO_HD void sync() const {}
+  static constexpr int SIZE = 1;                        // compile-time size, for per-lane register arrays
+  typedef long long acc_t;                              // wide enough for one lane's share of an integer sum
+  UVIO_HD unsigned reduce_add(unsigned v) const { return v; }
 };
 
 #ifdef __CUDACC__
@@ -31,6 +34,9 @@ struct GroupWarp {
   __device__ __forceinline__ int lane() const { return threadIdx.x & 31; }
   __device__ __forceinline__ int size() const { return 32; }
   __device__ __forceinline__ void sync() const { __syncwarp(); }
+  static constexpr int SIZE = 32;
+  typedef int acc_t;
+  __device__ __forceinline__ unsigned reduce_add(unsigned v) const { return __reduce_add_sync(0xffffffffu, v); }   // REDUX
 };
 struct GroupBlock {
   __device__ __forceinline__ int lane() const { return threadIdx.x; }

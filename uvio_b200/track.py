@@ -407,12 +407,12 @@ KERNEL_NAMES = ["k_hist", "k_lut_apply", "k_clahe_tiles", "k_clahe_apply", "k_py
 
 
 def device_stats(device: int = 0) -> dict:
-    out = (C.c_ulonglong * 8)()
+    out = (C.c_ulonglong * 12)()
     rc = lib().uvio_klt_device_stats(device, out)
     if rc != UVIO_OK:
         raise UvioError(rc, "uvio_klt_device_stats")
     return {"frames": out[0], "launches": out[1], "h2d_bytes": out[2], "d2h_bytes": out[3], "feed_calls": out[4],
-            "fast_pixels": out[5], "lk_point_levels": out[6], "lk_iterations": out[7]}
+            "fast_pixels": out[5], "lk_point_levels": out[6], "lk_iterations": out[7], "lk_chain_iterations": out[8]}
 
 
 def profile(device: int = 0, enable: int = -1) -> dict:
