@@ -50,6 +50,11 @@ typedef struct UvioKltParams {
   int win_size;         /* TrackKLT.h:144 hard-codes 15; only 15 is supported */
   int lk_max_iters;     /* TrackKLT.cpp:670,857: 30 */
   double lk_eps;        /* TrackKLT.cpp:670,857: 0.01 */
+  /* VioManagerOptions.h:409 downsample_cameras.  Non-zero: every fed image and mask is halved on the device with
+   * cv::pyrDown(src, dst, Size(cols / 2.0, rows / 2.0)) before the tracker sees it, which is what
+   * VioManager::track_image_and_update does in front of trackFEATS->feed_new_camera (ov_msckf/src/core/VioManager.cpp:268-278);
+   * the caller then feeds the full-size message and passes the already halved intrinsics (VioManagerOptions.h:251-260). */
+  int downsample_cameras;
 } UvioKltParams;
 
 /* One entry of the camera_calib map given to the TrackBase ctor (TrackBase.h:96, cam/CamBase.h). */

@@ -623,6 +623,21 @@ class TrackKLTOracle:
         return kpts0, kpts1, mask_out
 
 
+
+def downsample_message(images: Sequence[np.ndarray], masks: Sequence[np.ndarray]):
+    """The step VioManager::track_image_and_update runs on every message just before trackFEATS->feed_new_camera when
+    params.downsample_cameras is set (ov_msckf/src/core/VioManager.cpp:268-278): cv::pyrDown of each image and of each
+    mask to cv::Size(cols / 2.0, rows / 2.0) (doubles truncated by the cv::Size(int, int) constructor, so an odd
+    dimension loses its last row / column instead of rounding up as pyrDown's default size would).  The camera
+    intrinsics handed to the tracker are halved where the options are parsed (VioManagerOptions.h:251-260)."""
+    out_i, out_m = [], []
+    for img, mask in zip(images, masks):
+        rows, cols = img.shape[:2]
+        out_i.append(cv2.pyrDown(img, dstsize=(int(cols / 2.0), int(rows / 2.0))))
+        rows, cols = mask.shape[:2]
+        out_m.append(cv2.pyrDown(mask, dstsize=(int(cols / 2.0), int(rows / 2.0))))
+    return out_i, out_m
+
 def make_oracle(cfg, **over) -> "TrackKLTOracle":
     """Build an oracle tracker from a uvio_b200.configs.TrackerConfig-shaped object (duck-typed: no product import)."""
     cams = {i: Cam(c.model, tuple(c.intrinsics), tuple(c.dist)) for i, c in enumerate(cfg.cams)}

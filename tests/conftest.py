@@ -33,3 +33,32 @@ def pytest_collection_modifyitems(config, items):
 def built_lib():
     from uvio_b200 import build
     return build.build()
+
+
+# ---- host simulation (test scaffolding): the engine + ABI over CPU stand-ins of the launch wrappers ----------------------------
+HERE = os.path.dirname(os.path.abspath(__file__))
+SIM = os.path.join(HERE, "hostsim")
+SIM_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno-unknown-pragmas"]
+
+
+def sim_build(out, srcs, extra=()):
+    import subprocess
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    deps = srcs + [os.path.join(ROOT, "uvio_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "uvio_b200", "csrc"))]
+    deps += [os.path.join(SIM, f) for f in os.listdir(SIM) if f.endswith((".cpp", ".h"))]
+    if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
+        subprocess.check_call(["g++"] + SIM_FLAGS + list(extra) + ["-o", out] + srcs + ["-lpthread"])
+    return out
+
+
+@pytest.fixture()
+def sim_tracker(monkeypatch):
+    """make(cfg, **kw) -> tracker running engine.cpp + abi.cpp over tests/hostsim/launch_sim.cpp (no GPU, never the product)."""
+    from uvio_b200 import track
+    csrc = os.path.join(ROOT, "uvio_b200", "csrc")
+    lib = sim_build(os.path.join(SIM, "_sim", "libuvio_klt_sim.so"),
+                    [os.path.join(csrc, "engine.cpp"), os.path.join(csrc, "abi.cpp"), os.path.join(SIM, "launch_sim.cpp")], ["-I", SIM])
+    monkeypatch.setattr(track, "LIB_PATH", lib)
+    monkeypatch.setattr(track, "_lib", None)
+    yield lambda cfg, **kw: track.make_tracker(cfg, **kw)
+    monkeypatch.setattr(track, "_lib", None)

@@ -42,6 +42,15 @@ cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const
   return 0;
 }
 
+cudaError_t launch_downsample(cudaStream_t, const DownJob *jobs, int njobs, int, int) {
+  for (int j = 0; j < njobs; j++) {
+    const ImgView S = jobs[j].src, D = jobs[j].dst;
+    for (int oy = 0; oy < D.h; oy += PD_ROWS)
+      for (int ox = 0; ox < D.w; ox += PD_COLS) pyrdown_strip(S, (uint8_t *)D.p, D.w, D.h, D.pitch, ox, oy);
+  }
+  return 0;
+}
+
 cudaError_t launch_fast(cudaStream_t, const FastJob *jobs, int njobs, int, int, const PyrDesc *pyr_tab,
                         uint32_t *, unsigned *, unsigned *, uint32_t *out_host, unsigned *count_host) {
   GroupSeq g;

@@ -21,28 +21,12 @@ SIM = os.path.join(HERE, "hostsim")
 FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno-unknown-pragmas"]
 
 
-def _build(out, srcs, extra=()):
-    os.makedirs(os.path.dirname(out), exist_ok=True)
-    deps = srcs + [os.path.join(ROOT, "uvio_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "uvio_b200", "csrc"))]
-    if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
-        subprocess.check_call(["g++"] + FLAGS + list(extra) + ["-o", out] + srcs + ["-lpthread"])
-    return out
+from conftest import sim_build as _build
 
 
 @pytest.fixture(scope="module")
 def bodies():
     return ctypes.CDLL(_build(os.path.join(SIM, "_sim", "libbodies.so"), [os.path.join(SIM, "hostsim.cpp")], ["-I", SIM]))
-
-
-@pytest.fixture()
-def sim_tracker(monkeypatch):
-    csrc = os.path.join(ROOT, "uvio_b200", "csrc")
-    lib = _build(os.path.join(SIM, "_sim", "libuvio_klt_sim.so"),
-                 [os.path.join(csrc, "engine.cpp"), os.path.join(csrc, "abi.cpp"), os.path.join(SIM, "launch_sim.cpp")], ["-I", SIM])
-    monkeypatch.setattr(track, "LIB_PATH", lib)
-    monkeypatch.setattr(track, "_lib", None)
-    yield lambda cfg: track.make_tracker(cfg)
-    monkeypatch.setattr(track, "_lib", None)
 
 
 def _p(a):

@@ -39,9 +39,11 @@ public:
   typedef KeyPointMirror KeyPointT;
 #endif
 
-  // same argument list as TrackKLT::TrackKLT (TrackKLT.h:54-57); cuda_device is the only addition
+  // same argument list as TrackKLT::TrackKLT (TrackKLT.h:54-57); cuda_device and downsample_cameras are the only additions.
+  // downsample_cameras = params.downsample_cameras (VioManagerOptions.h:409): the tracker then takes the FULL-size message
+  // and halves images and masks on the device, so the caller drops its cv::pyrDown loop (VioManager.cpp:268-278).
   explicit TrackKLTGpu(CamMap cameras, int numfeats, int numaruco, bool stereo, HistogramMethod histmethod, int fast_threshold,
-                       int gridx, int gridy, int minpxdist, int cuda_device = 0)
+                       int gridx, int gridy, int minpxdist, int cuda_device = 0, bool downsample_cameras = false)
       : TrackBase(cameras, numfeats, numaruco, stereo, histmethod) {
     UvioKltParams p;
     uvio_klt_default_params(&p);
@@ -53,6 +55,7 @@ public:
     p.grid_x = gridx;
     p.grid_y = gridy;
     p.min_px_dist = minpxdist;
+    p.downsample_cameras = downsample_cameras ? 1 : 0;
     std::vector<UvioCamCalib> cc;
     for (auto const &kv : cameras) {
       UvioCamCalib c;

@@ -40,6 +40,7 @@ void uvio_klt_default_params(UvioKltParams *p) {
   p->win_size = 15;
   p->lk_max_iters = 30;
   p->lk_eps = 0.01;
+  p->downsample_cameras = 0;
 }
 
 int uvio_klt_create(const UvioKltParams *p, const UvioCamCalib *cams, int n_cams, int cuda_device, uvio_klt **out) {
@@ -65,6 +66,7 @@ int uvio_klt_create(const UvioKltParams *p, const UvioCamCalib *cams, int n_cams
   q.win_size = p->win_size;
   q.lk_max_iters = p->lk_max_iters;
   q.lk_eps = p->lk_eps;
+  q.downsample_cameras = p->downsample_cameras != 0;
   std::vector<CamCalib> cc(n_cams);
   for (int i = 0; i < n_cams; i++) {
     if (cams[i].model != UVIO_CAM_RADTAN && cams[i].model != UVIO_CAM_EQUI) return UVIO_E_ARG;

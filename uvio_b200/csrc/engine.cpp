@@ -207,6 +207,10 @@ struct Lane {
     prof.n = 0;
   }
   // round 1
+  JobVec<DownJob> down_jobs;     // downsample_cameras: frames (upload stream)
+  JobVec<DownJob> mask_jobs;     // ... and non-zero masks (main stream, finished before the host bookkeeping starts)
+  DevVec<uint8_t> mask_in;       // the full-size masks of this feed
+  MappedVec<uint8_t> mask_out;   // their halved versions, written by the kernel into host memory
   JobVec<PreJob> pre_jobs;
   DevVec<uint8_t> clahe_lut;
   JobVec<FastJob> fast_jobs;
@@ -280,15 +284,20 @@ class Context {
     tables_dirty = false;
     return OK;
   }
-  // device memory for one camera: a raw upload buffer and two pyramids
-  int alloc_camera(CamState &c, int w, int h, int pyr_levels, int win) {
+  // device memory for one camera: a raw upload buffer and two pyramids (plus the halved frame with downsample_cameras)
+  int alloc_camera(CamState &c, int in_w, int in_h, int pyr_levels, int win, bool downsample) {
     Context *ctx = this;
+    // cv::Size(cols / 2.0, rows / 2.0): the doubles are truncated (VioManager.cpp:274,276)
+    const int w = downsample ? in_w / 2 : in_w, h = downsample ? in_h / 2 : in_h;
+    if (w < 1 || h < 1) return E_ARG;
     const int L = pyr_max_level(w, h, pyr_levels, win);
     if (L + 1 > MAX_LEVELS) return E_ARG;
     auto pitch_of = [](int ww) { return (ww + 127) / 128 * 128; };
     // the upload buffer keeps the rows as tight as 16-byte loads allow, so that a tightly packed host frame is one 1-D copy
-    const int raw_pitch = (w + 15) / 16 * 16;
-    size_t raw_bytes = ((size_t)raw_pitch * h + 255) / 256 * 256, pyr_bytes = 0;
+    const int raw_pitch = (in_w + 15) / 16 * 16;
+    size_t raw_bytes = ((size_t)raw_pitch * in_h + 255) / 256 * 256, pyr_bytes = 0;
+    const int half_pitch = (w + 15) / 16 * 16;
+    const size_t half_bytes = downsample ? ((size_t)half_pitch * h + 255) / 256 * 256 : 0;
     int lw = w, lh = h;
     for (int l = 0; l <= L; l++) {
       pyr_bytes += (size_t)pitch_of(lw) * lh;
@@ -308,14 +317,22 @@ class Context {
     raw_arena += raw_bytes;
     raw_arena_left -= raw_bytes;
     uint8_t *base = nullptr;
-    CU_TRY(cudaMalloc((void **)&base, 2 * pyr_bytes + 256));
-    CU_TRY(cudaMemset(base, 0, 2 * pyr_bytes + 256));
+    CU_TRY(cudaMalloc((void **)&base, 2 * pyr_bytes + half_bytes + 256));
+    CU_TRY(cudaMemset(base, 0, 2 * pyr_bytes + half_bytes + 256));
     allocs.push_back(base);
     c.w = w;
     c.h = h;
-    c.raw = (int)raw_tab.size();
-    raw_tab.push_back(ImgView{raw_base, w, h, raw_pitch});
+    c.in_w = in_w;
+    c.in_h = in_h;
+    c.raw_in = (int)raw_tab.size();
+    raw_tab.push_back(ImgView{raw_base, in_w, in_h, raw_pitch});
+    c.raw = c.raw_in;
     uint8_t *p = base;
+    if (downsample) {
+      c.raw = (int)raw_tab.size();
+      raw_tab.push_back(ImgView{p, w, h, half_pitch});
+      p += half_bytes;
+    }
     for (int s = 0; s < 2; s++) {
       PyrDesc d;
       memset(&d, 0, sizeof(d));
@@ -900,8 +917,7 @@ static double now_us() {
 
 // keep a caller mask for the detection of the next feed (TrackKLT.cpp:129,245 detect on img_mask_last); returns whether any
 // pixel is non-zero.  An all-zero mask (the usual case) is only scanned, not copied.
-static bool copy_mask(const HostImage &m, std::vector<uint8_t> &dst, int w, int h) {
-  HOSTPROF(copy_mask);
+static bool mask_any_set(const HostImage &m, int w, int h) {
   if (!m.p) return false;
   bool nz = false;
   for (int y = 0; y < h && !nz; y++) {
@@ -919,7 +935,11 @@ static bool copy_mask(const HostImage &m, std::vector<uint8_t> &dst, int w, int 
     for (; x < w; x++) acc |= r[x];
     nz = acc != 0;
   }
-  if (!nz) return false;
+  return nz;
+}
+static bool copy_mask(const HostImage &m, std::vector<uint8_t> &dst, int w, int h) {
+  HOSTPROF(copy_mask);
+  if (!mask_any_set(m, w, h)) return false;
   for (int y = 0; y < h; y++) memcpy(dst.data() + (size_t)y * w, m.p + (size_t)y * m.stride, (size_t)w);
   return true;
 }
@@ -981,7 +1001,8 @@ int Pass::stage0() {
   ctx->prof_begin();
   g_prof = ctx->prof_on ? &ctx->prof : nullptr;
   // ---- host bookkeeping of the new messages: frame slots, masks, pre-processing jobs, units ---------------------------------
-  int nimg = 0, any_clahe = 0, max_band = 0;
+  int nimg = 0, any_clahe = 0, max_band = 0, n_down_jobs = 0, n_mask_jobs = 0;
+  size_t mask_in_bytes = 0, mask_out_bytes = 0;
   for (int i = 0; i < n; i++) nimg += reqs[i]->n;
   CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
   npre = 0;
@@ -992,7 +1013,13 @@ int Pass::stage0() {
     for (int k = 0; k < rq.n; k++) {
       CamState &c = *rig.find_cam(rq.sensor_ids[k]);
       c.cur ^= 1;
-      c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
+      if (!P.downsample_cameras) c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
+      else if ((c.mask_nonzero[c.cur] = mask_any_set(rq.masks[k], c.in_w, c.in_h))) {   // halved on the device below
+        n_mask_jobs++;
+        mask_in_bytes += (size_t)((c.in_w + 15) / 16 * 16) * c.in_h;
+        mask_out_bytes += (size_t)((c.w + 3) / 4 * 4) * c.h;
+      }
+      n_down_jobs += P.downsample_cameras != 0;
       ctx->pre_jobs.h[npre++] = PreJob{dev->raw_tab[c.raw], c.pyr[c.cur], P.histogram_method};   // src is settled below
       max_band = std::max(max_band, ((c.h + 7) / 8 + 1) * c.w);
       any_clahe |= P.histogram_method == 2;
@@ -1017,6 +1044,51 @@ int Pass::stage0() {
       }
     }
   }
+  if (n_mask_jobs > 0) {
+    // downsample_cameras with masks that mask something: cv::pyrDown of the mask (VioManager.cpp:275-277).  The host
+    // bookkeeping below reads the halved mask (first frames detect on the frame being fed), so this small job runs on the
+    // idle main stream and is waited for; the frames themselves go up on the upload stream meanwhile.
+    CU_TRY(ctx->mask_jobs.reserve((size_t)n_mask_jobs));
+    CU_TRY(ctx->mask_in.reserve(mask_in_bytes));
+    CU_TRY(ctx->mask_out.reserve(mask_out_bytes));
+    size_t in_off = 0, out_off = 0;
+    int nj = 0, max_w = 1, max_h = 1;
+    for (int i = 0; i < n; i++) {
+      FeedRequest &rq = *reqs[i];
+      if (!rq.rig->prm.downsample_cameras) continue;
+      for (int k = 0; k < rq.n; k++) {
+        CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
+        if (!c.mask_nonzero[c.cur]) continue;
+        const int ip = (c.in_w + 15) / 16 * 16, op = (c.w + 3) / 4 * 4;
+        CU_TRY(cudaMemcpy2DAsync(ctx->mask_in.d + in_off, (size_t)ip, rq.masks[k].p, rq.masks[k].stride, (size_t)c.in_w, (size_t)c.in_h,
+                                 cudaMemcpyDefault, ctx->stream));
+        ctx->mask_jobs.h[nj++] = DownJob{ImgView{ctx->mask_in.d + in_off, c.in_w, c.in_h, ip}, ImgView{ctx->mask_out.d + out_off, c.w, c.h, op}};
+        in_off += (size_t)ip * c.in_h;
+        out_off += (size_t)op * c.h;
+        max_w = std::max(max_w, c.w);
+        max_h = std::max(max_h, c.h);
+        ctx->stats[2] += (unsigned long long)c.in_w * c.in_h;
+        ctx->stats[3] += (unsigned long long)c.w * c.h;
+      }
+    }
+    CU_TRY(ctx->mask_jobs.upload(ctx->stream, (size_t)nj));
+    CU_TRY(launch_downsample(ctx->stream, ctx->mask_jobs.d, nj, max_w, max_h));
+    ctx->stats[1] += 1;
+    if (ctx->sync() != OK) return E_CUDA;
+    out_off = 0;
+    for (int i = 0; i < n; i++) {
+      FeedRequest &rq = *reqs[i];
+      if (!rq.rig->prm.downsample_cameras) continue;
+      for (int k = 0; k < rq.n; k++) {
+        CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
+        if (!c.mask_nonzero[c.cur]) continue;
+        const int op = (c.w + 3) / 4 * 4;
+        for (int y = 0; y < c.h; y++) memcpy(c.mask[c.cur].data() + (size_t)y * c.w, ctx->mask_out.h + out_off + (size_t)y * op, (size_t)c.w);
+        out_off += (size_t)op * c.h;
+      }
+    }
+  }
+  if (n_down_jobs > 0) CU_TRY(ctx->down_jobs.reserve((size_t)n_down_jobs));
   if (any_clahe) CU_TRY(ctx->clahe_lut.reserve((size_t)npre * CLAHE_TILES * CLAHE_TILES * 256));
   if (!ctx->sp_mask_ready) {
     CU_TRY(ctx->sp_mask.reserve(SP_N));
@@ -1074,18 +1146,24 @@ int Pass::stage0() {
       pend_bytes = 0;
       return e;
     };
-    int j = 0;
+    int j = 0, ndown = 0, max_dw = 1, max_dh = 1;
     for (int i = 0; i < n; i++) {
       FeedRequest &rq = *reqs[i];
       for (int k = 0; k < rq.n; k++, j++) {
         CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
         const HostImage &im = rq.images[k];
-        const ImgView &raw = dev->raw_tab[c.raw];
+        const ImgView &raw = dev->raw_tab[c.raw_in];
         cudaPointerAttributes attr;
         const bool on_device = cudaPointerGetAttributes(&attr, im.p) == cudaSuccess &&
                                (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+        if (rq.rig->prm.downsample_cameras) {
+          const ImgView full = on_device ? ImgView{im.p, im.w, im.h, (int)im.stride} : raw;
+          ctx->down_jobs.h[ndown++] = DownJob{full, dev->raw_tab[c.raw]};
+          max_dw = std::max(max_dw, c.w);
+          max_dh = std::max(max_dh, c.h);
+        }
         if (on_device) {
-          ctx->pre_jobs.h[j].src = ImgView{im.p, im.w, im.h, (int)im.stride};
+          if (!rq.rig->prm.downsample_cameras) ctx->pre_jobs.h[j].src = ImgView{im.p, im.w, im.h, (int)im.stride};
           continue;
         }
         cudaGetLastError();   // an unregistered host pointer is not an error
@@ -1112,6 +1190,11 @@ int Pass::stage0() {
       }
     }
     CU_TRY(flush());
+    if (ndown > 0) {   // downsample_cameras: halve the frames where they landed, in front of the pre-processing
+      CU_TRY(ctx->down_jobs.upload(ctx->up_stream, (size_t)ndown));
+      CU_TRY(launch_downsample(ctx->up_stream, ctx->down_jobs.d, ndown, max_dw, max_dh));
+      ctx->stats[1] += 1;
+    }
     CU_TRY(ctx->pre_jobs.upload(ctx->up_stream, (size_t)npre));
   }
   {
@@ -1289,9 +1372,9 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
       for (int q = 0; q < k; q++) if (rq.sensor_ids[q] == rq.sensor_ids[k]) { fail(rq, E_BADMSG); bad = true; }
       if (bad) break;
       if (c->raw < 0) {
-        int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size);
+        int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size, P.downsample_cameras != 0);
         if (e != OK) { fail(rq, e); bad = true; break; }
-      } else if (c->w != im.w || c->h != im.h) { fail(rq, E_SIZE); bad = true; break; }
+      } else if (c->in_w != im.w || c->in_h != im.h) { fail(rq, E_SIZE); bad = true; break; }
     }
     if (!bad) good.push_back(&rq);
   }

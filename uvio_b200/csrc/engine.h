@@ -28,6 +28,7 @@ struct Params {                 // TrackKLT ctor arguments (TrackKLT.h:54-57) + 
   int win_size = 15;            // TrackKLT.h:144 (only 15 is implemented)
   int lk_max_iters = 30;        // TrackKLT.cpp:670,857
   double lk_eps = 0.01;
+  int downsample_cameras = 0;   // VioManagerOptions.h:409: halve every image and mask in front of the tracker (VioManager.cpp:268-278)
 };
 
 struct CamCalib {
@@ -53,10 +54,12 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   size_t cam_id = 0;
   int cam_model_idx = -1;       // index into the context's CamModel table
   double max_focal = 0;
-  int w = 0, h = 0;             // size of the images this camera has been fed (fixed after the first frame)
+  int w = 0, h = 0;             // size of the images this camera tracks on (fixed after the first frame)
+  int in_w = 0, in_h = 0;       // size of the images it is fed: (w, h), or twice that with downsample_cameras
+  int raw_in = -1;              // upload buffer of the fed frame (== raw unless downsample_cameras)
   int pyr[2] = {-1, -1};        // the two pyramid slots in the context's table
   int cur = 0;                  // slot holding the frame being fed ("curr"); 1-cur is "last"
-  int raw = -1;                 // raw upload buffer index
+  int raw = -1;                 // the frame the pre-processing reads: the upload buffer, or its halved copy
   bool have_last = false;
   std::vector<Pt> pts_last;
   std::vector<size_t> ids_last;

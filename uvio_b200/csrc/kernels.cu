@@ -215,6 +215,33 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// downsample_cameras (ov_msckf/src/core/VioManager.cpp:268-278): cv::pyrDown of the message's images and masks to
+// Size(cols / 2.0, rows / 2.0), in front of feed_new_camera.  One lane per 4x4 output strip, grid = (strip chunks, jobs);
+// an HBM-bound byte pass (1 B read per source pixel, 1/4 B written).
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int DOWN_THREADS = 256;
+
+__global__ void __launch_bounds__(DOWN_THREADS) k_downsample(const DownJob *jobs) {
+  const DownJob job = jobs[blockIdx.y];
+  const ImgView S = job.src, D = job.dst;
+  const int nsx = (D.w + PD_COLS - 1) / PD_COLS, nsy = (D.h + PD_ROWS - 1) / PD_ROWS;
+  for (int sidx = blockIdx.x * DOWN_THREADS + threadIdx.x; sidx < nsx * nsy; sidx += gridDim.x * DOWN_THREADS) {
+    int sy = sidx / nsx, sx = sidx - sy * nsx;
+    pyrdown_strip(S, (uint8_t *)D.p, D.w, D.h, D.pitch, sx * PD_COLS, sy * PD_ROWS);
+  }
+}
+
+cudaError_t launch_downsample(cudaStream_t st, const DownJob *jobs, int njobs, int max_dst_w, int max_dst_h) {
+  if (njobs <= 0) return cudaSuccess;
+  const int strips = ((max_dst_w + PD_COLS - 1) / PD_COLS) * ((max_dst_h + PD_ROWS - 1) / PD_ROWS);
+  const int bx = (strips + DOWN_THREADS - 1) / DOWN_THREADS;
+  prof_mark(st, K_DOWNSAMPLE);
+  k_downsample<<<dim3(bx > 0 ? bx : 1, njobs), DOWN_THREADS, 0, st>>>(jobs);
+  prof_mark(st, -1);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // FAST on grid cells. grid = (max tiles per cell, jobs). The last tile of a job to finish compacts the job's list into
 // mapped host memory, so the host sees exactly `count` words per cell and nothing else crosses PCIe.
 // ---------------------------------------------------------------------------------------------------------------------

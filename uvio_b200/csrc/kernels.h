@@ -24,6 +24,11 @@ struct PreJob {                        // one image to pre-process this frame
   int method;                          // 0 none, 1 equalizeHist, 2 CLAHE   (TrackBase::HistogramMethod)
 };
 
+struct DownJob {                       // one image or mask to halve before the tracker sees it (VioManager.cpp:268-278)
+  ImgView src;                         // full-size frame (upload buffer or the caller's device memory) or mask
+  ImgView dst;                         // floor(w/2) x floor(h/2); device memory, or mapped host memory for masks
+};
+
 struct SubpixItem { float x, y; int pyr; int pad; };
 struct LkItem { float px, py, nx, ny; int prev_pyr, next_pyr; };
 struct LkOut { float x, y; };
@@ -37,7 +42,7 @@ struct RansacJob {
 
 // Optional per-kernel timing: when g_prof is set, every launch wrapper records a CUDA event before each kernel it launches
 // (and the engine one after the last), on the launching stream.
-enum KernelId { K_HIST = 0, K_LUT_APPLY, K_CLAHE_TILES, K_CLAHE_APPLY, K_PYRDOWN, K_FAST, K_SUBPIX, K_LK, K_RANSAC, K_PREPROCESS, K_COUNT };
+enum KernelId { K_HIST = 0, K_LUT_APPLY, K_CLAHE_TILES, K_CLAHE_APPLY, K_PYRDOWN, K_FAST, K_SUBPIX, K_LK, K_RANSAC, K_PREPROCESS, K_DOWNSAMPLE, K_COUNT };
 struct KernelProf {
   static constexpr int MAX_MARKS = 48;
   cudaEvent_t ev[MAX_MARKS];
@@ -62,6 +67,9 @@ inline void prof_mark(cudaStream_t st, int kernel_id) {
 // equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels: one cluster launch
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const PyrDesc *pyr_tab_dev, uint8_t *clahe_lut_dev /*njobs*64*256, CLAHE only*/, int any_clahe,
                               int max_band_bytes /* max over the jobs of (ceil(h/8)+1) * w: the rows one block stages by TMA */);
+
+// cv::pyrDown(src, dst, Size(cols / 2.0, rows / 2.0)) of every job: the downsample_cameras step in front of the tracker
+cudaError_t launch_downsample(cudaStream_t st, const DownJob *jobs_dev, int njobs, int max_dst_w, int max_dst_h);
 
 // ---- detection ----------------------------------------------------------------------------------------------------------
 // FAST + NMS on grid cells; compacts each job's corner list into out_host (mapped pinned) and writes its count.

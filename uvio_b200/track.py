@@ -28,7 +28,8 @@ ERR_NAMES = {0: "UVIO_OK", 1: "UVIO_E_BADMSG", 2: "UVIO_E_CAMID", 3: "UVIO_E_CUD
 class UvioKltParams(C.Structure):
     _fields_ = [("num_features", C.c_int), ("num_aruco", C.c_int), ("use_stereo", C.c_int), ("histogram_method", C.c_int),
                 ("fast_threshold", C.c_int), ("grid_x", C.c_int), ("grid_y", C.c_int), ("min_px_dist", C.c_int),
-                ("pyr_levels", C.c_int), ("win_size", C.c_int), ("lk_max_iters", C.c_int), ("lk_eps", C.c_double)]
+                ("pyr_levels", C.c_int), ("win_size", C.c_int), ("lk_max_iters", C.c_int), ("lk_eps", C.c_double),
+                ("downsample_cameras", C.c_int)]
 
 
 class UvioCamCalib(C.Structure):
@@ -222,12 +223,14 @@ class TrackKLT:
     camera id -> object with (model, intrinsics, dist) — e.g. uvio_b200.configs.CamCalib."""
 
     def __init__(self, camera_calib: Dict[int, object], numfeats: int, numaruco: int, stereo: bool, histmethod: int,
-                 fast_threshold: int, gridx: int, gridy: int, minpxdist: int, pyr_levels: int = 5, device: int = 0):
+                 fast_threshold: int, gridx: int, gridy: int, minpxdist: int, pyr_levels: int = 5, device: int = 0,
+                 downsample_cameras: bool = False):
         L = lib()
         p = UvioKltParams()
         L.uvio_klt_default_params(C.byref(p))
         p.num_features, p.num_aruco, p.use_stereo, p.histogram_method = int(numfeats), int(numaruco), int(bool(stereo)), int(histmethod)
         p.fast_threshold, p.grid_x, p.grid_y, p.min_px_dist, p.pyr_levels = int(fast_threshold), int(gridx), int(gridy), int(minpxdist), int(pyr_levels)
+        p.downsample_cameras = int(bool(downsample_cameras))     # VioManager.cpp:268-278 in front of feed_new_camera
         cams = (UvioCamCalib * len(camera_calib))()
         for i, (cid, c) in enumerate(camera_calib.items()):
             cams[i].cam_id = int(cid)
@@ -403,7 +406,7 @@ def make_tracker(cfg, device: int = 0, **over) -> TrackKLT:
 
 
 KERNEL_NAMES = ["k_hist", "k_lut_apply", "k_clahe_tiles", "k_clahe_apply", "k_pyrdown", "k_fast", "k_subpix", "k_lk", "k_ransac",
-                "k_preprocess"]
+                "k_preprocess", "k_downsample"]
 
 
 def device_stats(device: int = 0) -> dict:
