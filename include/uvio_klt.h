@@ -101,6 +101,16 @@ int uvio_klt_feed(uvio_klt *h, const UvioFrame *frame);
  * per stage for the whole batch).  The reference's equivalent is n TrackKLT instances fed from n threads. */
 int uvio_klt_feed_batch(uvio_klt *const *h, UvioFrame *frames, int n);
 
+/* Optional: announce the NEXT message of a tracker ahead of its feed -- what a driver does in the image-arrival callback
+ * (ov_msckf/src/ros/ROS1Visualizer.cpp:571-580 builds the CameraData there) while the estimator is still busy with the
+ * previous frame.  The images are uploaded, (halved,) equalised and their pyramids built asynchronously on a stream of
+ * their own; the call returns as soon as the work is queued.  Contract: the next uvio_klt_feed / uvio_klt_feed_batch
+ * of that tracker must be given the same message (same image pointers), and the image memory must stay valid and
+ * unchanged until that feed returns; masks are read by the feed, not here.  At most two messages per camera may be
+ * announced and not yet fed (UVIO_E_ARG otherwise).  Results are identical to a feed that was not announced. */
+int uvio_klt_submit(uvio_klt *h, const UvioFrame *frame);
+int uvio_klt_submit_batch(uvio_klt *const *h, UvioFrame *frames, int n);
+
 /* The update_feature calls the last feed made, in the reference's order (all left, then all right; TrackKLT.cpp:357-366,
  * mono :176-179). *n receives the count; at most cap entries are written. */
 int uvio_klt_get_new_observations(uvio_klt *h, UvioObs *out, int cap, int *n);

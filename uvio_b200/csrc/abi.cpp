@@ -92,7 +92,8 @@ void uvio_klt_destroy(uvio_klt *h) {
   delete h;
 }
 
-int uvio_klt_feed_batch(uvio_klt *const *hs, UvioFrame *frames, int n) {
+// feed_batch and submit_batch share everything but the engine call
+static int run_batch(uvio_klt *const *hs, UvioFrame *frames, int n, bool announce) {
   GUARD_BEGIN
   if (!hs || !frames || n <= 0) return UVIO_E_ARG;
   Context *ctx = hs[0] ? hs[0]->rig->ctx : nullptr;
@@ -115,7 +116,7 @@ int uvio_klt_feed_batch(uvio_klt *const *hs, UvioFrame *frames, int n) {
     r.status = UVIO_OK;
     bool ptrs = f.n_img > 0 && f.sensor_ids && f.img && f.img_stride && f.width && f.height;
     if (!ptrs) {
-      r.n = 0;   // rejected as a malformed message inside feed_batch
+      r.n = 0;   // rejected as a malformed message inside the engine
       r.images = r.masks = nullptr;
       continue;
     }
@@ -129,7 +130,7 @@ int uvio_klt_feed_batch(uvio_klt *const *hs, UvioFrame *frames, int n) {
     r.images = imgs[i].data();
     r.masks = masks[i].data();
   }
-  int rc = feed_batch(ctx, reqs.data(), n);
+  int rc = announce ? submit_batch(ctx, reqs.data(), n) : feed_batch(ctx, reqs.data(), n);
   for (int i = 0; i < n; i++) {
     frames[i].status = reqs[i].status;
     if (rc == UVIO_E_CUDA) {
@@ -140,6 +141,18 @@ int uvio_klt_feed_batch(uvio_klt *const *hs, UvioFrame *frames, int n) {
   }
   return rc;
   GUARD_END
+}
+
+int uvio_klt_feed_batch(uvio_klt *const *hs, UvioFrame *frames, int n) { return run_batch(hs, frames, n, false); }
+
+int uvio_klt_submit_batch(uvio_klt *const *hs, UvioFrame *frames, int n) { return run_batch(hs, frames, n, true); }
+
+int uvio_klt_submit(uvio_klt *h, const UvioFrame *frame) {
+  if (!h || !frame) return UVIO_E_ARG;
+  UvioFrame f = *frame;
+  uvio_klt *hs[1] = {h};
+  int rc = run_batch(hs, &f, 1, true);
+  return rc != UVIO_OK ? rc : f.status;
 }
 
 int uvio_klt_feed(uvio_klt *h, const UvioFrame *frame) {

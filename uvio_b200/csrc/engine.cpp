@@ -161,10 +161,28 @@ struct DevVec {
 
 class Context;
 
+// One frame to upload and pre-process: the shared front of a feed (frames that were not announced) and of submit_batch.
+struct PreItem {
+  CamState *cam;
+  const HostImage *im;
+  int slot;                      // destination pyramid slot
+  int method;                    // TrackBase::HistogramMethod
+  bool downsample;
+};
+struct PreBuffers {              // job lists of one upload round (a lane's, or one entry of the context's submit ring)
+  JobVec<PreJob> *pre;
+  JobVec<DownJob> *down;
+  DevVec<uint8_t> *clahe;
+};
+
 // One lane = one CUDA stream with its own job / result buffers.  A feed_batch call splits its trackers over the lanes and
 // runs them on separate host threads, so the host bookkeeping of one group overlaps the GPU rounds of the others.
 struct Lane {
-  Lane() { sp_items.prefer_mapped = lk_items.prefer_mapped = rs_jobs.prefer_mapped = true; }
+  Lane() {
+    sp_items.prefer_mapped = lk_items.prefer_mapped = rs_jobs.prefer_mapped = true;
+    const char *e = getenv("UVIO_KLT_FAST_MAPPED");   // the FAST list is read by every tile block of a cell: copied (measured)
+    fast_jobs.prefer_mapped = e && e[0] == '1';
+  }
   Context *dev = nullptr;
   int index = 0;
   cudaStream_t stream = nullptr;      // detection and tracking rounds
@@ -212,6 +230,8 @@ struct Lane {
   DevVec<uint8_t> mask_in;       // the full-size masks of this feed
   MappedVec<uint8_t> mask_out;   // their halved versions, written by the kernel into host memory
   JobVec<PreJob> pre_jobs;
+  std::vector<PreItem> pre_items;
+  std::vector<HostImage> zero_masks;
   DevVec<uint8_t> clahe_lut;
   JobVec<FastJob> fast_jobs;
   DevVec<uint32_t> fast_out_dev;
@@ -270,6 +290,17 @@ class Context {
   DevVec<CamModel> cam_dev;
   bool tables_dirty = true;
   std::vector<void *> allocs;   // image memory of all cameras
+  // submit_batch: frames announced ahead of their feed go up and are pre-processed on a stream of their own, one event
+  // per call out of a small ring; a feed makes its lanes wait for the events that cover its frames
+  static constexpr int PF_RING = 8;
+  cudaStream_t pf_stream = nullptr;
+  cudaEvent_t pf_evt[PF_RING] = {nullptr};
+  bool pf_used[PF_RING] = {false};
+  unsigned pf_seq = 0;
+  JobVec<PreJob> pf_pre[PF_RING];
+  JobVec<DownJob> pf_down[PF_RING];
+  DevVec<uint8_t> pf_clahe[PF_RING];
+  std::vector<PreItem> pf_items;
   uint8_t *raw_arena = nullptr;   // next free byte of the current upload-buffer chunk
   size_t raw_arena_left = 0;
 
@@ -317,8 +348,8 @@ class Context {
     raw_arena += raw_bytes;
     raw_arena_left -= raw_bytes;
     uint8_t *base = nullptr;
-    CU_TRY(cudaMalloc((void **)&base, 2 * pyr_bytes + half_bytes + 256));
-    CU_TRY(cudaMemset(base, 0, 2 * pyr_bytes + half_bytes + 256));
+    CU_TRY(cudaMalloc((void **)&base, PYR_SLOTS * pyr_bytes + half_bytes + 256));
+    CU_TRY(cudaMemset(base, 0, PYR_SLOTS * pyr_bytes + half_bytes + 256));
     allocs.push_back(base);
     c.w = w;
     c.h = h;
@@ -333,7 +364,7 @@ class Context {
       raw_tab.push_back(ImgView{p, w, h, half_pitch});
       p += half_bytes;
     }
-    for (int s = 0; s < 2; s++) {
+    for (int s = 0; s < PYR_SLOTS; s++) {
       PyrDesc d;
       memset(&d, 0, sizeof(d));
       d.nlv = L + 1;
@@ -447,12 +478,16 @@ class Pool {
 Context::~Context() {
   delete pool;
   lanes.clear();
+  if (pf_stream) cudaStreamDestroy(pf_stream);
+  for (int i = 0; i < PF_RING; i++)
+    if (pf_evt[i]) cudaEventDestroy(pf_evt[i]);
   for (void *p : allocs) cudaFree(p);
 }
 
-// Host threads per device context: UVIO_KLT_LANES, else a quarter of the process's share of the logical cores (one
-// process per GPU shares the host with its siblings), at most 8.  Every thread drives UVIO_KLT_DEPTH lanes (default 2)
-// alternately.  Measured on a 16-thread host with one B200: 4 x 2 and 8 x 1 are level, more lanes only shrink the launches.
+// Host threads per device context: UVIO_KLT_LANES, else half of the process's share of the logical cores (one process per
+// GPU shares the host with its siblings), at most 8.  Every thread drives UVIO_KLT_DEPTH lanes alternately: 1 when there
+// are 8 threads, else 2.  Measured on a 16-core host with one B200 (32 / 64 streams): 8 x 1 beats 4 x 2 by 3 % / 4 %
+// resident and 0 % / 16 % end to end; 12 or 16 threads lose to the shrinking launches and the busy cores.
 static int default_threads() {
   if (const char *e = getenv("UVIO_KLT_LANES")) {
     int v = atoi(e);
@@ -461,15 +496,15 @@ static int default_threads() {
   int hw = (int)std::thread::hardware_concurrency();
   int local_world = 1;
   if (const char *e = getenv("LOCAL_WORLD_SIZE")) local_world = atoi(e) > 0 ? atoi(e) : 1;
-  int v = hw / local_world / 4;
+  int v = hw / local_world / 2;
   return v < 1 ? 1 : (v > 8 ? 8 : v);
 }
-static int default_depth() {
+static int default_depth(int threads) {
   if (const char *e = getenv("UVIO_KLT_DEPTH")) {
     int v = atoi(e);
     if (v >= 1) return v > 4 ? 4 : v;
   }
-  return 2;
+  return threads >= 8 ? 1 : 2;
 }
 
 Context *context_for_device(int device, int *err) {
@@ -491,19 +526,31 @@ Context *context_for_device(int device, int *err) {
     return nullptr;
   }
   c->threads = default_threads();
-  const int nl = c->threads * default_depth();
+  int prio_lo = 0, prio_hi = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+  const int nl = c->threads * default_depth(c->threads);
   for (int i = 0; i < nl; i++) {
     std::unique_ptr<Lane> ln(new Lane);
     ln->dev = c.get();
     ln->index = i;
-    if ((e = cudaStreamCreateWithFlags(&ln->stream, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaStreamCreateWithFlags(&ln->up_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+    // the rounds a feed waits for run ahead of the pre-processing of frames that are only needed later
+    if ((e = cudaStreamCreateWithPriority(&ln->stream, cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&ln->up_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&ln->up_done, cudaEventDisableTiming)) != cudaSuccess) {
       if (err) *err = (int)e;
       return nullptr;
     }
     c->lanes.push_back(std::move(ln));
   }
+  if ((e = cudaStreamCreateWithPriority(&c->pf_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) {
+    if (err) *err = (int)e;
+    return nullptr;
+  }
+  for (int i = 0; i < Context::PF_RING; i++)
+    if ((e = cudaEventCreateWithFlags(&c->pf_evt[i], cudaEventDisableTiming)) != cudaSuccess) {
+      if (err) *err = (int)e;
+      return nullptr;
+    }
   c->pool = new Pool(c->threads - 1);
   Context *p = c.get();
   table[device] = std::move(c);
@@ -621,7 +668,7 @@ static void phase_a(Unit &u) {
   const int thr = std::min(20, (int)(0.5 * P.num_features));
   {
     CamState &c = *L.cam;
-    L.det_slot = u.first ? c.cur : 1 - c.cur;
+    L.det_slot = u.first ? c.cur : c.last();
     L.det_mask = mask_ptr(c, L.det_slot);
     { HOSTPROF(a_occ_init); occ_init(L.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y); }
     HOSTPROF(a_left_rest);
@@ -638,7 +685,7 @@ static void phase_a(Unit &u) {
   if (u.stereo) {
     Side &R = u.R;
     CamState &c = *R.cam;
-    R.det_slot = u.first ? c.cur : 1 - c.cur;
+    R.det_slot = u.first ? c.cur : c.last();
     R.det_mask = mask_ptr(c, R.det_slot);
     occ_init(R.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y);
     // The right pass (:722-780) runs after the left detection appended new stereo points to pts1, but it is a plain
@@ -810,7 +857,7 @@ static void emit_temporal(Lane *ctx, Unit &u, int &nlk, int &nrs) {
     s.lk_run = s.pts.size() >= 10;                                  // TrackKLT.cpp:848-852
     if (!s.lk_run) continue;
     s.lk_n = (int)s.pts.size();
-    for (auto &p : s.pts) ctx->lk_items.h[nlk++] = LkItem{p.x, p.y, p.x, p.y, c.pyr[1 - c.cur], c.pyr[c.cur]};
+    for (auto &p : s.pts) ctx->lk_items.h[nlk++] = LkItem{p.x, p.y, p.x, p.y, c.pyr[c.last()], c.pyr[c.cur]};
     RansacJob j;
     j.off = s.lk_off;
     j.n = s.lk_n;
@@ -956,7 +1003,10 @@ struct Pass {
   int rc = OK;          // E_CUDA once a stage failed; later stages are skipped
   int stage = 0;
   int npre = 0, njobs = 0, nsp = 0, nlk = 0, nrs = 0;
+  unsigned wait_evts = 0;   // events of the context's submit ring that cover announced frames of this pass
   double t0 = 0, t1 = 0, t2 = 0, t3 = 0, tmark = 0;
+  // make the lane's main stream wait for the new pyramids: its own upload stream and the submit rounds that hold its frames
+  cudaError_t wait_new_frames();
 
   void fail(FeedRequest &r, int code) {
     r.status = code;
@@ -995,34 +1045,161 @@ struct Pass {
   int result() const { return rc != OK ? rc : worst; }
 };
 
+// H2D of the frames (merged into as few copies as their layout allows), the optional halving, equalisation and pyramids,
+// all on stream st.  Frames already in device memory are consumed where they lie.
+static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, const std::vector<PreItem> &items, unsigned long long *stats,
+                            int group = 0) {
+  HOSTPROF(s0_memcpy);
+  const int nimg = (int)items.size();
+  if (nimg == 0) return OK;
+  int any_clahe = 0, max_band = 0, ndown = 0, max_dw = 1, max_dh = 1, n_down_jobs = 0;
+  std::vector<char> on_dev((size_t)nimg, 0);
+  for (auto &it : items) {
+    any_clahe |= it.method == 2;
+    n_down_jobs += it.downsample;
+  }
+  CU_TRY(B.pre->reserve((size_t)nimg));
+  if (n_down_jobs) CU_TRY(B.down->reserve((size_t)n_down_jobs));
+  if (any_clahe) CU_TRY(B.clahe->reserve((size_t)nimg * CLAHE_TILES * CLAHE_TILES * 256));
+  // Copies whose source and destination both continue the previous one are merged (a batch of tightly packed frames is one copy).
+  uint8_t *pend_dst = nullptr;
+  const uint8_t *pend_src = nullptr;
+  size_t pend_bytes = 0;
+  // A long copy is cut into pieces: the rounds of the feed that runs meanwhile read their job lists and write their results
+  // across the same PCIe link, and one 20 MB transfer ahead of them costs each round ~100 us (measured: tools/pcie_probe.py);
+  // between pieces the link takes their requests.
+  static const size_t piece = [] {
+    const char *e = getenv("UVIO_KLT_UPLOAD_PIECE");
+    long v = e ? atol(e) : (1l << 20);
+    return (size_t)(v < 4096 ? 4096 : v);
+  }();
+  auto flush = [&]() -> cudaError_t {
+    cudaError_t e = cudaSuccess;
+    for (size_t off = 0; off < pend_bytes && e == cudaSuccess; off += piece)
+      e = cudaMemcpyAsync(pend_dst + off, pend_src + off, std::min(piece, pend_bytes - off), cudaMemcpyHostToDevice, st);
+    pend_bytes = 0;
+    return e;
+  };
+  // Pass 1: the job lists (one small copy each, ahead of the frames).
+  { HOSTPROF(pre_pass1);
+  for (int j = 0; j < nimg; j++) {
+    const PreItem &it = items[j];
+    CamState &c = *it.cam;
+    const HostImage &im = *it.im;
+    B.pre->h[j] = PreJob{ctx->raw_tab[c.raw], c.pyr[it.slot], it.method};
+    max_band = std::max(max_band, ((c.h + 7) / 8 + 1) * c.w);
+    cudaPointerAttributes attr;
+    const bool on_device = cudaPointerGetAttributes(&attr, im.p) == cudaSuccess &&
+                           (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+    if (!on_device) cudaGetLastError();   // an unregistered host pointer is not an error
+    on_dev[j] = on_device;
+    if (it.downsample) {
+      const ImgView full = on_device ? ImgView{im.p, im.w, im.h, (int)im.stride} : ctx->raw_tab[c.raw_in];
+      B.down->h[ndown++] = DownJob{full, ctx->raw_tab[c.raw]};
+      max_dw = std::max(max_dw, c.w);
+      max_dh = std::max(max_dh, c.h);
+    } else if (on_device) {
+      B.pre->h[j].src = ImgView{im.p, im.w, im.h, (int)im.stride};
+    }
+  }
+  }
+  CU_TRY(B.pre->upload(st, (size_t)nimg));
+  if (ndown > 0) CU_TRY(B.down->upload(st, (size_t)ndown));
+  // Pass 2: group by group, the frames go up and are (halved and) pre-processed.  A feed issues one group; submit_batch cuts
+  // a batch into several so that the pyramids of the first frames are built while the last ones are still on the link, and
+  // so that no launch takes every SM from the rounds of the feed that is running meanwhile.
+  if (group <= 0 || group > nimg) group = nimg;
+  int down_at = 0;
+  HOSTPROF(pre_pass2);
+  for (int g0 = 0; g0 < nimg; g0 += group) {
+    const int g1 = std::min(nimg, g0 + group);
+    int gdown = 0;
+    for (int j = g0; j < g1; j++) {
+      const PreItem &it = items[j];
+      const HostImage &im = *it.im;
+      const ImgView &raw = ctx->raw_tab[it.cam->raw_in];
+      gdown += it.downsample;
+      if (on_dev[j]) continue;
+      stats[2] += (unsigned long long)im.w * im.h;
+      if ((size_t)raw.pitch == im.stride) {
+        const size_t bytes = (size_t)raw.pitch * (im.h - 1) + im.w, span = (size_t)raw.pitch * im.h;
+        if (pend_bytes && pend_src + pend_bytes == im.p && pend_dst + pend_bytes == raw.p) {
+          pend_bytes += span;
+        } else {
+          CU_TRY(flush());
+          pend_dst = (uint8_t *)raw.p;
+          pend_src = im.p;
+          pend_bytes = span;
+        }
+        if (span != bytes && (size_t)im.w != im.stride) {   // never read past the caller's last row
+          pend_bytes -= span - bytes;
+          CU_TRY(flush());
+        }
+      } else {
+        CU_TRY(flush());
+        CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault, st));
+      }
+    }
+    CU_TRY(flush());
+    if (gdown > 0) {   // downsample_cameras: halve the frames where they landed, in front of the pre-processing
+      CU_TRY(launch_downsample(st, B.down->d + down_at, gdown, max_dw, max_dh));
+      down_at += gdown;
+      stats[1] += 1;
+    }
+    HOSTPROF(s0_launch_preprocess);
+    CU_TRY(launch_preprocess(st, B.pre->d + g0, g1 - g0, ctx->pyr_dev.d, any_clahe ? B.clahe->d + (size_t)g0 * CLAHE_TILES * CLAHE_TILES * 256 : nullptr,
+                             any_clahe, max_band));
+    stats[1] += (unsigned)(1 + 2 * any_clahe);
+  }
+  return OK;
+}
+
+cudaError_t Pass::wait_new_frames() {
+  cudaError_t e = cudaStreamWaitEvent(ctx->stream, ctx->up_done, 0);
+  for (int i = 0; i < Context::PF_RING && e == cudaSuccess; i++)
+    if ((wait_evts >> i) & 1u) e = cudaStreamWaitEvent(ctx->stream, ctx->dev->pf_evt[i], 0);
+  return e;
+}
+
 int Pass::stage0() {
   Context *dev = ctx->dev;
   t0 = tmark = now_us();
   ctx->prof_begin();
   g_prof = ctx->prof_on ? &ctx->prof : nullptr;
   // ---- host bookkeeping of the new messages: frame slots, masks, pre-processing jobs, units ---------------------------------
-  int nimg = 0, any_clahe = 0, max_band = 0, n_down_jobs = 0, n_mask_jobs = 0;
+  int n_mask_jobs = 0;
   size_t mask_in_bytes = 0, mask_out_bytes = 0;
-  for (int i = 0; i < n; i++) nimg += reqs[i]->n;
-  CU_TRY(ctx->pre_jobs.reserve((size_t)nimg));
-  npre = 0;
+  std::vector<PreItem> &items = ctx->pre_items;
+  items.clear();
+  wait_evts = 0;
+  std::vector<HostImage> &zero_masks = ctx->zero_masks;   // masks of this pass already found to be all zero
+  zero_masks.clear();
   for (int i = 0; i < n; i++) {
     FeedRequest &rq = *reqs[i];
     Rig &rig = *rq.rig;
     const Params &P = rig.prm;
     for (int k = 0; k < rq.n; k++) {
       CamState &c = *rig.find_cam(rq.sensor_ids[k]);
-      c.cur ^= 1;
-      if (!P.downsample_cameras) c.mask_nonzero[c.cur] = copy_mask(rq.masks[k], c.mask[c.cur], c.w, c.h);
-      else if ((c.mask_nonzero[c.cur] = mask_any_set(rq.masks[k], c.in_w, c.in_h))) {   // halved on the device below
+      // frame number n_fed + 1 of this camera: announced earlier (submit_batch; already on its way or done) or uploaded now
+      const bool announced = c.n_sub > c.n_fed;
+      if (!announced) c.n_sub++;
+      c.n_fed++;
+      c.cur = (int)(c.n_fed % PYR_SLOTS);
+      if (announced) wait_evts |= 1u << c.sub_evt[c.cur];
+      else items.push_back(PreItem{&c, &rq.images[k], c.cur, P.histogram_method, P.downsample_cameras != 0});
+      // the same mask memory given to several cameras of this call (a rig's shared mask, a batch's common one) is scanned once
+      const HostImage &mk = rq.masks[k];
+      bool known_zero = false;
+      for (const HostImage &z : zero_masks) known_zero |= z.p == mk.p && z.stride == mk.stride && z.w == mk.w && z.h == mk.h;
+      if (known_zero) c.mask_nonzero[c.cur] = false;
+      else if (!P.downsample_cameras) c.mask_nonzero[c.cur] = copy_mask(mk, c.mask[c.cur], c.w, c.h);
+      else c.mask_nonzero[c.cur] = mask_any_set(mk, c.in_w, c.in_h);
+      if (!c.mask_nonzero[c.cur] && mk.p && !known_zero && zero_masks.size() < 16) zero_masks.push_back(mk);
+      if (P.downsample_cameras && c.mask_nonzero[c.cur]) {   // halved on the device below
         n_mask_jobs++;
         mask_in_bytes += (size_t)((c.in_w + 15) / 16 * 16) * c.in_h;
         mask_out_bytes += (size_t)((c.w + 3) / 4 * 4) * c.h;
       }
-      n_down_jobs += P.downsample_cameras != 0;
-      ctx->pre_jobs.h[npre++] = PreJob{dev->raw_tab[c.raw], c.pyr[c.cur], P.histogram_method};   // src is settled below
-      max_band = std::max(max_band, ((c.h + 7) / 8 + 1) * c.w);
-      any_clahe |= P.histogram_method == 2;
     }
     // units (TrackKLT.cpp:80-93)
     auto make_side = [&](Side &s, int k) { s.cam = rig.find_cam(rq.sensor_ids[k]); s.msg = k; };
@@ -1088,8 +1265,6 @@ int Pass::stage0() {
       }
     }
   }
-  if (n_down_jobs > 0) CU_TRY(ctx->down_jobs.reserve((size_t)n_down_jobs));
-  if (any_clahe) CU_TRY(ctx->clahe_lut.reserve((size_t)npre * CLAHE_TILES * CLAHE_TILES * 256));
   if (!ctx->sp_mask_ready) {
     CU_TRY(ctx->sp_mask.reserve(SP_N));
     CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
@@ -1132,79 +1307,16 @@ int Pass::stage0() {
     CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d, ctx->fast_cnt_dev.d,
                        ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   }
-  // ---- round 1b: upload + equalise + pyramid on the upload stream --------------------------------------------------------
+  // ---- round 1b: upload + equalise + pyramid on the upload stream (frames announced by submit_batch are on their way) -------
+  npre = (int)items.size();
   {
-    HOSTPROF(s0_memcpy);
-    // Frames already in device memory are consumed where they lie; host frames go to the upload buffers.  Copies whose
-    // source and destination both continue the previous one are merged (a batch of tightly packed frames is one copy).
-    uint8_t *pend_dst = nullptr;
-    const uint8_t *pend_src = nullptr;
-    size_t pend_bytes = 0;
-    auto flush = [&]() -> cudaError_t {
-      if (!pend_bytes) return cudaSuccess;
-      cudaError_t e = cudaMemcpyAsync(pend_dst, pend_src, pend_bytes, cudaMemcpyHostToDevice, ctx->up_stream);
-      pend_bytes = 0;
-      return e;
-    };
-    int j = 0, ndown = 0, max_dw = 1, max_dh = 1;
-    for (int i = 0; i < n; i++) {
-      FeedRequest &rq = *reqs[i];
-      for (int k = 0; k < rq.n; k++, j++) {
-        CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
-        const HostImage &im = rq.images[k];
-        const ImgView &raw = dev->raw_tab[c.raw_in];
-        cudaPointerAttributes attr;
-        const bool on_device = cudaPointerGetAttributes(&attr, im.p) == cudaSuccess &&
-                               (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
-        if (rq.rig->prm.downsample_cameras) {
-          const ImgView full = on_device ? ImgView{im.p, im.w, im.h, (int)im.stride} : raw;
-          ctx->down_jobs.h[ndown++] = DownJob{full, dev->raw_tab[c.raw]};
-          max_dw = std::max(max_dw, c.w);
-          max_dh = std::max(max_dh, c.h);
-        }
-        if (on_device) {
-          if (!rq.rig->prm.downsample_cameras) ctx->pre_jobs.h[j].src = ImgView{im.p, im.w, im.h, (int)im.stride};
-          continue;
-        }
-        cudaGetLastError();   // an unregistered host pointer is not an error
-        ctx->stats[2] += (unsigned long long)im.w * im.h;
-        if ((size_t)raw.pitch == im.stride) {
-          const size_t bytes = (size_t)raw.pitch * (im.h - 1) + im.w, span = (size_t)raw.pitch * im.h;
-          if (pend_bytes && pend_src + pend_bytes == im.p && pend_dst + pend_bytes == raw.p) {
-            pend_bytes += span;
-          } else {
-            CU_TRY(flush());
-            pend_dst = (uint8_t *)raw.p;
-            pend_src = im.p;
-            pend_bytes = span;
-          }
-          if (span != bytes && (size_t)im.w != im.stride) {   // never read past the caller's last row
-            pend_bytes -= span - bytes;
-            CU_TRY(flush());
-          }
-        } else {
-          CU_TRY(flush());
-          CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault,
-                                   ctx->up_stream));
-        }
-      }
-    }
-    CU_TRY(flush());
-    if (ndown > 0) {   // downsample_cameras: halve the frames where they landed, in front of the pre-processing
-      CU_TRY(ctx->down_jobs.upload(ctx->up_stream, (size_t)ndown));
-      CU_TRY(launch_downsample(ctx->up_stream, ctx->down_jobs.d, ndown, max_dw, max_dh));
-      ctx->stats[1] += 1;
-    }
-    CU_TRY(ctx->pre_jobs.upload(ctx->up_stream, (size_t)npre));
-  }
-  {
-    HOSTPROF(s0_launch_preprocess);
-    CU_TRY(launch_preprocess(ctx->up_stream, ctx->pre_jobs.d, npre, dev->pyr_dev.d, ctx->clahe_lut.d, any_clahe, max_band));
+    const PreBuffers B{&ctx->pre_jobs, &ctx->down_jobs, &ctx->clahe_lut};
+    int e = issue_preprocess(dev, ctx->up_stream, B, items, ctx->stats);
+    if (e != OK) { ctx->cuda_err = dev->cuda_err; return e; }
     CU_TRY(cudaEventRecord(ctx->up_done, ctx->up_stream));
   }
-  ctx->stats[1] += (npre > 0) ? (unsigned)(1 + 2 * any_clahe) : 0u;
   if (any_first) {
-    CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->up_done, 0));
+    CU_TRY(wait_new_frames());
     CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d, ctx->fast_cnt_dev.d,
                        ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
   }
@@ -1308,7 +1420,7 @@ int Pass::stage2() {
     max_n = std::max(max_n, std::max(u.L.lk_n, u.R.lk_n));
   }
   HOSTPROF(s2_launches);
-  CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->up_done, 0));   // the temporal LK reads the new pyramids
+  CU_TRY(wait_new_frames());   // the temporal LK reads the new pyramids
   CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)nlk));
   CU_TRY(ctx->rs_jobs.upload(ctx->stream, (size_t)nrs));
   CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,
@@ -1341,6 +1453,78 @@ int Pass::stage3() {
   return OK;
 }
 
+// The checks of TrackKLT::feed_new_camera on one message; new cameras get their device memory here.
+static int validate_request(Context *ctx, FeedRequest &rq, bool announcing) {
+  Rig &rig = *rq.rig;
+  const Params &P = rig.prm;
+  if (rq.n <= 0 || !rq.sensor_ids || !rq.images || (!announcing && !rq.masks)) return E_BADMSG;   // TrackKLT.cpp:37-43
+  if (P.use_stereo && rq.n > 2) return E_BADMSG;                                                  // :90-93
+  if (P.win_size != LK_WIN) return E_ARG;
+  for (int k = 0; k < rq.n; k++) {
+    CamState *c = rig.find_cam(rq.sensor_ids[k]);
+    if (!c) return E_CAMID;                                                                       // :53-54 (.at throws)
+    const HostImage &im = rq.images[k];
+    if (!im.p || im.w <= 0 || im.h <= 0 || im.w > 4095 || im.h > 4095) return E_BADMSG;
+    if (!announcing && rq.masks[k].p && (rq.masks[k].w != im.w || rq.masks[k].h != im.h)) return E_BADMSG;
+    for (int q = 0; q < k; q++)
+      if (rq.sensor_ids[q] == rq.sensor_ids[k]) return E_BADMSG;
+    if (c->raw < 0) {
+      int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size, P.downsample_cameras != 0);
+      if (e != OK) return e;
+    } else if (c->in_w != im.w || c->in_h != im.h) return E_SIZE;
+    const unsigned ahead = c->n_sub - c->n_fed;   // frames announced and not yet fed
+    if (announcing) {
+      if (ahead >= 2) return E_ARG;               // the third slot is the only one a feed in flight does not read
+    } else if (ahead > 0 && c->sub_src[(c->n_fed + 1) % PYR_SLOTS] != im.p) {
+      return E_ARG;                               // the feed after a submit must be given the announced frame
+    }
+  }
+  return OK;
+}
+
+int submit_batch(Context *ctx, FeedRequest *reqs, int n) {
+  HOSTPROF(submit_total);
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  int worst = OK;
+  std::vector<PreItem> &items = ctx->pf_items;
+  items.clear();
+  const int q = (int)(ctx->pf_seq++ % Context::PF_RING);
+  if (ctx->pf_used[q]) CU_TRY(cudaEventSynchronize(ctx->pf_evt[q]));   // its job lists are about to be rewritten (8 calls old)
+  for (int i = 0; i < n; i++) {
+    FeedRequest &rq = reqs[i];
+    rq.status = validate_request(ctx, rq, true);
+    if (rq.status != OK) {
+      rq.rig->last_error = rq.status;
+      if (rq.status > worst) worst = rq.status;
+      continue;
+    }
+    for (int k = 0; k < rq.n; k++) {
+      CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
+      c.n_sub++;
+      const int slot = (int)(c.n_sub % PYR_SLOTS);
+      c.sub_src[slot] = rq.images[k].p;
+      c.sub_evt[slot] = q;
+      items.push_back(PreItem{&c, &rq.images[k], slot, rq.rig->prm.histogram_method, rq.rig->prm.downsample_cameras != 0});
+    }
+  }
+  if (ctx->upload_tables() != OK) return E_CUDA;
+  HOSTPROF(submit_issue);
+  const PreBuffers B{&ctx->pf_pre[q], &ctx->pf_down[q], &ctx->pf_clahe[q]};
+  static const int group = [] {
+    // images per upload + pre-processing group of an announced batch; 0 = one group.  Measured (32 streams): groups of 8
+    // or 16 images cost more on the caller's thread (a cluster launch per group) than their earlier pyramids give back
+    const char *e = getenv("UVIO_KLT_SUBMIT_GROUP");
+    int v = e ? atoi(e) : 0;
+    return v < 0 ? 0 : v;
+  }();
+  int e = issue_preprocess(ctx, ctx->pf_stream, B, items, ctx->stats, group);
+  if (e != OK) return e;
+  CU_TRY(cudaEventRecord(ctx->pf_evt[q], ctx->pf_stream));
+  ctx->pf_used[q] = true;
+  return worst;
+}
+
 int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   HOSTPROF(fb_total);
   std::lock_guard<std::mutex> guard(ctx->mtx);
@@ -1355,28 +1539,11 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   std::vector<FeedRequest *> good;
   for (int i = 0; i < n; i++) {
     FeedRequest &rq = reqs[i];
-    Rig &rig = *rq.rig;
     rq.status = OK;
-    rig.obs.clear();
-    const Params &P = rig.prm;
-    if (rq.n <= 0 || !rq.sensor_ids || !rq.images || !rq.masks) { fail(rq, E_BADMSG); continue; }   // TrackKLT.cpp:37-43
-    if (P.use_stereo && rq.n > 2) { fail(rq, E_BADMSG); continue; }                                   // :90-93
-    if (P.win_size != LK_WIN) { fail(rq, E_ARG); continue; }
-    bool bad = false;
-    for (int k = 0; k < rq.n && !bad; k++) {
-      CamState *c = rig.find_cam(rq.sensor_ids[k]);
-      if (!c) { fail(rq, E_CAMID); bad = true; break; }                                               // :53-54 (.at throws)
-      const HostImage &im = rq.images[k];
-      if (!im.p || im.w <= 0 || im.h <= 0 || im.w > 4095 || im.h > 4095) { fail(rq, E_BADMSG); bad = true; break; }
-      if (rq.masks[k].p && (rq.masks[k].w != im.w || rq.masks[k].h != im.h)) { fail(rq, E_BADMSG); bad = true; break; }
-      for (int q = 0; q < k; q++) if (rq.sensor_ids[q] == rq.sensor_ids[k]) { fail(rq, E_BADMSG); bad = true; }
-      if (bad) break;
-      if (c->raw < 0) {
-        int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size, P.downsample_cameras != 0);
-        if (e != OK) { fail(rq, e); bad = true; break; }
-      } else if (c->in_w != im.w || c->in_h != im.h) { fail(rq, E_SIZE); bad = true; break; }
-    }
-    if (!bad) good.push_back(&rq);
+    rq.rig->obs.clear();
+    int e = validate_request(ctx, rq, false);
+    if (e != OK) fail(rq, e);
+    else good.push_back(&rq);
   }
   if (ctx->upload_tables() != OK) return E_CUDA;
   // ---- split the trackers over the lanes (contiguous shares); every host thread drives `depth` lanes stage by stage ---------
@@ -1422,7 +1589,7 @@ static int slot_pyr(Rig *rig, size_t cam_id, int slot, CamState **out) {
   CamState *c = rig->find_cam(cam_id);
   if (!c || c->raw < 0) return -1;
   *out = c;
-  return c->pyr[slot ? 1 - c->cur : c->cur];
+  return c->pyr[slot ? c->last() : c->cur];
 }
 
 int stage_get_level(Rig *rig, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *h, int *nlv) {

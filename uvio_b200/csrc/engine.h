@@ -50,6 +50,8 @@ struct HostImage {              // caller-owned view
   int w, h;
 };
 
+constexpr int PYR_SLOTS = 3;
+
 struct CamState {               // per camera id (TrackBase.h:180-190: img_last, img_mask_last, pts_last, ids_last)
   size_t cam_id = 0;
   int cam_model_idx = -1;       // index into the context's CamModel table
@@ -57,14 +59,20 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   int w = 0, h = 0;             // size of the images this camera tracks on (fixed after the first frame)
   int in_w = 0, in_h = 0;       // size of the images it is fed: (w, h), or twice that with downsample_cameras
   int raw_in = -1;              // upload buffer of the fed frame (== raw unless downsample_cameras)
-  int pyr[2] = {-1, -1};        // the two pyramid slots in the context's table
-  int cur = 0;                  // slot holding the frame being fed ("curr"); 1-cur is "last"
+  int pyr[PYR_SLOTS] = {-1, -1, -1};   // pyramid slots in the context's table; frame number k of this camera lives in slot k % 3
+  int cur = 0;                  // slot holding the frame being fed ("curr")
+  int last() const { return (cur + PYR_SLOTS - 1) % PYR_SLOTS; }   // slot of the frame before it ("last")
+  // frames announced ahead of their feed (submit_batch) are uploaded and pre-processed into the third slot while the feed of
+  // the frame before them is still reading the other two
+  unsigned n_sub = 0, n_fed = 0;                 // frames uploaded (by submit or by feed itself) / frames fed
+  const uint8_t *sub_src[PYR_SLOTS] = {nullptr, nullptr, nullptr};   // image pointer a submitted frame was announced with
+  int sub_evt[PYR_SLOTS] = {-1, -1, -1};         // context event that marks its pre-processing done
   int raw = -1;                 // the frame the pre-processing reads: the upload buffer, or its halved copy
   bool have_last = false;
   std::vector<Pt> pts_last;
   std::vector<size_t> ids_last;
-  std::vector<uint8_t> mask[2]; // host copies of the masks, indexed like pyr[]
-  bool mask_nonzero[2] = {false, false};
+  std::vector<uint8_t> mask[PYR_SLOTS]; // host copies of the masks, indexed like pyr[]
+  bool mask_nonzero[PYR_SLOTS] = {false, false, false};
 };
 
 enum Status { OK = 0, E_BADMSG = 1, E_CAMID = 2, E_CUDA = 3, E_ARG = 4, E_SIZE = 5 };
@@ -103,6 +111,9 @@ struct FeedRequest {            // one feed_new_camera call (utils/sensor_data.h
 
 // Feeds one frame to each of the given rigs (all on one device) with batched GPU rounds. Returns the worst status.
 int feed_batch(Context *ctx, FeedRequest *reqs, int n);
+// Announces the next message of each rig ahead of its feed: the frames are uploaded and pre-processed asynchronously and the
+// call returns at once.  The rig's next feed must be given the same images (same pointers), valid until that feed returns.
+int submit_batch(Context *ctx, FeedRequest *reqs, int n);
 
 Context *context_for_device(int device, int *err);
 int context_cuda_error(Context *ctx);

@@ -5,6 +5,7 @@
 
 #include <cooperative_groups.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "fast_body.h"

@@ -76,6 +76,8 @@ def lib():
         L.uvio_klt_destroy.restype = None
         L.uvio_klt_feed.argtypes = [vp, C.POINTER(UvioFrame)]
         L.uvio_klt_feed_batch.argtypes = [C.POINTER(vp), C.POINTER(UvioFrame), ci]
+        L.uvio_klt_submit.argtypes = [vp, C.POINTER(UvioFrame)]
+        L.uvio_klt_submit_batch.argtypes = [C.POINTER(vp), C.POINTER(UvioFrame), ci]
         L.uvio_klt_get_new_observations.argtypes = [vp, vp, ci, C.POINTER(ci)]
         L.uvio_klt_get_last.argtypes = [vp, sz, vp, vp, ci, C.POINTER(ci)]
         L.uvio_klt_set_num_features.argtypes = [vp, ci]
@@ -247,6 +249,7 @@ class TrackKLT:
         self.database = FeatureDatabase()                       # TrackBase.cpp:32
         self.num_features = int(numfeats)
         self._obs = np.zeros(4096, OBS_DTYPE)
+        self._announced: list = []
 
     def close(self):
         if getattr(self, "_h", None):
@@ -266,7 +269,18 @@ class TrackKLT:
         rc = lib().uvio_klt_feed(self._h, C.byref(f))
         self._after_feed(rc, message.timestamp)
 
+    def submit(self, message: CameraData):
+        """uvio_klt_submit: announce the next message (its upload and pre-processing start now); feed the same message next."""
+        keep: list = []
+        f = _pack_frame(message, keep)
+        rc = lib().uvio_klt_submit(self._h, C.byref(f))
+        if rc != UVIO_OK:
+            raise UvioError(rc, "uvio_klt_submit", lib().uvio_klt_cuda_error(self._h))
+        self._announced.append(keep)          # the image memory must outlive the feed
+
     def _after_feed(self, rc: int, timestamp: float):
+        if self._announced:
+            self._announced.pop(0)
         if rc == UVIO_E_BADMSG:
             raise SystemExit("[ERROR]: MESSAGE DATA SIZES DO NOT MATCH OR EMPTY!!!")   # std::exit(EXIT_FAILURE), TrackKLT.cpp:42
         if rc != UVIO_OK:
@@ -394,6 +408,19 @@ def feed_batch(trackers: Sequence[TrackKLT], messages: Sequence[CameraData]):
     rc = lib().uvio_klt_feed_batch(hs, frames, n)
     for t, m, f in zip(trackers, messages, frames):
         t._after_feed(f.status if rc in (UVIO_OK, f.status) else rc, m.timestamp)
+
+
+def submit_batch(trackers: Sequence[TrackKLT], messages: Sequence[CameraData]):
+    """uvio_klt_submit_batch: announce the next frame of each of n trackers (one upload + one pre-processing launch set)."""
+    n = len(trackers)
+    keep: list = []
+    frames = (UvioFrame * n)(*[_pack_frame(m, keep) for m in messages])
+    hs = (C.c_void_p * n)(*[t._h for t in trackers])
+    rc = lib().uvio_klt_submit_batch(hs, frames, n)
+    if rc != UVIO_OK:
+        raise UvioError(rc, "uvio_klt_submit_batch", lib().uvio_klt_cuda_error(trackers[0]._h))
+    for t in trackers:
+        t._announced.append(keep)
 
 
 def make_tracker(cfg, device: int = 0, **over) -> TrackKLT:
