@@ -161,10 +161,23 @@ struct DevVec {
 
 class Context;
 
+// after the stream was synchronised: every (kernel mark, next mark) interval is one kernel's duration
+static void fold_prof(KernelProf &prof, double *ms_sum, unsigned long long *launches) {
+  for (int i = 0; i + 1 < prof.n; i++) {
+    if (prof.id[i] < 0) continue;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, prof.ev[i], prof.ev[i + 1]) == cudaSuccess) {
+      ms_sum[prof.id[i]] += ms;
+      launches[prof.id[i]] += 1;
+    }
+  }
+  prof.n = 0;
+}
+
 // One frame to upload and pre-process: the shared front of a feed (frames that were not announced) and of submit_batch.
 struct PreItem {
   CamState *cam;
-  const HostImage *im;
+  HostImage im;                  // by value: an announced batch is issued after submit_batch has returned
   int slot;                      // destination pyramid slot
   int method;                    // TrackBase::HistogramMethod
   bool downsample;
@@ -212,17 +225,9 @@ struct Lane {
   void prof_end() {
     if (g_prof == &prof) g_prof = nullptr;
   }
-  void prof_fold() {   // after the stream was synchronised: every (kernel mark, next mark) interval is one kernel's duration
+  void prof_fold() {   // after the stream was synchronised
     if (!prof_on || g_prof != &prof) return;
-    for (int i = 0; i + 1 < prof.n; i++) {
-      if (prof.id[i] < 0) continue;
-      float ms = 0.f;
-      if (cudaEventElapsedTime(&ms, prof.ev[i], prof.ev[i + 1]) == cudaSuccess) {
-        prof_ms[prof.id[i]] += ms;
-        prof_launches[prof.id[i]] += 1;
-      }
-    }
-    prof.n = 0;
+    fold_prof(prof, prof_ms, prof_launches);
   }
   // round 1
   JobVec<DownJob> down_jobs;     // downsample_cameras: frames (upload stream)
@@ -300,13 +305,39 @@ class Context {
   JobVec<PreJob> pf_pre[PF_RING];
   JobVec<DownJob> pf_down[PF_RING];
   DevVec<uint8_t> pf_clahe[PF_RING];
-  std::vector<PreItem> pf_items;
+  std::vector<PreItem> pf_items[PF_RING];
+  // The queued work of submit_batch is issued by a thread of its own, so the caller gets on with the feed of the frame
+  // before (the issue costs ~60 us of CUDA calls per batch).  pf_issued = batches whose event has been recorded.
+  std::thread uploader;
+  std::mutex pf_mtx;
+  std::condition_variable pf_cv;
+  std::vector<int> pf_queue;                       // ring entries waiting to be issued, in order
+  unsigned long long pf_queued = 0, pf_issued = 0; // batches handed to / finished by the uploader (under pf_mtx)
+  unsigned long long pf_entry_seq[PF_RING] = {0};  // batch number last issued from each ring entry
+  bool pf_quit = false;
+  int pf_error = OK;
+  int pf_group = 0;
+  std::atomic<unsigned long long> pf_stats[3];     // [1] launches, [2] bytes uploaded (indices as in stats[])
+  // per-kernel timing of the announced batches (same switch as the lanes'): marks of a batch are folded before the next
+  KernelProf pf_prof;
+  std::atomic<bool> pf_prof_on{false};
+  unsigned pf_prof_mask = ~0u;
+  double pf_prof_ms[K_COUNT] = {0};
+  unsigned long long pf_prof_launches[K_COUNT] = {0};
+  void uploader_loop();
+  void uploader_drain();                           // returns when everything queued has been issued
+  int wait_issued(unsigned long long seq);         // returns once batch number `seq` has been issued
+  unsigned long long pf_queued_next() {            // number the batch being assembled will get
+    std::lock_guard<std::mutex> lk(pf_mtx);
+    return pf_queued + 1;
+  }
   uint8_t *raw_arena = nullptr;   // next free byte of the current upload-buffer chunk
   size_t raw_arena_left = 0;
 
   int upload_tables() {
     Context *ctx = this;
     if (!tables_dirty) return OK;
+    uploader_drain();   // it reads the tables that are about to move
     CU_TRY(cudaDeviceSynchronize());
     CU_TRY(pyr_dev.reserve(pyr_tab.size()));
     CU_TRY(cam_dev.reserve(cam_tab.size()));
@@ -475,7 +506,25 @@ class Pool {
   std::atomic<bool> quit{false};
 };
 
+void Context::uploader_drain() {
+  std::unique_lock<std::mutex> lk(pf_mtx);
+  pf_cv.wait(lk, [&] { return pf_issued == pf_queued; });
+}
+int Context::wait_issued(unsigned long long seq) {
+  std::unique_lock<std::mutex> lk(pf_mtx);
+  pf_cv.wait(lk, [&] { return pf_issued >= seq; });
+  return pf_error;
+}
+
 Context::~Context() {
+  if (uploader.joinable()) {
+    {
+      std::lock_guard<std::mutex> lk(pf_mtx);
+      pf_quit = true;
+    }
+    pf_cv.notify_all();
+    uploader.join();
+  }
   delete pool;
   lanes.clear();
   if (pf_stream) cudaStreamDestroy(pf_stream);
@@ -552,6 +601,8 @@ Context *context_for_device(int device, int *err) {
       return nullptr;
     }
   c->pool = new Pool(c->threads - 1);
+  for (auto &a : c->pf_stats) a.store(0);
+  c->uploader = std::thread([raw = c.get()] { raw->uploader_loop(); });
   Context *p = c.get();
   table[device] = std::move(c);
   return p;
@@ -1085,7 +1136,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
   for (int j = 0; j < nimg; j++) {
     const PreItem &it = items[j];
     CamState &c = *it.cam;
-    const HostImage &im = *it.im;
+    const HostImage &im = it.im;
     B.pre->h[j] = PreJob{ctx->raw_tab[c.raw], c.pyr[it.slot], it.method};
     max_band = std::max(max_band, ((c.h + 7) / 8 + 1) * c.w);
     cudaPointerAttributes attr;
@@ -1116,7 +1167,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
     int gdown = 0;
     for (int j = g0; j < g1; j++) {
       const PreItem &it = items[j];
-      const HostImage &im = *it.im;
+      const HostImage &im = it.im;
       const ImgView &raw = ctx->raw_tab[it.cam->raw_in];
       gdown += it.downsample;
       if (on_dev[j]) continue;
@@ -1174,6 +1225,7 @@ int Pass::stage0() {
   wait_evts = 0;
   std::vector<HostImage> &zero_masks = ctx->zero_masks;   // masks of this pass already found to be all zero
   zero_masks.clear();
+  unsigned long long need_seq = 0;   // last announced batch this pass consumes: its event must have been recorded
   for (int i = 0; i < n; i++) {
     FeedRequest &rq = *reqs[i];
     Rig &rig = *rq.rig;
@@ -1185,8 +1237,11 @@ int Pass::stage0() {
       if (!announced) c.n_sub++;
       c.n_fed++;
       c.cur = (int)(c.n_fed % PYR_SLOTS);
-      if (announced) wait_evts |= 1u << c.sub_evt[c.cur];
-      else items.push_back(PreItem{&c, &rq.images[k], c.cur, P.histogram_method, P.downsample_cameras != 0});
+      if (announced) {
+        wait_evts |= 1u << c.sub_evt[c.cur];
+        need_seq = std::max(need_seq, c.sub_seq[c.cur]);
+      }
+      else items.push_back(PreItem{&c, rq.images[k], c.cur, P.histogram_method, P.downsample_cameras != 0});
       // the same mask memory given to several cameras of this call (a rig's shared mask, a batch's common one) is scanned once
       const HostImage &mk = rq.masks[k];
       bool known_zero = false;
@@ -1221,6 +1276,7 @@ int Pass::stage0() {
       }
     }
   }
+  if (need_seq && dev->wait_issued(need_seq) != OK) { ctx->cuda_err = dev->cuda_err; return E_CUDA; }
   if (n_mask_jobs > 0) {
     // downsample_cameras with masks that mask something: cv::pyrDown of the mask (VioManager.cpp:275-277).  The host
     // bookkeeping below reads the halved mask (first frames detect on the frame being fed), so this small job runs on the
@@ -1469,6 +1525,7 @@ static int validate_request(Context *ctx, FeedRequest &rq, bool announcing) {
     for (int q = 0; q < k; q++)
       if (rq.sensor_ids[q] == rq.sensor_ids[k]) return E_BADMSG;
     if (c->raw < 0) {
+      ctx->uploader_drain();   // a new camera grows the tables a batch in flight may be reading
       int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size, P.downsample_cameras != 0);
       if (e != OK) return e;
     } else if (c->in_w != im.w || c->in_h != im.h) return E_SIZE;
@@ -1482,15 +1539,61 @@ static int validate_request(Context *ctx, FeedRequest &rq, bool announcing) {
   return OK;
 }
 
+// Issues the batches submit_batch queued: H2D pieces, the optional halving, equalisation + pyramids, then the batch's event.
+void Context::uploader_loop() {
+  Context *ctx = this;
+  cudaSetDevice(device);
+  while (true) {
+    int q;
+    {
+      std::unique_lock<std::mutex> lk(pf_mtx);
+      pf_cv.wait(lk, [&] { return pf_quit || !pf_queue.empty(); });
+      if (pf_queue.empty()) return;   // quit
+      q = pf_queue.front();
+    }
+    unsigned long long st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const PreBuffers B{&pf_pre[q], &pf_down[q], &pf_clahe[q]};
+    if (pf_prof_on.load()) {
+      if (!pf_prof.ready) {
+        for (int i = 0; i < KernelProf::MAX_MARKS; i++) cudaEventCreate(&pf_prof.ev[i]);
+        pf_prof.ready = true;
+      }
+      if (pf_prof.n > 0) {   // the batch before this one: wait for it and take its intervals
+        cudaStreamSynchronize(pf_stream);
+        std::lock_guard<std::mutex> lk(pf_mtx);
+        fold_prof(pf_prof, pf_prof_ms, pf_prof_launches);
+      }
+      pf_prof.open = false;
+      pf_prof.mask = pf_prof_mask;
+      g_prof = &pf_prof;
+    } else {
+      g_prof = nullptr;
+    }
+    int e = issue_preprocess(ctx, pf_stream, B, pf_items[q], st, pf_group);
+    if (e == OK && cudaEventRecord(pf_evt[q], pf_stream) != cudaSuccess) e = E_CUDA;
+    pf_stats[1] += st[1];
+    pf_stats[2] += st[2];
+    {
+      std::lock_guard<std::mutex> lk(pf_mtx);
+      pf_queue.erase(pf_queue.begin());
+      pf_issued++;
+      if (e != OK) pf_error = e;
+    }
+    pf_cv.notify_all();
+  }
+}
+
 int submit_batch(Context *ctx, FeedRequest *reqs, int n) {
   HOSTPROF(submit_total);
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
   int worst = OK;
-  std::vector<PreItem> &items = ctx->pf_items;
-  items.clear();
   const int q = (int)(ctx->pf_seq++ % Context::PF_RING);
-  if (ctx->pf_used[q]) CU_TRY(cudaEventSynchronize(ctx->pf_evt[q]));   // its job lists are about to be rewritten (8 calls old)
+  // the ring entry is about to be rewritten: its previous batch (8 calls old) must have been issued and have run
+  if (ctx->wait_issued(ctx->pf_entry_seq[q]) != OK) return E_CUDA;
+  if (ctx->pf_used[q]) CU_TRY(cudaEventSynchronize(ctx->pf_evt[q]));
+  std::vector<PreItem> &items = ctx->pf_items[q];
+  items.clear();
   for (int i = 0; i < n; i++) {
     FeedRequest &rq = reqs[i];
     rq.status = validate_request(ctx, rq, true);
@@ -1505,22 +1608,25 @@ int submit_batch(Context *ctx, FeedRequest *reqs, int n) {
       const int slot = (int)(c.n_sub % PYR_SLOTS);
       c.sub_src[slot] = rq.images[k].p;
       c.sub_evt[slot] = q;
-      items.push_back(PreItem{&c, &rq.images[k], slot, rq.rig->prm.histogram_method, rq.rig->prm.downsample_cameras != 0});
+      c.sub_seq[slot] = ctx->pf_queued_next();
+      items.push_back(PreItem{&c, rq.images[k], slot, rq.rig->prm.histogram_method, rq.rig->prm.downsample_cameras != 0});
     }
   }
   if (ctx->upload_tables() != OK) return E_CUDA;
-  HOSTPROF(submit_issue);
-  const PreBuffers B{&ctx->pf_pre[q], &ctx->pf_down[q], &ctx->pf_clahe[q]};
   static const int group = [] {
     // images per upload + pre-processing group of an announced batch; 0 = one group.  Measured (32 streams): groups of 8
-    // or 16 images cost more on the caller's thread (a cluster launch per group) than their earlier pyramids give back
+    // or 16 images cost more (a cluster launch per group) than their earlier pyramids give back
     const char *e = getenv("UVIO_KLT_SUBMIT_GROUP");
     int v = e ? atoi(e) : 0;
     return v < 0 ? 0 : v;
   }();
-  int e = issue_preprocess(ctx, ctx->pf_stream, B, items, ctx->stats, group);
-  if (e != OK) return e;
-  CU_TRY(cudaEventRecord(ctx->pf_evt[q], ctx->pf_stream));
+  {
+    std::lock_guard<std::mutex> lk(ctx->pf_mtx);
+    ctx->pf_group = group;
+    ctx->pf_queue.push_back(q);
+    ctx->pf_entry_seq[q] = ++ctx->pf_queued;
+  }
+  ctx->pf_cv.notify_all();
   ctx->pf_used[q] = true;
   return worst;
 }
@@ -1777,6 +1883,24 @@ int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long 
     if (ms) ms[k] = 0;
     if (launches) launches[k] = 0;
   }
+  ctx->uploader_drain();
+  {
+    cudaStreamSynchronize(ctx->pf_stream);
+    std::lock_guard<std::mutex> lk(ctx->pf_mtx);
+    if (ctx->pf_prof.n > 0) fold_prof(ctx->pf_prof, ctx->pf_prof_ms, ctx->pf_prof_launches);
+    for (int k = 0; k < K_COUNT; k++) {
+      if (ms) ms[k] += ctx->pf_prof_ms[k];
+      if (launches) launches[k] += ctx->pf_prof_launches[k];
+    }
+    if (enable >= 0) {
+      ctx->pf_prof_on.store(enable != 0);
+      ctx->pf_prof_mask = enable > 1 ? (unsigned)(enable >> 1) : ~0u;
+      if (enable) {
+        memset(ctx->pf_prof_ms, 0, sizeof(ctx->pf_prof_ms));
+        memset(ctx->pf_prof_launches, 0, sizeof(ctx->pf_prof_launches));
+      }
+    }
+  }
   for (auto &ln : ctx->lanes) {
     for (int k = 0; k < K_COUNT; k++) {
       if (ms) ms[k] += ln->prof_ms[k];
@@ -1797,6 +1921,8 @@ int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long 
 void context_stats(Context *ctx, unsigned long long out[12]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
   memcpy(out, ctx->stats, sizeof(ctx->stats));
+  out[1] += ctx->pf_stats[1].load();
+  out[2] += ctx->pf_stats[2].load();
   out[8] = out[9] = out[10] = out[11] = 0;
   unsigned long long w[4] = {0, 0, 0, 0};
   if (cudaSetDevice(ctx->device) == cudaSuccess && read_lk_work(w, 0) == cudaSuccess) {

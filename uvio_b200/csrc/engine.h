@@ -67,6 +67,7 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   unsigned n_sub = 0, n_fed = 0;                 // frames uploaded (by submit or by feed itself) / frames fed
   const uint8_t *sub_src[PYR_SLOTS] = {nullptr, nullptr, nullptr};   // image pointer a submitted frame was announced with
   int sub_evt[PYR_SLOTS] = {-1, -1, -1};         // context event that marks its pre-processing done
+  unsigned long long sub_seq[PYR_SLOTS] = {0, 0, 0};   // number of the announced batch it went up with
   int raw = -1;                 // the frame the pre-processing reads: the upload buffer, or its halved copy
   bool have_last = false;
   std::vector<Pt> pts_last;
