@@ -93,7 +93,7 @@ cudaError_t launch_subpix(cudaStream_t, const SubpixItem *items, int n, const Py
 }
 
 cudaError_t launch_lk(cudaStream_t, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
-                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev) {
+                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool) {
   GroupSeq g;
   LkSmem s;
   for (int i = 0; i < n; i++) {
@@ -114,7 +114,7 @@ cudaError_t read_lk_work(unsigned long long out[4], int) { out[0] = out[1] = out
 
 cudaError_t launch_ransac(cudaStream_t, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk,
                           const uint8_t *status, const CamModel *cams, float *p0n, float *p1n, float *p1n_host, uint8_t *mask_host,
-                          uint8_t *mask_dev) {
+                          uint8_t *mask_dev, bool) {
   GroupSeq g;
   std::vector<float> buf((size_t)4 * max_n + 4);
   for (int j = 0; j < njobs; j++) {

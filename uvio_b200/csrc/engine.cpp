@@ -101,6 +101,13 @@ static bool jobs_mapped() {
   }();
   return v;
 }
+static bool pdl_on() {   // UVIO_KLT_PDL=0 turns the programmatic dependent launches off (A/B measurements)
+  static const bool v = [] {
+    const char *e = getenv("UVIO_KLT_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return v;
+}
 static bool jobs_copied() {
   static const bool v = [] {
     const char *e = getenv("UVIO_KLT_JOBS");
@@ -1432,8 +1439,9 @@ int Pass::stage1() {
           }
     }
     CU_TRY(ctx->lk_items.upload(ctx->stream, (size_t)nlk));
+    // chained and with its items in mapped memory, the launch may overlap the sub-pixel kernel (it waits for it on the device)
     CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, chained ? ctx->sp_out_dev.d : nullptr, 30, 0.01,
-                     ctx->lk_out.d, ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d));
+                     ctx->lk_out.d, ctx->lk_status.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d, chained && ctx->lk_items.mapped && pdl_on()));
   }
   seg(2);
   return OK;
@@ -1482,7 +1490,8 @@ int Pass::stage2() {
   CU_TRY(launch_lk(ctx->stream, ctx->lk_items.d, nlk, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->lk_out.d, ctx->lk_status.d,
                    ctx->lk_out_dev.d, ctx->lk_status_dev.d));
   CU_TRY(launch_ransac(ctx->stream, ctx->rs_jobs.d, nrs, max_n, ctx->lk_items.d, ctx->lk_out_dev.d, ctx->lk_status_dev.d,
-                       dev->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d));
+                       dev->cam_dev.d, ctx->p0n_dev.d, ctx->p1n_dev.d, ctx->p1n.d, ctx->rs_mask.d, ctx->rs_mask_dev.d,
+                       nlk > 0 && ctx->rs_jobs.mapped && ctx->lk_items.mapped && pdl_on()));
   seg(4);
   return OK;
 }

@@ -289,10 +289,34 @@ cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int WARPS_PER_BLOCK = 4;
 
+// Programmatic dependent launch (sm_90+): a kernel launched with the attribute may be scheduled while the kernel before it
+// in the stream is still running; it reads what does not depend on that kernel (its job list, in host memory: one PCIe
+// round trip that would otherwise follow the launch), then waits for the predecessor's results with pdl_wait().
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_release_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <class... KArgs, class... Args>
+static cudaError_t launch_after(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool overlap_predecessor,
+                                Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = overlap_predecessor ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_subpix(const SubpixItem *items, int n, const PyrDesc *pyr_tab,
                                                                  const float *mask, float *out_xy, float *out_xy_dev) {
   __shared__ SubpixSmem sm[WARPS_PER_BLOCK];
   __shared__ float smask[SP_N];
+  pdl_release_dependents();   // the stereo LK chained on this launch may fetch its items meanwhile
   for (int i = threadIdx.x; i < SP_N; i += blockDim.x) smask[i] = mask[i];
   __syncthreads();
   const int wid = threadIdx.x >> 5, i = blockIdx.x * WARPS_PER_BLOCK + wid;
@@ -358,9 +382,11 @@ __global__ void LK_BOUNDS k_lk(const LkItem *items, int n, const PyrDesc *pyr_ta
                                                              uint8_t *status_dev) {
   __shared__ LkSmem sm[LK_WARPS_PER_BLOCK];
   const int wid = threadIdx.x >> 5, i = blockIdx.x * LK_WARPS_PER_BLOCK + wid;
+  pdl_release_dependents();   // the RANSAC launch behind this one may start on what it can do without the tracks
   if (i >= n) return;
   const LkItem it = items[i];
   float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
+  pdl_wait();                 // the refined corners (init_from_dev) and the kernel before this one's use of out_dev / status_dev
   if (init_from_dev) {
     px = nx = init_from_dev[2 * i];
     py = ny = init_from_dev[2 * i + 1];
@@ -402,14 +428,13 @@ cudaError_t read_lk_work(unsigned long long out[4], int reset) {
 }
 
 cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
-                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev) {
+                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool overlap) {
   if (n <= 0) return cudaSuccess;
   prof_mark(st, K_LK);
-  k_lk<<<(n + LK_WARPS_PER_BLOCK - 1) / LK_WARPS_PER_BLOCK, LK_WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, init_from_dev, max_count,
-                                                                                  eps * eps, out_host, status_host, out_dev,
-                                                                                  status_dev);
+  cudaError_t e = launch_after(k_lk, dim3((n + LK_WARPS_PER_BLOCK - 1) / LK_WARPS_PER_BLOCK), dim3(LK_WARPS_PER_BLOCK * 32), 0, st, overlap,
+                               items, n, pyr_tab, init_from_dev, max_count, eps * eps, out_host, status_host, out_dev, status_dev);
   prof_mark(st, -1);
-  return cudaGetLastError();
+  return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -425,12 +450,18 @@ __global__ void __launch_bounds__(RANSAC_THREADS) k_ransac(const RansacJob *jobs
   const RansacJob job = jobs[blockIdx.x];
   const int n = job.n;
   const CamModel c0 = cams[job.cam0], c1 = cams[job.cam1];
+  // the old points come from the job list (host): undistorted while the LK launch ahead of this one is still tracking
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const int k = job.off + i;
     float a, b;
     undistort_point(c0, items[k].px, items[k].py, a, b);
     p0n[2 * k] = a;
     p0n[2 * k + 1] = b;
+  }
+  pdl_wait();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int k = job.off + i;
+    float a, b;
     const LkOut o = lk[k];
     undistort_point(c1, o.x, o.y, a, b);
     p1n[2 * k] = a;
@@ -455,7 +486,7 @@ __global__ void __launch_bounds__(RANSAC_THREADS) k_ransac(const RansacJob *jobs
 
 cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk_dev,
                           const uint8_t *status_dev, const CamModel *cams_dev, float *p0n_dev, float *p1n_dev, float *p1n_host,
-                          uint8_t *mask_host, uint8_t *mask_dev) {
+                          uint8_t *mask_host, uint8_t *mask_dev, bool overlap) {
   if (njobs <= 0) return cudaSuccess;
   size_t dyn = (size_t)4 * max_n * sizeof(float);
   static size_t configured = 0;
@@ -465,10 +496,10 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
     configured = dyn;
   }
   prof_mark(st, K_RANSAC);
-  k_ransac<<<njobs, RANSAC_THREADS, dyn, st>>>(jobs, items, lk_dev, status_dev, cams_dev, p0n_dev, p1n_dev, p1n_host, mask_host,
-                                               mask_dev);
+  cudaError_t e = launch_after(k_ransac, dim3(njobs), dim3(RANSAC_THREADS), dyn, st, overlap, jobs, items, lk_dev, status_dev, cams_dev,
+                               p0n_dev, p1n_dev, p1n_host, mask_host, mask_dev);
   prof_mark(st, -1);
-  return cudaGetLastError();
+  return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 }  // namespace uvio
