@@ -1,0 +1,83 @@
+"""Detection issued ahead of the next feed (engine.cpp, Lane::Ahead): the occupancy pass and the FAST launch of feed t+1 are
+issued when feed t ends.  Whatever they read may still change before feed t+1 -- set_num_features, change_feat_id, another
+batch composition, a tracker that lost every point -- and must then be redone; results never differ from the oracle's."""
+import numpy as np
+import pytest
+
+from uvio_b200 import configs
+from uvio_b200.track import CameraData, feed_batch, make_tracker
+
+from util import frames_for, log_arrays, masks_for
+
+
+def _run(make, n=9):
+    from oracle.trackklt_cv2 import make_oracle
+    cfg = configs.EUROC_MAV.with_(num_features=40)
+    frames = frames_for(cfg, n, stream_id=17, events=True)
+    masks = masks_for(cfg)
+    ora, trk = make_oracle(cfg), make(cfg)
+    total = 0
+    for k, (l, r) in enumerate(frames):
+        if k == 3:                                  # VioManagerHelper.cpp:124: the feature budget is raised after initialisation
+            ora.set_num_features(120)
+            trk.set_num_features(120)
+        if k == 5 and ora.ids_last[0]:              # TrackBase.cpp:230-248
+            old = ora.ids_last[0][0]
+            ora.change_feat_id(old, old + 100000)
+            trk.change_feat_id(old, old + 100000)
+        if k == 7:                                  # a blank frame: tracks are lost, the next feed may start over
+            l, r = np.zeros_like(l), np.zeros_like(r)
+        n0 = len(ora.database.log)
+        ora.feed_new_camera(0.05 * k, [0, 1], [l, r], masks)
+        trk.feed_new_camera(CameraData(0.05 * k, [0, 1], [l, r], masks))
+        oi, oc, ouv, _ = log_arrays(ora.database.log[n0:])
+        obs = trk.new_observations()
+        assert np.array_equal(obs["id"].astype(np.int64), oi), f"frame {k}: id stream differs"
+        assert np.array_equal(obs["cam_id"].astype(np.int64), oc), f"frame {k}: camera stream differs"
+        if len(oi):
+            assert np.array_equal(np.c_[obs["u"], obs["v"]], ouv), f"frame {k}: positions not bit-exact"
+        last = trk.get_last_ids()
+        for c in (0, 1):
+            assert np.array_equal(last[c].astype(np.int64), np.array(ora.ids_last[c], np.int64)), f"frame {k} cam {c}: ids_last"
+        total += len(oi)
+    return total
+
+
+def test_ahead_invalidation_sim(sim_tracker):
+    assert _run(sim_tracker) > 200
+
+
+@pytest.mark.gpu
+def test_ahead_invalidation_gpu():
+    assert _run(lambda c: make_tracker(c, device=0), n=14) > 400
+
+
+@pytest.mark.gpu
+def test_ahead_changing_batches_gpu():
+    """The trackers of a lane change from call to call (batch of 5, then singles, then another order): each stream must
+    still equal its own single-tracker run."""
+    cfg = configs.EUROC_MAV.with_(num_features=80)
+    n_trk, n = 5, 9
+    masks = masks_for(cfg)
+    seqs = [frames_for(cfg, n, stream_id=60 + s) for s in range(n_trk)]
+    ref = []
+    for s in range(n_trk):
+        t = make_tracker(cfg, device=0)
+        out = []
+        for k in range(n):
+            t.feed_new_camera(CameraData(0.05 * k, [0, 1], list(seqs[s][k]), masks))
+            out.append(t.new_observations().tobytes())
+        ref.append(out)
+    trks = [make_tracker(cfg, device=0) for _ in range(n_trk)]
+    for k in range(n):
+        msgs = [CameraData(0.05 * k, [0, 1], list(seqs[s][k]), masks) for s in range(n_trk)]
+        if k % 3 == 0:
+            feed_batch(trks, msgs)
+        elif k % 3 == 1:
+            for s in range(n_trk):
+                trks[s].feed_new_camera(msgs[s])
+        else:
+            order = [3, 1, 4, 0, 2]
+            feed_batch([trks[i] for i in order], [msgs[i] for i in order])
+        for s in range(n_trk):
+            assert trks[s].new_observations().tobytes() == ref[s][k], f"frame {k} tracker {s}"

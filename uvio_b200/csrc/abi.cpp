@@ -192,6 +192,7 @@ int uvio_klt_set_num_features(uvio_klt *h, int n) {
   if (!h || n <= 0) return UVIO_E_ARG;
   std::lock_guard<std::mutex> lk(h->rig->mtx);
   h->rig->prm.num_features = n;
+  h->rig->epoch++;
   return UVIO_OK;
 }
 
@@ -201,6 +202,7 @@ int uvio_klt_change_feat_id(uvio_klt *h, size_t id_old, size_t id_new) {
   for (auto &c : h->rig->cams)                       // TrackBase.cpp:241-247
     for (auto &id : c.ids_last)
       if (id == id_old) id = id_new;
+  h->rig->epoch++;
   return UVIO_OK;
 }
 

@@ -244,6 +244,18 @@ struct Lane {
   JobVec<PreJob> pre_jobs;
   std::vector<PreItem> pre_items;
   std::vector<HostImage> zero_masks;
+  // Detection issued ahead: when a feed ends, the occupancy pass and the FAST launch of the NEXT feed of the same trackers
+  // depend only on state that is final by then (pts_last, the frame that will be "last", its mask), so they are issued
+  // before the call returns and run while the caller reads the observations and prepares the next message.  The next
+  // pass on this lane uses them if it is made of the same units and nothing they read has changed since.
+  struct Ahead {
+    bool valid = false;
+    std::vector<unsigned long long> serial;   // per unit: rig serial, rig epoch, unit index in the rig, stereo flag
+    std::vector<unsigned> epoch;
+    std::vector<Unit *> unit;
+    std::vector<char> stereo;
+    int njobs = 0;
+  } ahead;
   DevVec<uint8_t> clahe_lut;
   JobVec<FastJob> fast_jobs;
   DevVec<uint32_t> fast_out_dev;
@@ -616,6 +628,8 @@ Context *context_for_device(int device, int *err) {
 }
 
 Rig::Rig(Context *c, const Params &p, const CamCalib *cc, int n_cams) : ctx(c), prm(p) {
+  static std::atomic<unsigned long long> next_serial{1};
+  serial = next_serial.fetch_add(1);
   currid = 4 * (size_t)p.num_aruco + 1;   // TrackBase.cpp:34
   std::lock_guard<std::mutex> lk(c->mtx);
   for (int i = 0; i < n_cams; i++) {
@@ -719,14 +733,15 @@ static void emit_fast_jobs(Lane *ctx, Side &s, int threshold, int &njobs, size_t
 }
 
 // Phase A: occupancy passes and the list of cells to run FAST on.
-static void phase_a(Unit &u) {
+// ahead: run at the end of a feed for the NEXT one (the frame that is current now will be "last" then).
+static void phase_a(Unit &u, bool ahead = false) {
   HOSTPROF(phase_a);
   const Params &P = u.rig->prm;
   Side &L = u.L;
   const int thr = std::min(20, (int)(0.5 * P.num_features));
   {
     CamState &c = *L.cam;
-    L.det_slot = u.first ? c.cur : c.last();
+    L.det_slot = (u.first || ahead) ? c.cur : c.last();
     L.det_mask = mask_ptr(c, L.det_slot);
     { HOSTPROF(a_occ_init); occ_init(L.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y); }
     HOSTPROF(a_left_rest);
@@ -743,7 +758,7 @@ static void phase_a(Unit &u) {
   if (u.stereo) {
     Side &R = u.R;
     CamState &c = *R.cam;
-    R.det_slot = u.first ? c.cur : c.last();
+    R.det_slot = (u.first || ahead) ? c.cur : c.last();
     R.det_mask = mask_ptr(c, R.det_slot);
     occ_init(R.occ, c.w, c.h, P.min_px_dist, P.grid_x, P.grid_y);
     // The right pass (:722-780) runs after the left detection appended new stereo points to pts1, but it is a plain
@@ -1065,6 +1080,10 @@ struct Pass {
   double t0 = 0, t1 = 0, t2 = 0, t3 = 0, tmark = 0;
   // make the lane's main stream wait for the new pyramids: its own upload stream and the submit rounds that hold its frames
   cudaError_t wait_new_frames();
+  // occupancy passes + FAST jobs of every unit; launches FAST unless a first frame has to wait for its upload
+  int issue_detection(bool ahead, bool &any_first, int &max_cw, int &max_ch);
+  bool ahead_usable();
+  void issue_ahead();
 
   void fail(FeedRequest &r, int code) {
     r.status = code;
@@ -1219,6 +1238,97 @@ cudaError_t Pass::wait_new_frames() {
   return e;
 }
 
+int Pass::issue_detection(bool ahead, bool &any_first, int &max_cw, int &max_ch) {
+  Context *dev = ctx->dev;
+  size_t ncells = 0, nwords = 0;
+  max_cw = max_ch = 1;
+  any_first = false;
+  for (auto &u : units) {
+    if (u.failed) continue;
+    phase_a(u, ahead);
+    any_first |= u.first;
+    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+      Side &s = side ? u.R : u.L;
+      if (!s.detect) continue;
+      ncells += s.cells.size();
+      nwords += s.cells.size() * (size_t)(((s.geom.size_x + 1) / 2) * ((s.geom.size_y + 1) / 2));
+      max_cw = std::max(max_cw, s.geom.size_x);
+      max_ch = std::max(max_ch, s.geom.size_y);
+    }
+  }
+  CU_TRY(ctx->fast_jobs.reserve(ncells));
+  CU_TRY(ctx->fast_cnt.reserve(ncells));
+  CU_TRY(ctx->fast_out.reserve(nwords));
+  CU_TRY(ctx->fast_out_dev.reserve(nwords));
+  CU_TRY(ctx->fast_cnt_dev.reserve(ncells, true));
+  CU_TRY(ctx->fast_ticket.reserve(ncells, true));
+  njobs = 0;
+  nwords = 0;
+  for (auto &u : units) {
+    if (u.failed) continue;
+    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+      Side &s = side ? u.R : u.L;
+      if (s.detect) emit_fast_jobs(ctx, s, u.rig->prm.fast_threshold, njobs, nwords);
+    }
+  }
+  CU_TRY(ctx->fast_jobs.upload(ctx->stream, (size_t)njobs));
+  if (!any_first) {
+    HOSTPROF(s0_fast_launch);
+    CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d, ctx->fast_cnt_dev.d,
+                       ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  }
+  return OK;
+}
+
+static bool ahead_enabled() {   // UVIO_KLT_AHEAD=0: every feed issues its own detection (A/B measurements)
+  static const bool v = [] {
+    const char *e = getenv("UVIO_KLT_AHEAD");
+    return !(e && e[0] == '0');
+  }();
+  return v;
+}
+
+// The detection issued when the previous pass of this lane ended serves this pass if the units are the same and nothing
+// it read has changed: same trackers (by serial: an address may be reused), no set_num_features / change_feat_id since,
+// same stereo / mono shape, and no unit starting over (a tracker that lost every point detects on the NEW frame).
+bool Pass::ahead_usable() {
+  const Lane::Ahead &a = ctx->ahead;
+  if (!a.valid || a.unit.size() != units.size()) return false;
+  for (size_t i = 0; i < units.v.size(); i++) {
+    const Unit *u = units.v[i];
+    if (u != a.unit[i] || u->rig->serial != a.serial[i] || u->rig->epoch != a.epoch[i] || (char)u->stereo != a.stereo[i] ||
+        u->first || u->failed)
+      return false;
+  }
+  return true;
+}
+
+// End of a pass: issue the next pass's detection (see Lane::Ahead).  All or nothing per lane.
+void Pass::issue_ahead() {
+  Lane::Ahead &a = ctx->ahead;
+  a.valid = false;
+  // (when FAST itself is being timed, every feed issues its own detection inside the timed window)
+  if (!ahead_enabled() || (ctx->prof_on && ((ctx->prof.mask >> K_FAST) & 1u)) || rc != OK || units.size() == 0) return;
+  for (auto &u : units) {
+    if (u.failed || u.req->status != OK) return;
+    const bool empty = u.stereo ? (u.L.cam->pts_last.empty() && u.R.cam->pts_last.empty()) : u.L.cam->pts_last.empty();
+    if (empty) return;                              // its next feed starts over on the new frame (TrackKLT.cpp:110, :221)
+  }
+  a.serial.clear(); a.epoch.clear(); a.unit.clear(); a.stereo.clear();
+  for (auto &u : units) {
+    u.first = false;
+    a.serial.push_back(u.rig->serial);
+    a.epoch.push_back(u.rig->epoch);
+    a.unit.push_back(&u);
+    a.stereo.push_back((char)u.stereo);
+  }
+  bool any_first = false;
+  int cw, ch;
+  if (issue_detection(true, any_first, cw, ch) != OK || any_first) return;
+  a.njobs = njobs;
+  a.valid = true;
+}
+
 int Pass::stage0() {
   Context *dev = ctx->dev;
   t0 = tmark = now_us();
@@ -1334,41 +1444,17 @@ int Pass::stage0() {
     ctx->sp_mask_ready = true;
   }
   // ---- round 1a: FAST.  Detection runs on the previous frame's pyramid, which is already in HBM, so it is issued ahead of
-  // the upload (its job list would otherwise queue behind the images on the copy engine).  First frames detect on the
-  // frame that is being uploaded and wait for it.
-  size_t ncells = 0, nwords = 0;
+  // the upload (its job list would otherwise queue behind the images on the copy engine) -- or was issued when the previous
+  // feed of these trackers ended.  First frames detect on the frame that is being uploaded and wait for it.
   int max_cw = 1, max_ch = 1;
   bool any_first = false;
-  for (auto &u : units) {
-    phase_a(u);
-    any_first |= u.first;
-    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
-      Side &s = side ? u.R : u.L;
-      if (!s.detect) continue;
-      ncells += s.cells.size();
-      nwords += s.cells.size() * (size_t)(((s.geom.size_x + 1) / 2) * ((s.geom.size_y + 1) / 2));
-      max_cw = std::max(max_cw, s.geom.size_x);
-      max_ch = std::max(max_ch, s.geom.size_y);
-    }
-  }
-  CU_TRY(ctx->fast_jobs.reserve(ncells));
-  CU_TRY(ctx->fast_cnt.reserve(ncells));
-  CU_TRY(ctx->fast_out.reserve(nwords));
-  CU_TRY(ctx->fast_out_dev.reserve(nwords));
-  CU_TRY(ctx->fast_cnt_dev.reserve(ncells, true));
-  CU_TRY(ctx->fast_ticket.reserve(ncells, true));
-  njobs = 0;
-  nwords = 0;
-  for (auto &u : units)
-    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
-      Side &s = side ? u.R : u.L;
-      if (s.detect) emit_fast_jobs(ctx, s, u.rig->prm.fast_threshold, njobs, nwords);
-    }
-  CU_TRY(ctx->fast_jobs.upload(ctx->stream, (size_t)njobs));
-  if (!any_first) {
-    HOSTPROF(s0_fast_launch);
-    CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, njobs, max_cw, max_ch, dev->pyr_dev.d, ctx->fast_out_dev.d, ctx->fast_cnt_dev.d,
-                       ctx->fast_ticket.d, ctx->fast_out.d, ctx->fast_cnt.d));
+  if (ahead_usable()) {
+    njobs = ctx->ahead.njobs;
+    ctx->ahead.valid = false;
+  } else {
+    ctx->ahead.valid = false;
+    int e = issue_detection(false, any_first, max_cw, max_ch);
+    if (e != OK) return e;
   }
   // ---- round 1b: upload + equalise + pyramid on the upload stream (frames announced by submit_batch are on their way) -------
   npre = (int)items.size();
@@ -1504,6 +1590,7 @@ int Pass::stage3() {
   for (auto &u : units)
     if (!u.first && !u.failed) phase_d(ctx, u);
   const double t4 = now_us();
+  issue_ahead();
   seg(6);
   ctx->seg_us[7] += 1;
   ctx->prof_end();
@@ -1744,6 +1831,7 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
   CU_TRY(ctx->fast_out_dev.reserve(words));
   CU_TRY(ctx->fast_cnt_dev.reserve(1, true));
   CU_TRY(ctx->fast_ticket.reserve(1, true));
+  ctx->ahead.valid = false;   // the lane's FAST buffers are about to be reused
   ctx->fast_jobs.h[0] = FastJob{p, x0, y0, cw, ch, 0, (int)words, threshold};
   CU_TRY(ctx->fast_jobs.upload(ctx->stream, 1));
   CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, dev->pyr_dev.d, ctx->fast_out_dev.d,

@@ -90,6 +90,9 @@ class Rig {                     // one tracker = one TrackKLT instance
   std::vector<CamState> cams;                       // in the order given at creation
   std::unordered_map<size_t, int> cam_index;        // camera id -> index in cams
   size_t currid;                                    // TrackBase.cpp:34
+  unsigned long long serial = 0;                    // unique per Rig object ever created (handles may reuse an address)
+  unsigned epoch = 0;                               // bumped by set_num_features / change_feat_id: state a detection that was
+                                                    // issued ahead of its feed may have read
   std::vector<Obs> obs;                             // observations produced by the last feed, in update_feature order
   float stage_us[5] = {0, 0, 0, 0, 0};              // pyramid, detection, temporal klt, stereo klt, db update
   int last_error = 0;
