@@ -21,6 +21,10 @@ import subprocess
 import sys
 import time
 
+# One hardware work queue per CUDA stream (the default of 8 makes streams share queues: a lane's kernels then wait behind the
+# frame upload of another stream -- measured as one straggler lane per call).  Must be set before the CUDA context exists.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -165,15 +169,25 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
         if rc != 0:
             raise RuntimeError(f"uvio_klt_submit_batch failed: {rc}")
 
+    call_s = [0.0, 0.0, 0.0]          # wall-clock of the three ABI calls of a step, summed over the timed steps
+
     def one(t):
+        t0 = time.perf_counter()
         if announce and t + 1 < len(step_frames):
             rc = L.uvio_klt_submit_batch(hs, step_frames[t + 1], streams)
             if rc != 0:
                 raise RuntimeError(f"uvio_klt_submit_batch failed: {rc}")
+        t1 = time.perf_counter()
         rc = L.uvio_klt_feed_batch(hs, step_frames[t], streams)
         if rc != 0:
             raise RuntimeError(f"uvio_klt_feed_batch failed: {rc} (cuda {L.uvio_klt_cuda_error(trackers[0]._h)})")
+        t2 = time.perf_counter()
         L.uvio_klt_get_new_observations_batch(hs, streams, obs_buf.ctypes.data, cap, counts)
+        t3 = time.perf_counter()
+        if t >= warmup:
+            call_s[0] += t1 - t0
+            call_s[1] += t2 - t1
+            call_s[2] += t3 - t2
         return int(sum(counts))
 
     for t in range(warmup):
@@ -207,6 +221,8 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
     passes = max(1.0, hostp.pop("lane_passes"))
     delta["host_us_per_lane_pass"] = {k: round(v / passes, 1) for k, v in hostp.items()}
     delta["lanes"] = passes / max(1, steps)
+    delta["call_us_per_step"] = {"submit_batch": round(1e6 * call_s[0] / steps, 1), "feed_batch": round(1e6 * call_s[1] / steps, 1),
+                                 "get_new_observations_batch": round(1e6 * call_s[2] / steps, 1)}
     for t in trackers:
         t.close()
     return sec, n_obs, clk, delta, prof, wall
@@ -293,7 +309,8 @@ def run_ours(args):
                            "(exactly one upload of a step's frames inside the timed region per timed step)" if announce else "")},
         "gpu_launches": int(st["launches"]),
         "host": {"lanes": st["lanes"], "resident_us_per_lane_pass": st["host_us_per_lane_pass"],
-                 "e2e_us_per_lane_pass": st2["host_us_per_lane_pass"]},
+                 "e2e_us_per_lane_pass": st2["host_us_per_lane_pass"],
+                 "resident_call_us_per_step": st["call_us_per_step"], "e2e_call_us_per_step": st2["call_us_per_step"]},
         "clocks": clk,
     }
     line["config"]["ms_per_step_with_all_kernels_bracketed_by_events"] = 1e3 * sec3 / K

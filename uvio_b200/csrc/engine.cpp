@@ -188,6 +188,7 @@ struct PreItem {
   int slot;                      // destination pyramid slot
   int method;                    // TrackBase::HistogramMethod
   bool downsample;
+  int par;                       // parity of the frame number: which of the camera's two upload buffers it lands in
 };
 struct PreBuffers {              // job lists of one upload round (a lane's, or one entry of the context's submit ring)
   JobVec<PreJob> *pre;
@@ -317,9 +318,12 @@ class Context {
   // submit_batch: frames announced ahead of their feed go up and are pre-processed on a stream of their own, one event
   // per call out of a small ring; a feed makes its lanes wait for the events that cover its frames
   static constexpr int PF_RING = 8;
-  cudaStream_t pf_stream = nullptr;
+  cudaStream_t pf_stream = nullptr;        // kernels of the announced batches
+  cudaStream_t pf_copy_stream = nullptr;   // their H2D copies: batch k+1 goes up while batch k is pre-processed
+  cudaEvent_t pf_copied[PF_RING] = {nullptr};
   cudaEvent_t pf_evt[PF_RING] = {nullptr};
   bool pf_used[PF_RING] = {false};
+  bool pf_recorded[PF_RING] = {false};             // (uploader thread only) the entry's event has been recorded at least once
   unsigned pf_seq = 0;
   JobVec<PreJob> pf_pre[PF_RING];
   JobVec<DownJob> pf_down[PF_RING];
@@ -350,8 +354,8 @@ class Context {
     std::lock_guard<std::mutex> lk(pf_mtx);
     return pf_queued + 1;
   }
-  uint8_t *raw_arena = nullptr;   // next free byte of the current upload-buffer chunk
-  size_t raw_arena_left = 0;
+  uint8_t *raw_arena[2] = {nullptr, nullptr};   // next free byte of the current upload-buffer chunk (one arena per frame parity)
+  size_t raw_arena_left[2] = {0, 0};
 
   int upload_tables() {
     Context *ctx = this;
@@ -387,16 +391,19 @@ class Context {
     }
     // Upload buffers come from an arena in creation order: cameras created one after the other (the two cameras of a rig,
     // the rigs of a batch) get adjacent buffers, so frames that are adjacent in host memory go up as one copy.
-    if (raw_arena_left < raw_bytes) {
-      const size_t chunk = std::max<size_t>(raw_bytes, (size_t)64 << 20);
-      CU_TRY(cudaMalloc((void **)&raw_arena, chunk + 256));
-      CU_TRY(cudaMemset(raw_arena, 0, chunk + 256));
-      allocs.push_back(raw_arena);
-      raw_arena_left = chunk;
+    uint8_t *raw_base[2];
+    for (int par = 0; par < 2; par++) {
+      if (raw_arena_left[par] < raw_bytes) {
+        const size_t chunk = std::max<size_t>(raw_bytes, (size_t)64 << 20);
+        CU_TRY(cudaMalloc((void **)&raw_arena[par], chunk + 256));
+        CU_TRY(cudaMemset(raw_arena[par], 0, chunk + 256));
+        allocs.push_back(raw_arena[par]);
+        raw_arena_left[par] = chunk;
+      }
+      raw_base[par] = raw_arena[par];
+      raw_arena[par] += raw_bytes;
+      raw_arena_left[par] -= raw_bytes;
     }
-    uint8_t *raw_base = raw_arena;
-    raw_arena += raw_bytes;
-    raw_arena_left -= raw_bytes;
     uint8_t *base = nullptr;
     CU_TRY(cudaMalloc((void **)&base, PYR_SLOTS * pyr_bytes + half_bytes + 256));
     CU_TRY(cudaMemset(base, 0, PYR_SLOTS * pyr_bytes + half_bytes + 256));
@@ -405,9 +412,11 @@ class Context {
     c.h = h;
     c.in_w = in_w;
     c.in_h = in_h;
-    c.raw_in = (int)raw_tab.size();
-    raw_tab.push_back(ImgView{raw_base, in_w, in_h, raw_pitch});
-    c.raw = c.raw_in;
+    for (int par = 0; par < 2; par++) {
+      c.raw_in[par] = (int)raw_tab.size();
+      raw_tab.push_back(ImgView{raw_base[par], in_w, in_h, raw_pitch});
+    }
+    c.raw = -1;
     uint8_t *p = base;
     if (downsample) {
       c.raw = (int)raw_tab.size();
@@ -547,8 +556,11 @@ Context::~Context() {
   delete pool;
   lanes.clear();
   if (pf_stream) cudaStreamDestroy(pf_stream);
-  for (int i = 0; i < PF_RING; i++)
+  if (pf_copy_stream) cudaStreamDestroy(pf_copy_stream);
+  for (int i = 0; i < PF_RING; i++) {
     if (pf_evt[i]) cudaEventDestroy(pf_evt[i]);
+    if (pf_copied[i]) cudaEventDestroy(pf_copied[i]);
+  }
   for (void *p : allocs) cudaFree(p);
 }
 
@@ -574,6 +586,15 @@ static int default_depth(int threads) {
   }
   return threads >= 8 ? 1 : 2;
 }
+
+// The context uses 2 streams per lane and one for announced frames.  With the driver's default of 8 hardware work queues
+// several streams share a queue and falsely serialise: a lane's launch queued behind the 1 MiB pieces of a frame upload
+// waits for all of them (seen as one lane per call finishing 0.5-1 ms late).  The variable only counts if it is set
+// before the process creates its CUDA context, so a host that initialises CUDA first should export it itself.
+static const int g_connections_hint = [] {
+  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
+  return 0;
+}();
 
 Context *context_for_device(int device, int *err) {
   static std::mutex m;
@@ -610,12 +631,14 @@ Context *context_for_device(int device, int *err) {
     }
     c->lanes.push_back(std::move(ln));
   }
-  if ((e = cudaStreamCreateWithPriority(&c->pf_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) {
+  if ((e = cudaStreamCreateWithPriority(&c->pf_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
+      (e = cudaStreamCreateWithPriority(&c->pf_copy_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) {
     if (err) *err = (int)e;
     return nullptr;
   }
   for (int i = 0; i < Context::PF_RING; i++)
-    if ((e = cudaEventCreateWithFlags(&c->pf_evt[i], cudaEventDisableTiming)) != cudaSuccess) {
+    if ((e = cudaEventCreateWithFlags(&c->pf_evt[i], cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&c->pf_copied[i], cudaEventDisableTiming)) != cudaSuccess) {
       if (err) *err = (int)e;
       return nullptr;
     }
@@ -1124,8 +1147,13 @@ struct Pass {
 
 // H2D of the frames (merged into as few copies as their layout allows), the optional halving, equalisation and pyramids,
 // all on stream st.  Frames already in device memory are consumed where they lie.
+// copy_st / copied: when given, the copies go to a stream of their own and st waits for them through the event, so that the
+// upload of one batch overlaps the kernels of the batch before it (the frames alternate between two upload buffers).
 static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, const std::vector<PreItem> &items, unsigned long long *stats,
-                            int group = 0) {
+                            int group = 0, cudaStream_t copy_st = nullptr, cudaEvent_t copied = nullptr) {
+  const bool split = copy_st != nullptr && copy_st != st;
+  if (!split) copy_st = st;
+  else group = 0;
   HOSTPROF(s0_memcpy);
   const int nimg = (int)items.size();
   if (nimg == 0) return OK;
@@ -1153,7 +1181,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
   auto flush = [&]() -> cudaError_t {
     cudaError_t e = cudaSuccess;
     for (size_t off = 0; off < pend_bytes && e == cudaSuccess; off += piece)
-      e = cudaMemcpyAsync(pend_dst + off, pend_src + off, std::min(piece, pend_bytes - off), cudaMemcpyHostToDevice, st);
+      e = cudaMemcpyAsync(pend_dst + off, pend_src + off, std::min(piece, pend_bytes - off), cudaMemcpyHostToDevice, copy_st);
     pend_bytes = 0;
     return e;
   };
@@ -1163,7 +1191,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
     const PreItem &it = items[j];
     CamState &c = *it.cam;
     const HostImage &im = it.im;
-    B.pre->h[j] = PreJob{ctx->raw_tab[c.raw], c.pyr[it.slot], it.method};
+    B.pre->h[j] = PreJob{ctx->raw_tab[it.downsample ? c.raw : c.raw_in[it.par]], c.pyr[it.slot], it.method};
     max_band = std::max(max_band, ((c.h + 7) / 8 + 1) * c.w);
     cudaPointerAttributes attr;
     const bool on_device = cudaPointerGetAttributes(&attr, im.p) == cudaSuccess &&
@@ -1171,7 +1199,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
     if (!on_device) cudaGetLastError();   // an unregistered host pointer is not an error
     on_dev[j] = on_device;
     if (it.downsample) {
-      const ImgView full = on_device ? ImgView{im.p, im.w, im.h, (int)im.stride} : ctx->raw_tab[c.raw_in];
+      const ImgView full = on_device ? ImgView{im.p, im.w, im.h, (int)im.stride} : ctx->raw_tab[c.raw_in[it.par]];
       B.down->h[ndown++] = DownJob{full, ctx->raw_tab[c.raw]};
       max_dw = std::max(max_dw, c.w);
       max_dh = std::max(max_dh, c.h);
@@ -1180,8 +1208,8 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
     }
   }
   }
-  CU_TRY(B.pre->upload(st, (size_t)nimg));
-  if (ndown > 0) CU_TRY(B.down->upload(st, (size_t)ndown));
+  CU_TRY(B.pre->upload(copy_st, (size_t)nimg));
+  if (ndown > 0) CU_TRY(B.down->upload(copy_st, (size_t)ndown));
   // Pass 2: group by group, the frames go up and are (halved and) pre-processed.  A feed issues one group; submit_batch cuts
   // a batch into several so that the pyramids of the first frames are built while the last ones are still on the link, and
   // so that no launch takes every SM from the rounds of the feed that is running meanwhile.
@@ -1194,7 +1222,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
     for (int j = g0; j < g1; j++) {
       const PreItem &it = items[j];
       const HostImage &im = it.im;
-      const ImgView &raw = ctx->raw_tab[it.cam->raw_in];
+      const ImgView &raw = ctx->raw_tab[it.cam->raw_in[it.par]];
       gdown += it.downsample;
       if (on_dev[j]) continue;
       stats[2] += (unsigned long long)im.w * im.h;
@@ -1214,10 +1242,14 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
         }
       } else {
         CU_TRY(flush());
-        CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault, st));
+        CU_TRY(cudaMemcpy2DAsync((void *)raw.p, (size_t)raw.pitch, im.p, im.stride, (size_t)im.w, (size_t)im.h, cudaMemcpyDefault, copy_st));
       }
     }
     CU_TRY(flush());
+    if (split) {
+      CU_TRY(cudaEventRecord(copied, copy_st));
+      CU_TRY(cudaStreamWaitEvent(st, copied, 0));
+    }
     if (gdown > 0) {   // downsample_cameras: halve the frames where they landed, in front of the pre-processing
       CU_TRY(launch_downsample(st, B.down->d + down_at, gdown, max_dw, max_dh));
       down_at += gdown;
@@ -1358,7 +1390,7 @@ int Pass::stage0() {
         wait_evts |= 1u << c.sub_evt[c.cur];
         need_seq = std::max(need_seq, c.sub_seq[c.cur]);
       }
-      else items.push_back(PreItem{&c, rq.images[k], c.cur, P.histogram_method, P.downsample_cameras != 0});
+      else items.push_back(PreItem{&c, rq.images[k], c.cur, P.histogram_method, P.downsample_cameras != 0, (int)(c.n_sub & 1u)});
       // the same mask memory given to several cameras of this call (a rig's shared mask, a batch's common one) is scanned once
       const HostImage &mk = rq.masks[k];
       bool known_zero = false;
@@ -1620,7 +1652,7 @@ static int validate_request(Context *ctx, FeedRequest &rq, bool announcing) {
     if (!announcing && rq.masks[k].p && (rq.masks[k].w != im.w || rq.masks[k].h != im.h)) return E_BADMSG;
     for (int q = 0; q < k; q++)
       if (rq.sensor_ids[q] == rq.sensor_ids[k]) return E_BADMSG;
-    if (c->raw < 0) {
+    if (c->raw_in[0] < 0) {
       ctx->uploader_drain();   // a new camera grows the tables a batch in flight may be reading
       int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size, P.downsample_cameras != 0);
       if (e != OK) return e;
@@ -1665,8 +1697,14 @@ void Context::uploader_loop() {
     } else {
       g_prof = nullptr;
     }
-    int e = issue_preprocess(ctx, pf_stream, B, pf_items[q], st, pf_group);
+    // The copies of this batch overwrite the upload buffers of the same frame parity: whatever read them two announcements
+    // ago (or earlier: the kernel stream is in order) must be done.  The announcement before this one reads the other pair.
+    const int q2 = (q + PF_RING - 2) % PF_RING;
+    int e = OK;
+    if (pf_recorded[q2] && cudaStreamWaitEvent(pf_copy_stream, pf_evt[q2], 0) != cudaSuccess) e = E_CUDA;
+    if (e == OK) e = issue_preprocess(ctx, pf_stream, B, pf_items[q], st, pf_group, pf_copy_stream, pf_copied[q]);
     if (e == OK && cudaEventRecord(pf_evt[q], pf_stream) != cudaSuccess) e = E_CUDA;
+    pf_recorded[q] = true;
     pf_stats[1] += st[1];
     pf_stats[2] += st[2];
     {
@@ -1705,7 +1743,7 @@ int submit_batch(Context *ctx, FeedRequest *reqs, int n) {
       c.sub_src[slot] = rq.images[k].p;
       c.sub_evt[slot] = q;
       c.sub_seq[slot] = ctx->pf_queued_next();
-      items.push_back(PreItem{&c, rq.images[k], slot, rq.rig->prm.histogram_method, rq.rig->prm.downsample_cameras != 0});
+      items.push_back(PreItem{&c, rq.images[k], slot, rq.rig->prm.histogram_method, rq.rig->prm.downsample_cameras != 0, (int)(c.n_sub & 1u)});
     }
   }
   if (ctx->upload_tables() != OK) return E_CUDA;
@@ -1758,13 +1796,27 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     passes[l].reqs = good.data() + b;
     passes[l].n = (int)(e - b);
   }
+  static const bool trace = getenv("UVIO_KLT_TRACE_LANES") != nullptr;   // development: per-lane wall clock of a few calls
+  const double t_call = now_us();
+  std::vector<double> t_start(nl, 0), t_end(nl, 0);
   {
   HOSTPROF(fb_pool_run);
   ctx->pool->run(nthreads, [&](int t) {
     HOSTPROF(fb_thread);
+    if (trace) for (int l = t; l < nl; l += nthreads) t_start[l] = now_us();
     for (int stage = 0; stage < 4; stage++)
-      for (int l = t; l < nl; l += nthreads) passes[l].step();
+      for (int l = t; l < nl; l += nthreads) {
+        passes[l].step();
+        if (trace && stage == 3) t_end[l] = now_us();
+      }
   });
+  }
+  if (trace && (ctx->stats[4] % 8) == 5) {
+    fprintf(stderr, "[lanes] call %llu: pool done at +%.0f us; lane start/end:", ctx->stats[4], now_us() - t_call);
+    for (int l = 0; l < nl; l++)
+      fprintf(stderr, " [%d: s1@%.0f s2@%.0f s3@%.0f end@%.0f]", l, passes[l].t1 - t_call, passes[l].t2 - t_call, passes[l].t3 - t_call,
+              t_end[l] - t_call);
+    fprintf(stderr, "\n");
   }
   std::vector<int> rc(nl, OK);
   for (int l = 0; l < nl; l++) rc[l] = passes[l].result();
@@ -1789,7 +1841,7 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
 // ---------------------------------------------------------------------------------------------------------------------
 static int slot_pyr(Rig *rig, size_t cam_id, int slot, CamState **out) {
   CamState *c = rig->find_cam(cam_id);
-  if (!c || c->raw < 0) return -1;
+  if (!c || c->raw_in[0] < 0) return -1;
   *out = c;
   return c->pyr[slot ? c->last() : c->cur];
 }

@@ -58,7 +58,8 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   double max_focal = 0;
   int w = 0, h = 0;             // size of the images this camera tracks on (fixed after the first frame)
   int in_w = 0, in_h = 0;       // size of the images it is fed: (w, h), or twice that with downsample_cameras
-  int raw_in = -1;              // upload buffer of the fed frame (== raw unless downsample_cameras)
+  int raw_in[2] = {-1, -1};     // upload buffers of the fed frames: frame number k of this camera lands in raw_in[k & 1], so
+                                // that the upload of an announced frame overlaps the pre-processing of the one before it
   int pyr[PYR_SLOTS] = {-1, -1, -1};   // pyramid slots in the context's table; frame number k of this camera lives in slot k % 3
   int cur = 0;                  // slot holding the frame being fed ("curr")
   int last() const { return (cur + PYR_SLOTS - 1) % PYR_SLOTS; }   // slot of the frame before it ("last")
@@ -68,7 +69,7 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   const uint8_t *sub_src[PYR_SLOTS] = {nullptr, nullptr, nullptr};   // image pointer a submitted frame was announced with
   int sub_evt[PYR_SLOTS] = {-1, -1, -1};         // context event that marks its pre-processing done
   unsigned long long sub_seq[PYR_SLOTS] = {0, 0, 0};   // number of the announced batch it went up with
-  int raw = -1;                 // the frame the pre-processing reads: the upload buffer, or its halved copy
+  int raw = -1;                 // downsample_cameras: the halved frame the pre-processing reads (else it reads raw_in[])
   bool have_last = false;
   std::vector<Pt> pts_last;
   std::vector<size_t> ids_last;
