@@ -21,6 +21,7 @@ constexpr int LK_WIN = 15;                 // TrackKLT.h:144 (win_size 15x15, no
 constexpr int LK_NPIX = LK_WIN * LK_WIN;   // 225
 constexpr int LK_FP = 18;                  // template footprint rows/cols (16 + 1-px Scharr halo each side)
 constexpr int LK_FPW = 6;                  // 32-bit words staged per footprint row (24 bytes cover 18 + alignment slack)
+constexpr int LK_BW = 17;                  // blended-intensity grid of an interior template: 15 + a 1-px Scharr ring
 constexpr int LK_JW = 32;                  // rows/cols of the J window staged per level (search range +-8 px around the guess)
 constexpr int LK_JWW = 10;                 // words per staged J row (40 bytes cover 32 + alignment slack)
 
@@ -38,6 +39,7 @@ struct alignas(16) LkSmem {
   union {
     uint32_t jwin[LK_JW * LK_JWW];         // J window rows, REFLECT_101, as aligned words (after the template is built)
     Short2 dI[16 * 16];                    // Scharr (dx,dy) at ip .. ip+15, zero outside the frame (while it is built)
+    int blend[LK_BW * LK_BW];              // blended intensities (weights not yet shifted out) at ip-1 .. ip+15 (interior windows)
   };
   Short2 dIw[LK_NPIX + 3];                 // blended derivative patch
   short Iw[LK_NPIX + 7];                   // template, intensity * 32
@@ -122,10 +124,48 @@ UVIO_HD void lk_stage_template(G g, LkSmem &s, const ImgView &I, int ipx, int ip
   const uint8_t *foot = (const uint8_t *)s.footw + ((ipx - 1) - xa);   // foot[yy*24 + xx] = I(ip-1+xx, ip-1+yy)
   constexpr int FPP = LK_FPW * 4;
   const bool inside = ipx >= 0 && ipx + 16 <= I.w && ipy >= 0 && ipy + 16 <= I.h;   // no derivative sample falls outside
+  if (inside) {
+    // Blend first, differentiate second.  The bilinear blend (integer weights, no shift yet) and the Scharr stencil are
+    // both exact integer linear maps, so the blend of the Scharr image equals the Scharr stencil applied to the blended
+    // intensities B(x,y) = sum_w w * I(ip-1+x.., ip-1+y..), 17x17 of them (22 bits each, 27 after the stencil); the
+    // rounding shifts come last, exactly where the two-step form applies them.  The template itself is the centre tap:
+    // Iw = (B + 2^8) >> 9.  One pass of four byte loads per B replaces the 16x16 Scharr pass and the three blends per pixel.
+    for (int i = g.lane(); i < LK_BW * LK_BW; i += g.size()) {
+      int y = i / LK_BW, x = i - y * LK_BW;
+      const uint8_t *c = foot + y * FPP + x;
+      s.blend[i] = c[0] * iw00 + c[1] * iw01 + c[FPP] * iw10 + c[FPP + 1] * iw11;
+    }
+    g.sync();
+    for (int i = g.lane(); i < LK_NPIX; i += g.size()) {
+      int y = i / LK_WIN, x = i - y * LK_WIN;
+      const int *b = s.blend + (y + 1) * LK_BW + (x + 1);
+      int tl = b[-LK_BW - 1], tc = b[-LK_BW], tr = b[-LK_BW + 1], ml = b[-1], mr = b[1];
+      int bl = b[LK_BW - 1], bc = b[LK_BW], br = b[LK_BW + 1];
+      int ival = (b[0] + (1 << 8)) >> 9;
+      int ix = (3 * (tr - tl) + 10 * (mr - ml) + 3 * (br - bl) + (1 << 13)) >> 14;
+      int iy = (3 * (bl - tl) + 10 * (bc - tc) + 3 * (br - tr) + (1 << 13)) >> 14;
+      s.Iw[i] = (short)ival;
+      s.dIw[i] = Short2{(short)ix, (short)iy};
+      float xx = (float)(ix * ix), xy = (float)(ix * iy), yy = (float)(iy * iy);
+      if (x < 8) {
+        s.gsimd[0][y * 8 + x] = xx;
+        s.gsimd[1][y * 8 + x] = xy;
+        s.gsimd[2][y * 8 + x] = yy;
+      } else {
+        s.gtail[0][y * 7 + x - 8] = xx;
+        s.gtail[1][y * 7 + x - 8] = xy;
+        s.gtail[2][y * 7 + x - 8] = yy;
+      }
+    }
+    g.sync();
+    return;
+  }
+  // Windows that touch the frame border: derivative samples outside the frame are zero (calcScharrDeriv + BORDER_CONSTANT), which
+  // the blend must see as zeros, so the derivative image is formed first.
   for (int i = g.lane(); i < 256; i += g.size()) {
     int y = i >> 4, x = i & 15;
     int dx = 0, dy = 0;
-    if (inside || (ipx + x >= 0 && ipx + x < I.w && ipy + y >= 0 && ipy + y < I.h)) {
+    if (ipx + x >= 0 && ipx + x < I.w && ipy + y >= 0 && ipy + y < I.h) {
       const uint8_t *c = foot + (y + 1) * FPP + (x + 1);
       int tl = c[-FPP - 1], tc = c[-FPP], tr = c[-FPP + 1], ml = c[-1], mr = c[1];
       int bl = c[FPP - 1], bc = c[FPP], br = c[FPP + 1];
