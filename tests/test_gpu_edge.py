@@ -134,3 +134,30 @@ def test_ransac_tie_cases_match_cv2(built_lib):
     for k in ("a", "b"):
         mask, _p0n, _p1n = trk.stage_ransac(0, 0, g[f"p0_{k}"], g[f"p1_{k}"])
         assert np.array_equal(mask, g[f"mask_{k}"]), f"case {k}: {np.nonzero(mask != g[f'mask_{k}'])[0]}"
+
+
+def test_destroyed_trackers_give_their_device_memory_back(built_lib):
+    """uvio_klt_destroy (TrackBase::~TrackBase): pyramids are freed, upload buffers recycled -- creating and destroying
+    trackers in a loop must not grow the device footprint, and a recycled buffer must not change results."""
+    import torch
+    cfg = configs.HD_1000.with_(num_features=150)
+    frames = frames_for(cfg, 3, stream_id=3)
+    masks = masks_for(cfg)
+
+    def one_life():
+        t = make_tracker(cfg)
+        for k, (l, r) in enumerate(frames):
+            t.feed_new_camera(CameraData(0.05 * k, [0, 1], [l, r], masks))
+        out = t.new_observations().tobytes()
+        t.close()
+        return out
+
+    first = one_life()
+    one_life()
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for _ in range(12):
+        assert one_life() == first
+    torch.cuda.synchronize()
+    free1 = torch.cuda.mem_get_info()[0]
+    assert free0 - free1 < 8 << 20, f"device memory grew by {(free0 - free1) >> 20} MiB over 12 tracker lifetimes"

@@ -88,7 +88,7 @@ int uvio_klt_create(const UvioKltParams *p, const UvioCamCalib *cams, int n_cams
 
 void uvio_klt_destroy(uvio_klt *h) {
   if (!h) return;
-  delete h->rig;   // device memory of its cameras stays with the device context until process exit
+  delete h->rig;   // frees the pyramids of its cameras; their upload buffers are recycled by the device context
   delete h;
 }
 

@@ -167,6 +167,7 @@ struct DevVec {
 };
 
 class Context;
+static std::atomic<bool> g_contexts_gone{false};   // set when process exit has torn the device contexts down
 
 // after the stream was synchronised: every (kernel mark, next mark) interval is one kernel's duration
 static void fold_prof(KernelProf &prof, double *ms_sum, unsigned long long *launches) {
@@ -315,6 +316,9 @@ class Context {
   DevVec<CamModel> cam_dev;
   bool tables_dirty = true;
   std::vector<void *> allocs;   // image memory of all cameras
+  struct RawSlot { size_t bytes; uint8_t *p[2]; };
+  std::vector<RawSlot> raw_free;   // upload buffers of destroyed trackers, reused by cameras of the same size
+  void release_camera(CamState &c);
   // submit_batch: frames announced ahead of their feed go up and are pre-processed on a stream of their own, one event
   // per call out of a small ring; a feed makes its lanes wait for the events that cover its frames
   static constexpr int PF_RING = 8;
@@ -391,8 +395,15 @@ class Context {
     }
     // Upload buffers come from an arena in creation order: cameras created one after the other (the two cameras of a rig,
     // the rigs of a batch) get adjacent buffers, so frames that are adjacent in host memory go up as one copy.
-    uint8_t *raw_base[2];
-    for (int par = 0; par < 2; par++) {
+    uint8_t *raw_base[2] = {nullptr, nullptr};
+    for (size_t k = 0; k < raw_free.size(); k++)
+      if (raw_free[k].bytes == raw_bytes) {   // a destroyed tracker's buffers of the same size
+        raw_base[0] = raw_free[k].p[0];
+        raw_base[1] = raw_free[k].p[1];
+        raw_free.erase(raw_free.begin() + (long)k);
+        break;
+      }
+    for (int par = 0; par < 2 && !raw_base[par]; par++) {
       if (raw_arena_left[par] < raw_bytes) {
         const size_t chunk = std::max<size_t>(raw_bytes, (size_t)64 << 20);
         CU_TRY(cudaMalloc((void **)&raw_arena[par], chunk + 256));
@@ -408,6 +419,10 @@ class Context {
     CU_TRY(cudaMalloc((void **)&base, PYR_SLOTS * pyr_bytes + half_bytes + 256));
     CU_TRY(cudaMemset(base, 0, PYR_SLOTS * pyr_bytes + half_bytes + 256));
     allocs.push_back(base);
+    c.dev_base = base;
+    c.raw_ptr[0] = raw_base[0];
+    c.raw_ptr[1] = raw_base[1];
+    c.raw_bytes = raw_bytes;
     c.w = w;
     c.h = h;
     c.in_w = in_w;
@@ -545,6 +560,7 @@ int Context::wait_issued(unsigned long long seq) {
 }
 
 Context::~Context() {
+  g_contexts_gone.store(true);
   if (uploader.joinable()) {
     {
       std::lock_guard<std::mutex> lk(pf_mtx);
@@ -707,8 +723,31 @@ struct Unit {
   IdTable tab_a, tab_b;
 };
 
+// Device memory of a destroyed tracker's camera: the pyramids go back to the driver, the upload buffers to the free list.
+// (Its entries in the image tables stay; they are a few hundred bytes and are never referenced again.)
+void Context::release_camera(CamState &c) {
+  if (!c.dev_base) return;
+  for (size_t k = 0; k < allocs.size(); k++)
+    if (allocs[k] == c.dev_base) {
+      allocs.erase(allocs.begin() + (long)k);
+      break;
+    }
+  cudaFree(c.dev_base);
+  c.dev_base = nullptr;
+  raw_free.push_back(RawSlot{c.raw_bytes, {c.raw_ptr[0], c.raw_ptr[1]}});
+}
+
 Rig::~Rig() {
   for (Unit *u : unit_pool) delete u;
+  if (g_contexts_gone.load()) return;
+  bool any = false;
+  for (auto &c : cams) any |= c.dev_base != nullptr;
+  if (!any) return;
+  std::lock_guard<std::mutex> lk(ctx->mtx);
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return;
+  ctx->uploader_drain();
+  cudaDeviceSynchronize();   // a detection issued ahead or an announced frame of this tracker may still be running
+  for (auto &c : cams) ctx->release_camera(c);
 }
 Unit *Rig::unit_at(size_t i) {
   while (unit_pool.size() <= i) unit_pool.push_back(new Unit);

@@ -69,6 +69,9 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   const uint8_t *sub_src[PYR_SLOTS] = {nullptr, nullptr, nullptr};   // image pointer a submitted frame was announced with
   int sub_evt[PYR_SLOTS] = {-1, -1, -1};         // context event that marks its pre-processing done
   unsigned long long sub_seq[PYR_SLOTS] = {0, 0, 0};   // number of the announced batch it went up with
+  void *dev_base = nullptr;     // the camera's own device allocation (pyramids, halved frame); freed with its tracker
+  uint8_t *raw_ptr[2] = {nullptr, nullptr};   // its upload buffers (arena slots, recycled through the context's free list)
+  size_t raw_bytes = 0;
   int raw = -1;                 // downsample_cameras: the halved frame the pre-processing reads (else it reads raw_in[])
   bool have_last = false;
   std::vector<Pt> pts_last;
