@@ -254,6 +254,8 @@ struct Lane {
     bool valid = false;
     std::vector<unsigned long long> serial;   // per unit: rig serial, rig epoch, unit index in the rig, stereo flag
     std::vector<unsigned> epoch;
+    std::vector<unsigned long long> feeds;    // the tracker's feed count when the detection was issued: a feed through
+                                              // another lane in between (another batch composition) makes it stale
     std::vector<Unit *> unit;
     std::vector<char> stereo;
     int njobs = 0;
@@ -1367,7 +1369,8 @@ bool Pass::ahead_usable() {
   if (!a.valid || a.unit.size() != units.size()) return false;
   for (size_t i = 0; i < units.v.size(); i++) {
     const Unit *u = units.v[i];
-    if (u != a.unit[i] || u->rig->serial != a.serial[i] || u->rig->epoch != a.epoch[i] || (char)u->stereo != a.stereo[i] ||
+    if (u != a.unit[i] || u->rig->serial != a.serial[i] || u->rig->epoch != a.epoch[i] || u->rig->feeds != a.feeds[i] + 1 ||
+        (char)u->stereo != a.stereo[i] ||
         u->first || u->failed)
       return false;
   }
@@ -1385,11 +1388,12 @@ void Pass::issue_ahead() {
     const bool empty = u.stereo ? (u.L.cam->pts_last.empty() && u.R.cam->pts_last.empty()) : u.L.cam->pts_last.empty();
     if (empty) return;                              // its next feed starts over on the new frame (TrackKLT.cpp:110, :221)
   }
-  a.serial.clear(); a.epoch.clear(); a.unit.clear(); a.stereo.clear();
+  a.serial.clear(); a.epoch.clear(); a.feeds.clear(); a.unit.clear(); a.stereo.clear();
   for (auto &u : units) {
     u.first = false;
     a.serial.push_back(u.rig->serial);
     a.epoch.push_back(u.rig->epoch);
+    a.feeds.push_back(u.rig->feeds);
     a.unit.push_back(&u);
     a.stereo.push_back((char)u.stereo);
   }
@@ -1418,6 +1422,7 @@ int Pass::stage0() {
     FeedRequest &rq = *reqs[i];
     Rig &rig = *rq.rig;
     const Params &P = rig.prm;
+    rig.feeds++;
     for (int k = 0; k < rq.n; k++) {
       CamState &c = *rig.find_cam(rq.sensor_ids[k]);
       // frame number n_fed + 1 of this camera: announced earlier (submit_batch; already on its way or done) or uploaded now
