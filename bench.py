@@ -228,13 +228,17 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
     return sec, n_obs, clk, delta, prof, wall
 
 
-def _latency_leg(track, L, cfg, device, step_frames, n_frames):
-    """One stream fed frame by frame through uvio_klt_feed (host frames and masks): wall-clock of the synchronous call."""
+def _latency_leg(track, L, cfg, device, step_frames, n_frames, pause_s=0.0):
+    """One stream fed frame by frame through uvio_klt_feed (host frames and masks): wall-clock of the synchronous call.
+    pause_s > 0: frames arrive that far apart (a camera, not a file): the tracker uses the idle time for the detection
+    of the next feed, which then starts at its temporal LK."""
     t = track.make_tracker(cfg, device=device)
     obs = np.zeros((1024,), track.OBS_DTYPE)
     n = C.c_int()
     lat = []
     for k in range(n_frames):
+        if pause_s:
+            time.sleep(pause_s)
         t0 = time.perf_counter()
         rc = L.uvio_klt_feed(t._h, C.byref(step_frames[k][0]))
         L.uvio_klt_get_new_observations(t._h, obs.ctypes.data, 1024, C.byref(n))
@@ -244,7 +248,8 @@ def _latency_leg(track, L, cfg, device, step_frames, n_frames):
     t.close()
     lat = sorted(lat[5:])
     return {"p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(0.99 * len(lat)))], "frames": len(lat),
-            "what": "uvio_klt_feed + uvio_klt_get_new_observations, one euroc_mav stereo stream, pinned host frames and masks"}
+            "what": "uvio_klt_feed + uvio_klt_get_new_observations, one euroc_mav stereo stream, pinned host frames and masks"
+                    + (f", frames {1e3 * pause_s:.0f} ms apart" if pause_s else ", back to back")}
 
 
 def run_ours(args):
@@ -291,6 +296,7 @@ def run_ours(args):
     sec2, n_obs2, _clk2, st2, _prof2, wall2 = _run_leg(track, L, cfg, local, S, host_steps, W, K, dist, obs_buf, counts, False, lk_only, announce)
     sec3, _n3, _clk3, st3, prof3, _wall3 = _run_leg(track, L, cfg, local, S, dev_steps, W, K, dist, obs_buf, counts, False, 1, announce)
     lat = _latency_leg(track, L, cfg, local, host_steps, min(T, 60))
+    lat_paced = _latency_leg(track, L, cfg, local, host_steps, min(T, 60), pause_s=0.003)
     total_frames = world * S * K
     value = total_frames / sec
     e2e = total_frames / sec2
@@ -301,6 +307,7 @@ def run_ours(args):
         "data": "synthetic (uvio_b200.synth, seeded)",
         "config": config_dict(cfg, S, {"latency_ms_per_batched_step": 1e3 * sec / K,
                                         "single_stream_frame_latency_ms": lat,
+                                        "single_stream_frame_latency_ms_paced": lat_paced,
                                         "observations_per_frame": n_obs / max(1, S * K)}),
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": st2["h2d_bytes"] / K,
                 "d2h_bytes_per_step": st2["d2h_bytes"] / K, "ms_per_step": 1e3 * sec2 / K,

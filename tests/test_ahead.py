@@ -92,3 +92,42 @@ def test_ahead_changing_batches_sim(sim_tracker, monkeypatch):
 @pytest.mark.gpu
 def test_ahead_changing_batches_gpu():
     _changing_batches(lambda c: make_tracker(c, device=0), configs.EUROC_MAV.with_(num_features=400, min_px_dist=6), 5, 9)
+
+
+def _destroy_mid_sequence(make, cfg, n_trk, n, drop_at, drop):
+    """More trackers than lanes (several per lane); one is destroyed between two batched feeds, which shifts every later
+    tracker to another place of its lane or to another lane.  The survivors must not notice."""
+    masks = masks_for(cfg)
+    seqs = [frames_for(cfg, n, stream_id=80 + s) for s in range(n_trk)]
+    ref = []
+    for s in range(n_trk):
+        t = make(cfg)
+        out = []
+        for k in range(n):
+            t.feed_new_camera(CameraData(0.05 * k, [0, 1], list(seqs[s][k]), masks))
+            out.append(t.new_observations().tobytes())
+        ref.append(out)
+        t.close()
+    trks = {s: make(cfg) for s in range(n_trk)}
+    for k in range(n):
+        if k == drop_at:
+            trks.pop(drop).close()
+        alive = sorted(trks)
+        feed_batch([trks[s] for s in alive], [CameraData(0.05 * k, [0, 1], list(seqs[s][k]), masks) for s in alive])
+        for s in alive:
+            assert trks[s].new_observations().tobytes() == ref[s][k], f"frame {k} tracker {s}"
+
+
+def _small_cfg():
+    cams = tuple(configs.CamCalib(c.model, (c.intrinsics[0] * 320 / 752, c.intrinsics[1] * 240 / 480, 160.0, 120.0), c.dist)
+                 for c in configs.EUROC_MAV.cams)
+    return configs.EUROC_MAV.with_(name="small", width=320, height=240, num_features=300, min_px_dist=5, cams=cams)
+
+
+def test_ahead_destroy_mid_sequence_sim(sim_tracker):
+    _destroy_mid_sequence(sim_tracker, _small_cfg(), 11, 5, 2, 3)
+
+
+@pytest.mark.gpu
+def test_ahead_destroy_mid_sequence_gpu():
+    _destroy_mid_sequence(lambda c: make_tracker(c, device=0), configs.EUROC_MAV.with_(num_features=400, min_px_dist=6), 19, 7, 3, 5)

@@ -1,2 +1,6 @@
-UVIO_KLT_AHEAD=0 UVIO_KLT_LANES=1 UVIO_KLT_DEPTH=1 ncu --set full --clock-control none --import-source on -k regex:'k_(lk|preprocess|ransac|subpix|fast)' -s 36 -c 6 -o gpurun_out/step_full python bench.py --streams 32 --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_f.log 2>&1
-ls -la gpurun_out
+set -x
+python -m pytest tests -m gpu -x -q > gpurun_out/t.log 2>&1; echo "tests exit $?" >> gpurun_out/t.log
+python bench.py --streams 64 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_bg1_s64.log 2>&1
+UVIO_KLT_BACKGROUND=0 python bench.py --streams 64 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_bg0_s64.log 2>&1
+python bench.py --streams 32 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_bg1_s32.log 2>&1
+UVIO_KLT_BACKGROUND=0 python bench.py --streams 32 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_bg0_s32.log 2>&1

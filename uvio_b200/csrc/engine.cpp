@@ -227,9 +227,7 @@ struct Lane {
       for (int i = 0; i < KernelProf::MAX_MARKS; i++) cudaEventCreate(&prof.ev[i]);
       prof.ready = true;
     }
-    prof.n = 0;
-    prof.open = false;
-    g_prof = &prof;
+    g_prof = &prof;   // marks accumulate (a pass's background part records too) until prof_fold takes them
   }
   void prof_end() {
     if (g_prof == &prof) g_prof = nullptr;
@@ -259,6 +257,12 @@ struct Lane {
     std::vector<Unit *> unit;
     std::vector<char> stereo;
     int njobs = 0;
+    // level 1: FAST issued.  level 2: the whole detection (top-K, sub-pixel, stereo LK, ids) was finished in the background
+    // after the feed returned (Pass::background); currid_before = the trackers' id counters before it, put back if the
+    // result cannot be used.
+    int level = 0;
+    std::vector<size_t> currid_before;
+    int nsp = 0, nlk = 0;
   } ahead;
   DevVec<uint8_t> clahe_lut;
   JobVec<FastJob> fast_jobs;
@@ -319,6 +323,9 @@ class Context {
   bool tables_dirty = true;
   std::vector<void *> allocs;   // image memory of all cameras
   struct RawSlot { size_t bytes; uint8_t *p[2]; };
+  std::vector<struct Pass> *bg_passes = nullptr;   // the passes of the last feed_batch: their background part runs after it returned
+  void forget_rig(Rig *rig);       // a tracker is going away: detections issued ahead that list it are dropped
+  void background_wait();          // returns when no background part is running (pool->finish)
   std::vector<RawSlot> raw_free;   // upload buffers of destroyed trackers, reused by cameras of the same size
   void release_camera(CamState &c);
   // submit_batch: frames announced ahead of their feed go up and are pre-processed on a stream of their own, one event
@@ -500,8 +507,48 @@ class Pool {
     std::lock_guard<std::mutex> lk(m);
     job = nullptr;
   }
+  // Asynchronous variant: start() hands fn(0..n-1) to the workers and returns; finish() helps with what is left and waits.
+  // (One job at a time: run() and start() must not be called while a started job has not been finished.)
+  void start(int n, std::function<void(int)> fn) {
+    async_fn = std::move(fn);
+    if (threads.empty()) {   // no workers: the work is done when it is waited for
+      async_n = n;
+      async_active = true;
+      async_inline = true;
+      return;
+    }
+    {
+      std::lock_guard<std::mutex> lk(m);
+      job = &async_fn;
+      total = n;
+      pending.store(n);
+      const unsigned long long g = generation.load() + 1;
+      next.store(g << 32);
+      generation.store(g, std::memory_order_release);
+    }
+    if (sleepers.load() > 0) cv.notify_all();
+    async_n = n;
+    async_active = true;
+    async_inline = false;
+  }
+  void finish() {
+    if (!async_active) return;
+    if (async_inline) {
+      for (int i = 0; i < async_n; i++) async_fn(i);
+    } else {
+      drain(generation.load(), async_fn, async_n);
+      while (pending.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+      std::lock_guard<std::mutex> lk(m);
+      job = nullptr;
+    }
+    async_active = false;
+  }
+  bool busy() const { return async_active; }
 
  private:
+  std::function<void(int)> async_fn;
+  int async_n = 0;
+  bool async_active = false, async_inline = false;
   void loop() {
     unsigned long long seen = 0;
     while (true) {
@@ -551,6 +598,9 @@ class Pool {
   std::atomic<bool> quit{false};
 };
 
+void Context::background_wait() {
+  if (pool) pool->finish();
+}
 void Context::uploader_drain() {
   std::unique_lock<std::mutex> lk(pf_mtx);
   pf_cv.wait(lk, [&] { return pf_issued == pf_queued; });
@@ -660,7 +710,7 @@ Context *context_for_device(int device, int *err) {
       if (err) *err = (int)e;
       return nullptr;
     }
-  c->pool = new Pool(c->threads - 1);
+  c->pool = new Pool(c->threads);   // one worker per lane thread: the caller takes a share in run(), none in start()
   for (auto &a : c->pf_stats) a.store(0);
   c->uploader = std::thread([raw = c.get()] { raw->uploader_loop(); });
   Context *p = c.get();
@@ -740,16 +790,19 @@ void Context::release_camera(CamState &c) {
 }
 
 Rig::~Rig() {
+  if (!g_contexts_gone.load()) {
+    std::lock_guard<std::mutex> lk(ctx->mtx);
+    ctx->uploader_drain();
+    ctx->background_wait();
+    ctx->forget_rig(this);     // before the units go: the lanes' detections issued ahead point at them
+    bool any = false;
+    for (auto &c : cams) any |= c.dev_base != nullptr;
+    if (any && cudaSetDevice(ctx->device) == cudaSuccess) {
+      cudaDeviceSynchronize();   // a detection issued ahead or an announced frame of this tracker may still be running
+      for (auto &c : cams) ctx->release_camera(c);
+    }
+  }
   for (Unit *u : unit_pool) delete u;
-  if (g_contexts_gone.load()) return;
-  bool any = false;
-  for (auto &c : cams) any |= c.dev_base != nullptr;
-  if (!any) return;
-  std::lock_guard<std::mutex> lk(ctx->mtx);
-  if (cudaSetDevice(ctx->device) != cudaSuccess) return;
-  ctx->uploader_drain();
-  cudaDeviceSynchronize();   // a detection issued ahead or an announced frame of this tracker may still be running
-  for (auto &c : cams) ctx->release_camera(c);
 }
 Unit *Rig::unit_at(size_t i) {
   while (unit_pool.size() <= i) unit_pool.push_back(new Unit);
@@ -1148,6 +1201,8 @@ struct Pass {
   int issue_detection(bool ahead, bool &any_first, int &max_cw, int &max_ch);
   bool ahead_usable();
   void issue_ahead();
+  bool detected = false;   // this pass found its whole detection finished by the previous pass's background part
+  void background();       // runs after feed_batch has returned (pool workers): rounds 1-2 of the NEXT feed of these units
 
   void fail(FeedRequest &r, int code) {
     r.status = code;
@@ -1165,6 +1220,10 @@ struct Pass {
   int stage3();
   // run the next stage (synchronising the lane's stream first when the stage consumes GPU results)
   void step() {
+    if (detected && stage == 1) {   // nothing to wait for, nothing to do: the detection is already there
+      stage++;
+      return;
+    }
     if (rc == OK && n > 0) {
       cudaSetDevice(ctx->dev->device);
       g_prof = ctx->prof_on ? &ctx->prof : nullptr;
@@ -1361,26 +1420,49 @@ static bool ahead_enabled() {   // UVIO_KLT_AHEAD=0: every feed issues its own d
   return v;
 }
 
+// A background detection that will not be used: the id counters it advanced go back to where they were.  Every tracker in
+// the list is unfed since (a feed of any of them through another lane cancels first: feed_batch).
+static void cancel_ahead(Lane &ln) {
+  Lane::Ahead &a = ln.ahead;
+  if (a.valid && a.level == 2) {
+    for (size_t i = a.unit.size(); i-- > 0;) {   // in reverse: a tracker with several units ends at its earliest value
+      a.unit[i]->rig->currid = a.currid_before[i];
+      a.unit[i]->rig->bg_lane = -1;
+    }
+  }
+  a.valid = false;
+  a.level = 0;
+}
+
 // The detection issued when the previous pass of this lane ended serves this pass if the units are the same and nothing
 // it read has changed: same trackers (by serial: an address may be reused), no set_num_features / change_feat_id since,
-// same stereo / mono shape, and no unit starting over (a tracker that lost every point detects on the NEW frame).
+// no feed of any of them through another lane since, same stereo / mono shape, and no unit starting over (a tracker that
+// lost every point detects on the NEW frame).
 bool Pass::ahead_usable() {
   const Lane::Ahead &a = ctx->ahead;
   if (!a.valid || a.unit.size() != units.size()) return false;
   for (size_t i = 0; i < units.v.size(); i++) {
     const Unit *u = units.v[i];
     if (u != a.unit[i] || u->rig->serial != a.serial[i] || u->rig->epoch != a.epoch[i] || u->rig->feeds != a.feeds[i] + 1 ||
-        (char)u->stereo != a.stereo[i] ||
-        u->first || u->failed)
+        (char)u->stereo != a.stereo[i] || u->first || u->failed)
       return false;
   }
   return true;
+}
+
+static bool background_enabled() {   // UVIO_KLT_BACKGROUND=1 turns it on (off until it has been through the GPU suite)
+  static const bool v = [] {
+    const char *e = getenv("UVIO_KLT_BACKGROUND");
+    return e && e[0] == '1';
+  }();
+  return v;
 }
 
 // End of a pass: issue the next pass's detection (see Lane::Ahead).  All or nothing per lane.
 void Pass::issue_ahead() {
   Lane::Ahead &a = ctx->ahead;
   a.valid = false;
+  a.level = 0;
   // (when FAST itself is being timed, every feed issues its own detection inside the timed window)
   if (!ahead_enabled() || (ctx->prof_on && ((ctx->prof.mask >> K_FAST) & 1u)) || rc != OK || units.size() == 0) return;
   for (auto &u : units) {
@@ -1402,6 +1484,38 @@ void Pass::issue_ahead() {
   if (issue_detection(true, any_first, cw, ch) != OK || any_first) return;
   a.njobs = njobs;
   a.valid = true;
+  a.level = 1;
+}
+
+// After feed_batch has returned: the rest of the NEXT feed's detection for the units of this pass -- wait for the FAST that
+// issue_ahead launched, per-cell top-K, sub-pixel + stereo LK (round 2), then ids and the right-image pass -- so that the
+// next feed starts at its temporal LK.  Nothing here touches what the caller may read meanwhile (observations, pts_last);
+// the trackers' id counters are advanced and put back by cancel_ahead if the result is not used.
+void Pass::background() {
+  Lane::Ahead &a = ctx->ahead;
+  if (!a.valid || a.level != 1 || !background_enabled()) return;
+  if (ctx->prof_on && ((ctx->prof.mask >> K_SUBPIX) & 1u)) return;   // sub-pixel timed: keep it inside the timed window
+  cudaSetDevice(ctx->dev->device);
+  g_prof = ctx->prof_on ? &ctx->prof : nullptr;
+  auto give_up = [&] {
+    a.valid = false;
+    a.level = 0;
+    g_prof = nullptr;
+  };
+  if (ctx->sync() != OK) return give_up();
+  njobs = a.njobs;
+  tmark = now_us();
+  if (stage1() != OK || ctx->sync() != OK) return give_up();
+  a.currid_before.clear();
+  for (auto &u : units) a.currid_before.push_back(u.rig->currid);
+  bool ok = true;
+  for (auto &u : units) ok = ok && phase_c_detect(ctx, u) == OK;
+  a.level = 2;            // from here on cancel_ahead puts the id counters back
+  a.nsp = nsp;
+  a.nlk = nlk;
+  for (auto &u : units) u.rig->bg_lane = ctx->index;
+  if (!ok) cancel_ahead(*ctx);
+  g_prof = nullptr;
 }
 
 int Pass::stage0() {
@@ -1526,9 +1640,16 @@ int Pass::stage0() {
   bool any_first = false;
   if (ahead_usable()) {
     njobs = ctx->ahead.njobs;
+    if (ctx->ahead.level == 2) {
+      detected = true;
+      nsp = ctx->ahead.nsp;
+      nlk = ctx->ahead.nlk;
+      for (auto &u : units) u.rig->bg_lane = -1;
+    }
     ctx->ahead.valid = false;
+    ctx->ahead.level = 0;
   } else {
-    ctx->ahead.valid = false;
+    cancel_ahead(*ctx);
     int e = issue_detection(false, any_first, max_cw, max_ch);
     if (e != OK) return e;
   }
@@ -1616,7 +1737,7 @@ int Pass::stage2() {
   // ---- host: finish detection; round 3: temporal LK + RANSAC -----------------------------------------------------------
   size_t lk_bound = 0;
   for (auto &u : units) {
-    int e = phase_c_detect(ctx, u);
+    int e = detected ? OK : phase_c_detect(ctx, u);
     if (e != OK) { fail(*u.req, e); u.failed = true; continue; }
     if (u.first) {                                                   // TrackKLT.cpp:110-123 / :221-240: store, no DB update
       store_last(u.L, u.L.pts, u.L.ids);
@@ -1698,6 +1819,7 @@ static int validate_request(Context *ctx, FeedRequest &rq, bool announcing) {
       if (rq.sensor_ids[q] == rq.sensor_ids[k]) return E_BADMSG;
     if (c->raw_in[0] < 0) {
       ctx->uploader_drain();   // a new camera grows the tables a batch in flight may be reading
+      ctx->background_wait();  // ... and so may the background part of the last feed
       int e = ctx->alloc_camera(*c, im.w, im.h, P.pyr_levels, P.win_size, P.downsample_cameras != 0);
       if (e != OK) return e;
     } else if (c->in_w != im.w || c->in_h != im.h) return E_SIZE;
@@ -1809,10 +1931,20 @@ int submit_batch(Context *ctx, FeedRequest *reqs, int n) {
   return worst;
 }
 
+void Context::forget_rig(Rig *rig) {
+  for (auto &ln : lanes)
+    for (Unit *u : ln->ahead.unit)
+      if (ln->ahead.valid && u->rig == rig) {
+        cancel_ahead(*ln);
+        break;
+      }
+}
+
 int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   HOSTPROF(fb_total);
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
+  ctx->background_wait();   // the background part of the previous call (it may hold these trackers' detection)
   int worst = OK;
   auto fail = [&](FeedRequest &r, int code) {
     r.status = code;
@@ -1833,12 +1965,21 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
   // ---- split the trackers over the lanes (contiguous shares); every host thread drives `depth` lanes stage by stage ---------
   const int nl = std::max(1, std::min((int)ctx->lanes.size(), (int)good.size()));
   const int nthreads = std::max(1, std::min(ctx->threads, nl));
-  std::vector<Pass> passes(nl);
+  if (!ctx->bg_passes) ctx->bg_passes = new std::vector<Pass>;
+  std::vector<Pass> &passes = *ctx->bg_passes;   // they outlive the call: Pass::background runs after it
+  passes.clear();
+  passes.resize((size_t)nl);
   for (int l = 0; l < nl; l++) {
     size_t b = good.size() * (size_t)l / nl, e = good.size() * (size_t)(l + 1) / nl;
     passes[l].ctx = ctx->lanes[l].get();
     passes[l].reqs = good.data() + b;
     passes[l].n = (int)(e - b);
+    // a tracker whose finished detection sits in another lane (the batch was composed differently last time): drop that
+    // lane's result before anything of this call runs, so that the id counters are back where the reference has them
+    for (size_t i = b; i < e; i++) {
+      const int bl = good[i]->rig->bg_lane;
+      if (bl >= 0 && bl != l) cancel_ahead(*ctx->lanes[(size_t)bl]);
+    }
   }
   static const bool trace = getenv("UVIO_KLT_TRACE_LANES") != nullptr;   // development: per-lane wall clock of a few calls
   const double t_call = now_us();
@@ -1876,6 +2017,11 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     if (rc[l] > worst) worst = rc[l];
   }
   ctx->stats[4] += 1;
+  // The call returns here; the pool's workers go on with rounds 1-2 of the next feed of the same trackers (Pass::background).
+  if (worst != E_CUDA && background_enabled()) {
+    for (auto &p : passes) p.reqs = nullptr;   // the requests die with the call; the background part never looks at them
+    ctx->pool->start(nl, [ctx](int l) { (*ctx->bg_passes)[(size_t)l].background(); });
+  }
   return worst;
 }
 
@@ -1893,6 +2039,7 @@ static int slot_pyr(Rig *rig, size_t cam_id, int slot, CamState **out) {
 int stage_get_level(Rig *rig, size_t cam_id, int slot, int level, uint8_t *out, size_t out_stride, int *w, int *h, int *nlv) {
   Context *dev = rig->ctx;
   std::lock_guard<std::mutex> guard(dev->mtx);
+  dev->background_wait();
   Lane *ctx = dev->lanes[0].get();
   CamState *c;
   int p = slot_pyr(rig, cam_id, slot, &c);
@@ -1913,6 +2060,7 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
                int *n_out) {
   Context *dev = rig->ctx;
   std::lock_guard<std::mutex> guard(dev->mtx);
+  dev->background_wait();
   Lane *ctx = dev->lanes[0].get();
   CamState *c;
   int p = slot_pyr(rig, cam_id, slot, &c);
@@ -1927,7 +2075,7 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
   CU_TRY(ctx->fast_out_dev.reserve(words));
   CU_TRY(ctx->fast_cnt_dev.reserve(1, true));
   CU_TRY(ctx->fast_ticket.reserve(1, true));
-  ctx->ahead.valid = false;   // the lane's FAST buffers are about to be reused
+  cancel_ahead(*ctx);   // the lane's FAST buffers are about to be reused
   ctx->fast_jobs.h[0] = FastJob{p, x0, y0, cw, ch, 0, (int)words, threshold};
   CU_TRY(ctx->fast_jobs.upload(ctx->stream, 1));
   CU_TRY(launch_fast(ctx->stream, ctx->fast_jobs.d, 1, cw, ch, dev->pyr_dev.d, ctx->fast_out_dev.d,
@@ -1948,6 +2096,7 @@ int stage_fast(Rig *rig, size_t cam_id, int slot, int x0, int y0, int cw, int ch
 int stage_subpix(Rig *rig, size_t cam_id, int slot, const float *pts, int n, float *out) {
   Context *dev = rig->ctx;
   std::lock_guard<std::mutex> guard(dev->mtx);
+  dev->background_wait();
   Lane *ctx = dev->lanes[0].get();
   CamState *c;
   int p = slot_pyr(rig, cam_id, slot, &c);
@@ -1974,6 +2123,7 @@ int stage_lk(Rig *rig, size_t cam0, int slot0, size_t cam1, int slot1, const flo
              float *out, uint8_t *status, uint8_t *mask, float *p1n) {
   Context *dev = rig->ctx;
   std::lock_guard<std::mutex> guard(dev->mtx);
+  dev->background_wait();
   Lane *ctx = dev->lanes[0].get();
   CamState *c0, *c1;
   int p0 = slot_pyr(rig, cam0, slot0, &c0), p1 = slot_pyr(rig, cam1, slot1, &c1);
@@ -2029,6 +2179,7 @@ int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const fl
                  float *p1n) {
   Context *dev = rig->ctx;
   std::lock_guard<std::mutex> guard(dev->mtx);
+  dev->background_wait();
   Lane *ctx = dev->lanes[0].get();
   CamState *c0 = rig->find_cam(cam0), *c1 = rig->find_cam(cam1);
   if (!c0 || !c1) return E_CAMID;
@@ -2071,6 +2222,7 @@ int context_cuda_error(Context *ctx) { return ctx->cuda_err; }
 
 int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long long launches[K_COUNT]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
+  ctx->background_wait();
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
   for (int k = 0; k < K_COUNT; k++) {
     if (ms) ms[k] = 0;
@@ -2101,6 +2253,8 @@ int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long 
     }
     if (enable >= 0) {
       ln->prof_on = enable != 0;
+      ln->prof.n = 0;
+      ln->prof.open = false;
       ln->prof.mask = enable > 1 ? (unsigned)(enable >> 1) : ~0u;   // enable = 1: all kernels; 1 | mask<<1: only those
       if (enable) {
         memset(ln->prof_ms, 0, sizeof(ln->prof_ms));
@@ -2113,6 +2267,7 @@ int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long 
 
 void context_stats(Context *ctx, unsigned long long out[12]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
+  ctx->background_wait();
   memcpy(out, ctx->stats, sizeof(ctx->stats));
   out[1] += ctx->pf_stats[1].load();
   out[2] += ctx->pf_stats[2].load();
@@ -2129,6 +2284,7 @@ void context_stats(Context *ctx, unsigned long long out[12]) {
 // interval between the two records spans exactly the device work (and host gaps) of the feeds issued in between.
 void context_host_profile(Context *ctx, int reset, double us[8]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
+  ctx->background_wait();
   for (int k = 0; k < 8; k++) {
     if (us) us[k] = ctx->seg_us[k];
     if (reset) ctx->seg_us[k] = 0;
@@ -2137,6 +2293,7 @@ void context_host_profile(Context *ctx, int reset, double us[8]) {
 
 int context_timer(Context *ctx, int stop, float *ms) {
   std::lock_guard<std::mutex> guard(ctx->mtx);
+  ctx->background_wait();
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
   for (int i = 0; i < 2; i++)
     if (!ctx->ev[i]) CU_TRY(cudaEventCreate(&ctx->ev[i]));

@@ -95,6 +95,7 @@ class Rig {                     // one tracker = one TrackKLT instance
   std::unordered_map<size_t, int> cam_index;        // camera id -> index in cams
   size_t currid;                                    // TrackBase.cpp:34
   unsigned long long serial = 0;                    // unique per Rig object ever created (handles may reuse an address)
+  int bg_lane = -1;                                 // lane that holds a finished background detection of this tracker
   unsigned long long feeds = 0;                     // feeds this tracker has been through (whatever lane ran them)
   unsigned epoch = 0;                               // bumped by set_num_features / change_feat_id: state a detection that was
                                                     // issued ahead of its feed may have read
