@@ -1,5 +1,6 @@
 set -x
-python bench.py > gpurun_out/r1_bench.json 2>gpurun_out/b.err; echo "bench exit $?"
-python bench.py --impl reference > gpurun_out/r1_bench_reference.json 2>&1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/r1_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_l.log 2>&1
-python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1
+python -m pytest tests -m gpu -x -q > gpurun_out/t.log 2>&1; echo "tests exit $?" >> gpurun_out/t.log
+python bench.py --streams 64 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_e1_s64.log 2>&1
+UVIO_KLT_EARLY=0 python bench.py --streams 64 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_e0_s64.log 2>&1
+python bench.py --streams 32 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_e1_s32.log 2>&1
+UVIO_KLT_EARLY=0 python bench.py --streams 32 --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/b_e0_s32.log 2>&1
