@@ -115,7 +115,12 @@ def _destroy_mid_sequence(make, cfg, n_trk, n, drop_at, drop):
         alive = sorted(trks)
         feed_batch([trks[s] for s in alive], [CameraData(0.05 * k, [0, 1], list(seqs[s][k]), masks) for s in alive])
         for s in alive:
-            assert trks[s].new_observations().tobytes() == ref[s][k], f"frame {k} tracker {s}"
+            got = trks[s].new_observations()
+            if got.tobytes() != ref[s][k]:
+                want = np.frombuffer(ref[s][k], dtype=got.dtype)
+                bad = [i for i in range(min(len(got), len(want))) if got[i].tobytes() != want[i].tobytes()]
+                raise AssertionError(f"frame {k} tracker {s}: {len(got)} vs {len(want)} observations, {len(bad)} differ, first "
+                                     f"{bad[:3]}: got {[got[i] for i in bad[:3]]} want {[want[i] for i in bad[:3]]}")
 
 
 def _small_cfg():

@@ -159,7 +159,12 @@ struct DevVec {
     cap = 0;
     cudaError_t e = cudaMalloc((void **)&d, ncap * sizeof(T));
     if (e != cudaSuccess) return e;
-    if (zero) e = cudaMemset(d, 0, ncap * sizeof(T));
+    if (zero) {
+      // cudaMemset on device memory may return before it has run, and the lanes' streams are non-blocking: without the
+      // wait a kernel of the lane could start on counters that are zeroed under it (seen as a rare lost corner)
+      e = cudaMemset(d, 0, ncap * sizeof(T));
+      if (e == cudaSuccess) e = cudaStreamSynchronize(nullptr);
+    }
     cap = ncap;
     return e;
   }

@@ -22,8 +22,8 @@ constexpr int LK_NPIX = LK_WIN * LK_WIN;   // 225
 constexpr int LK_FP = 18;                  // template footprint rows/cols (16 + 1-px Scharr halo each side)
 constexpr int LK_FPW = 6;                  // 32-bit words staged per footprint row (24 bytes cover 18 + alignment slack)
 constexpr int LK_BW = 17;                  // blended-intensity grid of an interior template: 15 + a 1-px Scharr ring
-constexpr int LK_JW = 32;                  // rows/cols of the J window staged per level (search range +-8 px around the guess)
-constexpr int LK_JWW = 10;                 // words per staged J row (40 bytes cover 32 + alignment slack)
+constexpr int LK_JW = 24;                  // rows/cols of the J window staged per level (search range +-4 px around the guess; re-centred beyond)
+constexpr int LK_JWW = 7;                  // words per staged J row (28 bytes cover 24 + alignment slack)
 
 constexpr int LK_TAIL = 7 * LK_WIN;         // 105 window pixels in columns 8..14: the scalar tail of every row
 constexpr int LK_TAILP = 108;               // padded to whole 16-byte vectors
@@ -41,9 +41,9 @@ struct alignas(16) LkSmem {
     Short2 dI[16 * 16];                    // Scharr (dx,dy) at ip .. ip+15, zero outside the frame (while it is built)
     int blend[LK_BW * LK_BW];              // blended intensities (weights not yet shifted out) at ip-1 .. ip+15 (interior windows)
   };
-  Short2 dIw[LK_NPIX + 3];                 // blended derivative patch
+  alignas(16) Short2 dIw[LK_NPIX + 3];     // blended derivative patch (aligned: the sizes above are not multiples of 16)
   short Iw[LK_NPIX + 7];                   // template, intensity * 32
-  union {
+  union alignas(16) {                      // read with 16-byte loads (lk_tail_chain)
     struct {
       float gsimd[3][LK_WIN * 8];          // fp32(Ix*Ix), fp32(Ix*Iy), fp32(Iy*Iy), columns 0..7
       float gtail[3][LK_TAILP];            // the same, columns 8..14
