@@ -263,14 +263,20 @@ __global__ void __launch_bounds__(256) k_fast(const FastJob *jobs, const PyrDesc
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  unsigned n = __ldcg(&count_dev[blockIdx.y]);
-  if (n > (unsigned)job.out_cap) n = job.out_cap;
-  for (unsigned i = threadIdx.x; i < n; i += blockDim.x) out_host[job.out_off + i] = __ldcg(&out_dev[job.out_off + i]);
+  // One thread reads the count and re-arms the counters; the others take the count from shared memory.  (Every thread
+  // used to read count_dev itself while thread 0 went on to zero it: a warp scheduled late read 0 and skipped its share
+  // of the copy, leaving stale words in the host list -- seen as one tracker in ~6 % of 19-tracker runs diverging.)
+  __shared__ unsigned s_n;
   if (threadIdx.x == 0) {
-    count_host[blockIdx.y] = n;
+    unsigned c = __ldcg(&count_dev[blockIdx.y]);
+    s_n = c > (unsigned)job.out_cap ? (unsigned)job.out_cap : c;
     count_dev[blockIdx.y] = 0;
     ticket_dev[blockIdx.y] = 0;
   }
+  __syncthreads();
+  const unsigned n = s_n;
+  for (unsigned i = threadIdx.x; i < n; i += blockDim.x) out_host[job.out_off + i] = __ldcg(&out_dev[job.out_off + i]);
+  if (threadIdx.x == 0) count_host[blockIdx.y] = n;
 }
 
 cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max_cell_w, int max_cell_h, const PyrDesc *pyr_tab,
