@@ -1,5 +1,6 @@
-// Dependency-free mirror of the reference types on either side of the tracker, for builds without OpenCV / Eigen / Boost
-// (this container has none of them).  Names, members and method signatures follow the reference so that TrackKLTGpu.h
+// TEST SCAFFOLDING (not part of the product): dependency-free mirror of the reference types on either side of the tracker,
+// for builds without OpenCV / Eigen / Boost (this container has none of them).  Names, members, method signatures and --
+// what matters for a drop-in -- the virtual / non-virtual split of TrackBase follow the reference, so that TrackKLTGpu.h
 // compiles unchanged against either this header or the real ov_core headers (define UVIO_USE_REAL_OV_CORE).
 //
 //   ov_core::CameraData        ov_core/src/utils/sensor_data.h:55-80     images are {ptr, step, cols, rows} views here
@@ -16,6 +17,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <string>
 #include <unordered_map>
 #include <vector>
 
@@ -56,6 +58,41 @@ public:
   std::unordered_map<size_t, std::vector<std::array<float, 2>>> uvs;
   std::unordered_map<size_t, std::vector<std::array<float, 2>>> uvs_norm;
   std::unordered_map<size_t, std::vector<double>> timestamps;
+  // Feature.cpp:60-82: drop every measurement with a timestamp <= the given one
+  void clean_older_measurements(double timestamp) {
+    for (auto &pair : timestamps) {
+      auto &ts = pair.second;
+      auto &a = uvs[pair.first];
+      auto &b = uvs_norm[pair.first];
+      size_t k = 0;
+      for (size_t i = 0; i < ts.size(); i++)
+        if (!(ts[i] <= timestamp)) { ts[k] = ts[i]; a[k] = a[i]; b[k] = b[i]; k++; }
+      ts.resize(k); a.resize(k); b.resize(k);
+    }
+  }
+  // Feature.cpp:36-58 / :84-106: keep only (valid) / drop (invalid) the measurements at the listed timestamps
+  void clean_old_measurements(const std::vector<double> &valid_times) {
+    for (auto &pair : timestamps) {
+      auto &ts = pair.second;
+      auto &a = uvs[pair.first];
+      auto &b = uvs_norm[pair.first];
+      size_t k = 0;
+      for (size_t i = 0; i < ts.size(); i++)
+        if (std::find(valid_times.begin(), valid_times.end(), ts[i]) != valid_times.end()) { ts[k] = ts[i]; a[k] = a[i]; b[k] = b[i]; k++; }
+      ts.resize(k); a.resize(k); b.resize(k);
+    }
+  }
+  void clean_invalid_measurements(const std::vector<double> &invalid_times) {
+    for (auto &pair : timestamps) {
+      auto &ts = pair.second;
+      auto &a = uvs[pair.first];
+      auto &b = uvs_norm[pair.first];
+      size_t k = 0;
+      for (size_t i = 0; i < ts.size(); i++)
+        if (std::find(invalid_times.begin(), invalid_times.end(), ts[i]) == invalid_times.end()) { ts[k] = ts[i]; a[k] = a[i]; b[k] = b[i]; k++; }
+      ts.resize(k); a.resize(k); b.resize(k);
+    }
+  }
 };
 
 class FeatureDatabase {          // FeatureDatabase.h / .cpp
@@ -95,7 +132,7 @@ public:
       if (skip_deleted && it->second->to_delete) { ++it; continue; }
       bool has_newer_measurement = false;
       for (auto const &pair : it->second->timestamps) {
-        has_newer_measurement = (!pair.second.empty() && pair.second.back() > timestamp);
+        has_newer_measurement = (!pair.second.empty() && pair.second.back() >= timestamp);   // FeatureDatabase.cpp:104 (>=)
         if (has_newer_measurement) break;
       }
       if (!has_newer_measurement) {
@@ -133,6 +170,36 @@ public:
       else ++it;
     }
   }
+  // FeatureDatabase.cpp:226-243
+  void cleanup_measurements(double timestamp) {
+    std::lock_guard<std::mutex> lck(mtx);
+    for (auto it = features_idlookup.begin(); it != features_idlookup.end();) {
+      it->second->clean_older_measurements(timestamp);
+      int ct_meas = 0;
+      for (const auto &pair : it->second->timestamps) ct_meas += (int)pair.second.size();
+      if (ct_meas < 1) it = features_idlookup.erase(it);
+      else ++it;
+    }
+  }
+  // FeatureDatabase.cpp:128-167
+  std::vector<std::shared_ptr<Feature>> features_containing_older(double timestamp, bool remove = false, bool skip_deleted = false) {
+    std::vector<std::shared_ptr<Feature>> feats_old;
+    std::lock_guard<std::mutex> lck(mtx);
+    for (auto it = features_idlookup.begin(); it != features_idlookup.end();) {
+      if (skip_deleted && it->second->to_delete) { ++it; continue; }
+      bool found = false;
+      for (auto const &pair : it->second->timestamps) {
+        found = (!pair.second.empty() && pair.second.at(0) < timestamp);
+        if (found) break;
+      }
+      if (found) {
+        feats_old.push_back(it->second);
+        if (remove) { it = features_idlookup.erase(it); continue; }
+      }
+      ++it;
+    }
+    return feats_old;
+  }
   size_t size() {
     std::lock_guard<std::mutex> lck(mtx);
     return features_idlookup.size();
@@ -154,30 +221,63 @@ struct KeyPointMirror {          // cv::KeyPoint: consumers read .pt only (VioMa
   int octave = 0, class_id = -1;
 };
 
-class TrackBase {                // TrackBase.h:72-196 (display_* left out: drawing only)
-public:
+class TrackBase {                // TrackBase.h:72-196, with the reference's virtual / non-virtual split kept exactly:
+public:                          // virtual: ~TrackBase (:91), feed_new_camera (:97), display_active (:106), display_history (:116);
+                                 // plain members: get_feature_database (:123), change_feat_id (:134), get_last_obs (:137),
+                                 // get_last_ids (:143), get_num_features (:149), set_num_features (:152)
   enum HistogramMethod { NONE, HISTOGRAM, CLAHE };
   TrackBase(std::unordered_map<size_t, std::shared_ptr<CamCalibMirror>> cameras, int numfeats, int numaruco, bool stereo,
             HistogramMethod histmethod)
       : camera_calib(std::move(cameras)), database(new FeatureDatabase()), num_features(numfeats), use_stereo(stereo),
         histogram_method(histmethod) {
     currid = 4 * (size_t)numaruco + 1;   // TrackBase.cpp:34
+    if (mtx_feeds.empty() || mtx_feeds.size() != camera_calib.size()) {   // TrackBase.cpp:37-40
+      std::vector<std::mutex> list(camera_calib.size());
+      mtx_feeds.swap(list);
+    }
   }
   virtual ~TrackBase() {}
   virtual void feed_new_camera(const CameraData &message) = 0;
+  virtual void display_active(MatView &, int, int, int, int, int, int, std::string = "") {}                               // drawing only
+  virtual void display_history(MatView &, int, int, int, int, int, int, std::vector<size_t> = {}, std::string = "") {}   // drawing only
   std::shared_ptr<FeatureDatabase> get_feature_database() { return database; }
-  virtual std::unordered_map<size_t, std::vector<KeyPointMirror>> get_last_obs() = 0;
-  virtual std::unordered_map<size_t, std::vector<size_t>> get_last_ids() = 0;
+  // TrackBase.cpp:230-248, statement for statement (get_internal_data() returns the map BY VALUE, so the erase / insert act
+  // on temporaries and only feat->featid changes in the database; ids_last is rewritten without taking mtx_last_vars)
+  void change_feat_id(size_t id_old, size_t id_new) {
+    if (database->get_internal_data().find(id_old) != database->get_internal_data().end()) {
+      std::shared_ptr<Feature> feat = database->get_internal_data().at(id_old);
+      database->get_internal_data().erase(id_old);
+      feat->featid = id_new;
+      database->get_internal_data().insert({id_new, feat});
+    }
+    for (auto &cam_ids_pair : ids_last)
+      for (size_t i = 0; i < cam_ids_pair.second.size(); i++)
+        if (cam_ids_pair.second.at(i) == id_old) ids_last.at(cam_ids_pair.first).at(i) = id_new;
+  }
+  std::unordered_map<size_t, std::vector<KeyPointMirror>> get_last_obs() {
+    std::lock_guard<std::mutex> lckv(mtx_last_vars);
+    return pts_last;
+  }
+  std::unordered_map<size_t, std::vector<size_t>> get_last_ids() {
+    std::lock_guard<std::mutex> lckv(mtx_last_vars);
+    return ids_last;
+  }
   int get_num_features() { return num_features; }
-  virtual void set_num_features(int _num_features) { num_features = _num_features; }
-  virtual void change_feat_id(size_t id_old, size_t id_new) = 0;
+  void set_num_features(int _num_features) { num_features = _num_features; }
 
 protected:
   std::unordered_map<size_t, std::shared_ptr<CamCalibMirror>> camera_calib;
   std::shared_ptr<FeatureDatabase> database;
+  std::map<size_t, bool> camera_fisheye;
   int num_features;
   bool use_stereo;
   HistogramMethod histogram_method;
+  std::vector<std::mutex> mtx_feeds;
+  std::mutex mtx_last_vars;
+  std::map<size_t, MatView> img_last;
+  std::map<size_t, MatView> img_mask_last;
+  std::unordered_map<size_t, std::vector<KeyPointMirror>> pts_last;
+  std::unordered_map<size_t, std::vector<size_t>> ids_last;
   std::atomic<size_t> currid;
 };
 

@@ -1,10 +1,15 @@
 // Drives the GPU tracker exactly the way ov_core/src/test_tracking.cpp:288-381 drives TrackKLT: through TrackBase, with
 // CameraData messages, reading the FeatureDatabase afterwards.  Reads raw stereo frames from a file written by the
 // pytest wrapper and prints one line per update_feature call so the wrapper can compare them with the golden stream.
-//   usage: test_trackbase_shim frames.bin W H N
+//   usage: test_trackbase_shim frames.bin W H N [base]
+// With "base" the run follows the estimator's use of the NON-virtual TrackBase members through std::shared_ptr<TrackBase>:
+// the tracker starts with 25 features per camera (init_max_features / num_cameras, VioManager.cpp:131-135), set_num_features
+// raises the budget after a few frames (VioManagerHelper.cpp:124), get_last_obs() / get_last_ids() are read every frame
+// (VioManagerHelper.cpp:209-210, :235-237) and one id is renamed with change_feat_id (TrackBase.cpp:230-248).
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "../../uvio_b200/cpp/TrackKLTGpu.h"
@@ -28,7 +33,35 @@ int main(int argc, char **argv) {
     for (int i = 0; i < 8; i++) cam->values[i] = c ? c1[i] : c0[i];
     cams[(size_t)c] = cam;
   }
-  std::shared_ptr<TrackBase> trackFEATS(new TrackKLTGpu(cams, 200, 0, true, TrackBase::HISTOGRAM, 20, 5, 5, 10));
+  const bool base_mode = argc > 5 && std::string(argv[5]) == "base";
+  std::shared_ptr<TrackBase> trackFEATS(new TrackKLTGpu(cams, base_mode ? 25 : 200, 0, true, TrackBase::HISTOGRAM, 20, 5, 5, 10));
+  if (base_mode) {
+    for (int k = 0; k < N; k++) {
+      CameraData message;
+      message.timestamp = 0.05 * k;
+      for (int c = 0; c < 2; c++) {
+        message.sensor_ids.push_back(c);
+        message.images.push_back(MatView{buf.data() + ((size_t)k * 2 + c) * W * H, (size_t)W, W, H});
+        message.masks.push_back(MatView{zero.data(), (size_t)W, W, H});
+      }
+      if (k == 6) trackFEATS->set_num_features(150);                  // base member, not virtual
+      if (k == 9) {                                                   // rename the first left id, as a loop closure would
+        auto ids = trackFEATS->get_last_ids();
+        if (!ids.at(0).empty()) trackFEATS->change_feat_id(ids.at(0).front(), ids.at(0).front() + 100000);
+      }
+      trackFEATS->feed_new_camera(message);
+      std::unordered_map<size_t, std::vector<KeyPointMirror>> last_obs = trackFEATS->get_last_obs();
+      std::unordered_map<size_t, std::vector<size_t>> last_ids = trackFEATS->get_last_ids();
+      std::printf("nf %d %d\n", k, trackFEATS->get_num_features());
+      for (size_t c = 0; c < 2; c++) {
+        const std::vector<size_t> &ids = last_ids.at(c);              // .at(): throws if the base's maps were never filled
+        const std::vector<KeyPointMirror> &kp = last_obs.at(c);
+        if (ids.size() != kp.size()) return 3;
+        for (size_t i = 0; i < ids.size(); i++) std::printf("last %d %zu %zu %.9g %.9g\n", k, c, ids[i], kp[i].pt.x, kp[i].pt.y);
+      }
+    }
+    return 0;
+  }
   size_t prev = 0;
   for (int k = 0; k < N; k++) {
     CameraData message;

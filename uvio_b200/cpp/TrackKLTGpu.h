@@ -7,13 +7,22 @@
 //                      state->_options.max_aruco_features, params.use_stereo, params.histogram_method,
 //                      params.fast_threshold, params.grid_x, params.grid_y, params.min_px_dist));
 //
-// Compiled against ov_core_mirror.h here (no OpenCV / Eigen / Boost in this container).  With the real ov_core headers
-// (-DUVIO_USE_REAL_OV_CORE) the same class derives from the real ov_core::TrackBase: cv::Mat gives
-// data/step/cols/rows, CamBase gives is_fisheye()/get_value().
+// Only the reference's virtual members are overridden (~TrackBase, feed_new_camera; display_* keep the base's).  The plain
+// members the estimator calls through the base pointer work because the shim mirrors state in both directions around
+// every feed: before it, the base's num_features (set_num_features, VioManagerHelper.cpp:124) and any ids_last rewrite made
+// by TrackBase::change_feat_id (TrackBase.cpp:241-247) are pushed to the handle; after it, pts_last / ids_last of the base
+// are filled from the handle under mtx_last_vars, so get_last_obs() / get_last_ids() (VioManagerHelper.cpp:209-210) see them.
+//
+// Compiled against tests/cpp/ov_core_mirror.h in this repository's tests (no OpenCV / Eigen / Boost in this container; the
+// mirror keeps the reference's virtual / non-virtual split).  With the real ov_core headers (-DUVIO_USE_REAL_OV_CORE, see
+// INTEGRATION.md) the same class derives from the real ov_core::TrackBase: cv::Mat gives data/step/cols/rows, CamBase gives
+// get_value(); tests/test_shim_real_headers.py syntax-checks that branch against the reference's own headers.
 #pragma once
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <stdexcept>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/uvio_klt.h"
@@ -72,6 +81,7 @@ public:
     }
     int rc = uvio_klt_create(&p, cc.data(), (int)cc.size(), cuda_device, &handle);
     if (rc != UVIO_OK) throw std::runtime_error("TrackKLTGpu: uvio_klt_create failed (no CUDA device? there is no CPU fallback)");
+    pushed_num_features = numfeats;
   }
   ~TrackKLTGpu() override { uvio_klt_destroy(handle); }
 
@@ -105,6 +115,7 @@ public:
     f.width = w.data();
     f.height = h.data();
     f.status = 0;
+    sync_to_handle();
     int rc = uvio_klt_feed(handle, &f);
     if (rc == UVIO_E_BADMSG) {                                                        // TrackKLT.cpp:90-93
       std::fprintf(stderr, "[ERROR]: invalid number of images passed %zu, we only support mono or stereo tracking\n", n);
@@ -113,43 +124,44 @@ public:
     if (rc == UVIO_E_CAMID) throw std::out_of_range("TrackKLTGpu: unknown camera id");   // .at() in the reference (:53-54)
     if (rc != UVIO_OK) throw std::runtime_error("TrackKLTGpu: uvio_klt_feed failed");
     replay_observations(message.timestamp);
+    sync_from_handle();
   }
 
-  // TrackBase::get_last_obs / get_last_ids (TrackBase.h:134-146)
-  std::unordered_map<size_t, std::vector<KeyPointT>> get_last_obs() override {
-    std::unordered_map<size_t, std::vector<KeyPointT>> out;
-    for (auto const &kv : camera_calib) {
-      std::vector<size_t> ids;
-      std::vector<float> uv;
-      last_of(kv.first, ids, uv);
-      std::vector<KeyPointT> kps(ids.size());
-      for (size_t i = 0; i < ids.size(); i++) { kps[i].pt.x = uv[2 * i]; kps[i].pt.y = uv[2 * i + 1]; }
-      out[kv.first] = kps;
-    }
-    return out;
-  }
-  std::unordered_map<size_t, std::vector<size_t>> get_last_ids() override {
-    std::unordered_map<size_t, std::vector<size_t>> out;
-    for (auto const &kv : camera_calib) {
-      std::vector<float> uv;
-      last_of(kv.first, out[kv.first], uv);
-    }
-    return out;
-  }
-  void set_num_features(int _num_features) override {   // TrackBase.h:152
-    num_features = _num_features;
-    uvio_klt_set_num_features(handle, _num_features);
-  }
-  // TrackBase.cpp:230-248, including its quirk: get_internal_data() returns the map by value, so only featid changes
-  void change_feat_id(size_t id_old, size_t id_new) override {
-    auto data = database->get_internal_data();
-    auto it = data.find(id_old);
-    if (it != data.end()) it->second->featid = id_new;
-    uvio_klt_change_feat_id(handle, id_old, id_new);
-  }
+  // get_last_obs / get_last_ids / set_num_features / change_feat_id are NOT virtual in the reference (TrackBase.h:134-152) and
+  // the estimator calls them through std::shared_ptr<TrackBase> (VioManagerHelper.cpp:124, :209-210), so they cannot be
+  // overridden: the shim keeps the BASE's own state in step with the handle instead (sync_to_handle / sync_from_handle).
   uvio_klt *native_handle() { return handle; }
 
 protected:
+  // base -> handle: what the non-virtual setters changed on the base since the last feed
+  void sync_to_handle() {
+    if (num_features != pushed_num_features) {                       // TrackBase::set_num_features (TrackBase.h:152)
+      uvio_klt_set_num_features(handle, num_features);
+      pushed_num_features = num_features;
+    }
+    // TrackBase::change_feat_id rewrote entries of ids_last in place (TrackBase.cpp:241-247): forward every (old -> new)
+    std::lock_guard<std::mutex> lckv(mtx_last_vars);
+    for (auto const &kv : ids_synced) {
+      auto it = ids_last.find(kv.first);
+      if (it == ids_last.end() || it->second.size() != kv.second.size()) continue;
+      for (size_t i = 0; i < kv.second.size(); i++)
+        if (it->second[i] != kv.second[i]) uvio_klt_change_feat_id(handle, kv.second[i], it->second[i]);
+    }
+  }
+  // handle -> base: pts_last / ids_last as TrackKLT leaves them (TrackKLT.cpp:369-381), under the same mutex
+  void sync_from_handle() {
+    std::vector<size_t> ids;
+    std::vector<float> uv;
+    std::lock_guard<std::mutex> lckv(mtx_last_vars);
+    for (auto const &kv : camera_calib) {
+      last_of(kv.first, ids, uv);
+      std::vector<KeyPointT> &kps = pts_last[kv.first];
+      kps.assign(ids.size(), KeyPointT());
+      for (size_t i = 0; i < ids.size(); i++) { kps[i].pt.x = uv[2 * i]; kps[i].pt.y = uv[2 * i + 1]; }
+      ids_last[kv.first] = ids;
+      ids_synced[kv.first] = ids;
+    }
+  }
   void replay_observations(double timestamp) {
     int n = 0;
     uvio_klt_get_new_observations(handle, nullptr, 0, &n);
@@ -167,6 +179,8 @@ protected:
   }
   uvio_klt *handle = nullptr;
   std::vector<UvioObs> obs;
+  int pushed_num_features = 0;                                        // the feature budget the handle was last given
+  std::unordered_map<size_t, std::vector<size_t>> ids_synced;         // ids_last as the handle had them after the last feed
 };
 
 }  // namespace ov_core
