@@ -136,3 +136,39 @@ def test_ahead_destroy_mid_sequence_sim(sim_tracker):
 @pytest.mark.gpu
 def test_ahead_destroy_mid_sequence_gpu():
     _destroy_mid_sequence(lambda c: make_tracker(c, device=0), configs.EUROC_MAV.with_(num_features=400, min_px_dist=6), 19, 7, 3, 5)
+
+
+def _camera_subsets(make, n=8):
+    """One tracker fed [0]-only and [1]-only messages in turn, then the pair in swapped order (TrackBase.h:60-65 allows all
+    of it: the reference keys its state by camera id, TrackKLT.cpp:80-89).  A detection issued ahead for the unit that held
+    the OTHER camera must not be taken over (round 1 accepted it: units are indexed by message position)."""
+    from oracle.trackklt_cv2 import make_oracle
+    for stereo, plan in ((False, [[0], [1]] * (n // 2)), (False, [[0, 1], [1, 0]] * (n // 2)), (True, [[0, 1], [1, 0]] * (n // 2))):
+        cfg = configs.EUROC_MAV.with_(num_features=300, min_px_dist=6, use_stereo=stereo)   # budget never reached: every feed detects
+        frames = frames_for(cfg, n, stream_id=23, events=False)
+        masks = masks_for(cfg)
+        ora, trk = make_oracle(cfg), make(cfg)
+        for k, cams in enumerate(plan):
+            imgs = [frames[k][c] for c in cams]
+            n0 = len(ora.database.log)
+            ora.feed_new_camera(0.05 * k, cams, imgs, [masks[c] for c in cams])
+            trk.feed_new_camera(CameraData(0.05 * k, cams, imgs, [masks[c] for c in cams]))
+            oi, oc, ouv, _ = log_arrays(ora.database.log[n0:])
+            obs = trk.new_observations()
+            what = f"stereo={stereo} plan={plan[:2]} frame {k}"
+            assert np.array_equal(obs["id"].astype(np.int64), oi), f"{what}: id stream differs"
+            assert np.array_equal(obs["cam_id"].astype(np.int64), oc), f"{what}: camera stream differs"
+            if len(oi):
+                assert np.array_equal(np.c_[obs["u"], obs["v"]], ouv), f"{what}: positions not bit-exact"
+            last = trk.get_last_ids()
+            for c in cams:
+                assert np.array_equal(last[c].astype(np.int64), np.array(ora.ids_last.get(c, []), np.int64)), f"{what} cam {c}: ids_last"
+
+
+def test_ahead_camera_subsets_sim(sim_tracker):
+    _camera_subsets(sim_tracker, n=6)
+
+
+@pytest.mark.gpu
+def test_ahead_camera_subsets_gpu():
+    _camera_subsets(lambda c: make_tracker(c, device=0), n=10)

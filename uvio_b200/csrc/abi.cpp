@@ -3,6 +3,8 @@
 
 #include <string.h>
 
+#include <algorithm>
+#include <functional>
 #include <new>
 #include <vector>
 
@@ -47,8 +49,8 @@ int uvio_klt_create(const UvioKltParams *p, const UvioCamCalib *cams, int n_cams
   GUARD_BEGIN
   if (!p || !cams || n_cams <= 0 || !out) return UVIO_E_ARG;
   if (p->num_features <= 0 || p->grid_x <= 0 || p->grid_y <= 0 || p->min_px_dist <= 0 || p->pyr_levels < 0 || p->win_size != 15 ||
-      p->histogram_method < 0 || p->histogram_method > 2 || p->lk_max_iters <= 0)
-    return UVIO_E_ARG;
+      p->histogram_method < 0 || p->histogram_method > 2 || p->lk_max_iters != 30 || p->lk_eps != 0.01)
+    return UVIO_E_ARG;   // the LK termination criteria are the reference's constants (TrackKLT.cpp:670,857); others are refused
   *out = nullptr;
   int err = 0;
   Context *ctx = context_for_device(cuda_device, &err);
@@ -105,9 +107,16 @@ static int run_batch(uvio_klt *const *hs, UvioFrame *frames, int n, bool announc
     for (int k = 0; k < i; k++)
       if (hs[k] == hs[i]) return UVIO_E_ARG;
   }
+  {
+    // the handles' locks are taken in address order, whatever order the caller lists them in: two threads feeding
+    // overlapping sets ([A, B] against [B, A]) cannot deadlock
+    std::vector<Rig *> order(n);
+    for (int i = 0; i < n; i++) order[i] = hs[i]->rig;
+    std::sort(order.begin(), order.end(), [](Rig *a, Rig *b) { return std::less<Rig *>()(a, b); });
+    for (Rig *r : order) locks.emplace_back(r->mtx);
+  }
   for (int i = 0; i < n; i++) {
     const UvioFrame &f = frames[i];
-    locks.emplace_back(hs[i]->rig->mtx);
     FeedRequest &r = reqs[i];
     r.rig = hs[i]->rig;
     r.timestamp = f.timestamp;
@@ -191,6 +200,7 @@ int uvio_klt_get_last(uvio_klt *h, size_t cam_id, size_t *ids, float *uv, int ca
 int uvio_klt_set_num_features(uvio_klt *h, int n) {
   if (!h || n <= 0) return UVIO_E_ARG;
   std::lock_guard<std::mutex> lk(h->rig->mtx);
+  context_quiesce(h->rig->ctx);   // a background detection of the last feed may be reading num_features / currid / ids_last
   h->rig->prm.num_features = n;
   h->rig->epoch++;
   return UVIO_OK;
@@ -199,6 +209,7 @@ int uvio_klt_set_num_features(uvio_klt *h, int n) {
 int uvio_klt_change_feat_id(uvio_klt *h, size_t id_old, size_t id_new) {
   if (!h) return UVIO_E_ARG;
   std::lock_guard<std::mutex> lk(h->rig->mtx);
+  context_quiesce(h->rig->ctx);
   for (auto &c : h->rig->cams)                       // TrackBase.cpp:241-247
     for (auto &id : c.ids_last)
       if (id == id_old) id = id_new;

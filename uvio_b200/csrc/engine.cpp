@@ -261,6 +261,9 @@ struct Lane {
                                               // another lane in between (another batch composition) makes it stale
     std::vector<Unit *> unit;
     std::vector<char> stereo;
+    // the cameras each unit held: units are indexed by message position, and a tracker may be fed cam0-only, then cam1-only
+    // messages, or the same pair in another order (TrackBase.h:60-65; all state is keyed by camera id, TrackKLT.cpp:80-89)
+    std::vector<CamState *> cam_l, cam_r;
     int njobs = 0;
     // level 1: FAST issued.  level 2: the whole detection (top-K, sub-pixel, stereo LK, ids) was finished in the background
     // after the feed returned (Pass::background); currid_before = the trackers' id counters before it, put back if the
@@ -1449,7 +1452,7 @@ bool Pass::ahead_usable() {
   for (size_t i = 0; i < units.v.size(); i++) {
     const Unit *u = units.v[i];
     if (u != a.unit[i] || u->rig->serial != a.serial[i] || u->rig->epoch != a.epoch[i] || u->rig->feeds != a.feeds[i] + 1 ||
-        (char)u->stereo != a.stereo[i] || u->first || u->failed)
+        (char)u->stereo != a.stereo[i] || u->first || u->failed || u->L.cam != a.cam_l[i] || (u->stereo && u->R.cam != a.cam_r[i]))
       return false;
   }
   return true;
@@ -1475,9 +1478,11 @@ void Pass::issue_ahead() {
     const bool empty = u.stereo ? (u.L.cam->pts_last.empty() && u.R.cam->pts_last.empty()) : u.L.cam->pts_last.empty();
     if (empty) return;                              // its next feed starts over on the new frame (TrackKLT.cpp:110, :221)
   }
-  a.serial.clear(); a.epoch.clear(); a.feeds.clear(); a.unit.clear(); a.stereo.clear();
+  a.serial.clear(); a.epoch.clear(); a.feeds.clear(); a.unit.clear(); a.stereo.clear(); a.cam_l.clear(); a.cam_r.clear();
   for (auto &u : units) {
     u.first = false;
+    a.cam_l.push_back(u.L.cam);
+    a.cam_r.push_back(u.stereo ? u.R.cam : nullptr);
     a.serial.push_back(u.rig->serial);
     a.epoch.push_back(u.rig->epoch);
     a.feeds.push_back(u.rig->feeds);
@@ -2224,6 +2229,11 @@ int stage_ransac(Rig *rig, size_t cam0, size_t cam1, const float *pts0, const fl
 }
 
 int context_cuda_error(Context *ctx) { return ctx->cuda_err; }
+
+void context_quiesce(Context *ctx) {
+  std::lock_guard<std::mutex> guard(ctx->mtx);
+  ctx->background_wait();
+}
 
 int context_profile(Context *ctx, int enable, double ms[K_COUNT], unsigned long long launches[K_COUNT]) {
   std::lock_guard<std::mutex> guard(ctx->mtx);

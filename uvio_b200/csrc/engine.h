@@ -127,6 +127,8 @@ int submit_batch(Context *ctx, FeedRequest *reqs, int n);
 
 Context *context_for_device(int device, int *err);
 int context_cuda_error(Context *ctx);
+// waits (under the context lock) until no background part of a feed is running: call before mutating tracker state it reads
+void context_quiesce(Context *ctx);
 void context_stats(Context *ctx, unsigned long long out[12]);
 int context_timer(Context *ctx, int stop, float *ms);
 void context_host_profile(Context *ctx, int reset, double us[8]);

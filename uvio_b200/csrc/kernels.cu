@@ -8,6 +8,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "fast_body.h"
 #include "image_body.h"
 #include "lk_body.h"
@@ -195,13 +197,18 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
   if (njobs <= 0) return cudaSuccess;
   // dynamic shared memory for the staged band of rows (0 = bands too large: the kernel reads global memory directly)
   int band_bytes = max_band_bytes <= PRE_MAX_BAND_BYTES ? (max_band_bytes + 127) / 128 * 128 : 0;
-  static thread_local int attr_set_for_device = -1;
-  int device = 0;
-  cudaGetDevice(&device);
-  if (attr_set_for_device != device) {
-    cudaError_t e = cudaFuncSetAttribute(k_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_MAX_BAND_BYTES);
+  {
+    static std::mutex m;
+    static bool attr_set[64] = {false};   // per device: the attribute belongs to the (function, device) pair
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
     if (e != cudaSuccess) return e;
-    attr_set_for_device = device;
+    std::lock_guard<std::mutex> lk(m);
+    if (device < 0 || device >= 64 || !attr_set[device]) {
+      e = cudaFuncSetAttribute(k_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_MAX_BAND_BYTES);
+      if (e != cudaSuccess) return e;
+      if (device >= 0 && device < 64) attr_set[device] = true;
+    }
   }
   if (any_clahe) {
     prof_mark(st, K_CLAHE_TILES);
@@ -495,11 +502,19 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
                           uint8_t *mask_host, uint8_t *mask_dev, bool overlap) {
   if (njobs <= 0) return cudaSuccess;
   size_t dyn = (size_t)4 * max_n * sizeof(float);
-  static size_t configured = 0;
-  if (dyn > configured && dyn + sizeof(RansacSmem) > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(k_ransac, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+  if (dyn + sizeof(RansacSmem) > 48 * 1024) {
+    // the attribute belongs to the (function, device) pair and lanes of several devices launch concurrently
+    static std::mutex m;
+    static size_t configured[64] = {0};
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
     if (e != cudaSuccess) return e;
-    configured = dyn;
+    std::lock_guard<std::mutex> lk(m);
+    if (device < 0 || device >= 64 || dyn > configured[device]) {
+      e = cudaFuncSetAttribute(k_ransac, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+      if (e != cudaSuccess) return e;
+      if (device >= 0 && device < 64) configured[device] = dyn;
+    }
   }
   prof_mark(st, K_RANSAC);
   cudaError_t e = launch_after(k_ransac, dim3(njobs), dim3(RANSAC_THREADS), dyn, st, overlap, jobs, items, lk_dev, status_dev, cams_dev,
