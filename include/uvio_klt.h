@@ -48,8 +48,8 @@ typedef struct UvioKltParams {
   int min_px_dist;      /* minpxdist */
   int pyr_levels;       /* TrackKLT.h:143 hard-codes 5 */
   int win_size;         /* TrackKLT.h:144 hard-codes 15; only 15 is supported */
-  int lk_max_iters;     /* TrackKLT.cpp:670,857: 30 */
-  double lk_eps;        /* TrackKLT.cpp:670,857: 0.01 */
+  int lk_max_iters;     /* TrackKLT.cpp:670,857: 30; only 30 is supported (UVIO_E_ARG otherwise) */
+  double lk_eps;        /* TrackKLT.cpp:670,857: 0.01; only 0.01 is supported */
   /* VioManagerOptions.h:409 downsample_cameras.  Non-zero: every fed image and mask is halved on the device with
    * cv::pyrDown(src, dst, Size(cols / 2.0, rows / 2.0)) before the tracker sees it, which is what
    * VioManager::track_image_and_update does in front of trackFEATS->feed_new_camera (ov_msckf/src/core/VioManager.cpp:268-278);
@@ -174,6 +174,28 @@ int uvio_klt_stage_lk(uvio_klt *h, size_t cam0, int slot0, size_t cam1, int slot
 /* CamBase::undistort_cv on both point sets + cv::findFundamentalMat(FM_RANSAC, 2/max_focal, 0.999) (TrackKLT.cpp:860-873) */
 int uvio_klt_stage_ransac(uvio_klt *h, size_t cam0, size_t cam1, const float *pts0, const float *pts1, int n, uint8_t *mask,
                           float *p0n, float *p1n);
+
+/* ---- allocation-free entry point --------------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * CLAHE exactly as the tracker applies it (cv::createCLAHE(10.0, Size(8,8))->apply; the arithmetic of k_clahe_tiles /
+ * k_clahe_apply, bit-identical to level 0 of uvio_klt_stage_get_level for a UVIO_HIST_CLAHE tracker) of n_images CV_8UC1
+ * images that already live in DEVICE memory: image i is read at src_dev + i*src_image_stride (rows src_pitch bytes apart)
+ * and written to dst_dev + i*dst_image_stride (rows dst_pitch apart); src and dst must not overlap.  The two kernels are
+ * queued on cuda_stream (a cudaStream_t, NULL = the default stream) of the CURRENT device and the call returns without
+ * synchronising.  It calls no cudaMalloc / cudaFree / allocating routine: the per-tile LUT scratch (16 KiB per image)
+ * is a file-scope __device__ array of UVIO_CLAHE_NOALLOC_MAX_IMAGES * 16 KiB = 512 KiB that every GPU loading the library
+ * holds until exit.  Limits: n_images <= UVIO_CLAHE_NOALLOC_MAX_IMAGES, 1 <= width, height <= UVIO_CLAHE_NOALLOC_MAX_DIM;
+ * anything beyond is refused with UVIO_E_ARG and a message in err (err_cap bytes, may be NULL).  The first call on a
+ * device resolves the array's device address (cudaGetSymbolAddress): make that call outside graph capture.  All calls on
+ * a GPU share the one array, which keeps the last call's LUTs (every call rewrites all it reads, nothing needs clearing):
+ * two calls whose kernels may overlap on the GPU -- different streams without an ordering event -- race; order them. */
+#define UVIO_CLAHE_NOALLOC_MAX_IMAGES 32
+#define UVIO_CLAHE_NOALLOC_MAX_DIM 8192
+int uvio_klt_clahe_noalloc(const uint8_t *src_dev, size_t src_pitch, size_t src_image_stride, uint8_t *dst_dev, size_t dst_pitch,
+                           size_t dst_image_stride, int width, int height, int n_images, void *cuda_stream, char *err,
+                           size_t err_cap);
 
 #ifdef __cplusplus
 }
