@@ -26,7 +26,7 @@ META = dict(cv2_version=cv2.__version__, ipp=False)
 
 SEQUENCES = [("euroc_mav", configs.EUROC_MAV, 24, 0, False), ("tum_vi", configs.TUM_VI, 16, 0, False),
              ("rs_d455", configs.RS_D455, 12, 0, False), ("uzhfpv_indoor", configs.UZHFPV_INDOOR, 12, 0, False),
-             ("euroc_mono", configs.EUROC_MAV, 16, 3, True)]
+             ("euroc_mono", configs.EUROC_MAV, 16, 3, True), ("hd_1000", configs.HD_1000, 12, 0, False)]
 
 
 def sequence_fixture(name, cfg, n, stream_id, mono):
@@ -92,6 +92,9 @@ def stage_fixture():
 
 
 if __name__ == "__main__":
+    only = sys.argv[1:]                      # e.g. `make_golden.py hd_1000` regenerates one sequence
     for args in SEQUENCES:
-        sequence_fixture(*args)
-    stage_fixture()
+        if not only or args[0] in only:
+            sequence_fixture(*args)
+    if not only or "stages" in only:
+        stage_fixture()

@@ -11,7 +11,7 @@ from util import frames_for, masks_for
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 SEQ_CFG = {"euroc_mav": configs.EUROC_MAV, "tum_vi": configs.TUM_VI, "rs_d455": configs.RS_D455,
-           "uzhfpv_indoor": configs.UZHFPV_INDOOR, "euroc_mono": configs.EUROC_MAV}
+           "uzhfpv_indoor": configs.UZHFPV_INDOOR, "euroc_mono": configs.EUROC_MAV, "hd_1000": configs.HD_1000}
 
 
 def load(name):

@@ -14,7 +14,7 @@ from util import frames_for, masks_for
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("name", ["euroc_mav", "tum_vi", "rs_d455", "uzhfpv_indoor", "euroc_mono"])
+@pytest.mark.parametrize("name", ["euroc_mav", "tum_vi", "rs_d455", "uzhfpv_indoor", "euroc_mono", "hd_1000"])
 def test_sequence_matches_golden(built_lib, name):
     assert check_tracker_against_golden(name, lambda cfg: make_tracker(cfg)) > 1000
 

@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 
 CFGS = [configs.EUROC_MAV, configs.TUM_VI, configs.RS_D455, configs.UZHFPV_INDOOR,
         configs.EUROC_MAV.with_(name="euroc_none", histogram=configs.HIST_NONE),
-        configs.EUROC_MAV.with_(name="euroc_pyr3", pyr_levels=3)]
+        configs.EUROC_MAV.with_(name="euroc_pyr3", pyr_levels=3), configs.HD_1000, configs.HD_1000_PYR5]
 
 
 def _equalize(img, method):

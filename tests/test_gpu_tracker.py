@@ -31,7 +31,7 @@ def _compare_frame(k, trk, obs, ref, cfg_name):
 
 
 SEQ = [(configs.EUROC_MAV, 40), (configs.TUM_VI, 30), (configs.RS_D455, 25), (configs.UZHFPV_INDOOR, 25),
-       (configs.EUROC_MAV.with_(name="euroc_pyr3", pyr_levels=3), 20), (configs.HD_1000, 12)]
+       (configs.EUROC_MAV.with_(name="euroc_pyr3", pyr_levels=3), 20), (configs.HD_1000, 12), (configs.HD_1000_PYR5, 6)]
 
 
 @pytest.mark.parametrize("cfg,n", SEQ, ids=lambda v: getattr(v, "name", str(v)))

@@ -73,7 +73,10 @@ _UZH = (
 EUROC_MAV = TrackerConfig("euroc_mav", 752, 480, 200, 20, 5, 5, 10, HIST_HISTOGRAM, cams=_EUROC)
 TUM_VI = TrackerConfig("tum_vi", 512, 512, 250, 20, 5, 5, 15, HIST_HISTOGRAM, use_mask=True, cams=_TUMVI)
 RS_D455 = TrackerConfig("rs_d455", 640, 480, 400, 30, 5, 5, 15, HIST_CLAHE, cams=_D455)
-HD_1000 = TrackerConfig("hd_1000", 1280, 720, 1000, 20, 5, 5, 10, HIST_HISTOGRAM, cams=_HD)
+# BASELINE.json configs[3]: "1280x720 stereo high-density tracking, 1000 features, 4 pyramid levels" (no reference file).  The
+# reference itself cannot express 4 (TrackKLT.h:143 hard-codes 5): HD_1000_PYR5 is that variant (5 -> effective L = 5 at 1280x720).
+HD_1000 = TrackerConfig("hd_1000", 1280, 720, 1000, 20, 5, 5, 10, HIST_HISTOGRAM, pyr_levels=4, cams=_HD)
+HD_1000_PYR5 = HD_1000.with_(name="hd_1000_pyr5", pyr_levels=5)
 UZHFPV_INDOOR = TrackerConfig("uzhfpv_indoor", 640, 480, 200, 50, 5, 5, 15, HIST_HISTOGRAM, cams=_UZH)
 
 CONFIGS = {c.name: c for c in (EUROC_MAV, TUM_VI, RS_D455, HD_1000, UZHFPV_INDOOR)}
