@@ -95,7 +95,14 @@ void uvio_klt_destroy(uvio_klt *h);
 
 /* TrackKLT::feed_new_camera (TrackKLT.cpp:34-94). Synchronous: on return the observations of this frame are available
  * through uvio_klt_get_new_observations, as the caller of the reference expects of the FeatureDatabase
- * (VioManager.cpp:281 then :369-375). */
+ * (VioManager.cpp:281 then :369-375).
+ * Two documented differences from the reference, both inside cv::findFundamentalMat (TrackKLT.cpp:873):
+ *  - every correspondence of a camera identical (the same frame delivered twice, two blank frames): OpenCV asserts
+ *    (matrix.cpp:764) and the reference, which does not catch it, terminates; this tracker keeps the tracked points (the
+ *    zero-motion model fits all of them) and returns UVIO_OK;
+ *  - a camera holding 10..13 points: OpenCV silently switches to LMedS, whose winner is decided by rounding noise (cv2's own
+ *    mask changes under a one-ulp change of one input in 60-80 % of such cases); the mask returned here is a valid LMedS
+ *    outcome (tests/test_lmeds.py) but not necessarily the one a given OpenCV build draws.  DESIGN.md section 5. */
 int uvio_klt_feed(uvio_klt *h, const UvioFrame *frame);
 /* The same for n independent trackers living on one device, with the GPU work of all of them batched (one launch set
  * per stage for the whole batch).  The reference's equivalent is n TrackKLT instances fed from n threads. */

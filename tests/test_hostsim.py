@@ -136,6 +136,6 @@ def test_kernel_bodies_against_stage_goldens(bodies):
     assert np.array_equal(mask, g["ransac_mask"])
 
 
-@pytest.mark.parametrize("name,n", [("euroc_mav", 8), ("tum_vi", 6), ("rs_d455", 4), ("euroc_mono", 6)])
+@pytest.mark.parametrize("name,n", [("euroc_mav", 8), ("tum_vi", 6), ("rs_d455", 4), ("euroc_mono", 6), ("hd_1000", 3)])
 def test_host_logic_against_golden_sequences(sim_tracker, name, n):
     assert check_tracker_against_golden(name, sim_tracker, n=n) > 300
