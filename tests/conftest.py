@@ -41,6 +41,13 @@ SIM = os.path.join(HERE, "hostsim")
 SIM_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno-unknown-pragmas"]
 
 
+def SIM_SOURCES():
+    """engine + C ABIs over the CPU stand-ins of every launch wrapper (tests/hostsim)"""
+    csrc = os.path.join(ROOT, "uvio_b200", "csrc")
+    return ([os.path.join(csrc, f) for f in ("engine.cpp", "abi.cpp", "featdb.cpp")] +
+            [os.path.join(SIM, f) for f in ("launch_sim.cpp", "featdb_sim.cpp")])
+
+
 def sim_build(out, srcs, extra=()):
     import subprocess
     os.makedirs(os.path.dirname(out), exist_ok=True)
@@ -57,7 +64,7 @@ def sim_tracker(monkeypatch):
     from uvio_b200 import track
     csrc = os.path.join(ROOT, "uvio_b200", "csrc")
     lib = sim_build(os.path.join(SIM, "_sim", "libuvio_klt_sim.so"),
-                    [os.path.join(csrc, "engine.cpp"), os.path.join(csrc, "abi.cpp"), os.path.join(SIM, "launch_sim.cpp")], ["-I", SIM])
+                    SIM_SOURCES(), ["-I", SIM])
     monkeypatch.setattr(track, "LIB_PATH", lib)
     monkeypatch.setattr(track, "_lib", None)
     yield lambda cfg, **kw: track.make_tracker(cfg, **kw)

@@ -20,10 +20,10 @@ def _build(built_lib, tmp_path):
 
 def _sim_lib():
     """engine.cpp + abi.cpp over the CPU stand-ins of the launch wrappers (tests/hostsim): the same C ABI without a GPU."""
-    from conftest import SIM, sim_build
+    from conftest import SIM, SIM_SOURCES, sim_build
     csrc = os.path.join(ROOT, "uvio_b200", "csrc")
     return sim_build(os.path.join(SIM, "_sim", "libuvio_klt_sim.so"),
-                     [os.path.join(csrc, "engine.cpp"), os.path.join(csrc, "abi.cpp"), os.path.join(SIM, "launch_sim.cpp")], ["-I", SIM])
+                     SIM_SOURCES(), ["-I", SIM])
 
 
 def test_cpp_shim_nonvirtual_members_host_simulation(tmp_path):

@@ -13,8 +13,7 @@ from uvio_b200 import track  # noqa: E402
 
 csrc = os.path.join(ROOT, "uvio_b200", "csrc")
 track.LIB_PATH = conftest.sim_build(os.path.join(conftest.SIM, "_sim", "libuvio_klt_sim.so"),
-                                    [os.path.join(csrc, "engine.cpp"), os.path.join(csrc, "abi.cpp"), os.path.join(conftest.SIM, "launch_sim.cpp")],
-                                    ["-I", conftest.SIM])
+                                    conftest.SIM_SOURCES(), ["-I", conftest.SIM])
 mod = importlib.import_module(os.path.basename(sys.argv[1])[:-3])
 fn = getattr(mod, sys.argv[2])
 args = [int(a) if a.lstrip("-").isdigit() else a for a in sys.argv[3:]]

@@ -1,0 +1,301 @@
+// C ABI of the device-side feature-track store (include/uvio_featdb.h) over the kernels of featdb_kernels.cu.
+// Host side = memory management and argument marshalling only; every decision about features and measurements is taken by
+// the kernels (featdb_body.h).  Calls are synchronous: when one returns, its effect is in HBM and its counts are on the host.
+#include "../../include/uvio_featdb.h"
+
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <new>
+#include <set>
+#include <utility>
+#include <vector>
+
+#include "featdb.h"
+
+using namespace uvio;
+
+struct uvio_featdb {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::mutex mtx;
+  FdbStore S;                    // host copy of the descriptor (device pointers)
+  FdbStore *S_dev = nullptr;
+  void *slab = nullptr;
+  int *cnt_h = nullptr;          // mapped: the kernels' copy of cnt[16] (cnt[8..10] = the last query's counts)
+  FdbObsIn *in_h = nullptr, *in_d = nullptr;   // staging of one update batch
+  unsigned long long *keys_h = nullptr, *keys_d = nullptr;
+  void *args_h = nullptr, *args_d = nullptr;   // mapped: one argument struct
+  int cap_in = 0;
+  std::vector<UvioObs> scratch;
+};
+
+namespace {
+
+template <class T>
+T *carve(char *&p, size_t n) {
+  T *r = (T *)p;
+  p += (n * sizeof(T) + 255) / 256 * 256;
+  return r;
+}
+template <class T>
+size_t need(size_t n) { return (n * sizeof(T) + 255) / 256 * 256; }
+
+int pow2_at_least(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+#define FDB_TRY(expr)                            \
+  do {                                           \
+    if ((expr) != cudaSuccess) return UVIO_E_CUDA; \
+  } while (0)
+
+int sync_status(uvio_featdb *db) {
+  if (cudaStreamSynchronize(db->stream) != cudaSuccess) return UVIO_E_CUDA;
+  return db->cnt_h[3] == 0 ? UVIO_OK : UVIO_E_SIZE;
+}
+
+int run_update(uvio_featdb *db, double timestamp, const UvioObs *obs, int n) {
+  if (n <= 0) return UVIO_OK;
+  if (n > db->cap_in) return UVIO_E_SIZE;
+  for (int i = 0; i < n; i++) db->in_h[i] = FdbObsIn{(unsigned long long)obs[i].id, (unsigned long long)obs[i].cam_id, obs[i].u, obs[i].v, obs[i].un, obs[i].vn};
+  FDB_TRY(cudaMemcpyAsync(db->in_d, db->in_h, sizeof(FdbObsIn) * (size_t)n, cudaMemcpyHostToDevice, db->stream));
+  FdbUpdateArgs *a = (FdbUpdateArgs *)db->args_h;
+  *a = FdbUpdateArgs{db->in_d, n, timestamp};
+  FDB_TRY(launch_fdb_update(db->stream, db->S_dev, (const FdbUpdateArgs *)db->args_d, 1));
+  return sync_status(db);
+}
+
+}  // namespace
+
+extern "C" {
+
+int uvio_featdb_create(int cuda_device, int max_observations, int max_features, uvio_featdb **out) {
+  if (!out || max_observations < 16 || max_features < 16 || max_observations > (1 << 26) || max_features > (1 << 24)) return UVIO_E_ARG;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || cuda_device < 0 || cuda_device >= count) return UVIO_E_CUDA;   // no CPU fallback
+  if (cudaSetDevice(cuda_device) != cudaSuccess) return UVIO_E_CUDA;
+  uvio_featdb *db = new (std::nothrow) uvio_featdb;
+  if (!db) return UVIO_E_ARG;
+  db->device = cuda_device;
+  FdbStore &S = db->S;
+  memset(&S, 0, sizeof(S));
+  S.cap_obs = max_observations;
+  S.cap_feat = max_features;
+  S.cap_hash = pow2_at_least(2 * max_features);
+  S.cap_batch = std::max(64, max_observations / 8);
+  const size_t nq = (size_t)S.cap_feat * FDB_MAXCAM + 2;
+  const size_t nc = std::max(std::max((size_t)S.cap_obs, nq), (size_t)S.cap_batch) + 2;
+  size_t bytes = need<unsigned long long>(S.cap_obs) + need<double>(S.cap_obs) + need<FdbMeas>(S.cap_obs) + 2 * need<int>(S.cap_obs) +
+                 need<int>(S.cap_batch + 2) + 2 * need<unsigned long long>(S.cap_feat) + 2 * need<uint8_t>(S.cap_feat) +
+                 need<unsigned long long>(S.cap_hash) + need<int>(S.cap_hash) + 4 * need<int>(nc) + 2 * need<uint8_t>(S.cap_feat) +
+                 need<int>(S.cap_feat + 2) + need<int>(2048) + 2 * need<int>(nc) + need<unsigned long long>(nc) + need<double>(nc) +
+                 need<FdbMeas>(nc) + 2 * need<int>(nc) + 2 * need<unsigned long long>(S.cap_feat) + need<uint8_t>(S.cap_feat) +
+                 need<int>(S.cap_feat + 2) + 2 * need<int>(nq) + need<double>(S.cap_obs) + 2 * need<float>(2 * (size_t)S.cap_obs) + 4096;
+  auto fail = [&](int code) {
+    uvio_featdb_destroy(db);
+    return code;
+  };
+  if (cudaMalloc(&db->slab, bytes) != cudaSuccess) return fail(UVIO_E_CUDA);
+  if (cudaMemset(db->slab, 0, bytes) != cudaSuccess) return fail(UVIO_E_CUDA);
+  char *p = (char *)db->slab;
+  S.o_key = carve<unsigned long long>(p, S.cap_obs);
+  S.o_t = carve<double>(p, S.cap_obs);
+  S.o_m = carve<FdbMeas>(p, S.cap_obs);
+  S.o_cam = carve<int>(p, S.cap_obs);
+  S.o_feat = carve<int>(p, S.cap_obs);
+  S.batch_start = carve<int>(p, S.cap_batch + 2);
+  S.f_key = carve<unsigned long long>(p, S.cap_feat);
+  S.f_featid = carve<unsigned long long>(p, S.cap_feat);
+  S.f_del = carve<uint8_t>(p, S.cap_feat);
+  S.f_alive = carve<uint8_t>(p, S.cap_feat);
+  S.h_key = carve<unsigned long long>(p, S.cap_hash);
+  S.h_val = carve<int>(p, S.cap_hash);
+  S.q_cnt = carve<int>(p, nc);
+  S.q_first = carve<int>(p, nc);
+  S.q_last = carve<int>(p, nc);
+  S.q_cursor = carve<int>(p, nc);
+  S.q_hit = carve<uint8_t>(p, S.cap_feat);
+  S.q_sel = carve<uint8_t>(p, S.cap_feat);
+  S.q_featpos = carve<int>(p, S.cap_feat + 2);
+  S.q_part = carve<int>(p, 2048);
+  S.c_keep = carve<int>(p, nc);
+  S.c_pos = carve<int>(p, nc);
+  S.c_u64 = carve<unsigned long long>(p, nc);
+  S.c_f64 = carve<double>(p, nc);
+  S.c_m = carve<FdbMeas>(p, nc);
+  S.c_i32a = carve<int>(p, nc);
+  S.c_i32b = carve<int>(p, nc);
+  S.r_featid = carve<unsigned long long>(p, S.cap_feat);
+  S.r_key = carve<unsigned long long>(p, S.cap_feat);
+  S.r_del = carve<uint8_t>(p, S.cap_feat);
+  S.r_row0 = carve<int>(p, S.cap_feat + 2);
+  S.r_row_cam = carve<int>(p, nq);
+  S.r_off = carve<int>(p, nq);
+  S.r_t = carve<double>(p, S.cap_obs);
+  S.r_uv = carve<float>(p, 2 * (size_t)S.cap_obs);
+  S.r_uvn = carve<float>(p, 2 * (size_t)S.cap_obs);
+  S.cnt = carve<int>(p, 16);
+  S.r_cnt = S.cnt + 8;
+  int *cnt_d = nullptr;
+  if (cudaHostAlloc((void **)&db->cnt_h, 16 * sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer((void **)&cnt_d, db->cnt_h, 0) != cudaSuccess)
+    return fail(UVIO_E_CUDA);
+  S.cnt_pub = cnt_d;
+  if ((size_t)(p - (char *)db->slab) > bytes) return fail(UVIO_E_ARG);
+  db->cap_in = S.cap_obs;
+  if (cudaHostAlloc((void **)&db->in_h, sizeof(FdbObsIn) * (size_t)db->cap_in, cudaHostAllocDefault) != cudaSuccess ||
+      cudaMalloc((void **)&db->in_d, sizeof(FdbObsIn) * (size_t)db->cap_in) != cudaSuccess ||
+      cudaHostAlloc((void **)&db->keys_h, sizeof(unsigned long long) * (size_t)S.cap_feat, cudaHostAllocDefault) != cudaSuccess ||
+      cudaMalloc((void **)&db->keys_d, sizeof(unsigned long long) * (size_t)S.cap_feat) != cudaSuccess ||
+      cudaHostAlloc(&db->args_h, 256, cudaHostAllocMapped) != cudaSuccess || cudaHostGetDevicePointer(&db->args_d, db->args_h, 0) != cudaSuccess ||
+      cudaMalloc((void **)&db->S_dev, sizeof(FdbStore)) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaMemcpy(db->S_dev, &S, sizeof(FdbStore), cudaMemcpyHostToDevice) != cudaSuccess ||
+      launch_fdb_init(db->stream, db->S_dev, 1) != cudaSuccess || cudaStreamSynchronize(db->stream) != cudaSuccess)
+    return fail(UVIO_E_CUDA);
+  *out = db;
+  return UVIO_OK;
+}
+
+void uvio_featdb_destroy(uvio_featdb *db) {
+  if (!db) return;
+  cudaSetDevice(db->device);
+  if (db->stream) {
+    cudaStreamSynchronize(db->stream);
+    cudaStreamDestroy(db->stream);
+  }
+  if (db->slab) cudaFree(db->slab);
+  if (db->cnt_h) cudaFreeHost(db->cnt_h);
+  if (db->in_h) cudaFreeHost(db->in_h);
+  if (db->in_d) cudaFree(db->in_d);
+  if (db->keys_h) cudaFreeHost(db->keys_h);
+  if (db->keys_d) cudaFree(db->keys_d);
+  if (db->args_h) cudaFreeHost(db->args_h);
+  if (db->S_dev) cudaFree(db->S_dev);
+  delete db;
+}
+
+int uvio_featdb_update(uvio_featdb *db, double timestamp, const UvioObs *obs, int n) {
+  if (!db || n < 0 || (n > 0 && !obs)) return UVIO_E_ARG;
+  std::lock_guard<std::mutex> lk(db->mtx);
+  if (cudaSetDevice(db->device) != cudaSuccess) return UVIO_E_CUDA;
+  for (int i = 0; i < n; i++)
+    if (obs[i].cam_id >= (size_t)FDB_MAXCAM || (unsigned long long)obs[i].id == FDB_EMPTY) return UVIO_E_ARG;
+  // a batch may hold one observation per (id, camera): a list that repeats one (never the tracker's) is cut there
+  std::set<std::pair<unsigned long long, unsigned long long>> seen;
+  int b = 0;
+  for (int i = 0; i < n; i++) {
+    const std::pair<unsigned long long, unsigned long long> k((unsigned long long)obs[i].id, (unsigned long long)obs[i].cam_id);
+    if (!seen.insert(k).second) {
+      int rc = run_update(db, timestamp, obs + b, i - b);
+      if (rc != UVIO_OK) return rc;
+      b = i;
+      seen.clear();
+      seen.insert(k);
+    }
+  }
+  return run_update(db, timestamp, obs + b, n - b);
+}
+
+int uvio_featdb_update_from_tracker(uvio_featdb *db, uvio_klt *tracker, double timestamp) {
+  if (!db || !tracker) return UVIO_E_ARG;
+  int n = 0;
+  int rc = uvio_klt_get_new_observations(tracker, nullptr, 0, &n);
+  if (rc != UVIO_OK) return rc;
+  std::vector<UvioObs> tmp((size_t)std::max(n, 1));
+  rc = uvio_klt_get_new_observations(tracker, tmp.data(), n, &n);
+  if (rc != UVIO_OK) return rc;
+  return uvio_featdb_update(db, timestamp, tmp.data(), n);
+}
+
+int uvio_featdb_query(uvio_featdb *db, int kind, double timestamp, size_t key, int remove, int skip_deleted, int *n_features, int *n_rows,
+                      int *n_observations) {
+  if (!db || kind < 0 || kind > 4) return UVIO_E_ARG;
+  std::lock_guard<std::mutex> lk(db->mtx);
+  if (cudaSetDevice(db->device) != cudaSuccess) return UVIO_E_CUDA;
+  FdbQueryArgs *a = (FdbQueryArgs *)db->args_h;
+  *a = FdbQueryArgs{kind, timestamp, (unsigned long long)key, remove, skip_deleted};
+  FDB_TRY(launch_fdb_query(db->stream, db->S_dev, (const FdbQueryArgs *)db->args_d, 1));
+  int rc = sync_status(db);
+  if (n_features) *n_features = db->cnt_h[8];
+  if (n_rows) *n_rows = db->cnt_h[9];
+  if (n_observations) *n_observations = db->cnt_h[10];
+  return rc;
+}
+
+int uvio_featdb_fetch(uvio_featdb *db, size_t *featid, size_t *key, uint8_t *to_delete, int *row0, int *row_cam, int *off, double *t, float *uv,
+                      float *uvn) {
+  if (!db) return UVIO_E_ARG;
+  std::lock_guard<std::mutex> lk(db->mtx);
+  if (cudaSetDevice(db->device) != cudaSuccess) return UVIO_E_CUDA;
+  const size_t nf = (size_t)db->cnt_h[8], nr = (size_t)db->cnt_h[9], no = (size_t)db->cnt_h[10];
+  const FdbStore &S = db->S;
+  static_assert(sizeof(size_t) == sizeof(unsigned long long), "size_t is 64 bits on every host this ABI targets");
+  if (featid && nf) FDB_TRY(cudaMemcpyAsync(featid, S.r_featid, nf * 8, cudaMemcpyDeviceToHost, db->stream));
+  if (key && nf) FDB_TRY(cudaMemcpyAsync(key, S.r_key, nf * 8, cudaMemcpyDeviceToHost, db->stream));
+  if (to_delete && nf) FDB_TRY(cudaMemcpyAsync(to_delete, S.r_del, nf, cudaMemcpyDeviceToHost, db->stream));
+  if (row0) FDB_TRY(cudaMemcpyAsync(row0, S.r_row0, (nf + 1) * 4, cudaMemcpyDeviceToHost, db->stream));
+  if (row_cam && nr) FDB_TRY(cudaMemcpyAsync(row_cam, S.r_row_cam, nr * 4, cudaMemcpyDeviceToHost, db->stream));
+  if (off) FDB_TRY(cudaMemcpyAsync(off, S.r_off, (nr + 1) * 4, cudaMemcpyDeviceToHost, db->stream));
+  if (t && no) FDB_TRY(cudaMemcpyAsync(t, S.r_t, no * 8, cudaMemcpyDeviceToHost, db->stream));
+  if (uv && no) FDB_TRY(cudaMemcpyAsync(uv, S.r_uv, no * 8, cudaMemcpyDeviceToHost, db->stream));
+  if (uvn && no) FDB_TRY(cudaMemcpyAsync(uvn, S.r_uvn, no * 8, cudaMemcpyDeviceToHost, db->stream));
+  FDB_TRY(cudaStreamSynchronize(db->stream));
+  return UVIO_OK;
+}
+
+int uvio_featdb_result_device(uvio_featdb *db, const void *ptrs[9]) {
+  if (!db || !ptrs) return UVIO_E_ARG;
+  const FdbStore &S = db->S;
+  const void *p[9] = {S.r_featid, S.r_key, S.r_del, S.r_row0, S.r_row_cam, S.r_off, S.r_t, S.r_uv, S.r_uvn};
+  memcpy(ptrs, p, sizeof(p));
+  return UVIO_OK;
+}
+
+static int mark(uvio_featdb *db, const size_t *keys, int n, int what, size_t new_id) {
+  if (!db || n < 0 || (n > 0 && !keys)) return UVIO_E_ARG;
+  if (n == 0) return UVIO_OK;
+  std::lock_guard<std::mutex> lk(db->mtx);
+  if (cudaSetDevice(db->device) != cudaSuccess) return UVIO_E_CUDA;
+  for (int b = 0; b < n; b += db->S.cap_feat) {
+    const int m = std::min(db->S.cap_feat, n - b);
+    for (int i = 0; i < m; i++) db->keys_h[i] = (unsigned long long)keys[b + i];
+    FDB_TRY(cudaMemcpyAsync(db->keys_d, db->keys_h, 8 * (size_t)m, cudaMemcpyHostToDevice, db->stream));
+    FdbMarkArgs *a = (FdbMarkArgs *)db->args_h;
+    *a = FdbMarkArgs{db->keys_d, m, what, (unsigned long long)new_id};
+    FDB_TRY(launch_fdb_mark(db->stream, db->S_dev, (const FdbMarkArgs *)db->args_d, 1));
+    FDB_TRY(cudaStreamSynchronize(db->stream));
+  }
+  return UVIO_OK;
+}
+
+int uvio_featdb_mark_to_delete(uvio_featdb *db, const size_t *keys, int n) { return mark(db, keys, n, 0, 0); }
+int uvio_featdb_change_feat_id(uvio_featdb *db, size_t id_old, size_t id_new) { return mark(db, &id_old, 1, 1, id_new); }
+
+static int cleanup(uvio_featdb *db, int mode, double timestamp) {
+  if (!db) return UVIO_E_ARG;
+  std::lock_guard<std::mutex> lk(db->mtx);
+  if (cudaSetDevice(db->device) != cudaSuccess) return UVIO_E_CUDA;
+  FdbCleanupArgs *a = (FdbCleanupArgs *)db->args_h;
+  *a = FdbCleanupArgs{mode, timestamp};
+  FDB_TRY(launch_fdb_cleanup(db->stream, db->S_dev, (const FdbCleanupArgs *)db->args_d, 1));
+  return sync_status(db);
+}
+int uvio_featdb_cleanup(uvio_featdb *db) { return cleanup(db, 0, 0.0); }
+int uvio_featdb_cleanup_measurements(uvio_featdb *db, double timestamp) { return cleanup(db, 1, timestamp); }
+int uvio_featdb_cleanup_measurements_exact(uvio_featdb *db, double timestamp) { return cleanup(db, 2, timestamp); }
+
+int uvio_featdb_size(uvio_featdb *db, int *n_features, int *n_observations) {
+  if (!db) return UVIO_E_ARG;
+  std::lock_guard<std::mutex> lk(db->mtx);
+  if (n_features) *n_features = db->cnt_h[4];
+  if (n_observations) *n_observations = db->cnt_h[0];
+  return UVIO_OK;
+}
+
+}  // extern "C"
