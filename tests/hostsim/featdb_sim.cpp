@@ -32,3 +32,11 @@ cudaError_t launch_fdb_mark(cudaStream_t, const FdbStore *stores, const FdbMarkA
 }
 
 }  // namespace uvio
+
+#include "../../uvio_b200/csrc/tri.h"
+namespace uvio {
+cudaError_t launch_triangulate(cudaStream_t, TriFeatures F, const TriClone *clones, int n_clones, TriOptions opt, TriResult *out) {
+  for (int f = 0; f < F.n_features; f++) tri_feature(F, f, clones, n_clones, opt, out[f]);
+  return 0;
+}
+}  // namespace uvio

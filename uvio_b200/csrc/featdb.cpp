@@ -299,3 +299,93 @@ int uvio_featdb_size(uvio_featdb *db, int *n_features, int *n_observations) {
 }
 
 }  // extern "C"
+
+// ---- batched triangulation (include/uvio_tri.h) --------------------------------------------------------------------------
+#include "../../include/uvio_tri.h"
+#include "tri.h"
+
+static_assert(sizeof(UvioClonePose) == sizeof(TriClone) && sizeof(UvioTriOptions) == sizeof(TriOptions) && sizeof(UvioTriResult) == sizeof(TriResult),
+              "the ABI structs and the kernel's structs are the same bytes");
+
+namespace {
+struct TriScratch {           // per call: clone table + results in device memory
+  TriClone *clones = nullptr;
+  TriResult *out = nullptr;
+  ~TriScratch() {
+    if (clones) cudaFree(clones);
+    if (out) cudaFree(out);
+  }
+};
+int run_triangulate(cudaStream_t st, TriFeatures F, const UvioClonePose *clones, int n_clones, const UvioTriOptions *opt, UvioTriResult *out) {
+  if (F.n_features == 0) return UVIO_OK;
+  TriScratch s;
+  FDB_TRY(cudaMalloc((void **)&s.clones, sizeof(TriClone) * (size_t)std::max(n_clones, 1)));
+  FDB_TRY(cudaMalloc((void **)&s.out, sizeof(TriResult) * (size_t)F.n_features));
+  if (n_clones) FDB_TRY(cudaMemcpyAsync(s.clones, clones, sizeof(TriClone) * (size_t)n_clones, cudaMemcpyHostToDevice, st));
+  TriOptions o;
+  memcpy(&o, opt, sizeof(o));
+  FDB_TRY(launch_triangulate(st, F, s.clones, n_clones, o, s.out));
+  FDB_TRY(cudaMemcpyAsync(out, s.out, sizeof(TriResult) * (size_t)F.n_features, cudaMemcpyDeviceToHost, st));
+  FDB_TRY(cudaStreamSynchronize(st));
+  for (int f = 0; f < F.n_features; f++)
+    if (out[f].ok_triangulation < 0 || out[f].ok_refine < 0) return UVIO_E_ARG;   // a measurement without a clone pose (.at() throws in the reference)
+  return UVIO_OK;
+}
+}  // namespace
+
+extern "C" {
+
+void uvio_tri_default_options(UvioTriOptions *o) {   // FeatureInitializerOptions.h:35-69
+  if (!o) return;
+  o->triangulate_1d = 0;
+  o->refine_features = 1;
+  o->max_runs = 5;
+  o->init_lamda = 1e-3;
+  o->max_lamda = 1e10;
+  o->min_dx = 1e-6;
+  o->min_dcost = 1e-6;
+  o->lam_mult = 10;
+  o->min_dist = 0.10;
+  o->max_dist = 60;
+  o->max_baseline = 40;
+  o->max_cond_number = 10000;
+}
+
+int uvio_tri_triangulate_featdb(uvio_featdb *db, const UvioClonePose *clones, int n_clones, const UvioTriOptions *opt, UvioTriResult *out) {
+  if (!db || n_clones < 0 || (n_clones > 0 && !clones) || !opt || !out) return UVIO_E_ARG;
+  std::lock_guard<std::mutex> lk(db->mtx);
+  if (cudaSetDevice(db->device) != cudaSuccess) return UVIO_E_CUDA;
+  const FdbStore &S = db->S;
+  TriFeatures F{db->cnt_h[8], S.r_row0, S.r_row_cam, S.r_off, S.r_t, S.r_uvn};
+  return run_triangulate(db->stream, F, clones, n_clones, opt, out);
+}
+
+int uvio_tri_triangulate(int cuda_device, int n_features, const int *row0, const int *row_cam, const int *off, const double *t, const float *uvn,
+                         const UvioClonePose *clones, int n_clones, const UvioTriOptions *opt, UvioTriResult *out) {
+  if (n_features < 0 || n_clones < 0 || (n_clones > 0 && !clones) || !opt) return UVIO_E_ARG;
+  if (n_features == 0) return UVIO_OK;
+  if (!row0 || !row_cam || !off || !t || !uvn || !out) return UVIO_E_ARG;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || cuda_device < 0 || cuda_device >= count) return UVIO_E_CUDA;   // no CPU fallback
+  if (cudaSetDevice(cuda_device) != cudaSuccess) return UVIO_E_CUDA;
+  const int nr = row0[n_features], no = off[nr];
+  if (nr < 0 || no < 0) return UVIO_E_ARG;
+  char *slab = nullptr;
+  const size_t b0 = need<int>(n_features + 1), b1 = need<int>(nr + 1), b2 = need<int>(nr + 1), b3 = need<double>(no + 1), b4 = need<float>(2 * (size_t)no + 2);
+  FDB_TRY(cudaMalloc((void **)&slab, b0 + b1 + b2 + b3 + b4));
+  struct Free { char *p; ~Free() { cudaFree(p); } } guard{slab};
+  char *p = slab;
+  int *d_row0 = carve<int>(p, n_features + 1), *d_cam = carve<int>(p, nr + 1), *d_off = carve<int>(p, nr + 1);
+  double *d_t = carve<double>(p, no + 1);
+  float *d_uvn = carve<float>(p, 2 * (size_t)no + 2);
+  cudaStream_t st = nullptr;   // the default stream: this entry point is a synchronous convenience
+  FDB_TRY(cudaMemcpyAsync(d_row0, row0, 4 * (size_t)(n_features + 1), cudaMemcpyHostToDevice, st));
+  if (nr) FDB_TRY(cudaMemcpyAsync(d_cam, row_cam, 4 * (size_t)nr, cudaMemcpyHostToDevice, st));
+  FDB_TRY(cudaMemcpyAsync(d_off, off, 4 * (size_t)(nr + 1), cudaMemcpyHostToDevice, st));
+  if (no) FDB_TRY(cudaMemcpyAsync(d_t, t, 8 * (size_t)no, cudaMemcpyHostToDevice, st));
+  if (no) FDB_TRY(cudaMemcpyAsync(d_uvn, uvn, 8 * (size_t)no, cudaMemcpyHostToDevice, st));
+  TriFeatures F{n_features, d_row0, d_cam, d_off, d_t, d_uvn};
+  return run_triangulate(st, F, clones, n_clones, opt, out);
+}
+
+}  // extern "C"
