@@ -13,6 +13,7 @@
 #include "../../uvio_b200/csrc/lk_body.h"
 #include "../../uvio_b200/csrc/ransac_body.h"
 #include "../../uvio_b200/csrc/subpix_body.h"
+#include "../../uvio_b200/csrc/track_body.h"
 
 using namespace uvio;
 
@@ -140,5 +141,20 @@ int hs_cell_top_k(const uint32_t *words, int count, int cw, int ch, int K, float
     out[3 * i + 2] = top[i].response;
   }
   return (int)top.size();
+}
+
+// the device-side pipeline's version of the same step (track_body.h): bitonic order by position, then the first K positions
+// of libstdc++'s std::sort by response.  heap != 0 forces the heap-sort fallback of introsort over the whole range.
+int hs_dv_top_k(const uint32_t *words, int count, int K, int heap, uint32_t *out) {
+  int m = 1;
+  while (m < count) m <<= 1;
+  std::vector<uint32_t> buf((size_t)m, 0xFFFFFFFFu);
+  memcpy(buf.data(), words, sizeof(uint32_t) * (size_t)count);
+  dv_bitonic_by_position(GroupSeq(), buf.data(), m);
+  if (heap) dv_heap_sort(buf.data(), buf.data() + count);
+  else dv_sort_prefix(buf.data(), count, K);
+  const int kn = count < K ? count : K;
+  memcpy(out, buf.data(), sizeof(uint32_t) * (size_t)kn);
+  return kn;
 }
 }  // extern "C"

@@ -1,10 +1,14 @@
 // TEST SCAFFOLDING ONLY — see tests/hostsim/cuda_runtime.h. CPU stand-ins for the launch_* wrappers of kernels.cu: the
 // same *_body.h code, one lane (GroupSeq), looping over what would be thread blocks / warps.
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <vector>
 
 #include "../../uvio_b200/csrc/kernels.h"
 #include "../../uvio_b200/csrc/lk_body.h"
 #include "../../uvio_b200/csrc/subpix_body.h"
+#include "../../uvio_b200/csrc/track_body.h"
 
 namespace uvio {
 
@@ -83,6 +87,7 @@ cudaError_t launch_subpix(cudaStream_t, const SubpixItem *items, int n, const Py
   GroupSeq g;
   SubpixSmem s;
   for (int i = 0; i < n; i++) {
+    if (items[i].pyr < 0) continue;   // an unused slot of the device-side pipeline
     float x = items[i].x, y = items[i].y;
     subpix_point(g, s, pyr_tab[items[i].pyr].lv[0], mask, 20, 0.001 * 0.001, x, y);
     out_xy[2 * i] = x;
@@ -98,6 +103,7 @@ cudaError_t launch_lk(cudaStream_t, const LkItem *items, int n, const PyrDesc *p
   LkSmem s;
   for (int i = 0; i < n; i++) {
     const LkItem it = items[i];
+    if (it.prev_pyr < 0) continue;    // an unused slot of the device-side pipeline
     float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
     if (init_from_dev) { px = nx = init_from_dev[2 * i]; py = ny = init_from_dev[2 * i + 1]; }
     const PyrDesc &P0 = pyr_tab[it.prev_pyr], &P1 = pyr_tab[it.next_pyr];
@@ -134,6 +140,47 @@ cudaError_t launch_ransac(cudaStream_t, const RansacJob *jobs, int njobs, int ma
     }
     for (int i = 0; i < job.n; i++) mask_host[job.off + i] = run ? (uint8_t)(status[job.off + i] && mask_dev[job.off + i]) : 0;
   }
+  return 0;
+}
+
+// ---- device-side bookkeeping (track_body.h) with one lane ----------------------------------------------------------------------
+cudaError_t launch_dv_occupancy(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  if (getenv("UVIO_DV_TRACE")) fprintf(stderr, "[sim] device-side pipeline: %d trackers\n", n_heads);
+  for (int h = 0; h < n_heads; h++)
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_occupancy(GroupSeq(), units[u], X);
+  return 0;
+}
+cudaError_t launch_dv_fast(cudaStream_t, const DvGlobals &X, const PyrDesc *pyr_tab, int n_slots, int, int) {
+  GroupSeq g;
+  FastSmem s;
+  for (int slot = 0; slot < n_slots; slot++) {
+    const FastJob job = X.fast_jobs[slot];
+    if (job.w == 0) continue;
+    for (int ty = 0; ty < job.h; ty += FT_H)
+      for (int tx = 0; tx < job.w; tx += FT_W) fast_tile(g, s, pyr_tab[job.img].lv[0], job, tx, ty, job.threshold, X.fast_out, &X.fast_cnt[slot]);
+  }
+  return 0;
+}
+cudaError_t launch_dv_topk(cudaStream_t, const DvUnit *units, int n_units, int, const DvGlobals &X) {
+  std::vector<uint32_t> buf(64);   // smaller than most cells: the in-place (global) sort path is exercised too
+  for (int u = 0; u < n_units; u++)
+    for (int side = 0; side < (units[u].stereo ? 2 : 1); side++)
+      for (int r = 0; r < units[u].C; r++) dv_topk(GroupSeq(), units[u], X, side, r, buf.data(), (int)buf.size());
+  return 0;
+}
+cudaError_t launch_dv_select(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  for (int h = 0; h < n_heads; h++)
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_select(GroupSeq(), units[u], X);
+  return 0;
+}
+cudaError_t launch_dv_assign(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  for (int h = 0; h < n_heads; h++)
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_assign(GroupSeq(), units[u], X);
+  return 0;
+}
+cudaError_t launch_dv_merge(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  for (int h = 0; h < n_heads; h++)
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_merge(GroupSeq(), units[u], X);
   return 0;
 }
 

@@ -61,6 +61,45 @@ def test_cell_top_k_matches_real_std_sort(bodies):
         np.testing.assert_array_equal(out[:got], exp, err_msg=f"trial {trial}: n={n} K={K} cell {cw}x{ch}")
 
 
+def test_device_top_k_matches_real_std_sort(bodies):
+    """The device-side pipeline's per-cell top-K (track_body.h: bitonic order by position + dv_sort_prefix, libstdc++'s
+    introsort restated without the standard library, heap-sort fallback included) against the real std::sort."""
+    from oracle.trackklt_cv2 import std_sort_perm
+    import subprocess, os, ctypes
+    rng = np.random.default_rng(9)
+    L = bodies
+    # the real std::make_heap + std::sort_heap, for the fallback introsort takes when its depth limit is hit
+    src = os.path.join(SIM, "_sim", "heapsort_ref.cpp")
+    lib = os.path.join(SIM, "_sim", "libheapsort_ref.so")
+    os.makedirs(os.path.dirname(src), exist_ok=True)
+    open(src, "w").write('#include <algorithm>\n#include <cstdint>\nextern "C" void ref_heap_sort(uint32_t *a, int n) {\n'
+                         '  auto c = [](uint32_t x, uint32_t y) { return (x >> 24) > (y >> 24); };\n'
+                         '  std::make_heap(a, a + n, c); std::sort_heap(a, a + n, c); }\n')
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", lib, src])
+    R = ctypes.CDLL(lib)
+    for trial in range(400):
+        cw, ch = int(rng.integers(8, 160)), int(rng.integers(8, 110))
+        n = int(rng.integers(1, min(cw * ch, 2500 if trial % 9 == 0 else 700)))
+        K = int(rng.integers(1, 45))
+        pos = rng.choice(cw * ch, size=n, replace=False)
+        nresp = int(rng.integers(1, 40))
+        score = rng.integers(20, 20 + nresp, size=n).astype(np.uint32)
+        words = (score << 24) | ((pos // cw).astype(np.uint32) << 12) | (pos % cw).astype(np.uint32)
+        words = np.ascontiguousarray(words[rng.permutation(n)], dtype=np.uint32)
+        rm = words[np.argsort(words & 0xFFFFFF, kind="stable")]
+        want = rm[std_sort_perm((rm >> 24).astype(np.float32))][:K]
+        out = np.zeros(K, np.uint32)
+        got = L.hs_dv_top_k(_p(words), n, K, 0, _p(out))
+        assert got == min(K, n)
+        np.testing.assert_array_equal(out[:got], want, err_msg=f"trial {trial}: n={n} K={K}")
+        if trial % 4 == 0:
+            full = np.zeros(n, np.uint32)
+            L.hs_dv_top_k(_p(words), n, n, 1, _p(full))
+            ref = rm.copy()
+            R.ref_heap_sort(_p(ref), n)
+            np.testing.assert_array_equal(full, ref, err_msg=f"trial {trial}: heap-sort fallback n={n}")
+
+
 def test_ransac_root_order_on_tie_cases(bodies):
     """Two models of one 7-point sample with the same best inlier count: the winner is the one cv::run7Point lists first
     (tests/golden/ransac_ties.npz, masks from cv2; see tests/golden/make_ransac_ties.py)."""

@@ -213,6 +213,7 @@ int uvio_klt_change_feat_id(uvio_klt *h, size_t id_old, size_t id_new) {
   for (auto &c : h->rig->cams)                       // TrackBase.cpp:241-247
     for (auto &id : c.ids_last)
       if (id == id_old) id = id_new;
+  h->rig->dv_dirty = true;   // the device-side pipeline re-uploads ids_last before the next feed
   h->rig->epoch++;
   return UVIO_OK;
 }

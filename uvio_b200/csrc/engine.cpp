@@ -23,6 +23,7 @@
 #include "hostlogic.h"
 #include "lk_body.h"
 #include "subpix_body.h"
+#include "track_body.h"
 
 namespace uvio {
 
@@ -294,6 +295,20 @@ struct Lane {
   MappedVec<float> p1n;
   MappedVec<uint8_t> rs_mask;
   DevVec<uint8_t> rs_mask_dev;
+
+  // device-side pipeline (Pass::device_feed): unit descriptors and the batch-wide job / result arrays, all in HBM
+  JobVec<DvUnit> dv_units;
+  JobVec<DvHead> dv_heads;
+  DevVec<FastJob> dv_fast_jobs;
+  DevVec<uint32_t> dv_fast_out;
+  DevVec<unsigned> dv_fast_cnt;
+  DevVec<SubpixItem> dv_sp_items;
+  DevVec<float> dv_sp_out;
+  DevVec<LkItem> dv_lk1_items, dv_lk2_items;
+  DevVec<LkOut> dv_lk1_out, dv_lk2_out;
+  DevVec<uint8_t> dv_lk1_status, dv_lk2_status, dv_rs_mask, dv_rs_mask_raw;
+  DevVec<RansacJob> dv_rs_jobs;
+  DevVec<float> dv_p0n, dv_p1n;
 
   int sync() {
     cudaError_t e = cudaStreamSynchronize(stream);
@@ -797,6 +812,9 @@ void Context::release_camera(CamState &c) {
   raw_free.push_back(RawSlot{c.raw_bytes, {c.raw_ptr[0], c.raw_ptr[1]}});
 }
 
+struct DvRig;
+static void dv_destroy(DvRig *d);   // defined with DvRig below
+
 Rig::~Rig() {
   if (!g_contexts_gone.load()) {
     std::lock_guard<std::mutex> lk(ctx->mtx);
@@ -811,6 +829,7 @@ Rig::~Rig() {
     }
   }
   for (Unit *u : unit_pool) delete u;
+  if (dv && !g_contexts_gone.load()) dv_destroy(dv);
 }
 Unit *Rig::unit_at(size_t i) {
   while (unit_pool.size() <= i) unit_pool.push_back(new Unit);
@@ -1156,6 +1175,158 @@ static void phase_d(Lane *ctx, Unit &u) {
   store_last(R, good_r, ids_r);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Device-side pipeline: per-tracker memory.  One device slab (state + work areas) and one mapped host slab (the state's
+// mirror and the observation list) per tracker, laid out for the tracker's feature budget and image sizes.
+// ---------------------------------------------------------------------------------------------------------------------
+struct DvCamMem {
+  float *pts_last = nullptr; unsigned long long *ids_last = nullptr; int *n_last = nullptr;        // device
+  float *pts = nullptr; unsigned long long *ids = nullptr;
+  uint8_t *close = nullptr; int *first = nullptr, *grid = nullptr, *cells = nullptr, *top_n = nullptr, *ctl = nullptr;
+  uint32_t *top = nullptr;
+  float *h_pts_last = nullptr; unsigned long long *h_ids_last = nullptr; int *h_n_last = nullptr;  // mapped: host pointers
+  float *m_pts_last = nullptr; unsigned long long *m_ids_last = nullptr; int *m_n_last = nullptr;  // ... and their device aliases
+  uint8_t *mask[PYR_SLOTS] = {nullptr, nullptr, nullptr};                                          // device copies of non-zero masks
+};
+struct DvUnitMem {
+  int *scr[4] = {nullptr, nullptr, nullptr, nullptr}, *part = nullptr, *uctl = nullptr;
+  float *tmp_pts = nullptr; unsigned long long *tmp_ids = nullptr;
+  DvObs *h_obs = nullptr, *m_obs = nullptr; int *h_n_obs = nullptr, *m_n_obs = nullptr;
+};
+struct DvRig {
+  int nf = 0, P = 0, C = 0, K = 0, size_x = 0, size_y = 0, cell_cap = 0, obs_cap = 0;
+  std::vector<int> cam_w, cam_h;
+  void *slab = nullptr, *host_slab = nullptr;
+  unsigned long long *currid = nullptr, *h_currid = nullptr, *m_currid = nullptr;   // device; mapped host pointer; its device alias
+  std::vector<DvCamMem> cam;
+  std::vector<DvUnitMem> unit;
+  ~DvRig() {
+    if (slab) cudaFree(slab);
+    if (host_slab) cudaFreeHost(host_slab);
+  }
+};
+
+static void dv_destroy(DvRig *d) { delete d; }
+
+static bool device_pipeline_enabled() {   // UVIO_KLT_PIPELINE=host selects the round-1 path (bookkeeping on host threads)
+  static const bool v = [] {
+    const char *e = getenv("UVIO_KLT_PIPELINE");
+    return !(e && strcmp(e, "host") == 0);
+  }();
+  return v;
+}
+
+template <class T>
+static T *dv_carve(char *&p, size_t n) {
+  T *r = (T *)p;
+  p += (n * sizeof(T) + 255) / 256 * 256;
+  return r;
+}
+
+// (re)builds the tracker's device memory when its feature budget or image sizes changed; uploads pts_last / ids_last / currid
+// when the host copy is newer (first use, set_num_features, change_feat_id, a feed through the host path)
+static int dv_prepare(Context *ctx, Rig &rig) {
+  const Params &P = rig.prm;
+  bool rebuild = rig.dv == nullptr || rig.dv->nf != P.num_features || rig.dv->cam_w.size() != rig.cams.size();
+  if (!rebuild)
+    for (size_t k = 0; k < rig.cams.size(); k++) rebuild |= rig.dv->cam_w[k] != rig.cams[k].w || rig.dv->cam_h[k] != rig.cams[k].h;
+  if (rebuild) {
+    CU_TRY(cudaDeviceSynchronize());   // nothing of this tracker may be in flight while its memory moves
+    delete rig.dv;
+    rig.dv = new DvRig;
+    DvRig &D = *rig.dv;
+    D.nf = P.num_features;
+    D.C = P.grid_x * P.grid_y;
+    int max_w = 1, max_h = 1;
+    for (auto &c : rig.cams) { max_w = std::max(max_w, c.w); max_h = std::max(max_h, c.h); D.cam_w.push_back(c.w); D.cam_h.push_back(c.h); }
+    const GridGeom geom = grider_geom(max_w, max_h, P.num_features, P.grid_x, P.grid_y);
+    D.K = geom.per_cell;
+    D.size_x = geom.size_x;   // (per camera at use; the largest here sizes the FAST output)
+    D.size_y = geom.size_y;
+    int cap = std::max(1, ((geom.size_x + 1) / 2) * ((geom.size_y + 1) / 2));
+    D.cell_cap = 1;
+    while (D.cell_cap < cap) D.cell_cap <<= 1;   // a power of two: a cell's top-K block may bitonic-sort in place
+    D.P = P.num_features + 2 * D.C * D.K + 64;
+    D.obs_cap = 2 * D.P;
+    const size_t ncam = rig.cams.size(), scr = (size_t)std::max(D.P, D.C * D.K) + D.C + 16;
+    D.cam.resize(ncam);
+    D.unit.resize(ncam);
+    // the same walk lays the two slabs out twice: once from address 0 to size them, once over the real allocations
+    auto layout = [&](char *p, char *hp, ptrdiff_t to_dev, size_t &dev_bytes, size_t &host_bytes) {
+      char *p0 = p, *hp0 = hp;
+      D.currid = dv_carve<unsigned long long>(p, 1);
+      D.h_currid = dv_carve<unsigned long long>(hp, 1);
+      D.m_currid = (unsigned long long *)((char *)D.h_currid + to_dev);
+      for (size_t k = 0; k < ncam; k++) {
+        DvCamMem &m = D.cam[k];
+        const CamState &c = rig.cams[k];
+        const size_t cells = (size_t)(c.w / std::max(1, P.min_px_dist) + 1) * (size_t)(c.h / std::max(1, P.min_px_dist) + 1);
+        m.pts_last = dv_carve<float>(p, 2 * (size_t)D.P);
+        m.ids_last = dv_carve<unsigned long long>(p, D.P);
+        m.n_last = dv_carve<int>(p, 1);
+        m.pts = dv_carve<float>(p, 2 * (size_t)D.P);
+        m.ids = dv_carve<unsigned long long>(p, D.P);
+        m.close = dv_carve<uint8_t>(p, cells);
+        m.first = dv_carve<int>(p, cells);
+        m.grid = dv_carve<int>(p, D.C);
+        m.cells = dv_carve<int>(p, D.C);
+        m.top = dv_carve<uint32_t>(p, (size_t)D.C * D.K);
+        m.top_n = dv_carve<int>(p, D.C);
+        m.ctl = dv_carve<int>(p, 16);
+        m.h_pts_last = dv_carve<float>(hp, 2 * (size_t)D.P);
+        m.h_ids_last = dv_carve<unsigned long long>(hp, D.P);
+        m.h_n_last = dv_carve<int>(hp, 1);
+        m.m_pts_last = (float *)((char *)m.h_pts_last + to_dev);
+        m.m_ids_last = (unsigned long long *)((char *)m.h_ids_last + to_dev);
+        m.m_n_last = (int *)((char *)m.h_n_last + to_dev);
+        for (int q = 0; q < PYR_SLOTS; q++) m.mask[q] = dv_carve<uint8_t>(p, (size_t)c.w * c.h);
+      }
+      for (size_t k = 0; k < ncam; k++) {
+        DvUnitMem &u = D.unit[k];
+        for (int q = 0; q < 4; q++) u.scr[q] = dv_carve<int>(p, scr);
+        u.part = dv_carve<int>(p, 1024);
+        u.uctl = dv_carve<int>(p, 16);
+        u.tmp_pts = dv_carve<float>(p, 2 * (size_t)D.P);
+        u.tmp_ids = dv_carve<unsigned long long>(p, D.P);
+        u.h_obs = dv_carve<DvObs>(hp, D.obs_cap);
+        u.h_n_obs = dv_carve<int>(hp, 1);
+        u.m_obs = (DvObs *)((char *)u.h_obs + to_dev);
+        u.m_n_obs = (int *)((char *)u.h_n_obs + to_dev);
+      }
+      dev_bytes = (size_t)(p - p0);
+      host_bytes = (size_t)(hp - hp0);
+    };
+    size_t dev_bytes = 0, host_bytes = 0, chk_d = 0, chk_h = 0;
+    layout(nullptr, nullptr, 0, dev_bytes, host_bytes);
+    CU_TRY(cudaMalloc(&D.slab, dev_bytes + 256));
+    CU_TRY(cudaMemset(D.slab, 0, dev_bytes + 256));
+    CU_TRY(cudaHostAlloc(&D.host_slab, host_bytes + 256, cudaHostAllocMapped));
+    memset(D.host_slab, 0, host_bytes + 256);
+    char *hd = nullptr;
+    CU_TRY(cudaHostGetDevicePointer((void **)&hd, D.host_slab, 0));
+    layout((char *)D.slab, (char *)D.host_slab, hd - (char *)D.host_slab, chk_d, chk_h);
+    rig.dv_dirty = true;
+  }
+  if (rig.dv_dirty) {
+    DvRig &D = *rig.dv;
+    CU_TRY(cudaDeviceSynchronize());
+    const unsigned long long id = (unsigned long long)rig.currid;
+    CU_TRY(cudaMemcpy(D.currid, &id, sizeof(id), cudaMemcpyHostToDevice));
+    for (size_t k = 0; k < rig.cams.size(); k++) {
+      const CamState &c = rig.cams[k];
+      const int n = (int)std::min(c.pts_last.size(), (size_t)D.P);
+      if (n) {
+        CU_TRY(cudaMemcpy(D.cam[k].pts_last, c.pts_last.data(), sizeof(Pt) * (size_t)n, cudaMemcpyHostToDevice));
+        std::vector<unsigned long long> ids(c.ids_last.begin(), c.ids_last.begin() + n);
+        CU_TRY(cudaMemcpy(D.cam[k].ids_last, ids.data(), 8 * (size_t)n, cudaMemcpyHostToDevice));
+      }
+      CU_TRY(cudaMemcpy(D.cam[k].n_last, &n, sizeof(int), cudaMemcpyHostToDevice));
+    }
+    rig.dv_dirty = false;
+  }
+  return OK;
+}
+
 static double now_us() {
   return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -1223,6 +1394,9 @@ struct Pass {
     tmark = t;
   }
   int stage0();
+  int stage0_book();
+  int stage0_issue();
+  int device_feed();     // the whole feed as one chain of launches with the bookkeeping on the device (track_body.h)
   int stage1();
   int stage2();
   int stage3();
@@ -1529,6 +1703,13 @@ void Pass::background() {
 }
 
 int Pass::stage0() {
+  int e = stage0_book();
+  if (e != OK) return e;
+  return stage0_issue();
+}
+
+// host bookkeeping of the new messages: frame slots, masks, pre-processing jobs, units (shared by the host and the device path)
+int Pass::stage0_book() {
   Context *dev = ctx->dev;
   t0 = tmark = now_us();
   ctx->prof_begin();
@@ -1643,6 +1824,12 @@ int Pass::stage0() {
     CU_TRY(upload_subpix_mask(ctx->sp_mask.d, ctx->stream));
     ctx->sp_mask_ready = true;
   }
+  return OK;
+}
+
+int Pass::stage0_issue() {
+  Context *dev = ctx->dev;
+  std::vector<PreItem> &items = ctx->pre_items;
   // ---- round 1a: FAST.  Detection runs on the previous frame's pyramid, which is already in HBM, so it is issued ahead of
   // the upload (its job list would otherwise queue behind the images on the copy engine) -- or was issued when the previous
   // feed of these trackers ended.  First frames detect on the frame that is being uploaded and wait for it.
@@ -1796,6 +1983,7 @@ int Pass::stage3() {
   t3 = now_us();
   for (auto &u : units)
     if (!u.first && !u.failed) phase_d(ctx, u);
+  for (auto &u : units) u.rig->dv_dirty = true;   // a device-side copy of this state, if any, is stale now
   const double t4 = now_us();
   issue_ahead();
   seg(6);
@@ -1808,6 +1996,203 @@ int Pass::stage3() {
     s[2] = (float)(t3 - t2);   // temporal KLT + RANSAC
     s[3] = 0.f;                // stereo KLT is part of the detection round here
     s[4] = (float)(t4 - t3);   // merge + observations
+  }
+  return OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The device-side pipeline: one feed_batch call = one chain of launches on the lane's stream, bookkeeping included
+// (track_body.h), one synchronisation at the end.  All trackers of the call go through one lane.
+//   up_stream : H2D of the new frames -> k_preprocess                                  (announced frames: already under way)
+//   stream    : k_dv_occupancy -> k_dv_fast -> k_dv_topk -> k_dv_select -> k_subpix -> k_lk (stereo) -> k_dv_assign
+//               -> [event: new pyramids] -> k_lk (temporal) -> k_ransac -> k_dv_merge
+// The host then copies the observation lists and the pts_last / ids_last mirrors out of mapped memory.
+// ---------------------------------------------------------------------------------------------------------------------
+int Pass::device_feed() {
+  Context *dev = ctx->dev;
+  int e = stage0_book();
+  if (e != OK) return e;
+  cudaStream_t st = ctx->stream;
+  // ---- per-tracker device memory; unit descriptors ---------------------------------------------------------------------------
+  for (int i = 0; i < n; i++) {
+    e = dv_prepare(dev, *reqs[i]->rig);
+    if (e != OK) { ctx->cuda_err = dev->cuda_err; return e; }
+  }
+  const int nu = (int)units.size();
+  CU_TRY(ctx->dv_units.reserve((size_t)std::max(nu, 1)));
+  CU_TRY(ctx->dv_heads.reserve((size_t)std::max(n, 1)));
+  int job_slots = 0, sp_slots = 0, lk_slots = 0, max_c = 1, max_cw = 1, max_ch = 1, max_p = 1, nheads = 0;
+  size_t fast_words = 0;
+  bool any_first = false;
+  {
+    int k = 0;
+    Rig *prev = nullptr;
+    for (auto &u : units) {
+      Rig &rig = *u.rig;
+      DvRig &D = *rig.dv;
+      const Params &P = rig.prm;
+      DvUnit &U = ctx->dv_units.h[k];
+      memset(&U, 0, sizeof(U));
+      const int unit_idx = u.stereo ? 0 : u.L.msg;
+      U.stereo = u.stereo;
+      U.first = u.first && !u.failed;
+      any_first |= u.first;
+      U.num_features = P.num_features;
+      U.gx = P.grid_x; U.gy = P.grid_y; U.mpd = P.min_px_dist; U.fast_threshold = P.fast_threshold;
+      const GridGeom geom = grider_geom(u.L.cam->w, u.L.cam->h, P.num_features, P.grid_x, P.grid_y);
+      U.size_x = geom.size_x; U.size_y = geom.size_y; U.per_cell = geom.per_cell;
+      U.P = D.P; U.C = D.C; U.K = D.K;
+      U.job_base = job_slots; U.fast_base = (int)fast_words; U.cell_cap = D.cell_cap;
+      U.sp_base = sp_slots; U.lk_base = lk_slots; U.rs_base = 2 * k;
+      U.currid = D.currid;
+      U.h_currid = D.m_currid;
+      for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+        Side &s = side ? u.R : u.L;
+        CamState &c = *s.cam;
+        const int ci = (int)(s.cam - rig.cams.data());
+        DvCamMem &m = D.cam[ci];
+        DvSide &S = U.s[side];
+        S.w = c.w; S.h = c.h;
+        const int det_slot = u.first ? c.cur : c.last();
+        S.det_pyr = c.pyr[det_slot]; S.last_pyr = c.pyr[c.last()]; S.cur_pyr = c.pyr[c.cur];
+        S.cam_model = c.cam_model_idx; S.cam_id = c.cam_id; S.thr = 2.0 / c.max_focal;
+        S.det_mask = c.mask_nonzero[det_slot] ? m.mask[det_slot] : nullptr;
+        S.cur_mask = c.mask_nonzero[c.cur] ? m.mask[c.cur] : nullptr;
+        S.pts_last = m.pts_last; S.ids_last = m.ids_last; S.n_last = m.n_last;
+        S.pts = m.pts; S.ids = m.ids; S.close = m.close; S.first = m.first; S.grid = m.grid; S.cells = m.cells;
+        S.top = m.top; S.top_n = m.top_n; S.ctl = m.ctl;
+        S.h_pts_last = m.m_pts_last; S.h_ids_last = m.m_ids_last; S.h_n_last = m.m_n_last;
+        max_cw = std::max(max_cw, geom.size_x);
+        max_ch = std::max(max_ch, geom.size_y);
+      }
+      if (!u.stereo) U.s[1] = U.s[0];   // never used; keeps every pointer valid
+      DvUnitMem &um = D.unit[(size_t)unit_idx];
+      U.scr_a = um.scr[0]; U.scr_b = um.scr[1]; U.scr_c = um.scr[2]; U.scr_d = um.scr[3];
+      U.part = um.part; U.tmp_pts = um.tmp_pts; U.tmp_ids = um.tmp_ids; U.uctl = um.uctl;
+      U.obs = um.m_obs; U.n_obs = um.m_n_obs; U.obs_cap = D.obs_cap;
+      *um.h_n_obs = 0;
+      job_slots += 2 * D.C;
+      fast_words += 2 * (size_t)D.C * D.cell_cap;
+      sp_slots += 2 * D.C * D.K;
+      lk_slots += 2 * D.P;
+      max_c = std::max(max_c, D.C);
+      max_p = std::max(max_p, D.P);
+      if (u.failed) { U.first = 1; U.num_features = 0; }   // (units of rejected messages never get here; kept for safety)
+      if (&rig != prev) {
+        ctx->dv_heads.h[nheads++] = DvHead{k, 1};
+        prev = &rig;
+      } else {
+        ctx->dv_heads.h[nheads - 1].count++;                 // the mono units of one rig share its id counter: same block, in order
+      }
+      k++;
+    }
+  }
+  // masks with a non-zero pixel are needed on the device (occupancy, cell selection, merge)
+  for (int i = 0; i < n; i++) {
+    FeedRequest &rq = *reqs[i];
+    for (int k = 0; k < rq.n; k++) {
+      CamState &c = *rq.rig->find_cam(rq.sensor_ids[k]);
+      if (!c.mask_nonzero[c.cur]) continue;
+      const int ci = (int)(&c - rq.rig->cams.data());
+      CU_TRY(cudaMemcpyAsync(rq.rig->dv->cam[ci].mask[c.cur], c.mask[c.cur].data(), (size_t)c.w * c.h, cudaMemcpyHostToDevice, st));
+    }
+  }
+  CU_TRY(ctx->dv_fast_jobs.reserve((size_t)job_slots));
+  CU_TRY(ctx->dv_fast_cnt.reserve((size_t)job_slots, true));
+  CU_TRY(ctx->dv_fast_out.reserve(fast_words));
+  CU_TRY(ctx->dv_sp_items.reserve((size_t)sp_slots));
+  CU_TRY(ctx->dv_sp_out.reserve(2 * (size_t)sp_slots));
+  CU_TRY(ctx->dv_lk1_items.reserve((size_t)sp_slots));
+  CU_TRY(ctx->dv_lk1_out.reserve((size_t)sp_slots));
+  CU_TRY(ctx->dv_lk1_status.reserve((size_t)sp_slots));
+  CU_TRY(ctx->dv_lk2_items.reserve((size_t)lk_slots));
+  CU_TRY(ctx->dv_lk2_out.reserve((size_t)lk_slots));
+  CU_TRY(ctx->dv_lk2_status.reserve((size_t)lk_slots));
+  CU_TRY(ctx->dv_rs_mask.reserve((size_t)lk_slots));
+  CU_TRY(ctx->dv_rs_mask_raw.reserve((size_t)lk_slots));
+  CU_TRY(ctx->dv_rs_jobs.reserve(2 * (size_t)std::max(nu, 1)));
+  CU_TRY(ctx->dv_p0n.reserve(2 * (size_t)lk_slots));
+  CU_TRY(ctx->dv_p1n.reserve(2 * (size_t)lk_slots));
+  DvGlobals X;
+  X.fast_jobs = ctx->dv_fast_jobs.d; X.fast_out = ctx->dv_fast_out.d; X.fast_cnt = ctx->dv_fast_cnt.d;
+  X.sp_items = ctx->dv_sp_items.d; X.sp_out = ctx->dv_sp_out.d;
+  X.lk1_items = ctx->dv_lk1_items.d; X.lk1_out = ctx->dv_lk1_out.d; X.lk1_status = ctx->dv_lk1_status.d;
+  X.lk2_items = ctx->dv_lk2_items.d; X.lk2_out = ctx->dv_lk2_out.d;
+  X.rs_jobs = ctx->dv_rs_jobs.d; X.p1n = ctx->dv_p1n.d; X.rs_mask = ctx->dv_rs_mask.d;
+  CU_TRY(ctx->dv_units.upload(st, (size_t)nu));
+  CU_TRY(ctx->dv_heads.upload(st, (size_t)nheads));
+  // ---- the new frames go up and are pre-processed on the upload stream (frames announced by submit_batch are on their way) ----
+  npre = (int)ctx->pre_items.size();
+  {
+    const PreBuffers B{&ctx->pre_jobs, &ctx->down_jobs, &ctx->clahe_lut};
+    e = issue_preprocess(dev, ctx->up_stream, B, ctx->pre_items, ctx->stats);
+    if (e != OK) { ctx->cuda_err = dev->cuda_err; return e; }
+    CU_TRY(cudaEventRecord(ctx->up_done, ctx->up_stream));
+  }
+  seg(0);
+  if (nu > 0) {
+    if (any_first) CU_TRY(wait_new_frames());   // first frames detect on the frame that is being uploaded (TrackKLT.cpp:110, :221)
+    const DvUnit *U = ctx->dv_units.d;
+    const DvHead *H = ctx->dv_heads.d;
+    CU_TRY(launch_dv_occupancy(st, U, H, nheads, X));
+    CU_TRY(launch_dv_fast(st, X, dev->pyr_dev.d, job_slots, max_cw, max_ch));
+    CU_TRY(launch_dv_topk(st, U, nu, max_c, X));
+    CU_TRY(launch_dv_select(st, U, H, nheads, X));
+    CU_TRY(launch_subpix(st, ctx->dv_sp_items.d, sp_slots, dev->pyr_dev.d, ctx->sp_mask.d, ctx->dv_sp_out.d, nullptr));
+    CU_TRY(launch_lk(st, ctx->dv_lk1_items.d, sp_slots, dev->pyr_dev.d, ctx->dv_sp_out.d, 30, 0.01, ctx->dv_lk1_out.d, ctx->dv_lk1_status.d,
+                     ctx->dv_lk1_out.d, ctx->dv_lk1_status.d));
+    CU_TRY(launch_dv_assign(st, U, H, nheads, X));
+    if (!any_first) CU_TRY(wait_new_frames());  // the temporal LK reads the new pyramids
+    CU_TRY(launch_lk(st, ctx->dv_lk2_items.d, lk_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
+                     ctx->dv_lk2_out.d, ctx->dv_lk2_status.d));
+    CU_TRY(launch_ransac(st, ctx->dv_rs_jobs.d, 2 * nu, max_p, ctx->dv_lk2_items.d, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, dev->cam_dev.d,
+                         ctx->dv_p0n.d, ctx->dv_p1n.d, ctx->dv_p1n.d, ctx->dv_rs_mask.d, ctx->dv_rs_mask_raw.d));
+    CU_TRY(launch_dv_merge(st, U, H, nheads, X));
+    ctx->stats[1] += 10;
+  } else {
+    CU_TRY(wait_new_frames());
+  }
+  seg(2);
+  if (ctx->sync() != OK) return E_CUDA;
+  seg(5);
+  ctx->prof_fold();
+  // ---- results: observation lists and the pts_last / ids_last mirrors, out of mapped memory ------------------------------------
+  t1 = t2 = t3 = now_us();
+  for (auto &u : units) {
+    Rig &rig = *u.rig;
+    DvRig &D = *rig.dv;
+    const int unit_idx = u.stereo ? 0 : u.L.msg;
+    DvUnitMem &um = D.unit[(size_t)unit_idx];
+    const int no = std::min(*um.h_n_obs, D.obs_cap);
+    static_assert(sizeof(Obs) == sizeof(DvObs), "the observation structs are the same bytes");
+    const size_t at = rig.obs.size();
+    rig.obs.resize(at + (size_t)no);
+    if (no) memcpy(rig.obs.data() + at, um.h_obs, sizeof(Obs) * (size_t)no);
+    ctx->stats[3] += sizeof(Obs) * (size_t)no;
+    for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
+      CamState &c = *(side ? u.R : u.L).cam;
+      DvCamMem &m = D.cam[(size_t)(&c - rig.cams.data())];
+      const int nl = std::min(*m.h_n_last, D.P);
+      c.pts_last.resize((size_t)nl);
+      c.ids_last.resize((size_t)nl);
+      if (nl) memcpy(c.pts_last.data(), m.h_pts_last, sizeof(Pt) * (size_t)nl);
+      for (int i = 0; i < nl; i++) c.ids_last[(size_t)i] = (size_t)m.h_ids_last[i];
+      c.have_last = true;
+      ctx->stats[3] += 16ull * (size_t)nl;
+    }
+  }
+  for (auto &u : units) u.rig->currid = (size_t)*u.rig->dv->h_currid;   // the id counter's mirror (written by k_dv_assign)
+  ctx->stats[0] += (unsigned long long)n;
+  const double t4 = now_us();
+  seg(6);
+  ctx->seg_us[7] += 1;
+  ctx->prof_end();
+  for (int i = 0; i < n; i++) {
+    float *sus = reqs[i]->rig->stage_us;
+    sus[0] = (float)(t1 - t0);
+    sus[1] = sus[2] = sus[3] = 0.f;
+    sus[4] = (float)(t4 - t3);
   }
   return OK;
 }
@@ -1972,6 +2357,36 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     else good.push_back(&rq);
   }
   if (ctx->upload_tables() != OK) return E_CUDA;
+  if (device_pipeline_enabled()) {
+    // the device-side pipeline: every tracker of the call through one lane, one chain of launches, one synchronisation
+    for (auto &ln : ctx->lanes) cancel_ahead(*ln);
+    if (!ctx->bg_passes) ctx->bg_passes = new std::vector<Pass>;
+    std::vector<Pass> &one = *ctx->bg_passes;
+    one.clear();
+    one.resize(1);
+    Lane &ln = *ctx->lanes[0];
+    one[0].ctx = &ln;
+    one[0].reqs = good.data();
+    one[0].n = (int)good.size();
+    int rc = OK;
+    if (!good.empty()) {
+      g_prof = ln.prof_on ? &ln.prof : nullptr;
+      rc = one[0].device_feed();
+      g_prof = nullptr;
+    }
+    if (one[0].worst > worst) worst = one[0].worst;
+    if (rc > worst) worst = rc;
+    for (int k = 0; k < 8; k++) {
+      ctx->stats[k] += ln.stats[k];
+      ln.stats[k] = 0;
+      ctx->seg_us[k] += ln.seg_us[k];
+      ln.seg_us[k] = 0;
+    }
+    if (ln.cuda_err) ctx->cuda_err = ln.cuda_err;
+    ctx->stats[4] += 1;
+    one[0].reqs = nullptr;
+    return worst;
+  }
   // ---- split the trackers over the lanes (contiguous shares); every host thread drives `depth` lanes stage by stage ---------
   const int nl = std::max(1, std::min((int)ctx->lanes.size(), (int)good.size()));
   const int nthreads = std::max(1, std::min(ctx->threads, nl));

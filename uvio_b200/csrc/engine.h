@@ -105,6 +105,8 @@ class Rig {                     // one tracker = one TrackKLT instance
   int cuda_error = 0;
   std::mutex mtx;                                   // serialises feed / getters on this handle
   CamState *find_cam(size_t id);
+  struct DvRig *dv = nullptr;                       // device-side pipeline: the tracker's state and work areas in HBM (engine.cpp)
+  bool dv_dirty = true;                             // pts_last / ids_last / currid changed on the host since the device copy was made
   std::vector<Unit *> unit_pool;                    // scratch reused from feed to feed (keeps its vectors' capacity)
   Unit *unit_at(size_t i);
 };

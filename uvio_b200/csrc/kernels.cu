@@ -15,6 +15,7 @@
 #include "lk_body.h"
 #include "ransac_body.h"
 #include "subpix_body.h"
+#include "track_body.h"
 
 namespace cg = cooperative_groups;
 
@@ -335,6 +336,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_subpix(const SubpixIte
   const int wid = threadIdx.x >> 5, i = blockIdx.x * WARPS_PER_BLOCK + wid;
   if (i >= n) return;
   const SubpixItem it = items[i];
+  if (it.pyr < 0) return;   // an unused slot of the device-side pipeline
   float x = it.x, y = it.y;
   subpix_point(GroupWarp(), sm[wid], pyr_tab[it.pyr].lv[0], smask, 20, 0.001 * 0.001, x, y);
   if ((threadIdx.x & 31) == 0) {
@@ -399,6 +401,7 @@ __global__ void LK_BOUNDS k_lk(const LkItem *items, int n, const PyrDesc *pyr_ta
   if (i >= n) return;
   const LkItem it = items[i];
   float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
+  if (it.prev_pyr < 0) return;   // an unused slot of the device-side pipeline (exiting counts as the PDL trigger)
   pdl_wait();                 // the refined corners (init_from_dev) and the kernel before this one's use of out_dev / status_dev
   if (init_from_dev) {
     px = nx = init_from_dev[2 * i];
@@ -521,6 +524,99 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
                                p0n_dev, p1n_dev, p1n_host, mask_host, mask_dev);
   prof_mark(st, -1);
   return e != cudaSuccess ? e : cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Device-side bookkeeping (track_body.h): the kernels between the pixel kernels of a feed.  One block per tracker.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int DV_THREADS = 256;
+constexpr int DV_TOPK_SMEM = 4096;   // corner words a cell's top-K block sorts in shared memory (more: in the job's own global region)
+
+__global__ void __launch_bounds__(DV_THREADS) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X) {
+  const DvHead h = heads[blockIdx.x];
+  for (int u = h.first; u < h.first + h.count; u++) dv_occupancy(GroupBlock(), units[u], X);
+}
+
+// FAST over the job slots the occupancy kernel filled: a fixed grid walks (job, tile) pairs; unused slots have w == 0
+__global__ void __launch_bounds__(256) k_dv_fast(DvGlobals X, const PyrDesc *pyr_tab, int n_slots, int max_tiles) {
+  __shared__ FastSmem s;
+  for (int w = blockIdx.x; w < n_slots * max_tiles; w += gridDim.x) {
+    const int slot = w / max_tiles, tile = w - slot * max_tiles;
+    const FastJob job = X.fast_jobs[slot];
+    if (job.w == 0) continue;
+    const int tiles_x = (job.w + FT_W - 1) / FT_W, tiles_y = (job.h + FT_H - 1) / FT_H;
+    if (tile >= tiles_x * tiles_y) continue;
+    fast_tile(GroupBlock(), s, pyr_tab[job.img].lv[0], job, (tile % tiles_x) * FT_W, (tile / tiles_x) * FT_H, job.threshold, X.fast_out,
+              &X.fast_cnt[slot]);
+  }
+}
+
+// per-cell top-K in std::sort order: one block per job slot; grid = (2C max, units)
+__global__ void __launch_bounds__(DV_THREADS) k_dv_topk(const DvUnit *units, DvGlobals X) {
+  __shared__ uint32_t buf[DV_TOPK_SMEM];
+  const DvUnit &U = units[blockIdx.y];
+  const int side = blockIdx.x / U.C, r = blockIdx.x - side * U.C;
+  if (side > 1 || (side == 1 && !U.stereo)) return;
+  dv_topk(GroupBlock(), U, X, side, r, buf, DV_TOPK_SMEM);
+}
+
+__global__ void __launch_bounds__(DV_THREADS) k_dv_select(const DvUnit *units, const DvHead *heads, DvGlobals X) {
+  const DvHead h = heads[blockIdx.x];
+  for (int u = h.first; u < h.first + h.count; u++) dv_select(GroupBlock(), units[u], X);
+}
+__global__ void __launch_bounds__(DV_THREADS) k_dv_assign(const DvUnit *units, const DvHead *heads, DvGlobals X) {
+  const DvHead h = heads[blockIdx.x];
+  for (int u = h.first; u < h.first + h.count; u++) dv_assign(GroupBlock(), units[u], X);
+}
+__global__ void __launch_bounds__(DV_THREADS) k_dv_merge(const DvUnit *units, const DvHead *heads, DvGlobals X) {
+  const DvHead h = heads[blockIdx.x];
+  for (int u = h.first; u < h.first + h.count; u++) dv_merge(GroupBlock(), units[u], X);
+}
+
+cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  if (n_heads <= 0) return cudaSuccess;
+  prof_mark(st, K_DV_LOGIC);
+  k_dv_occupancy<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  prof_mark(st, -1);
+  return cudaGetLastError();
+}
+cudaError_t launch_dv_fast(cudaStream_t st, const DvGlobals &X, const PyrDesc *pyr_tab, int n_slots, int max_cell_w, int max_cell_h) {
+  if (n_slots <= 0) return cudaSuccess;
+  const int tiles = ((max_cell_w + FT_W - 1) / FT_W) * ((max_cell_h + FT_H - 1) / FT_H);
+  const long work = (long)n_slots * tiles;
+  const int grid = (int)(work < 148 * 8 ? work : 148 * 8);   // 8 blocks of 256 threads per SM
+  prof_mark(st, K_FAST);
+  k_dv_fast<<<grid, 256, 0, st>>>(X, pyr_tab, n_slots, tiles);
+  prof_mark(st, -1);
+  return cudaGetLastError();
+}
+cudaError_t launch_dv_topk(cudaStream_t st, const DvUnit *units, int n_units, int max_c, const DvGlobals &X) {
+  if (n_units <= 0) return cudaSuccess;
+  prof_mark(st, K_DV_TOPK);
+  k_dv_topk<<<dim3(2 * max_c, n_units), DV_THREADS, 0, st>>>(units, X);
+  prof_mark(st, -1);
+  return cudaGetLastError();
+}
+cudaError_t launch_dv_select(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  if (n_heads <= 0) return cudaSuccess;
+  prof_mark(st, K_DV_LOGIC);
+  k_dv_select<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  prof_mark(st, -1);
+  return cudaGetLastError();
+}
+cudaError_t launch_dv_assign(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  if (n_heads <= 0) return cudaSuccess;
+  prof_mark(st, K_DV_LOGIC);
+  k_dv_assign<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  prof_mark(st, -1);
+  return cudaGetLastError();
+}
+cudaError_t launch_dv_merge(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+  if (n_heads <= 0) return cudaSuccess;
+  prof_mark(st, K_DV_LOGIC);
+  k_dv_merge<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  prof_mark(st, -1);
+  return cudaGetLastError();
 }
 
 }  // namespace uvio

@@ -42,7 +42,7 @@ struct RansacJob {
 
 // Optional per-kernel timing: when g_prof is set, every launch wrapper records a CUDA event before each kernel it launches
 // (and the engine one after the last), on the launching stream.
-enum KernelId { K_HIST = 0, K_LUT_APPLY, K_CLAHE_TILES, K_CLAHE_APPLY, K_PYRDOWN, K_FAST, K_SUBPIX, K_LK, K_RANSAC, K_PREPROCESS, K_DOWNSAMPLE, K_COUNT };
+enum KernelId { K_HIST = 0, K_LUT_APPLY, K_CLAHE_TILES, K_CLAHE_APPLY, K_PYRDOWN, K_FAST, K_SUBPIX, K_LK, K_RANSAC, K_PREPROCESS, K_DOWNSAMPLE, K_DV_LOGIC, K_DV_TOPK, K_COUNT };
 struct KernelProf {
   static constexpr int MAX_MARKS = 48;
   cudaEvent_t ev[MAX_MARKS];
@@ -90,6 +90,18 @@ cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc
 cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk_dev,
                           const uint8_t *status_dev, const CamModel *cams_dev, float *p0n_dev, float *p1n_dev,
                           float *p1n_host, uint8_t *mask_host, uint8_t *mask_dev, bool overlap = false);
+
+// ---- device-side bookkeeping (track_body.h): occupancy -> FAST -> top-K -> select -> [sub-pixel, stereo LK] -> assign ->
+// [temporal LK, RANSAC] -> merge, all on one stream without a host round trip
+struct DvUnit;
+struct DvHead;
+struct DvGlobals;
+cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units_dev, const DvHead *heads_dev, int n_heads, const DvGlobals &X);
+cudaError_t launch_dv_fast(cudaStream_t st, const DvGlobals &X, const PyrDesc *pyr_tab_dev, int n_slots, int max_cell_w, int max_cell_h);
+cudaError_t launch_dv_topk(cudaStream_t st, const DvUnit *units_dev, int n_units, int max_c, const DvGlobals &X);
+cudaError_t launch_dv_select(cudaStream_t st, const DvUnit *units_dev, const DvHead *heads_dev, int n_heads, const DvGlobals &X);
+cudaError_t launch_dv_assign(cudaStream_t st, const DvUnit *units_dev, const DvHead *heads_dev, int n_heads, const DvGlobals &X);
+cudaError_t launch_dv_merge(cudaStream_t st, const DvUnit *units_dev, const DvHead *heads_dev, int n_heads, const DvGlobals &X);
 
 cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t st);
 // LK work counters since the last reset: [0] point-levels (templates staged), [1] iterations, [2] points
