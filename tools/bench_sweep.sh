@@ -1,0 +1,13 @@
+#!/bin/bash
+# usage: tools/bench_sweep.sh VAR v1 v2 ...   -- bench.py (no CPU arm) once per value of an environment variable; prints value / e2e
+VAR=$1; shift
+for v in "$@"; do
+  env $VAR=$v python bench.py --no-cpu-baseline > gpurun_out/sweep_${VAR}_$v.json 2> gpurun_out/sweep_${VAR}_$v.err || { echo "$VAR=$v FAILED"; tail -3 gpurun_out/sweep_${VAR}_$v.err; continue; }
+  python - "$VAR" "$v" <<'PY'
+import json, sys
+d = json.load(open(f"gpurun_out/sweep_{sys.argv[1]}_{sys.argv[2]}.json"))
+r = d["roofline"]
+print(f"{sys.argv[1]}={sys.argv[2]}: resident {d['value']:.0f} e2e {d['e2e']['value']:.0f} ms/step {d['ms_per_step']:.3f} launches {d['gpu_launches']} "
+      f"busy {r['gpu_busy_ms_per_step']:.2f} shares {{k: v for k, v in r['kernel_time_share_of_gpu_time'].items() if v}} host {d['host']['resident_us_per_lane_pass']} calls {d['host']['resident_call_us_per_step']}")
+PY
+done

@@ -175,6 +175,17 @@ int uvio_klt_feed(uvio_klt *h, const UvioFrame *frame) {
 int uvio_klt_get_new_observations(uvio_klt *h, UvioObs *out, int cap, int *n) {
   if (!h || !n) return UVIO_E_ARG;
   std::lock_guard<std::mutex> lk(h->rig->mtx);
+  if (!h->rig->dv_obs.empty()) {   // device-side pipeline: straight out of the mapped memory the merge kernel wrote
+    static_assert(sizeof(Obs) == sizeof(UvioObs), "same bytes");
+    int total = 0;
+    for (auto &part : h->rig->dv_obs) {
+      const int take = out ? std::max(0, std::min(part.second, cap - total)) : 0;
+      if (take) memcpy(out + total, part.first, sizeof(UvioObs) * (size_t)take);
+      total += part.second;
+    }
+    *n = total;
+    return UVIO_OK;
+  }
   const std::vector<Obs> &o = h->rig->obs;
   *n = (int)o.size();
   for (int i = 0; out && i < cap && i < (int)o.size(); i++) out[i] = UvioObs{o[i].id, o[i].cam_id, o[i].u, o[i].v, o[i].un, o[i].vn};
@@ -184,6 +195,7 @@ int uvio_klt_get_new_observations(uvio_klt *h, UvioObs *out, int cap, int *n) {
 int uvio_klt_get_last(uvio_klt *h, size_t cam_id, size_t *ids, float *uv, int cap, int *n) {
   if (!h || !n) return UVIO_E_ARG;
   std::lock_guard<std::mutex> lk(h->rig->mtx);
+  dv_sync_mirror(*h->rig);
   CamState *c = h->rig->find_cam(cam_id);
   if (!c) return UVIO_E_CAMID;
   *n = (int)c->pts_last.size();
@@ -210,6 +222,7 @@ int uvio_klt_change_feat_id(uvio_klt *h, size_t id_old, size_t id_new) {
   if (!h) return UVIO_E_ARG;
   std::lock_guard<std::mutex> lk(h->rig->mtx);
   context_quiesce(h->rig->ctx);
+  dv_sync_mirror(*h->rig);
   for (auto &c : h->rig->cams)                       // TrackBase.cpp:241-247
     for (auto &id : c.ids_last)
       if (id == id_old) id = id_new;

@@ -1227,6 +1227,7 @@ static T *dv_carve(char *&p, size_t n) {
 // when the host copy is newer (first use, set_num_features, change_feat_id, a feed through the host path)
 static int dv_prepare(Context *ctx, Rig &rig) {
   const Params &P = rig.prm;
+  if (rig.dv_mirror_stale && (rig.dv_dirty || rig.dv == nullptr || rig.dv->nf != P.num_features)) dv_sync_mirror(rig);
   bool rebuild = rig.dv == nullptr || rig.dv->nf != P.num_features || rig.dv->cam_w.size() != rig.cams.size();
   if (!rebuild)
     for (size_t k = 0; k < rig.cams.size(); k++) rebuild |= rig.dv->cam_w[k] != rig.cams[k].w || rig.dv->cam_h[k] != rig.cams[k].h;
@@ -1310,6 +1311,7 @@ static int dv_prepare(Context *ctx, Rig &rig) {
   if (rig.dv_dirty) {
     DvRig &D = *rig.dv;
     CU_TRY(cudaDeviceSynchronize());
+    for (auto &c : rig.cams) c.dv_n_last = -1;     // the host vectors are the truth now (dv_sync_mirror ran before they were edited)
     const unsigned long long id = (unsigned long long)rig.currid;
     CU_TRY(cudaMemcpy(D.currid, &id, sizeof(id), cudaMemcpyHostToDevice));
     for (size_t k = 0; k < rig.cams.size(); k++) {
@@ -1396,7 +1398,8 @@ struct Pass {
   int stage0();
   int stage0_book();
   int stage0_issue();
-  int device_feed();     // the whole feed as one chain of launches with the bookkeeping on the device (track_body.h)
+  int device_feed();     // the whole feed as one chain of launches with the bookkeeping on the device (track_body.h): issue
+  int device_collect();  // ... wait for it and take the results over
   int stage1();
   int stage2();
   int stage3();
@@ -1761,7 +1764,7 @@ int Pass::stage0_book() {
       u.req = &rq; u.stereo = true;
       make_side(u.L, 0);
       make_side(u.R, 1);
-      u.first = u.L.cam->pts_last.empty() && u.R.cam->pts_last.empty();                               // :221
+      u.first = u.L.cam->no_points() && u.R.cam->no_points();                                         // :221
       if (!u.first && (!u.L.cam->have_last || !u.R.cam->have_last)) { fail(rq, E_BADMSG); continue; }
       units.push_back(&u);
     } else {
@@ -1769,7 +1772,7 @@ int Pass::stage0_book() {
         Unit &u = *rig.unit_at((size_t)k);
         u.req = &rq; u.stereo = false;
         make_side(u.L, k);
-        u.first = u.L.cam->pts_last.empty();                                                          // :110
+        u.first = u.L.cam->no_points();                                                                // :110
         units.push_back(&u);
       }
     }
@@ -1983,7 +1986,11 @@ int Pass::stage3() {
   t3 = now_us();
   for (auto &u : units)
     if (!u.first && !u.failed) phase_d(ctx, u);
-  for (auto &u : units) u.rig->dv_dirty = true;   // a device-side copy of this state, if any, is stale now
+  for (auto &u : units) {   // a device-side copy of this state, if any, is stale now
+    u.rig->dv_dirty = true;
+    u.rig->dv_mirror_stale = false;
+    for (auto &c : u.rig->cams) c.dv_n_last = -1;
+  }
   const double t4 = now_us();
   issue_ahead();
   seg(6);
@@ -2154,10 +2161,15 @@ int Pass::device_feed() {
     CU_TRY(wait_new_frames());
   }
   seg(2);
+  return OK;
+}
+
+// second half of the device-side feed: wait for the chain, then point the trackers at what the GPU left in mapped memory
+// (observation lists, pts_last / ids_last mirrors); nothing is copied until somebody asks for it
+int Pass::device_collect() {
   if (ctx->sync() != OK) return E_CUDA;
   seg(5);
   ctx->prof_fold();
-  // ---- results: observation lists and the pts_last / ids_last mirrors, out of mapped memory ------------------------------------
   t1 = t2 = t3 = now_us();
   for (auto &u : units) {
     Rig &rig = *u.rig;
@@ -2166,23 +2178,18 @@ int Pass::device_feed() {
     DvUnitMem &um = D.unit[(size_t)unit_idx];
     const int no = std::min(*um.h_n_obs, D.obs_cap);
     static_assert(sizeof(Obs) == sizeof(DvObs), "the observation structs are the same bytes");
-    const size_t at = rig.obs.size();
-    rig.obs.resize(at + (size_t)no);
-    if (no) memcpy(rig.obs.data() + at, um.h_obs, sizeof(Obs) * (size_t)no);
+    if (no > 0) rig.dv_obs.emplace_back((const Obs *)um.h_obs, no);
     ctx->stats[3] += sizeof(Obs) * (size_t)no;
     for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
       CamState &c = *(side ? u.R : u.L).cam;
       DvCamMem &m = D.cam[(size_t)(&c - rig.cams.data())];
-      const int nl = std::min(*m.h_n_last, D.P);
-      c.pts_last.resize((size_t)nl);
-      c.ids_last.resize((size_t)nl);
-      if (nl) memcpy(c.pts_last.data(), m.h_pts_last, sizeof(Pt) * (size_t)nl);
-      for (int i = 0; i < nl; i++) c.ids_last[(size_t)i] = (size_t)m.h_ids_last[i];
+      c.dv_n_last = std::min(*m.h_n_last, D.P);
       c.have_last = true;
-      ctx->stats[3] += 16ull * (size_t)nl;
+      ctx->stats[3] += 16ull * (size_t)c.dv_n_last;
     }
+    rig.dv_mirror_stale = true;
+    rig.currid = (size_t)*D.h_currid;   // the id counter's mirror (written by k_dv_assign)
   }
-  for (auto &u : units) u.rig->currid = (size_t)*u.rig->dv->h_currid;   // the id counter's mirror (written by k_dv_assign)
   ctx->stats[0] += (unsigned long long)n;
   const double t4 = now_us();
   seg(6);
@@ -2195,6 +2202,22 @@ int Pass::device_feed() {
     sus[4] = (float)(t4 - t3);
   }
   return OK;
+}
+
+void dv_sync_mirror(Rig &rig) {
+  if (!rig.dv_mirror_stale || !rig.dv) return;
+  DvRig &D = *rig.dv;
+  for (size_t k = 0; k < rig.cams.size(); k++) {
+    CamState &c = rig.cams[k];
+    if (c.dv_n_last < 0) continue;
+    const DvCamMem &m = D.cam[k];
+    const int nl = c.dv_n_last;
+    c.pts_last.resize((size_t)nl);
+    c.ids_last.resize((size_t)nl);
+    if (nl) memcpy(c.pts_last.data(), m.h_pts_last, sizeof(Pt) * (size_t)nl);
+    for (int i = 0; i < nl; i++) c.ids_last[(size_t)i] = (size_t)m.h_ids_last[i];
+  }
+  rig.dv_mirror_stale = false;
 }
 
 // The checks of TrackKLT::feed_new_camera on one message; new cameras get their device memory here.
@@ -2352,39 +2375,57 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     FeedRequest &rq = reqs[i];
     rq.status = OK;
     rq.rig->obs.clear();
+    rq.rig->dv_obs.clear();
     int e = validate_request(ctx, rq, false);
     if (e != OK) fail(rq, e);
     else good.push_back(&rq);
   }
   if (ctx->upload_tables() != OK) return E_CUDA;
   if (device_pipeline_enabled()) {
-    // the device-side pipeline: every tracker of the call through one lane, one chain of launches, one synchronisation
+    // The device-side pipeline: the trackers of the call are cut into a few groups, each a chain of launches on its own
+    // stream (so that the latency-bound kernels of one group run under the LK of another), all issued by this thread;
+    // then one wait per group.  No host thread pool, no host bookkeeping between kernels.
+    static const int max_groups = [] {
+      const char *e = getenv("UVIO_KLT_GROUPS");
+      int v = e ? atoi(e) : 4;
+      return v < 1 ? 1 : (v > 16 ? 16 : v);
+    }();
     for (auto &ln : ctx->lanes) cancel_ahead(*ln);
+    const int ng = std::max(1, std::min(std::min(max_groups, (int)ctx->lanes.size()), ((int)good.size() + 3) / 4));
     if (!ctx->bg_passes) ctx->bg_passes = new std::vector<Pass>;
-    std::vector<Pass> &one = *ctx->bg_passes;
-    one.clear();
-    one.resize(1);
-    Lane &ln = *ctx->lanes[0];
-    one[0].ctx = &ln;
-    one[0].reqs = good.data();
-    one[0].n = (int)good.size();
+    std::vector<Pass> &grp = *ctx->bg_passes;
+    grp.clear();
+    grp.resize((size_t)ng);
     int rc = OK;
-    if (!good.empty()) {
+    for (int g = 0; g < ng && !good.empty(); g++) {
+      size_t b = good.size() * (size_t)g / ng, e = good.size() * (size_t)(g + 1) / ng;
+      Lane &ln = *ctx->lanes[(size_t)g];
+      grp[g].ctx = &ln;
+      grp[g].reqs = good.data() + b;
+      grp[g].n = (int)(e - b);
       g_prof = ln.prof_on ? &ln.prof : nullptr;
-      rc = one[0].device_feed();
+      int r = grp[g].device_feed();
       g_prof = nullptr;
+      if (r != OK) { grp[g].rc = r; rc = std::max(rc, r); }
     }
-    if (one[0].worst > worst) worst = one[0].worst;
+    for (int g = 0; g < ng && !good.empty(); g++) {
+      Lane &ln = *ctx->lanes[(size_t)g];
+      g_prof = ln.prof_on ? &ln.prof : nullptr;
+      int r = grp[g].rc == OK ? grp[g].device_collect() : (cudaStreamSynchronize(ln.stream), grp[g].rc);
+      g_prof = nullptr;
+      rc = std::max(rc, r);
+      if (grp[g].worst > worst) worst = grp[g].worst;
+      for (int k = 0; k < 8; k++) {
+        ctx->stats[k] += ln.stats[k];
+        ln.stats[k] = 0;
+        ctx->seg_us[k] += ln.seg_us[k];
+        ln.seg_us[k] = 0;
+      }
+      if (ln.cuda_err) ctx->cuda_err = ln.cuda_err;
+      grp[g].reqs = nullptr;
+    }
     if (rc > worst) worst = rc;
-    for (int k = 0; k < 8; k++) {
-      ctx->stats[k] += ln.stats[k];
-      ln.stats[k] = 0;
-      ctx->seg_us[k] += ln.seg_us[k];
-      ln.seg_us[k] = 0;
-    }
-    if (ln.cuda_err) ctx->cuda_err = ln.cuda_err;
     ctx->stats[4] += 1;
-    one[0].reqs = nullptr;
     return worst;
   }
   // ---- split the trackers over the lanes (contiguous shares); every host thread drives `depth` lanes stage by stage ---------

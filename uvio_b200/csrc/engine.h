@@ -10,6 +10,7 @@
 
 #include <mutex>
 #include <unordered_map>
+#include <utility>
 #include <vector>
 
 #include "kernels.h"
@@ -74,6 +75,8 @@ struct CamState {               // per camera id (TrackBase.h:180-190: img_last,
   size_t raw_bytes = 0;
   int raw = -1;                 // downsample_cameras: the halved frame the pre-processing reads (else it reads raw_in[])
   bool have_last = false;
+  int dv_n_last = -1;           // device-side pipeline: points after the last feed (-1: pts_last below is current)
+  bool no_points() const { return dv_n_last >= 0 ? dv_n_last == 0 : pts_last.empty(); }
   std::vector<Pt> pts_last;
   std::vector<size_t> ids_last;
   std::vector<uint8_t> mask[PYR_SLOTS]; // host copies of the masks, indexed like pyr[]
@@ -107,6 +110,8 @@ class Rig {                     // one tracker = one TrackKLT instance
   CamState *find_cam(size_t id);
   struct DvRig *dv = nullptr;                       // device-side pipeline: the tracker's state and work areas in HBM (engine.cpp)
   bool dv_dirty = true;                             // pts_last / ids_last / currid changed on the host since the device copy was made
+  bool dv_mirror_stale = false;                     // the last feed's pts_last / ids_last are still in mapped memory only (dv_sync_mirror)
+  std::vector<std::pair<const Obs *, int>> dv_obs;  // the last feed's observations where the GPU wrote them (mapped memory), in order
   std::vector<Unit *> unit_pool;                    // scratch reused from feed to feed (keeps its vectors' capacity)
   Unit *unit_at(size_t i);
 };
@@ -128,6 +133,8 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n);
 int submit_batch(Context *ctx, FeedRequest *reqs, int n);
 
 Context *context_for_device(int device, int *err);
+// device-side pipeline: brings CamState::pts_last / ids_last up to date with what the last feed left in mapped memory
+void dv_sync_mirror(Rig &rig);
 int context_cuda_error(Context *ctx);
 // waits (under the context lock) until no background part of a feed is running: call before mutating tracker state it reads
 void context_quiesce(Context *ctx);

@@ -119,19 +119,14 @@ UVIO_HD int fdb_find(const FdbStore &S, unsigned long long key) {
 // exclusive scan of in[0..n) into out[0..n], out[n] = total; in == out is allowed.  Every lane takes a contiguous chunk.
 template <class G>
 UVIO_HD void fdb_scan(G g, const int *in, int *out, int n, int *part) {
+  (void)part;
   const int lanes = g.size(), chunk = (n + lanes - 1) / lanes;
   const int b = g.lane() * chunk, e = b + chunk < n ? b + chunk : n;
   int s = 0;
   for (int i = b; i < e; i++) s += in[i];
-  part[g.lane()] = s;
-  g.sync();
-  if (g.lane() == 0) {
-    int run = 0;
-    for (int l = 0; l < lanes; l++) { int v = part[l]; part[l] = run; run += v; }
-    out[n] = run;
-  }
-  g.sync();
-  int run = part[g.lane()];
+  int total;
+  int run = g.exclusive_sum(s, total);     // lane order == chunk order
+  if (g.lane() == 0) out[n] = total;
   for (int i = b; i < e; i++) { int v = in[i]; out[i] = run; run += v; }
   g.sync();
 }

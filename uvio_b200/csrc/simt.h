@@ -27,6 +27,8 @@ struct GroupSeq {
   static constexpr int SIZE = 1;                        // compile-time size, for per-lane register arrays
   typedef long long acc_t;                              // wide enough for one lane's share of an integer sum
   UVIO_HD unsigned reduce_add(unsigned v) const { return v; }
+  // exclusive prefix sum of one value per lane, in lane order; total = sum over the group.  Every lane must call it.
+  UVIO_HD int exclusive_sum(int v, int &total) const { total = v; return 0; }
 };
 
 #ifdef __CUDACC__
@@ -42,6 +44,33 @@ struct GroupBlock {
   __device__ __forceinline__ int lane() const { return threadIdx.x; }
   __device__ __forceinline__ int size() const { return blockDim.x; }
   __device__ __forceinline__ void sync() const { __syncthreads(); }
+  // block-wide exclusive prefix sum (warp shuffles + one shared word per warp); blockDim.x a multiple of 32, <= 1024
+  __device__ __forceinline__ int exclusive_sum(int v, int &total) const {
+    __shared__ int warp_sum[33];
+    const int lane_id = threadIdx.x & 31, warp_id = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    int inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane_id >= d) inc += up;
+    }
+    __syncthreads();                       // the previous call's readers are done with warp_sum
+    if (lane_id == 31) warp_sum[warp_id] = inc;
+    __syncthreads();
+    if (warp_id == 0) {
+      int w = lane_id < nwarps ? warp_sum[lane_id] : 0, winc = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, winc, d);
+        if (lane_id >= d) winc += up;
+      }
+      if (lane_id < nwarps) warp_sum[lane_id] = winc - w;
+      if (lane_id == 31) warp_sum[32] = winc;
+    }
+    __syncthreads();
+    total = warp_sum[32];
+    return warp_sum[warp_id] + inc - v;
+  }
 };
 #endif
 

@@ -433,7 +433,7 @@ def make_tracker(cfg, device: int = 0, **over) -> TrackKLT:
 
 
 KERNEL_NAMES = ["k_hist", "k_lut_apply", "k_clahe_tiles", "k_clahe_apply", "k_pyrdown", "k_fast", "k_subpix", "k_lk", "k_ransac",
-                "k_preprocess", "k_downsample"]
+                "k_preprocess", "k_downsample", "k_dv_logic", "k_dv_topk"]
 
 
 def device_stats(device: int = 0) -> dict:
