@@ -2,27 +2,28 @@
 """bench.py — stereo frames/s of the TrackKLT hot path (BASELINE.json metric) on N B200s.
 
   python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run, one rank per GPU)
+  python bench.py --config {euroc_mav,tum_vi,rs_d455,hd_1000,uzhfpv_8}     one of BASELINE.json's five configurations
   python bench.py --impl reference ...                     the CPU tracker (cv2-driven oracle) on the host cores
 
-Workload (config.workload): BASELINE configs[0], the configuration the metric is quoted on — euroc_mav, 752x480 stereo,
-200 features per camera, 5x5 grid, FAST threshold 20, histogram equalisation, reference pyramid (5 requested levels).
-One "step" feeds one new stereo frame to each of S independent synthetic camera streams on a GPU as ONE batched
-uvio_klt_feed_batch call (streams are the unit that shards; no data-path collective).  value = frames all
-ranks processed / max-over-ranks time, inputs already resident in HBM; e2e = the same call with pinned HOST frames (the
-upload and the result read-back are inside the timed region).
+Workload of the default line (config.workload): the configuration the metric is quoted on — euroc_mav, 752x480 stereo, 200
+features per camera, 5x5 grid, FAST threshold 20, histogram equalisation, the reference's pyramid (5 requested levels).
+S independent synthetic camera streams live on a GPU (streams are the unit that shards; no data-path
+collective).  One "step" feeds R consecutive stereo frames to every stream: R batched uvio_klt_feed_batch calls, S * R
+frames.  value = frames all ranks processed / max-over-ranks device time with the frames already resident in HBM; e2e = the
+same calls on pinned HOST frames, the upload and the result read-back inside the timed region.
 """
 from __future__ import annotations
 
 import argparse
 import ctypes as C
 import json
+import mmap
 import os
 import subprocess
 import sys
 import time
 
-# One hardware work queue per CUDA stream (the default of 8 makes streams share queues: a lane's kernels then wait behind the
-# frame upload of another stream -- measured as one straggler lane per call).  Must be set before the CUDA context exists.
+# One hardware work queue per CUDA stream (the default of 8 makes streams share queues).  Must be set before the CUDA context exists.
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 import numpy as np
@@ -32,51 +33,67 @@ sys.path.insert(0, ROOT)
 
 METRIC = "stereo_frames_per_sec_tracked_TrackKLT_752x480"
 UNIT = "frames/s"
+# BASELINE.json configs -> (tracker configuration, streams per GPU)
+BENCH_CONFIGS = {"euroc_mav": ("EUROC_MAV", 64), "tum_vi": ("TUM_VI", 64), "rs_d455": ("RS_D455", 64), "hd_1000": ("HD_1000", 16),
+                 "uzhfpv_8": ("UZHFPV_INDOOR", 8)}
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--streams", type=int, default=int(os.environ.get("UVIO_BENCH_STREAMS", "64")), help="streams per GPU")
+    ap.add_argument("--config", default="euroc_mav", choices=sorted(BENCH_CONFIGS))
+    ap.add_argument("--streams", type=int, default=int(os.environ.get("UVIO_BENCH_STREAMS", "0")), help="streams per GPU (0: the config's default)")
+    ap.add_argument("--frames-per-step", type=int, default=32, help="consecutive frames fed to every stream in one step")
+    ap.add_argument("--pool", type=int, default=40, help="distinct frames per stream; a run walks them forwards and backwards")
     ap.add_argument("--distinct", type=int, default=8, help="distinct synthetic sequences per GPU (others are time-shifted copies)")
     ap.add_argument("--cpu-frames", type=int, default=120, help="frames of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
 
-def workload_config():
+def workload_config(name="euroc_mav"):
     from uvio_b200 import configs
-    return configs.EUROC_MAV
+    return getattr(configs, BENCH_CONFIGS[name][0])
 
 
-def config_dict(cfg, streams, extra=None):
+def config_dict(cfg, streams, frames_per_step, extra=None):
+    hist = {0: "no equalisation", 1: "equalizeHist", 2: "CLAHE"}[cfg.histogram]
     d = {"workload": f"TrackKLT {cfg.name} {cfg.width}x{cfg.height} stereo, {cfg.num_features} feats/cam, "
-                     f"{cfg.grid_x}x{cfg.grid_y} grid, fast_thresh {cfg.fast_threshold}, equalizeHist, pyr_levels {cfg.pyr_levels} "
-                     "(reference-faithful; effective top level 4)",
-         "streams_per_gpu": streams, "frames_per_step": streams,
-         "l2_policy": "every step reads new frames (inputs of a run >> 126 MB L2); no explicit flush"}
+                     f"{cfg.grid_x}x{cfg.grid_y} grid, fast_thresh {cfg.fast_threshold}, {hist}, pyr_levels {cfg.pyr_levels}"
+                     + (" (reference-faithful; effective top level 4)" if cfg.name == "euroc_mav" else ""),
+         "streams_per_gpu": streams, "frames_per_step": streams * frames_per_step, "feeds_per_step": frames_per_step,
+         "l2_policy": "every feed reads frames that were last touched a whole pool ago (pool >> 126 MB L2); no explicit flush"}
     if extra:
         d.update(extra)
     return d
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-# synthetic input: D distinct sequences per rank, stream s replays sequence s % D shifted by 5*(s // D) frames
+# synthetic input: D distinct sequences per rank, stream s replays sequence s % D shifted by 5*(s // D) frames.  A run walks
+# the pool forwards, then backwards (camera motion reversed), and so on: continuous motion from a bounded amount of memory.
 # ---------------------------------------------------------------------------------------------------------------------
-def make_frames(cfg, rank, streams, distinct, n_steps):
+def make_frames(cfg, rank, streams, distinct, n_pool):
     from uvio_b200.synth import SynthStereoStream
     distinct = max(1, min(distinct, streams))
     shift = 5
-    need = n_steps + shift * ((streams - 1) // distinct)
+    need = n_pool + shift * ((streams - 1) // distinct)
     seqs = []
     for d in range(distinct):
         s = SynthStereoStream(cfg.width, cfg.height, stream_id=1000 * rank + d, events=False)
         seqs.append([s.frame(k) for k in range(need)])
-    # frames[step][stream] = (left, right)
-    return [[seqs[s % distinct][k + shift * (s // distinct)] for s in range(streams)] for k in range(n_steps)]
+    return [[seqs[s % distinct][k + shift * (s // distinct)] for s in range(streams)] for k in range(n_pool)]
+
+
+def pool_index(t, n_pool):
+    """frame of the pool that feed number t reads: 0, 1, .., n-1, n-2, .., 1, 0, 1, .."""
+    if n_pool <= 1:
+        return 0
+    period = 2 * n_pool - 2
+    k = t % period
+    return k if k < n_pool else period - k
 
 
 class ClockSampler:
@@ -88,14 +105,14 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                       "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.p = None
 
     def stop(self):
         if self.p is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.12)
         self.p.terminate()
         try:
             out, _ = self.p.communicate(timeout=5)
@@ -120,20 +137,47 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
 
 
+_keep_alive = []
+
+
+def pinned_hugepage_buffer(nbytes):
+    """Host buffer the way a camera driver that wants the full PCIe rate allocates its frame ring: a
+    2 MiB-aligned anonymous mapping advised to transparent huge pages, touched, then cudaHostRegister'ed.  On this pool's
+    hosts such a buffer uploads 2-4x faster than a cudaHostAlloc one of the same size (tools/h2d_probe.py)."""
+    import torch
+    H = 2 << 20
+    size = (nbytes + H - 1) // H * H + H
+    m = mmap.mmap(-1, size, flags=mmap.MAP_PRIVATE | mmap.MAP_ANONYMOUS)
+    a = np.frombuffer(m, dtype=np.uint8)
+    off = (-a.ctypes.data) % H
+    try:
+        m.madvise(mmap.MADV_HUGEPAGE)
+    except Exception:
+        pass
+    a[:] = 0
+    v = a[off:off + nbytes]
+    r = torch.cuda.cudart().cudaHostRegister(v.ctypes.data, (nbytes + 4095) // 4096 * 4096, 0)
+    if int(r) != 0:
+        raise RuntimeError(f"cudaHostRegister failed: {r}")
+    _keep_alive.append((m, a))
+    return v
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------------
-def _frame_structs(track, base_ptr, n_steps, streams, h, w, mask_ptr, keep):
-    """UvioFrame[n_steps][streams] over a [T, S, 2, H, W] uint8 block starting at base_ptr (host or device memory)."""
+def _frame_structs(track, base_ptr, n_pool, streams, h, w, keep):
+    """UvioFrame[n_pool][streams] over a [n_pool, S, 2, H, W] uint8 block starting at base_ptr (host or device memory).
+    Masks are NULL (= all zeros, include/uvio_klt.h): a caller that passes real masks pays a host scan of each per feed."""
     ids = (C.c_size_t * 2)(0, 1)
     strides = (C.c_size_t * 2)(w, w)
     ws = (C.c_int * 2)(w, w)
     hs = (C.c_int * 2)(h, h)
-    masks = (C.c_void_p * 2)(mask_ptr, mask_ptr)
+    masks = (C.c_void_p * 2)(None, None)
     keep.extend([ids, strides, ws, hs, masks])
     img_bytes = h * w
     steps = []
-    for t in range(n_steps):
+    for t in range(n_pool):
         arr = (track.UvioFrame * streams)()
         for s in range(streams):
             p0 = base_ptr + ((t * streams + s) * 2) * img_bytes
@@ -153,45 +197,43 @@ def _frame_structs(track, base_ptr, n_steps, streams, h, w, mask_ptr, keep):
     return steps
 
 
-def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, obs_buf, counts, sample_clocks, prof_enable,
-             announce=True):
-    """warmup + timed steps on fresh trackers; returns (seconds max-over-ranks, n_obs, clocks, stats delta, profile).
-    announce: step t+1 is announced (uvio_klt_submit_batch: its upload and pre-processing start) right before step t is
-    fed, so every timed step issues exactly one upload inside the timed region -- the one of the step after it."""
+def _run_leg(track, L, cfg, device, streams, pool, warm_feeds, timed_feeds, dist, obs_buf, counts, sample_clocks, prof_enable, announce=True):
+    """warm_feeds + timed_feeds batched feeds on fresh trackers; returns (seconds max-over-ranks, n_obs, clocks, stats, profile).
+    announce: feed t+1 is announced (uvio_klt_submit_batch: its upload and pre-processing start) right before feed t is
+    issued, so every timed feed has exactly one upload inside the timed region -- the one of the feed after it."""
     import torch
     trackers = [track.make_tracker(cfg, device=device) for _ in range(streams)]
     hs = (C.c_void_p * streams)(*[t._h for t in trackers])
     cap = obs_buf.shape[1]
     n_obs = 0
-
+    n_pool = len(pool)
     if announce:
-        rc = L.uvio_klt_submit_batch(hs, step_frames[0], streams)
+        rc = L.uvio_klt_submit_batch(hs, pool[pool_index(0, n_pool)], streams)
         if rc != 0:
             raise RuntimeError(f"uvio_klt_submit_batch failed: {rc}")
+    call_s = [0.0, 0.0, 0.0]          # wall-clock of the three ABI calls of a feed, summed over the timed feeds
 
-    call_s = [0.0, 0.0, 0.0]          # wall-clock of the three ABI calls of a step, summed over the timed steps
-
-    def one(t):
+    def one(t, timed):
         t0 = time.perf_counter()
-        if announce and t + 1 < len(step_frames):
-            rc = L.uvio_klt_submit_batch(hs, step_frames[t + 1], streams)
+        if announce:
+            rc = L.uvio_klt_submit_batch(hs, pool[pool_index(t + 1, n_pool)], streams)
             if rc != 0:
                 raise RuntimeError(f"uvio_klt_submit_batch failed: {rc}")
         t1 = time.perf_counter()
-        rc = L.uvio_klt_feed_batch(hs, step_frames[t], streams)
+        rc = L.uvio_klt_feed_batch(hs, pool[pool_index(t, n_pool)], streams)
         if rc != 0:
             raise RuntimeError(f"uvio_klt_feed_batch failed: {rc} (cuda {L.uvio_klt_cuda_error(trackers[0]._h)})")
         t2 = time.perf_counter()
         L.uvio_klt_get_new_observations_batch(hs, streams, obs_buf.ctypes.data, cap, counts)
         t3 = time.perf_counter()
-        if t >= warmup:
+        if timed:
             call_s[0] += t1 - t0
             call_s[1] += t2 - t1
             call_s[2] += t3 - t2
         return int(sum(counts))
 
-    for t in range(warmup):
-        one(t)
+    for t in range(warm_feeds):
+        one(t, False)
     torch.cuda.synchronize(device)
     if dist is not None:
         dist.barrier()
@@ -201,8 +243,8 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
     clocks = ClockSampler(device) if sample_clocks else None
     L.uvio_klt_timer_start(device)
     t_wall = time.perf_counter()
-    for t in range(warmup, warmup + steps):
-        n_obs += one(t)
+    for t in range(warm_feeds, warm_feeds + timed_feeds):
+        n_obs += one(t, True)
     ms = C.c_float()
     L.uvio_klt_timer_stop(device, C.byref(ms))
     torch.cuda.synchronize(device)
@@ -219,45 +261,43 @@ def _run_leg(track, L, cfg, device, streams, step_frames, warmup, steps, dist, o
         dist.barrier()
     delta = {k: s1[k] - s0[k] for k in s0}
     passes = max(1.0, hostp.pop("lane_passes"))
-    delta["host_us_per_lane_pass"] = {k: round(v / passes, 1) for k, v in hostp.items()}
-    delta["lanes"] = passes / max(1, steps)
-    delta["call_us_per_step"] = {"submit_batch": round(1e6 * call_s[0] / steps, 1), "feed_batch": round(1e6 * call_s[1] / steps, 1),
-                                 "get_new_observations_batch": round(1e6 * call_s[2] / steps, 1)}
+    delta["host_us_per_group_pass"] = {k: round(v / passes, 1) for k, v in hostp.items()}
+    delta["groups"] = passes / max(1, timed_feeds)
+    delta["call_us_per_feed"] = {"submit_batch": round(1e6 * call_s[0] / timed_feeds, 1), "feed_batch": round(1e6 * call_s[1] / timed_feeds, 1),
+                                 "get_new_observations_batch": round(1e6 * call_s[2] / timed_feeds, 1)}
     for t in trackers:
         t.close()
     return sec, n_obs, clk, delta, prof, wall
 
 
-def _latency_leg(track, L, cfg, device, step_frames, n_frames, pause_s=0.0):
-    """One stream fed frame by frame through uvio_klt_feed (host frames and masks): wall-clock of the synchronous call.
-    pause_s > 0: frames arrive that far apart (a camera, not a file): the tracker uses the idle time for the detection
-    of the next feed, which then starts at its temporal LK."""
+def _latency_leg(track, L, cfg, device, pool, n_frames, pause_s=0.0):
+    """One stream fed frame by frame through uvio_klt_feed (host frames): wall-clock of the synchronous call."""
     t = track.make_tracker(cfg, device=device)
-    obs = np.zeros((1024,), track.OBS_DTYPE)
+    obs = np.zeros((4096,), track.OBS_DTYPE)
     n = C.c_int()
     lat = []
     for k in range(n_frames):
         if pause_s:
             time.sleep(pause_s)
         t0 = time.perf_counter()
-        rc = L.uvio_klt_feed(t._h, C.byref(step_frames[k][0]))
-        L.uvio_klt_get_new_observations(t._h, obs.ctypes.data, 1024, C.byref(n))
+        rc = L.uvio_klt_feed(t._h, C.byref(pool[pool_index(k, len(pool))][0]))
+        L.uvio_klt_get_new_observations(t._h, obs.ctypes.data, 4096, C.byref(n))
         lat.append(1e3 * (time.perf_counter() - t0))
         if rc != 0:
             raise RuntimeError(f"uvio_klt_feed failed: {rc}")
     t.close()
     lat = sorted(lat[5:])
     return {"p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(0.99 * len(lat)))], "frames": len(lat),
-            "what": "uvio_klt_feed + uvio_klt_get_new_observations, one euroc_mav stereo stream, pinned host frames and masks"
+            "what": f"uvio_klt_feed + uvio_klt_get_new_observations, one {cfg.name} stereo stream, pinned host frames"
                     + (f", frames {1e3 * pause_s:.0f} ms apart" if pause_s else ", back to back")}
 
 
 def run_ours(args):
     import torch
-    from uvio_b200 import build, track
+    from uvio_b200 import build, shard, track
     build.build()
     L = track.lib()
-    cfg = workload_config()
+    cfg = workload_config(args.config)
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -269,35 +309,38 @@ def run_ours(args):
         import torch.distributed as dist_mod
         dist_mod.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
         dist = dist_mod
-    S, W, K = args.streams, args.warmup, args.steps
-    T = W + K + 1          # one frame beyond the timed region: the last timed step announces (uploads) it
+    S = args.streams or BENCH_CONFIGS[args.config][1]
+    W, K, R, NP = args.warmup, args.steps, max(1, args.frames_per_step), max(2, args.pool)
     announce = os.environ.get("UVIO_BENCH_ANNOUNCE", "1") != "0"
     h, w = cfg.height, cfg.width
-    frames = make_frames(cfg, rank, S, args.distinct, T)
-    host = torch.empty((T, S, 2, h, w), dtype=torch.uint8).pin_memory()
-    hv = host.numpy()
-    for t in range(T):
+    frames = make_frames(cfg, rank, S, args.distinct, NP)
+    hv_flat = pinned_hugepage_buffer(NP * S * 2 * h * w)
+    hv = hv_flat.reshape(NP, S, 2, h, w)
+    for t in range(NP):
         for s in range(S):
             hv[t, s, 0] = frames[t][s][0]
             hv[t, s, 1] = frames[t][s][1]
     del frames
-    dev = host.to(f"cuda:{local}")
-    zero_mask = np.zeros((h, w), np.uint8)
+    dev = torch.from_numpy(hv).to(f"cuda:{local}")
     keep = []
-    dev_steps = _frame_structs(track, dev.data_ptr(), T, S, h, w, None, keep)
-    host_steps = _frame_structs(track, host.data_ptr(), T, S, h, w, zero_mask.ctypes.data, keep)
-    obs_buf = np.zeros((S, 1024), track.OBS_DTYPE)
+    dev_pool = _frame_structs(track, dev.data_ptr(), NP, S, h, w, keep)
+    host_pool = _frame_structs(track, hv.ctypes.data, NP, S, h, w, keep)
+    obs_buf = np.zeros((S, 4096), track.OBS_DTYPE)
     counts = (C.c_int * S)()
     # leg 1: frames resident in HBM; leg 2: end to end from pinned host memory (upload + results inside the timed region).
     # Both legs time only the dominant kernel (k_lk: two event records around each of its launches); leg 3 repeats leg 1
     # with every kernel bracketed by events to get the per-kernel shares -- its throughput is not reported.
     lk_only = 1 | ((1 << track.KERNEL_NAMES.index("k_lk")) << 1)
-    sec, n_obs, clk, st, prof, wall = _run_leg(track, L, cfg, local, S, dev_steps, W, K, dist, obs_buf, counts, True, lk_only, announce)
-    sec2, n_obs2, _clk2, st2, _prof2, wall2 = _run_leg(track, L, cfg, local, S, host_steps, W, K, dist, obs_buf, counts, False, lk_only, announce)
-    sec3, _n3, _clk3, st3, prof3, _wall3 = _run_leg(track, L, cfg, local, S, dev_steps, W, K, dist, obs_buf, counts, False, 1, announce)
-    lat = _latency_leg(track, L, cfg, local, host_steps, min(T, 60))
-    lat_paced = _latency_leg(track, L, cfg, local, host_steps, min(T, 60), pause_s=0.003)
-    total_frames = world * S * K
+    wf, tf = W * R, K * R
+    sec, n_obs, clk, st, prof, wall = _run_leg(track, L, cfg, local, S, dev_pool, wf, tf, dist, obs_buf, counts, True, lk_only, announce)
+    sec2, n_obs2, _c2, st2, _p2, wall2 = _run_leg(track, L, cfg, local, S, host_pool, wf, tf, dist, obs_buf, counts, False, lk_only, announce)
+    sec3, _n3, _c3, st3, prof3, _w3 = _run_leg(track, L, cfg, local, S, dev_pool, R, min(tf, 4 * R), dist, obs_buf, counts, False, 1, announce)
+    lat = _latency_leg(track, L, cfg, local, host_pool, 60)
+    lat_paced = _latency_leg(track, L, cfg, local, host_pool, 60, pause_s=0.003)
+    # the one collective of the path: run statistics all-gathered over NCCL / NVLink
+    gathered = shard.gather_stats(dist, {"frames": S * tf, "observations": n_obs, "seconds": sec, "launches": st["launches"],
+                                         "h2d_bytes": st2["h2d_bytes"], "d2h_bytes": st2["d2h_bytes"]}, device=f"cuda:{local}")
+    total_frames = world * S * tf
     value = total_frames / sec
     e2e = total_frames / sec2
     line = {
@@ -305,71 +348,142 @@ def run_ours(args):
         "ms_per_step": 1e3 * sec / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8 images, int32 FAST/LK inner products, fp32 LK normal equations, fp64 cornerSubPix/RANSAC",
         "data": "synthetic (uvio_b200.synth, seeded)",
-        "config": config_dict(cfg, S, {"latency_ms_per_batched_step": 1e3 * sec / K,
-                                        "single_stream_frame_latency_ms": lat,
-                                        "single_stream_frame_latency_ms_paced": lat_paced,
-                                        "observations_per_frame": n_obs / max(1, S * K)}),
+        "config": config_dict(cfg, S, R, {"ms_per_feed": 1e3 * sec / tf, "timed_region_s": sec,
+                                          "single_stream_frame_latency_ms": lat, "single_stream_frame_latency_ms_paced": lat_paced,
+                                          "observations_per_frame": n_obs / max(1, S * tf),
+                                          "pipeline": os.environ.get("UVIO_KLT_PIPELINE", "device"),
+                                          "masks": "NULL (documented as all zeros)"}),
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": st2["h2d_bytes"] / K,
-                "d2h_bytes_per_step": st2["d2h_bytes"] / K, "ms_per_step": 1e3 * sec2 / K,
-                "note": "uvio_klt_feed_batch + uvio_klt_get_new_observations_batch on pinned host frames and host masks"
-                        + ("; step t+1 is announced with uvio_klt_submit_batch before step t is fed, so its upload overlaps step t "
-                           "(exactly one upload of a step's frames inside the timed region per timed step)" if announce else "")},
+                "d2h_bytes_per_step": st2["d2h_bytes"] / K, "ms_per_step": 1e3 * sec2 / K, "ms_per_feed": 1e3 * sec2 / tf,
+                "note": "uvio_klt_feed_batch + uvio_klt_get_new_observations_batch on pinned host frames (2 MiB-aligned transparent-huge-page "
+                        "mapping, cudaHostRegister'ed)"
+                        + ("; feed t+1 is announced with uvio_klt_submit_batch before feed t is issued, so its upload overlaps feed t "
+                           "(exactly one upload of a feed's frames inside the timed region per timed feed)" if announce else "")},
         "gpu_launches": int(st["launches"]),
-        "host": {"lanes": st["lanes"], "resident_us_per_lane_pass": st["host_us_per_lane_pass"],
-                 "e2e_us_per_lane_pass": st2["host_us_per_lane_pass"],
-                 "resident_call_us_per_step": st["call_us_per_step"], "e2e_call_us_per_step": st2["call_us_per_step"]},
+        "host": {"groups": st["groups"], "resident_us_per_group_pass": st["host_us_per_group_pass"],
+                 "e2e_us_per_group_pass": st2["host_us_per_group_pass"],
+                 "resident_call_us_per_feed": st["call_us_per_feed"], "e2e_call_us_per_feed": st2["call_us_per_feed"]},
+        "stats_gather": {"backend": "nccl" if dist is not None else "none (1 rank)", "job": gathered["job"],
+                         "frames_per_rank": [r["frames"] for r in gathered["per_rank"]]},
         "clocks": clk,
     }
-    line["config"]["ms_per_step_with_all_kernels_bracketed_by_events"] = 1e3 * sec3 / K
-    return line, (prof, prof3, st3), st, K, S, cfg, rank, world, dist
+    line["config"]["ms_per_feed_with_all_kernels_bracketed_by_events"] = 1e3 * sec3 / max(1, min(tf, 4 * R))
+    return line, (prof, prof3, st3), st, tf, S, cfg, rank, world, dist
 
 
 # ---------------------------------------------------------------------------------------------------------------------
 # CPU arm: the cv2-driven restatement of the reference (oracle/) — the one place bench.py may execute oracle code
 # ---------------------------------------------------------------------------------------------------------------------
 def _cpu_worker(job):
-    """One independent stream on one host thread; returns (frames, seconds)."""
-    stream_id, n_warm, n_frames, cv_threads = job
+    """One independent stream on one host thread; returns (frames, seconds, seconds inside the OpenCV kernels or None)."""
+    stream_id, n_warm, n_frames, cv_threads, cfg_name, split = job
     import cv2
     cv2.setNumThreads(cv_threads)
     cv2.setRNGSeed(0)                                   # VioManager.cpp:66-67
-    from oracle.trackklt_cv2 import make_oracle
+    from oracle import trackklt_cv2 as T
     from uvio_b200.synth import SynthStereoStream
-    cfg = workload_config()
+    cfg = workload_config(cfg_name)
+    inside = [0.0]
+    if split:                                           # time spent inside the OpenCV kernels; the rest is the Python driver
+        def timed(fn):
+            def wrapped(*a, **k):
+                t0 = time.perf_counter()
+                try:
+                    return fn(*a, **k)
+                finally:
+                    inside[0] += time.perf_counter() - t0
+            return wrapped
+        for name in ("equalize", "build_pyramid", "fast_detect", "corner_subpix", "lk_track", "fundamental_ransac_mask"):
+            setattr(T, name, timed(getattr(T, name)))
+        T.Cam.undistort = timed(T.Cam.undistort)
     s = SynthStereoStream(cfg.width, cfg.height, stream_id=stream_id, events=False)
     frames = [s.frame(k) for k in range(n_warm + n_frames)]
     masks = [np.zeros((cfg.height, cfg.width), np.uint8)] * 2
-    o = make_oracle(cfg)
+    o = T.make_oracle(cfg)
     for k in range(n_warm):
         o.feed_new_camera(0.05 * k, [0, 1], list(frames[k]), masks)
+    inside[0] = 0.0
     t0 = time.perf_counter()
     for k in range(n_warm, n_warm + n_frames):
         o.feed_new_camera(0.05 * k, [0, 1], list(frames[k]), masks)
-    return n_frames, time.perf_counter() - t0
+    return n_frames, time.perf_counter() - t0, (inside[0] if split else None)
 
 
-def cpu_throughput(n_procs, n_frames, n_warm=10, cv_threads=1):
+def cpu_throughput(n_procs, n_frames, n_warm=10, cv_threads=1, cfg_name="euroc_mav", split=False):
     """Aggregate frames/s of n_procs independent streams, one process each (SURVEY 8(d) CPU baseline plan)."""
     import multiprocessing as mp
-    jobs = [(9000 + i, n_warm, n_frames, cv_threads) for i in range(n_procs)]
-    if n_procs == 1:
-        res = [_cpu_worker(jobs[0])]
-    else:
-        with mp.get_context("spawn").Pool(n_procs) as pool:
-            res = pool.map(_cpu_worker, jobs)
-    # streams run concurrently: aggregate = sum of per-stream rates
-    return sum(f / s for f, s in res), max(s for _f, s in res)
+    jobs = [(9000 + i, n_warm, n_frames, cv_threads, cfg_name, split) for i in range(n_procs)]
+    with mp.get_context("spawn").Pool(n_procs) as pool:      # always a child process: the wrappers of `split` stay there
+        res = pool.map(_cpu_worker, jobs)
+    return sum(f / s for f, s, _i in res), max(s for _f, s, _i in res), res
 
 
-def cpu_baseline_entry(n_frames):
+def c_restatement_seconds_per_frame(cfg, n=6):
+    """The no-Python cross-check: the plain-C restatement of every OpenCV routine on the path (oracle/stages.c),
+    single thread, on the work of one steady-state stereo frame: equalise + pyramid of both images, FAST on 5 of the 25 cells
+    per camera (a steady-state top-up), cornerSubPix of 30 corners, LK of 2 x num_features points."""
+    from oracle import cstages
+    from uvio_b200.synth import SynthStereoStream
+    s = SynthStereoStream(cfg.width, cfg.height, stream_id=77, events=False)
+    fr = [s.frame(k) for k in range(n + 1)]
+    sx, sy = cfg.width // cfg.grid_x, cfg.height // cfg.grid_y
+    rng = np.random.default_rng(1)
+    pts = np.c_[rng.uniform(20, cfg.width - 20, cfg.num_features), rng.uniform(20, cfg.height - 20, cfg.num_features)].astype(np.float32)
+    prev = None
+    t_total = 0.0
+    for k in range(n + 1):
+        t0 = time.perf_counter()
+        cur = []
+        for img in fr[k]:
+            if cfg.histogram == 2:
+                eq = cstages.clahe(img)
+            elif cfg.histogram == 1:
+                eq = cstages.equalize_hist(img)
+            else:
+                eq = img
+            cur.append(cstages.build_pyramid(eq, cfg.pyr_levels))
+        for lv in cur:
+            for c in range(5):
+                gx, gy = c % cfg.grid_x, c // cfg.grid_x
+                cstages.fast(np.ascontiguousarray(lv[0][gy * sy:(gy + 1) * sy, gx * sx:(gx + 1) * sx]), cfg.fast_threshold)
+            cstages.corner_subpix(lv[0], pts[:15])
+        if prev is not None:
+            for a, b in zip(prev, cur):
+                cstages.lk(a, b, pts, pts)
+        dt = time.perf_counter() - t0
+        if prev is not None:
+            t_total += dt
+        prev = cur
+    return t_total / n
+
+
+def cpu_baseline_entry(n_frames, cfg_name):
     import cv2
     cores = os.cpu_count() or 1
+    cfg = workload_config(cfg_name)
     # reference default: one tracker with cv::setNumThreads(4) (VioManagerOptions.h:412)
-    fps, sec = cpu_throughput(1, n_frames, cv_threads=4)
-    return {"value": fps, "unit": UNIT, "cores": 4, "kind": "port",
-            "sample": f"{n_frames} stereo frames of one synthetic stream after 10 warm-up frames, cv2 {cv2.__version__} (IPP off), "
-                      f"cv::setNumThreads(4) as the reference default; host has {cores} logical cores; {sec:.1f} s of CPU work",
-            "what": "oracle/trackklt_cv2.py: the reference's TrackKLT control flow restated line by line over the real OpenCV kernels"}
+    fps, sec, res = cpu_throughput(1, n_frames, cv_threads=4, cfg_name=cfg_name, split=True)
+    inside = res[0][2]
+    entry = {"value": fps, "unit": UNIT, "cores": 4, "kind": "port",
+             "sample": f"{n_frames} stereo frames of one synthetic {cfg.name} stream after 10 warm-up frames, cv2 {cv2.__version__} (IPP off), "
+                       f"cv::setNumThreads(4) as the reference default; host has {cores} logical cores; {sec:.1f} s of CPU work",
+             "what": "oracle/trackklt_cv2.py: the reference's TrackKLT control flow restated line by line over the real OpenCV kernels",
+             "python_driver_share": round(1.0 - inside / sec, 3),
+             "python_driver_note": "share of the sample's wall time spent OUTSIDE the OpenCV kernels (the restated control flow in Python): "
+                                   "the C++ reference is at most this much faster than the port"}
+    try:
+        fps_all, sec_all, _r = cpu_throughput(1, max(30, n_frames // 2), cv_threads=-1, cfg_name=cfg_name)
+        entry["all_threads"] = {"value": fps_all, "unit": UNIT, "what": "the same stream with cv::setNumThreads(-1) (all cores)", "cores": cores}
+    except Exception as e:      # noqa: BLE001
+        entry["all_threads"] = {"error": str(e)}
+    try:
+        spf = c_restatement_seconds_per_frame(cfg)
+        entry["c_restatement"] = {"value": 1.0 / spf, "unit": UNIT, "cores": 1,
+                                  "what": "oracle/stages.c (plain C, no Python, no OpenCV, one thread) on the kernels of one steady-state stereo "
+                                          "frame: equalise + pyramid x2, FAST on 5 cells per camera, cornerSubPix of 30 corners, LK of 2 x N points"}
+    except Exception as e:      # noqa: BLE001
+        entry["c_restatement"] = {"error": str(e)}
+    return entry
 
 
 def run_reference(args):
@@ -378,20 +492,23 @@ def run_reference(args):
     if rank != 0:
         return None
     import cv2
-    cfg = workload_config()
+    cfg = workload_config(args.config)
     cores = os.cpu_count() or 1
     procs = max(1, min(cores, 64))
-    per_step = 4                                       # frames per stream per "step" (bounded sample)
+    per_step = 4                                       # frames per stream per "step" (bounded sample of a step's frames)
     n_frames = max(8, per_step * args.steps)
     n_warm = max(3, per_step * args.warmup)
-    fps, sec = cpu_throughput(procs, n_frames, n_warm=n_warm, cv_threads=1)
+    fps, sec, _res = cpu_throughput(procs, n_frames, n_warm=n_warm, cv_threads=1, cfg_name=args.config)
     sample = (f"{procs} independent streams x {n_frames} stereo frames ({per_step} per step) after {n_warm} warm-up frames, one process "
               f"per stream, cv2 {cv2.__version__} single-threaded per process, IPP off")
+    S = args.streams or BENCH_CONFIGS[args.config][1]
     return {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * sec / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8 / fp32 / fp64 (OpenCV CPU)", "data": "synthetic (uvio_b200.synth, seeded)",
-        "config": config_dict(cfg, procs, {"note": "CPU arm: streams_per_gpu = concurrent host processes"}),
+        "config": config_dict(cfg, S, max(1, args.frames_per_step),
+                              {"note": f"CPU arm: {procs} concurrent host processes stand in for the streams; each step is a bounded sample "
+                                       f"({per_step} frames per process) of the GPU arm's step"}),
         "cpu_baseline": {"value": fps, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -399,28 +516,13 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-# roofline of the dominant kernel (CUDA events recorded around every launch inside the library, leg 1)
+# rooflines.  k_lk (the kernel with the largest share of GPU time) is bound by instruction issue, not by HBM: its entry is
+# warp-instructions per second against 148 SMs x 4 schedulers x SM clock, instructions per feature taken from the committed
+# ncu capture of the same kernel, duration measured live with CUDA events around every launch of the timed region.  The
+# image-wide pass (k_preprocess) is the HBM-shaped kernel of the path: roofline_image_passes.
 # ---------------------------------------------------------------------------------------------------------------------
-def roofline_entry(profs, stats, K, S, cfg):
-    prof_timed, prof_all, stats_all = profs
-    name_all = max(prof_all.items(), key=lambda kv: kv[1][0])[0]
-    in_timed = prof_timed.get(name_all, (0.0, 0))[1] > 0
-    prof = dict(prof_all)
-    if in_timed:
-        prof[name_all] = prof_timed[name_all]          # the dominant kernel's duration comes from the timed region
-    else:
-        stats = stats_all
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak = float(json.load(open(peaks_path))["hbm_gbs"])
-        peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)"
-    else:
-        peak, peak_src = 6650.0, "B200_PROFILING.md fallback"
-    total_ms = sum(ms for ms, _n in prof_all.values())
-    name, (ms, launches) = name_all, prof[name_all]
-    P = cfg.width * cfg.height
+def _levels(cfg):
     lv = [(cfg.width, cfg.height)]
-    from uvio_b200.track import lib  # noqa: F401  (levels follow cv::buildOpticalFlowPyramid's stop rule)
     w, h = cfg.width, cfg.height
     for _ in range(cfg.pyr_levels):
         nw, nh = (w + 1) // 2, (h + 1) // 2
@@ -428,58 +530,91 @@ def roofline_entry(profs, stats, K, S, cfg):
             break
         w, h = nw, nh
         lv.append((w, h))
+    return lv
+
+
+def _load_profile(name):
+    for rnd in ("r2", "r1"):
+        p = os.path.join(ROOT, "profiles", f"{rnd}_{name}")
+        if os.path.exists(p):
+            return json.load(open(p)), os.path.relpath(p, ROOT)
+    return None, None
+
+
+def roofline_entry(profs, stats, feeds, S, cfg, clk):
+    prof_timed, prof_all, stats_all = profs
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak_hbm = float(json.load(open(peaks_path))["hbm_gbs"])
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)"
+    else:
+        peak_hbm, peak_src = 6650.0, "B200_PROFILING.md fallback"
+    total_ms = sum(ms for ms, _n in prof_all.values())
+    share = {k: round(v[0] / total_ms, 4) for k, v in prof_all.items() if total_ms and v[0] > 0}
+    lv = _levels(cfg)
+    P = cfg.width * cfg.height
     sig = sum(a * b for a, b in lv)
-    imgs = 2 * S * K
-    alg = {                                             # algorithmic bytes over the whole timed leg
-        "k_hist": imgs * P, "k_lut_apply": imgs * 2 * P, "k_clahe_tiles": imgs * P, "k_clahe_apply": imgs * 2 * P,
-        "k_pyrdown": imgs * ((sig - lv[-1][0] * lv[-1][1]) + (sig - P)),
-        "k_preprocess": imgs * (3 * P + (sig - lv[-1][0] * lv[-1][1]) + (sig - P)),   # hist read + LUT read/write + pyramid read/write
-        "k_fast": stats["fast_pixels"],
-        "k_subpix": None,
-        "k_lk": 324 * stats["lk_point_levels"] + 256 * stats["lk_iterations"],
-        "k_ransac": None,
-    }[name]
-    share = {k: (v[0] / total_ms if total_ms else 0.0) for k, v in prof_all.items()}
-    # the image-wide pass (north_star: "HBM GB/s against the HBM roofline for the image-wide passes"): k_preprocess, timed in the
-    # leg that brackets every kernel; with announced steps one launch holds all images of a step
+    # ---- dominant kernel -------------------------------------------------------------------------------------------------
+    name = max(prof_all.items(), key=lambda kv: kv[1][0])[0]
+    ms, launches = prof_timed.get(name, (0.0, 0))
+    in_timed = launches > 0
+    if not in_timed:
+        ms, launches = prof_all[name]
+    entry = {"kernel": name, "launches": launches, "avg_launch_ms": ms / max(1, launches),
+             "kernel_time_share_of_gpu_time": share, "gpu_busy_ms_per_feed": total_ms / max(1, prof_all[name][1] / 2 if name == "k_lk" else 1),
+             "timing": ("CUDA events around every launch of this kernel inside the timed region (resident leg), on the launching streams; "
+                        "the shares come from a separate short leg with every kernel bracketed") if in_timed else
+                       "separate profiling leg (the kernel was not bracketed in the timed region)"}
+    if name == "k_lk":
+        cap, cap_path = _load_profile("lk_ncu.json")
+        feats = stats["lk_point_levels"] / max(1, len(lv))                      # features tracked in the timed leg
+        sm_mhz = (clk or {}).get("sm_mhz") or 1965.0
+        peak = 148 * 4 * sm_mhz * 1e6 / 1e9                                     # G warp-instructions / s
+        if cap:
+            inst = cap["smsp__inst_executed_sum"] / cap["features_in_launch"] * feats
+            ach = inst / (ms / 1e3) / 1e9
+            entry.update({"bound": "issue", "unit": "G warp-inst/s", "achieved": ach, "peak": peak, "frac": ach / peak,
+                          "peak_source": f"148 SMs x 4 schedulers x {sm_mhz:.0f} MHz (SM clock sampled during the timed region)",
+                          "warp_instructions_per_feature": cap["smsp__inst_executed_sum"] / cap["features_in_launch"],
+                          "instructions_source": cap_path + ": " + cap.get("capture", ""),
+                          "fp32_pipe_utilisation": cap.get("fma_pipe_utilisation"), "alu_pipe_utilisation": cap.get("alu_pipe_utilisation"),
+                          "ncu_issue_slot_utilisation": cap.get("issue_active"), "ncu_duration_us": cap.get("duration_us"),
+                          "traffic": (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["features_in_launch"] * feats / max(1, launches),
+                          "algorithmic_bytes_per_launch": (324 * stats["lk_point_levels"] + 256 * stats["lk_iterations"]) / max(1, launches),
+                          "features_per_launch": feats / max(1, launches),
+                          "note": "LK is an L2 / shared-memory gather with ordered fp32 accumulation: bound by instruction issue, not by HBM "
+                                  "(traffic = DRAM bytes per launch scaled from the capture; algorithmic bytes = 324 B per point-level + 256 B "
+                                  "per iteration, SURVEY 8(d), for reference)"})
+        else:
+            entry.update({"bound": "issue", "achieved": None, "frac": None, "note": "no ncu capture of k_lk under profiles/"})
+    else:
+        imgs = 2 * S * feeds
+        alg = {"k_preprocess": imgs * (3 * P + (sig - lv[-1][0] * lv[-1][1]) + (sig - P)), "k_fast": stats["fast_pixels"]}.get(name)
+        if alg and ms > 0:
+            ach = alg / (ms / 1e3) / 1e9
+            entry.update({"bound": "hbm", "unit": "GB/s", "achieved": ach, "peak": peak_hbm, "peak_source": peak_src, "frac": ach / peak_hbm,
+                          "traffic": None, "algorithmic_bytes_per_launch": alg / max(1, launches)})
+        else:
+            entry.update({"bound": "latency", "achieved": None, "frac": None,
+                          "note": "the dominant kernel is latency-bound per-tracker work with no meaningful byte or flop count"})
+    # ---- the image-wide pass ------------------------------------------------------------------------------------------------
     image_pass = None
     pms, pl = prof_all.get("k_preprocess", (0.0, 0))
     if pl > 0 and pms > 0:
+        feeds_all = max(1, prof_all["k_lk"][1] // 2) if prof_all.get("k_lk", (0, 0))[1] else feeds
+        imgs = 2 * S * feeds_all
         per_img = 3 * P + (sig - lv[-1][0] * lv[-1][1]) + (sig - P)
+        if cfg.histogram == 2:
+            per_img += 3 * P                                                    # the CLAHE passes in front of it
         ach = imgs * per_img / (pms / 1e3) / 1e9
-        image_pass = {"bound": "hbm", "kernel": "k_preprocess", "unit": "GB/s", "achieved": ach, "peak": peak, "frac": ach / peak,
-                      "launches": pl, "avg_launch_ms": pms / pl, "images_per_launch": imgs / pl,
+        image_pass = {"bound": "hbm", "kernel": "k_preprocess", "unit": "GB/s", "achieved": ach, "peak": peak_hbm, "peak_source": peak_src,
+                      "frac": ach / peak_hbm, "launches": pl, "avg_launch_ms": pms / pl, "images_per_launch": imgs / pl,
                       "algorithmic_bytes_per_image": per_img, "traffic": None,
                       "timing": "CUDA events around every launch, profiling leg (every kernel bracketed), on the launching stream"}
-        tp = os.path.join(ROOT, "profiles", "r1_preprocess_traffic.json")
-        if os.path.exists(tp):
-            cap = json.load(open(tp))
+        cap, cap_path = _load_profile("preprocess_traffic.json")
+        if cap:
             image_pass["traffic"] = (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["images_in_launch"] * imgs / pl
-            image_pass["traffic_source"] = cap["capture"]
-    entry = {"bound": "hbm", "kernel": name, "unit": "GB/s", "peak": peak, "peak_source": peak_src, "traffic": None,
-             "launches": launches, "avg_launch_ms": ms / max(1, launches),
-             "kernel_time_share_of_gpu_time": {k: round(v, 4) for k, v in share.items()},
-             "gpu_busy_ms_per_step": total_ms / K,
-             "timing": ("CUDA events around every launch of this kernel inside the timed region (resident leg), on the launching "
-                        "streams; the shares come from a separate leg with every kernel bracketed") if in_timed else
-                       "separate profiling leg (the kernel was not bracketed in the timed region)"}
-    if alg is None or ms <= 0:
-        entry.update({"achieved": None, "frac": None, "note": "dominant kernel is latency-bound serial work with no meaningful byte count"})
-    else:
-        ach = alg / (ms / 1e3) / 1e9
-        entry.update({"achieved": ach, "frac": ach / peak, "algorithmic_bytes_per_launch": alg / max(1, launches)})
-        tpath = os.path.join(ROOT, "profiles", "r1_lk_traffic.json")
-        if name == "k_lk" and os.path.exists(tpath):
-            cap = json.load(open(tpath))
-            per_feature = (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["features_in_launch"]
-            feats = stats["lk_point_levels"] / max(1, len(lv)) / max(1, launches)      # features per launch in this run
-            entry["traffic"] = per_feature * feats
-            entry["traffic_source"] = (f"{cap['capture']}: {per_feature:.0f} DRAM bytes per feature, scaled to this run's "
-                                       f"{feats:.0f} features per launch")
-        if name == "k_lk":
-            entry["note"] = ("LK is an L2/shared-memory gather + ordered fp32 accumulation, not an HBM stream: algorithmic bytes = 324 B "
-                             "per point-level template footprint + 256 B per iteration J footprint (SURVEY 8(d)); the fraction is "
-                             "reported against the HBM peak only because the contract asks for one")
+            image_pass["traffic_source"] = cap_path + ": " + cap.get("capture", "")
     entry["image_pass"] = image_pass
     return entry
 
@@ -491,12 +626,12 @@ def main():
         if line is not None:
             print(json.dumps(line), flush=True)
         return
-    line, prof, st, K, S, cfg, rank, world, dist = run_ours(args)
+    line, prof, st, feeds, S, cfg, rank, world, dist = run_ours(args)
     if rank == 0:
-        line["roofline"] = roofline_entry(prof, st, K, S, cfg)
+        line["roofline"] = roofline_entry(prof, st, feeds, S, cfg, line.get("clocks"))
         line["roofline_image_passes"] = line["roofline"].pop("image_pass")
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_entry(args.cpu_frames)
+            line["cpu_baseline"] = cpu_baseline_entry(args.cpu_frames, args.config)
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line), flush=True)

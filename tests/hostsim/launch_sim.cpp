@@ -144,18 +144,29 @@ cudaError_t launch_ransac(cudaStream_t, const RansacJob *jobs, int njobs, int ma
 }
 
 // ---- device-side bookkeeping (track_body.h) with one lane ----------------------------------------------------------------------
-cudaError_t launch_dv_occupancy(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+struct SimSmem {
+  std::vector<unsigned long long> a, b;
+  std::vector<float> p;
+  DvSmem get(int P) {
+    a.assign((size_t)P, 0xA5A5A5A5A5A5A5A5ull);
+    b.assign((size_t)P, 0xA5A5A5A5A5A5A5A5ull);
+    p.assign(2 * (size_t)P, -1e30f);
+    return DvSmem{a.data(), b.data(), p.data()};
+  }
+};
+cudaError_t launch_dv_occupancy(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (getenv("UVIO_DV_TRACE")) fprintf(stderr, "[sim] device-side pipeline: %d trackers\n", n_heads);
+  SimSmem sm;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_occupancy(GroupSeq(), units[u], X);
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_occupancy(GroupSeq(), units[u], X, sm.get(max_p));
   return 0;
 }
-cudaError_t launch_dv_fast(cudaStream_t, const DvGlobals &X, const PyrDesc *pyr_tab, int n_slots, int, int) {
+cudaError_t launch_dv_fast(cudaStream_t, const DvGlobals &X, const PyrDesc *pyr_tab, int, int, int) {
   GroupSeq g;
   FastSmem s;
-  for (int slot = 0; slot < n_slots; slot++) {
+  for (int a = 0; a < *X.fast_n_active; a++) {
+    const int slot = X.fast_active[a];
     const FastJob job = X.fast_jobs[slot];
-    if (job.w == 0) continue;
     for (int ty = 0; ty < job.h; ty += FT_H)
       for (int tx = 0; tx < job.w; tx += FT_W) fast_tile(g, s, pyr_tab[job.img].lv[0], job, tx, ty, job.threshold, X.fast_out, &X.fast_cnt[slot]);
   }
@@ -168,19 +179,23 @@ cudaError_t launch_dv_topk(cudaStream_t, const DvUnit *units, int n_units, int, 
       for (int r = 0; r < units[u].C; r++) dv_topk(GroupSeq(), units[u], X, side, r, buf.data(), (int)buf.size());
   return 0;
 }
-cudaError_t launch_dv_select(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+cudaError_t launch_dv_select(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
+  SimSmem sm;
+  *X.fast_n_active = 0;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_select(GroupSeq(), units[u], X);
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_select(GroupSeq(), units[u], X, sm.get(max_p));
   return 0;
 }
-cudaError_t launch_dv_assign(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+cudaError_t launch_dv_assign(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
+  SimSmem sm;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_assign(GroupSeq(), units[u], X);
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_assign(GroupSeq(), units[u], X, sm.get(max_p));
   return 0;
 }
-cudaError_t launch_dv_merge(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+cudaError_t launch_dv_merge(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
+  SimSmem sm;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_merge(GroupSeq(), units[u], X);
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_merge(GroupSeq(), units[u], X, sm.get(max_p));
   return 0;
 }
 

@@ -208,6 +208,7 @@ struct PreBuffers {              // job lists of one upload round (a lane's, or 
 struct Lane {
   Lane() {
     sp_items.prefer_mapped = lk_items.prefer_mapped = rs_jobs.prefer_mapped = true;
+    dv_units.prefer_mapped = dv_heads.prefer_mapped = true;   // read in place: a copy would queue behind the frames on the copy engine
     const char *e = getenv("UVIO_KLT_FAST_MAPPED");   // the FAST list is read by every tile block of a cell: copied (measured)
     fast_jobs.prefer_mapped = e && e[0] == '1';
   }
@@ -302,6 +303,9 @@ struct Lane {
   DevVec<FastJob> dv_fast_jobs;
   DevVec<uint32_t> dv_fast_out;
   DevVec<unsigned> dv_fast_cnt;
+  DevVec<int> dv_fast_active;    // [slots] + the counter in its last word
+  cudaStream_t lk_stream = nullptr;   // the issue-bound LK launches of the device-side pipeline run at low priority, so that the
+  cudaEvent_t lk_go = nullptr, lk_done = nullptr;   // latency-bound kernels of another group get SM slots as soon as LK blocks retire
   DevVec<SubpixItem> dv_sp_items;
   DevVec<float> dv_sp_out;
   DevVec<LkItem> dv_lk1_items, dv_lk2_items;
@@ -319,6 +323,9 @@ struct Lane {
     if (stream) cudaStreamDestroy(stream);
     if (up_stream) cudaStreamDestroy(up_stream);
     if (up_done) cudaEventDestroy(up_done);
+    if (lk_stream) cudaStreamDestroy(lk_stream);
+    if (lk_go) cudaEventDestroy(lk_go);
+    if (lk_done) cudaEventDestroy(lk_done);
   }
 };
 
@@ -716,7 +723,10 @@ Context *context_for_device(int device, int *err) {
     // the rounds a feed waits for run ahead of the pre-processing of frames that are only needed later
     if ((e = cudaStreamCreateWithPriority(&ln->stream, cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&ln->up_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&ln->up_done, cudaEventDisableTiming)) != cudaSuccess) {
+        (e = cudaEventCreateWithFlags(&ln->up_done, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&ln->lk_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&ln->lk_go, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&ln->lk_done, cudaEventDisableTiming)) != cudaSuccess) {
       if (err) *err = (int)e;
       return nullptr;
     }
@@ -2051,7 +2061,7 @@ int Pass::device_feed() {
       U.size_x = geom.size_x; U.size_y = geom.size_y; U.per_cell = geom.per_cell;
       U.P = D.P; U.C = D.C; U.K = D.K;
       U.job_base = job_slots; U.fast_base = (int)fast_words; U.cell_cap = D.cell_cap;
-      U.sp_base = sp_slots; U.lk_base = lk_slots; U.rs_base = 2 * k;
+      U.sp_base = sp_slots; U.spr_base = -1 - sp_slots; U.lk_base = lk_slots; U.rs_base = 2 * k;   // spr_base is fixed up below
       U.currid = D.currid;
       U.h_currid = D.m_currid;
       for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
@@ -2081,7 +2091,7 @@ int Pass::device_feed() {
       *um.h_n_obs = 0;
       job_slots += 2 * D.C;
       fast_words += 2 * (size_t)D.C * D.cell_cap;
-      sp_slots += 2 * D.C * D.K;
+      sp_slots += D.C * D.K;
       lk_slots += 2 * D.P;
       max_c = std::max(max_c, D.C);
       max_p = std::max(max_p, D.P);
@@ -2095,6 +2105,10 @@ int Pass::device_feed() {
       k++;
     }
   }
+  // sub-pixel slots: the left corners of every unit first (they are also the stereo-LK slots), then the right corners
+  for (int k = 0; k < nu; k++) ctx->dv_units.h[k].spr_base = sp_slots + (-1 - ctx->dv_units.h[k].spr_base);
+  const int spl_slots = sp_slots;
+  sp_slots *= 2;
   // masks with a non-zero pixel are needed on the device (occupancy, cell selection, merge)
   for (int i = 0; i < n; i++) {
     FeedRequest &rq = *reqs[i];
@@ -2108,11 +2122,12 @@ int Pass::device_feed() {
   CU_TRY(ctx->dv_fast_jobs.reserve((size_t)job_slots));
   CU_TRY(ctx->dv_fast_cnt.reserve((size_t)job_slots, true));
   CU_TRY(ctx->dv_fast_out.reserve(fast_words));
+  CU_TRY(ctx->dv_fast_active.reserve((size_t)job_slots + 1, true));
   CU_TRY(ctx->dv_sp_items.reserve((size_t)sp_slots));
   CU_TRY(ctx->dv_sp_out.reserve(2 * (size_t)sp_slots));
-  CU_TRY(ctx->dv_lk1_items.reserve((size_t)sp_slots));
-  CU_TRY(ctx->dv_lk1_out.reserve((size_t)sp_slots));
-  CU_TRY(ctx->dv_lk1_status.reserve((size_t)sp_slots));
+  CU_TRY(ctx->dv_lk1_items.reserve((size_t)spl_slots));
+  CU_TRY(ctx->dv_lk1_out.reserve((size_t)spl_slots));
+  CU_TRY(ctx->dv_lk1_status.reserve((size_t)spl_slots));
   CU_TRY(ctx->dv_lk2_items.reserve((size_t)lk_slots));
   CU_TRY(ctx->dv_lk2_out.reserve((size_t)lk_slots));
   CU_TRY(ctx->dv_lk2_status.reserve((size_t)lk_slots));
@@ -2123,6 +2138,7 @@ int Pass::device_feed() {
   CU_TRY(ctx->dv_p1n.reserve(2 * (size_t)lk_slots));
   DvGlobals X;
   X.fast_jobs = ctx->dv_fast_jobs.d; X.fast_out = ctx->dv_fast_out.d; X.fast_cnt = ctx->dv_fast_cnt.d;
+  X.fast_active = ctx->dv_fast_active.d; X.fast_n_active = ctx->dv_fast_active.d + ctx->dv_fast_active.cap - 1;
   X.sp_items = ctx->dv_sp_items.d; X.sp_out = ctx->dv_sp_out.d;
   X.lk1_items = ctx->dv_lk1_items.d; X.lk1_out = ctx->dv_lk1_out.d; X.lk1_status = ctx->dv_lk1_status.d;
   X.lk2_items = ctx->dv_lk2_items.d; X.lk2_out = ctx->dv_lk2_out.d;
@@ -2142,20 +2158,25 @@ int Pass::device_feed() {
     if (any_first) CU_TRY(wait_new_frames());   // first frames detect on the frame that is being uploaded (TrackKLT.cpp:110, :221)
     const DvUnit *U = ctx->dv_units.d;
     const DvHead *H = ctx->dv_heads.d;
-    CU_TRY(launch_dv_occupancy(st, U, H, nheads, X));
+    CU_TRY(launch_dv_occupancy(st, U, H, nheads, X, max_p));
     CU_TRY(launch_dv_fast(st, X, dev->pyr_dev.d, job_slots, max_cw, max_ch));
     CU_TRY(launch_dv_topk(st, U, nu, max_c, X));
-    CU_TRY(launch_dv_select(st, U, H, nheads, X));
+    CU_TRY(launch_dv_select(st, U, H, nheads, X, max_p));
     CU_TRY(launch_subpix(st, ctx->dv_sp_items.d, sp_slots, dev->pyr_dev.d, ctx->sp_mask.d, ctx->dv_sp_out.d, nullptr));
-    CU_TRY(launch_lk(st, ctx->dv_lk1_items.d, sp_slots, dev->pyr_dev.d, ctx->dv_sp_out.d, 30, 0.01, ctx->dv_lk1_out.d, ctx->dv_lk1_status.d,
+    CU_TRY(launch_lk(st, ctx->dv_lk1_items.d, spl_slots, dev->pyr_dev.d, ctx->dv_sp_out.d, 30, 0.01, ctx->dv_lk1_out.d, ctx->dv_lk1_status.d,
                      ctx->dv_lk1_out.d, ctx->dv_lk1_status.d));
-    CU_TRY(launch_dv_assign(st, U, H, nheads, X));
+    CU_TRY(launch_dv_assign(st, U, H, nheads, X, max_p));
     if (!any_first) CU_TRY(wait_new_frames());  // the temporal LK reads the new pyramids
-    CU_TRY(launch_lk(st, ctx->dv_lk2_items.d, lk_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
+    // the temporal LK (the bulk of the feed's instructions) on the lane's low-priority stream, fenced by two events
+    CU_TRY(cudaEventRecord(ctx->lk_go, st));
+    CU_TRY(cudaStreamWaitEvent(ctx->lk_stream, ctx->lk_go, 0));
+    CU_TRY(launch_lk(ctx->lk_stream, ctx->dv_lk2_items.d, lk_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
                      ctx->dv_lk2_out.d, ctx->dv_lk2_status.d));
+    CU_TRY(cudaEventRecord(ctx->lk_done, ctx->lk_stream));
+    CU_TRY(cudaStreamWaitEvent(st, ctx->lk_done, 0));
     CU_TRY(launch_ransac(st, ctx->dv_rs_jobs.d, 2 * nu, max_p, ctx->dv_lk2_items.d, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, dev->cam_dev.d,
                          ctx->dv_p0n.d, ctx->dv_p1n.d, ctx->dv_p1n.d, ctx->dv_rs_mask.d, ctx->dv_rs_mask_raw.d));
-    CU_TRY(launch_dv_merge(st, U, H, nheads, X));
+    CU_TRY(launch_dv_merge(st, U, H, nheads, X, max_p));
     ctx->stats[1] += 10;
   } else {
     CU_TRY(wait_new_frames());

@@ -79,11 +79,13 @@ __device__ __forceinline__ unsigned long long fdb_cas64(unsigned long long *p, u
 __device__ __forceinline__ void fdb_min(int *p, int v) { atomicMin(p, v); }
 __device__ __forceinline__ void fdb_max(int *p, int v) { atomicMax(p, v); }
 __device__ __forceinline__ void fdb_add(int *p, int v) { atomicAdd(p, v); }
+__device__ __forceinline__ int fdb_add_ret(int *p, int v) { return atomicAdd(p, v); }
 #else
 inline unsigned long long fdb_cas64(unsigned long long *p, unsigned long long cmp, unsigned long long v) { unsigned long long o = *p; if (o == cmp) *p = v; return o; }
 inline void fdb_min(int *p, int v) { if (v < *p) *p = v; }
 inline void fdb_max(int *p, int v) { if (v > *p) *p = v; }
 inline void fdb_add(int *p, int v) { *p += v; }
+inline int fdb_add_ret(int *p, int v) { int o = *p; *p += v; return o; }
 #endif
 
 // loads of words other lanes of the block update with atomics in the same kernel: read at L2, never a stale L1 line

@@ -532,18 +532,29 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
 constexpr int DV_THREADS = 256;
 constexpr int DV_TOPK_SMEM = 4096;   // corner words a cell's top-K block sorts in shared memory (more: in the job's own global region)
 
-__global__ void __launch_bounds__(DV_THREADS) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X) {
-  const DvHead h = heads[blockIdx.x];
-  for (int u = h.first; u < h.first + h.count; u++) dv_occupancy(GroupBlock(), units[u], X);
+// dynamic shared memory of the bookkeeping kernels: two id lists and one point list of P entries each (DvSmem)
+__device__ __forceinline__ DvSmem dv_smem(int P) {
+  extern __shared__ __align__(16) unsigned long long dv_dyn[];
+  DvSmem sm;
+  sm.ids0 = dv_dyn;
+  sm.ids1 = dv_dyn + P;
+  sm.pts = (float *)(dv_dyn + 2 * P);
+  return sm;
 }
 
-// FAST over the job slots the occupancy kernel filled: a fixed grid walks (job, tile) pairs; unused slots have w == 0
-__global__ void __launch_bounds__(256) k_dv_fast(DvGlobals X, const PyrDesc *pyr_tab, int n_slots, int max_tiles) {
+__global__ void __launch_bounds__(DV_THREADS) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
+  const DvHead h = heads[blockIdx.x];
+  for (int u = h.first; u < h.first + h.count; u++) dv_occupancy(GroupBlock(), units[u], X, dv_smem(P));
+}
+
+// FAST over the cells the occupancy kernel listed: a fixed grid walks (active job, tile) pairs
+__global__ void __launch_bounds__(256) k_dv_fast(DvGlobals X, const PyrDesc *pyr_tab, int max_tiles) {
   __shared__ FastSmem s;
-  for (int w = blockIdx.x; w < n_slots * max_tiles; w += gridDim.x) {
-    const int slot = w / max_tiles, tile = w - slot * max_tiles;
+  const int n_active = *X.fast_n_active;
+  for (int w = blockIdx.x; w < n_active * max_tiles; w += gridDim.x) {
+    const int a = w / max_tiles, tile = w - a * max_tiles;
+    const int slot = X.fast_active[a];
     const FastJob job = X.fast_jobs[slot];
-    if (job.w == 0) continue;
     const int tiles_x = (job.w + FT_W - 1) / FT_W, tiles_y = (job.h + FT_H - 1) / FT_H;
     if (tile >= tiles_x * tiles_y) continue;
     fast_tile(GroupBlock(), s, pyr_tab[job.img].lv[0], job, (tile % tiles_x) * FT_W, (tile / tiles_x) * FT_H, job.threshold, X.fast_out,
@@ -560,23 +571,33 @@ __global__ void __launch_bounds__(DV_THREADS) k_dv_topk(const DvUnit *units, DvG
   dv_topk(GroupBlock(), U, X, side, r, buf, DV_TOPK_SMEM);
 }
 
-__global__ void __launch_bounds__(DV_THREADS) k_dv_select(const DvUnit *units, const DvHead *heads, DvGlobals X) {
+__global__ void __launch_bounds__(DV_THREADS) k_dv_select(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
-  for (int u = h.first; u < h.first + h.count; u++) dv_select(GroupBlock(), units[u], X);
+  if (blockIdx.x == 0 && threadIdx.x == 0) *X.fast_n_active = 0;   // FAST and the top-K are done with the list: re-armed for the next feed
+  for (int u = h.first; u < h.first + h.count; u++) dv_select(GroupBlock(), units[u], X, dv_smem(P));
 }
-__global__ void __launch_bounds__(DV_THREADS) k_dv_assign(const DvUnit *units, const DvHead *heads, DvGlobals X) {
+__global__ void __launch_bounds__(DV_THREADS) k_dv_assign(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
-  for (int u = h.first; u < h.first + h.count; u++) dv_assign(GroupBlock(), units[u], X);
+  for (int u = h.first; u < h.first + h.count; u++) dv_assign(GroupBlock(), units[u], X, dv_smem(P));
 }
-__global__ void __launch_bounds__(DV_THREADS) k_dv_merge(const DvUnit *units, const DvHead *heads, DvGlobals X) {
+__global__ void __launch_bounds__(DV_THREADS) k_dv_merge(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
-  for (int u = h.first; u < h.first + h.count; u++) dv_merge(GroupBlock(), units[u], X);
+  for (int u = h.first; u < h.first + h.count; u++) dv_merge(GroupBlock(), units[u], X, dv_smem(P));
 }
 
-cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+template <class K>
+static cudaError_t dv_smem_attr(K kernel, size_t bytes) {   // the attribute belongs to the (function, device) pair
+  if (bytes <= 48 * 1024) return cudaSuccess;
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+static size_t dv_smem_bytes(int P) { return (size_t)P * 24; }
+
+cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (n_heads <= 0) return cudaSuccess;
+  cudaError_t e = dv_smem_attr(k_dv_occupancy, dv_smem_bytes(max_p));
+  if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_occupancy<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  k_dv_occupancy<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
@@ -586,7 +607,7 @@ cudaError_t launch_dv_fast(cudaStream_t st, const DvGlobals &X, const PyrDesc *p
   const long work = (long)n_slots * tiles;
   const int grid = (int)(work < 148 * 8 ? work : 148 * 8);   // 8 blocks of 256 threads per SM
   prof_mark(st, K_FAST);
-  k_dv_fast<<<grid, 256, 0, st>>>(X, pyr_tab, n_slots, tiles);
+  k_dv_fast<<<grid, 256, 0, st>>>(X, pyr_tab, tiles);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
@@ -597,24 +618,30 @@ cudaError_t launch_dv_topk(cudaStream_t st, const DvUnit *units, int n_units, in
   prof_mark(st, -1);
   return cudaGetLastError();
 }
-cudaError_t launch_dv_select(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+cudaError_t launch_dv_select(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (n_heads <= 0) return cudaSuccess;
+  cudaError_t e = dv_smem_attr(k_dv_select, dv_smem_bytes(max_p));
+  if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_select<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  k_dv_select<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
-cudaError_t launch_dv_assign(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+cudaError_t launch_dv_assign(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (n_heads <= 0) return cudaSuccess;
+  cudaError_t e = dv_smem_attr(k_dv_assign, dv_smem_bytes(max_p));
+  if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_assign<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  k_dv_assign<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
-cudaError_t launch_dv_merge(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X) {
+cudaError_t launch_dv_merge(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (n_heads <= 0) return cudaSuccess;
+  cudaError_t e = dv_smem_attr(k_dv_merge, dv_smem_bytes(max_p));
+  if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_merge<<<n_heads, DV_THREADS, 0, st>>>(units, heads, X);
+  k_dv_merge<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
   prof_mark(st, -1);
   return cudaGetLastError();
 }

@@ -63,7 +63,8 @@ struct DvUnit {
   int P, C, K;                                     // capacities: points per camera, cells, corners per cell
   int job_base;                                    // FAST job slots [job_base, job_base + 2C): left cells, right cells
   int fast_base, cell_cap;                         // FAST output words: job slot s owns [fast_base + s' * cell_cap, ...)
-  int sp_base;                                     // sub-pixel / stereo-LK slots [sp_base, sp_base + 2CK): left compact, right by (cell, k)
+  int sp_base;                                     // sub-pixel + stereo-LK slots of the left corners [sp_base, sp_base + CK), compact
+  int spr_base;                                    // sub-pixel slots of the right corners [spr_base, spr_base + CK), by (cell, k); all left slots of a launch come first
   int lk_base;                                     // temporal-LK slots [lk_base, lk_base + 2P): left, right
   int rs_base;                                     // RANSAC jobs rs_base (left), rs_base + 1 (right)
   unsigned long long *currid;                      // TrackBase::currid of the tracker (device)
@@ -85,6 +86,7 @@ struct DvGlobals {
   FastJob *fast_jobs;
   uint32_t *fast_out;
   unsigned *fast_cnt;
+  int *fast_active, *fast_n_active;  // job slots that hold a cell to scan, compacted (any order), and their number
   SubpixItem *sp_items;
   const float *sp_out;            // [2 * slot]
   LkItem *lk1_items;              // stereo LK of new left corners, indexed like the sub-pixel slots
@@ -96,6 +98,23 @@ struct DvGlobals {
   const float *p1n;
   const uint8_t *rs_mask;         // klt status && RANSAC inlier
 };
+
+// Fast scratch private to the block (shared memory on the device): the id / point lists the brute-force membership and box
+// tests walk.  Each holds at least P entries.
+struct DvSmem {
+  unsigned long long *ids0, *ids1;
+  float *pts;                   // [2 * P]
+};
+template <class G>
+UVIO_HD void dv_stage_ids(G g, unsigned long long *dst, const unsigned long long *src, int n) {
+  for (int i = g.lane(); i < n; i += g.size()) dst[i] = src[i];
+  g.sync();
+}
+template <class G>
+UVIO_HD void dv_stage_pts(G g, float *dst, const float *src, int n) {
+  for (int i = g.lane(); i < 2 * n; i += g.size()) dst[i] = src[i];
+  g.sync();
+}
 
 UVIO_HD int dv_resize_nn_src(int d, int dst_len, int src_len) {   // cv::resize INTER_NEAREST source index (TrackKLT.cpp:480)
   double f = (double)dst_len / (double)src_len;
@@ -280,10 +299,10 @@ UVIO_HD void dv_topk(G g, const DvUnit &U, const DvGlobals &X, int side, int r, 
 
 // ---- occupancy pass of one camera (TrackKLT.cpp:409-464 / :545-600 / :722-780), cell selection and FAST jobs -----------------
 // is a pixel inside one of the 255-boxes painted around the first n points of S.pts (mask_updated minus the mask, :457-461)?
-UVIO_HD bool dv_boxed(const DvSide &S, int n, int mpd, long at) {
+UVIO_HD bool dv_boxed(const DvSide &S, const float *pts, int n, int mpd, long at) {
   const int y = (int)(at / S.w), x = (int)(at - (long)y * S.w);
   for (int i = 0; i < n; i++) {
-    const int bx = (int)S.pts[2 * i], by = (int)S.pts[2 * i + 1];
+    const int bx = (int)pts[2 * i], by = (int)pts[2 * i + 1];
     if (bx - mpd < 0 || bx + mpd >= S.w || by - mpd < 0 || by + mpd >= S.h) continue;   // the box was not painted (:457)
     const int dx = x - bx, dy = y - by;
     if (dx >= -mpd && dx <= mpd && dy >= -mpd && dy <= mpd) return true;
@@ -308,46 +327,58 @@ UVIO_HD int dv_occ_base(const DvUnit &U, const DvSide &S, float px, float py, in
   return y_close * cw + x_close + 1;
 }
 
-// the cells to extract from (x-outer / y-inner, :483-492) and their FAST jobs; one lane
-UVIO_HD void dv_cells_and_jobs(const DvUnit &U, const DvGlobals &X, int side, bool detect) {
+// the cells to extract from (x-outer / y-inner, :483-492) and their FAST jobs; the whole group (lane i <-> cell x = i / gy, y = i % gy)
+template <class G>
+UVIO_HD void dv_cells_and_jobs(G g, const DvUnit &U, const DvGlobals &X, int side, bool detect) {
   const DvSide &S = U.s[side];
-  int nc = 0;
-  if (detect) {
-    const int nfg = (int)((double)U.num_features / (double)(U.gx * U.gy)) + 1;
-    int req = (int)(0.5 * nfg);
-    if (req < 1) req = 1;
-    for (int x = 0; x < U.gx; x++)
-      for (int y = 0; y < U.gy; y++) {
-        int m = 0;
-        if (S.det_mask) m = S.det_mask[(size_t)dv_resize_nn_src(y, U.gy, S.h) * S.w + dv_resize_nn_src(x, U.gx, S.w)];
-        int gcount = S.grid[y * U.gx + x];
-        if (gcount > 255) gcount = 255;
-        if (gcount < req && m != 255) S.cells[nc++] = (x << 16) | y;
-      }
+  const int nfg = (int)((double)U.num_features / (double)(U.gx * U.gy)) + 1;
+  int req = (int)(0.5 * nfg);
+  if (req < 1) req = 1;
+  int total = 0;
+  for (int base = 0; base < U.C; base += g.size()) {        // C <= group size in practice: one round
+    const int i = base + g.lane();
+    int valid = 0;
+    if (detect && i < U.C) {
+      const int x = i / U.gy, y = i - x * U.gy;
+      int m = 0;
+      if (S.det_mask) m = S.det_mask[(size_t)dv_resize_nn_src(y, U.gy, S.h) * S.w + dv_resize_nn_src(x, U.gx, S.w)];
+      int gcount = fdb_ldi(&S.grid[y * U.gx + x]);
+      if (gcount > 255) gcount = 255;
+      valid = gcount < req && m != 255;
+    }
+    int round_total;
+    const int pos = g.exclusive_sum(valid, round_total);
+    if (valid) S.cells[total + pos] = ((i / U.gy) << 16) | (i % U.gy);
+    total += round_total;
   }
-  S.ctl[1] = nc;
-  S.ctl[2] = detect;
-  for (int r = 0; r < U.C; r++) {
+  g.sync();
+  if (g.lane() == 0) {
+    S.ctl[1] = total;
+    S.ctl[2] = detect;
+  }
+  for (int r = g.lane(); r < U.C; r += g.size()) {
     FastJob j;
     j.img = S.det_pyr;
     j.x0 = j.y0 = j.w = j.h = 0;
     j.out_off = U.fast_base + (side * U.C + r) * U.cell_cap;
     j.out_cap = U.cell_cap;
     j.threshold = U.fast_threshold;
-    if (r < nc) {
+    if (r < total) {
       const int x = (S.cells[r] >> 16) * U.size_x, y = (S.cells[r] & 0xFFFF) * U.size_y;
       if (!(x + U.size_x > S.w || y + U.size_y > S.h)) {   // Grider_GRID.h:117
         j.x0 = x; j.y0 = y; j.w = U.size_x; j.h = U.size_y;
         const int cap = ((j.w + 1) / 2) * ((j.h + 1) / 2);
         if (cap < j.out_cap) j.out_cap = cap;
+        X.fast_active[fdb_add_ret(X.fast_n_active, 1)] = U.job_base + side * U.C + r;   // compact list of the slots FAST must visit (any order)
       }
     }
     X.fast_jobs[U.job_base + side * U.C + r] = j;
   }
+  g.sync();
 }
 
 template <class G>
-UVIO_HD void dv_occupancy_side(G g, const DvUnit &U, const DvGlobals &X, int side) {
+UVIO_HD void dv_occupancy_side(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm, int side) {
   const DvSide &S = U.s[side];
   const DvSide &L = U.s[0];
   const int mpd = U.mpd;
@@ -357,6 +388,7 @@ UVIO_HD void dv_occupancy_side(G g, const DvUnit &U, const DvGlobals &X, int sid
   g.sync();
   const int n = U.first ? 0 : *S.n_last;
   const int nl = side ? L.ctl[0] : 0;                       // right pass: ids of the kept left points are exempt (:754-759)
+  if (side) dv_stage_ids(g, sm.ids0, L.ids, nl);
   for (int i = g.lane(); i < n; i += g.size()) {
     int gcell = 0;
     const int c = dv_occ_base(U, S, S.pts_last[2 * i], S.pts_last[2 * i + 1], gcell);
@@ -372,7 +404,7 @@ UVIO_HD void dv_occupancy_side(G g, const DvUnit &U, const DvGlobals &X, int sid
       keep = fdb_ldi(&S.first[c - 1]) == i;                // the first point of its close cell
       if (!keep && side) {                                  // a later one survives only as a stereo id
         const unsigned long long id = S.ids_last[i];
-        for (int k = 0; k < nl && !keep; k++) keep = L.ids[k] == id;
+        for (int k = 0; k < nl && !keep; k++) keep = sm.ids0[k] == id;
       }
     }
     U.scr_c[i] = keep;
@@ -393,21 +425,20 @@ UVIO_HD void dv_occupancy_side(G g, const DvUnit &U, const DvGlobals &X, int sid
   if (g.lane() == 0) {
     S.ctl[0] = kept;
     S.ctl[4] = kept;
-    const int thr = 20 < (int)(0.5 * U.num_features) ? 20 : (int)(0.5 * U.num_features);
-    const int need = U.num_features - kept;
-    // mono returns when need < thr (:470); stereo detects when need > thr (:609, :785)
-    const bool detect = (U.stereo || side) ? (need > thr) : !(need < thr);
-    dv_cells_and_jobs(U, X, side, detect);
   }
-  g.sync();
+  const int thr = 20 < (int)(0.5 * U.num_features) ? 20 : (int)(0.5 * U.num_features);
+  const int need = U.num_features - kept;
+  // mono returns when need < thr (:470); stereo detects when need > thr (:609, :785)
+  const bool detect = (U.stereo || side) ? (need > thr) : !(need < thr);
+  dv_cells_and_jobs(g, U, X, side, detect);
 }
 
 template <class G>
-UVIO_HD void dv_occupancy(G g, const DvUnit &U, const DvGlobals &X) {
+UVIO_HD void dv_occupancy(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm) {
   if (g.lane() == 0) { U.uctl[0] = 0; U.uctl[1] = 0; }
-  dv_occupancy_side(g, U, X, 0);
+  dv_occupancy_side(g, U, X, sm, 0);
   if (U.stereo) {
-    dv_occupancy_side(g, U, X, 1);
+    dv_occupancy_side(g, U, X, sm, 1);
   } else {                                                  // the right job slots of a mono unit exist but are never used
     for (int r = g.lane(); r < U.C; r += g.size()) {
       FastJob j;
@@ -429,10 +460,11 @@ UVIO_HD void dv_corner_xy(const DvUnit &U, const DvSide &S, int r, uint32_t w, f
 }
 
 template <class G>
-UVIO_HD void dv_select(G g, const DvUnit &U, const DvGlobals &X) {
+UVIO_HD void dv_select(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm) {
   const DvSide &L = U.s[0], &R = U.s[1];
   const int CK = U.C * U.K;
   const int n_old = L.ctl[4];
+  dv_stage_pts(g, sm.pts, L.pts, L.ctl[2] ? n_old : 0);
   for (int idx = g.lane(); idx < CK; idx += g.size()) {
     const int r = idx / U.K, k = idx - r * U.K;
     int ok = 0;
@@ -442,7 +474,7 @@ UVIO_HD void dv_select(G g, const DvUnit &U, const DvGlobals &X) {
       const int x = (int)fx, y = (int)fy;
       if (!(x < 0 || x > L.w || y < 0 || y > L.h)) {
         const long at = (long)y * L.w + x;
-        ok = !((L.det_mask && L.det_mask[at] > 127) || dv_boxed(L, n_old, U.mpd, at));
+        ok = !((L.det_mask && L.det_mask[at] > 127) || dv_boxed(L, sm.pts, n_old, U.mpd, at));
       }
     }
     U.scr_a[idx] = ok;
@@ -470,8 +502,7 @@ UVIO_HD void dv_select(G g, const DvUnit &U, const DvGlobals &X) {
       dv_corner_xy(U, R, r, R.top[idx], it.x, it.y);
       it.pyr = R.det_pyr;
     }
-    X.sp_items[U.sp_base + CK + idx] = it;
-    X.lk1_items[U.sp_base + CK + idx] = LkItem{0, 0, 0, 0, -1, -1};
+    X.sp_items[U.spr_base + idx] = it;
   }
   if (g.lane() == 0) U.uctl[0] = nsel;
   g.sync();
@@ -507,7 +538,7 @@ UVIO_HD void dv_close_reject(G g, const DvUnit &U, const DvSide &S, const float 
 
 // ---- finish the detection (phase C of the host path) and emit the temporal LK / RANSAC work -------------------------------------
 template <class G>
-UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X) {
+UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm) {
   const DvSide &L = U.s[0], &R = U.s[1];
   const int CK = U.C * U.K;
   const int nsel = U.uctl[0];
@@ -619,6 +650,7 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X) {
       }
       g.sync();
       const int nv = U.scr_d[CK];
+      dv_stage_pts(g, sm.pts, R.pts, nR);
       const uint8_t *mask0 = (L.w == R.w && L.h == R.h) ? L.det_mask : nullptr;   // :721 clones mask0 (sic)
       for (int idx = g.lane(); idx < nv * U.K; idx += g.size()) {
         const int vi = idx / U.K, k = idx - vi * U.K;
@@ -630,7 +662,7 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X) {
           const int x = (int)fx, y = (int)fy;
           if (!(x < 0 || x > R.w || y < 0 || y > R.h)) {
             const long at = (long)y * R.w + x;
-            ok = !((mask0 && mask0[at] > 127) || dv_boxed(R, nR, U.mpd, at));
+            ok = !((mask0 && mask0[at] > 127) || dv_boxed(R, sm.pts, nR, U.mpd, at));
           }
         }
         U.scr_c[idx] = ok;
@@ -642,7 +674,7 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X) {
         if (U.scr_c[idx]) {
           const int vi = idx / U.K, k = idx - vi * U.K;
           const int r = U.scr_d[CK + 1 + vi];
-          const int sp = U.sp_base + CK + r * U.K + k;
+          const int sp = U.spr_base + r * U.K + k;
           const int d = U.scr_b[idx];
           U.tmp_pts[2 * d] = X.sp_out[2 * (size_t)sp];
           U.tmp_pts[2 * d + 1] = X.sp_out[2 * (size_t)sp + 1];
@@ -727,7 +759,7 @@ UVIO_HD void dv_store_last(G g, const DvSide &S, const float *pts, const unsigne
 }
 
 template <class G>
-UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X) {
+UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm) {
   if (U.first) return;                                                      // stored by dv_assign
   const DvSide &L = U.s[0], &R = U.s[1];
   const int nL = L.ctl[0], offL = U.lk_base, offR = U.lk_base + U.P;
@@ -766,6 +798,7 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X) {
   }
   const int nR = R.ctl[0];
   const bool runR = R.ctl[3] != 0;
+  dv_stage_ids(g, sm.ids0, R.ids, nR);
   // left loop (:306-338).  scr_a = left kept, scr_c = index of the paired right point or -1
   for (int i = g.lane(); i < nL; i += g.size()) {
     int keep = 0, pair = -1;
@@ -775,7 +808,7 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X) {
         const unsigned long long id = L.ids[i];
         int ir = -1;                                                         // first index in ids_right_old (:314-320)
         for (int k = 0; k < nR; k++)
-          if (R.ids[k] == id) { ir = k; break; }
+          if (sm.ids0[k] == id) { ir = k; break; }
         const bool okL = X.rs_mask[offL + i] != 0;
         if (okL && ir >= 0 && runR && X.rs_mask[offR + ir]) {
           const LkOut q = X.lk2_out[offR + ir];
@@ -818,15 +851,17 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X) {
     }
   g.sync();
   // right loop (:341-354): tracked right points whose id is not in good_ids_right yet.  scr_a = kept
+  for (int l = g.lane(); l < nL; l += g.size()) sm.ids1[l] = U.scr_c[l] >= 0 ? sm.ids0[U.scr_c[l]] : ~0ull;   // ids paired by the left loop
+  g.sync();
   for (int i = g.lane(); i < nR; i += g.size()) {
     int keep = 0;
     if (runR) {
       const LkOut q = X.lk2_out[offR + i];
       if (!(q.x < 0 || q.y < 0 || (int)q.x >= R.w || (int)q.y >= R.h) && X.rs_mask[offR + i]) {
-        const unsigned long long id = R.ids[i];
+        const unsigned long long id = sm.ids0[i];
         bool added = false;
-        for (int l = 0; l < nL && !added; l++) added = U.scr_c[l] >= 0 && R.ids[U.scr_c[l]] == id;
-        for (int k = 0; k < i && !added; k++) added = R.ids[k] == id && X.rs_mask[offR + k];   // a duplicate id earlier in this loop
+        for (int l = 0; l < nL && !added; l++) added = sm.ids1[l] == id;
+        for (int k = 0; k < i && !added; k++) added = sm.ids0[k] == id && X.rs_mask[offR + k];   // a duplicate id earlier in this loop
         keep = !added;
       }
     }
