@@ -98,7 +98,7 @@ cudaError_t launch_subpix(cudaStream_t, const SubpixItem *items, int n, const Py
 }
 
 cudaError_t launch_lk(cudaStream_t, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
-                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool) {
+                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool, const int *out_idx) {
   GroupSeq g;
   LkSmem s;
   for (int i = 0; i < n; i++) {
@@ -110,8 +110,9 @@ cudaError_t launch_lk(cudaStream_t, const LkItem *items, int n, const PyrDesc *p
     LkParams prm{P0.nlv - 1, max_count, eps * eps, 1e-4};
     uint8_t st;
     lk_track_point(g, s, P0.lv, P1.lv, prm, px, py, nx, ny, st);
-    out_host[i] = out_dev[i] = LkOut{nx, ny};
-    status_host[i] = status_dev[i] = st;
+    const int at = out_idx ? out_idx[i] : i;
+    out_host[at] = out_dev[at] = LkOut{nx, ny};
+    status_host[at] = status_dev[at] = st;
   }
   return 0;
 }

@@ -308,7 +308,9 @@ struct Lane {
   cudaEvent_t lk_go = nullptr, lk_done = nullptr;   // latency-bound kernels of another group get SM slots as soon as LK blocks retire
   DevVec<SubpixItem> dv_sp_items;
   DevVec<float> dv_sp_out;
-  DevVec<LkItem> dv_lk1_items, dv_lk2_items;
+  DevVec<LkItem> dv_lk1_items, dv_lk2_items, dv_lk2n_items;
+  DevVec<int> dv_lk2n_out;
+  cudaEvent_t occ_done = nullptr;
   DevVec<LkOut> dv_lk1_out, dv_lk2_out;
   DevVec<uint8_t> dv_lk1_status, dv_lk2_status, dv_rs_mask, dv_rs_mask_raw;
   DevVec<RansacJob> dv_rs_jobs;
@@ -326,6 +328,7 @@ struct Lane {
     if (lk_stream) cudaStreamDestroy(lk_stream);
     if (lk_go) cudaEventDestroy(lk_go);
     if (lk_done) cudaEventDestroy(lk_done);
+    if (occ_done) cudaEventDestroy(occ_done);
   }
 };
 
@@ -726,7 +729,8 @@ Context *context_for_device(int device, int *err) {
         (e = cudaEventCreateWithFlags(&ln->up_done, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&ln->lk_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&ln->lk_go, cudaEventDisableTiming)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&ln->lk_done, cudaEventDisableTiming)) != cudaSuccess) {
+        (e = cudaEventCreateWithFlags(&ln->lk_done, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&ln->occ_done, cudaEventDisableTiming)) != cudaSuccess) {
       if (err) *err = (int)e;
       return nullptr;
     }
@@ -1201,7 +1205,7 @@ struct DvCamMem {
 struct DvUnitMem {
   int *scr[4] = {nullptr, nullptr, nullptr, nullptr}, *part = nullptr, *uctl = nullptr;
   float *tmp_pts = nullptr; unsigned long long *tmp_ids = nullptr;
-  DvObs *h_obs = nullptr, *m_obs = nullptr; int *h_n_obs = nullptr, *m_n_obs = nullptr;
+  DvObs *h_obs = nullptr, *m_obs = nullptr, *d_obs = nullptr; int *h_n_obs = nullptr, *m_n_obs = nullptr;
 };
 struct DvRig {
   int nf = 0, P = 0, C = 0, K = 0, size_x = 0, size_y = 0, cell_cap = 0, obs_cap = 0;
@@ -1299,6 +1303,7 @@ static int dv_prepare(Context *ctx, Rig &rig) {
         u.uctl = dv_carve<int>(p, 16);
         u.tmp_pts = dv_carve<float>(p, 2 * (size_t)D.P);
         u.tmp_ids = dv_carve<unsigned long long>(p, D.P);
+        u.d_obs = dv_carve<DvObs>(p, D.obs_cap);
         u.h_obs = dv_carve<DvObs>(hp, D.obs_cap);
         u.h_n_obs = dv_carve<int>(hp, 1);
         u.m_obs = (DvObs *)((char *)u.h_obs + to_dev);
@@ -2061,7 +2066,7 @@ int Pass::device_feed() {
       U.size_x = geom.size_x; U.size_y = geom.size_y; U.per_cell = geom.per_cell;
       U.P = D.P; U.C = D.C; U.K = D.K;
       U.job_base = job_slots; U.fast_base = (int)fast_words; U.cell_cap = D.cell_cap;
-      U.sp_base = sp_slots; U.spr_base = -1 - sp_slots; U.lk_base = lk_slots; U.rs_base = 2 * k;   // spr_base is fixed up below
+      U.sp_base = sp_slots; U.spr_base = -1 - sp_slots; U.lk_base = lk_slots; U.lkn_base = 2 * sp_slots; U.rs_base = 2 * k;   // spr_base is fixed up below
       U.currid = D.currid;
       U.h_currid = D.m_currid;
       for (int side = 0; side < (u.stereo ? 2 : 1); side++) {
@@ -2087,7 +2092,7 @@ int Pass::device_feed() {
       DvUnitMem &um = D.unit[(size_t)unit_idx];
       U.scr_a = um.scr[0]; U.scr_b = um.scr[1]; U.scr_c = um.scr[2]; U.scr_d = um.scr[3];
       U.part = um.part; U.tmp_pts = um.tmp_pts; U.tmp_ids = um.tmp_ids; U.uctl = um.uctl;
-      U.obs = um.m_obs; U.n_obs = um.m_n_obs; U.obs_cap = D.obs_cap;
+      U.obs = um.m_obs; U.obs_dev = um.d_obs; U.n_obs = um.m_n_obs; U.obs_cap = D.obs_cap;
       *um.h_n_obs = 0;
       job_slots += 2 * D.C;
       fast_words += 2 * (size_t)D.C * D.cell_cap;
@@ -2129,6 +2134,8 @@ int Pass::device_feed() {
   CU_TRY(ctx->dv_lk1_out.reserve((size_t)spl_slots));
   CU_TRY(ctx->dv_lk1_status.reserve((size_t)spl_slots));
   CU_TRY(ctx->dv_lk2_items.reserve((size_t)lk_slots));
+  CU_TRY(ctx->dv_lk2n_items.reserve((size_t)sp_slots));
+  CU_TRY(ctx->dv_lk2n_out.reserve((size_t)sp_slots));
   CU_TRY(ctx->dv_lk2_out.reserve((size_t)lk_slots));
   CU_TRY(ctx->dv_lk2_status.reserve((size_t)lk_slots));
   CU_TRY(ctx->dv_rs_mask.reserve((size_t)lk_slots));
@@ -2142,6 +2149,7 @@ int Pass::device_feed() {
   X.sp_items = ctx->dv_sp_items.d; X.sp_out = ctx->dv_sp_out.d;
   X.lk1_items = ctx->dv_lk1_items.d; X.lk1_out = ctx->dv_lk1_out.d; X.lk1_status = ctx->dv_lk1_status.d;
   X.lk2_items = ctx->dv_lk2_items.d; X.lk2_out = ctx->dv_lk2_out.d;
+  X.lk2n_items = ctx->dv_lk2n_items.d; X.lk2n_out = ctx->dv_lk2n_out.d;
   X.rs_jobs = ctx->dv_rs_jobs.d; X.p1n = ctx->dv_p1n.d; X.rs_mask = ctx->dv_rs_mask.d;
   CU_TRY(ctx->dv_units.upload(st, (size_t)nu));
   CU_TRY(ctx->dv_heads.upload(st, (size_t)nheads));
@@ -2159,6 +2167,18 @@ int Pass::device_feed() {
     const DvUnit *U = ctx->dv_units.d;
     const DvHead *H = ctx->dv_heads.d;
     CU_TRY(launch_dv_occupancy(st, U, H, nheads, X, max_p));
+    // The temporal LK of the points that survived the occupancy pass (the bulk of the feed's instructions) starts now, on the
+    // lane's low-priority stream, beside the latency-bound detection chain; only the new points wait for the detection.
+    CU_TRY(cudaEventRecord(ctx->occ_done, st));
+    CU_TRY(cudaStreamWaitEvent(ctx->lk_stream, ctx->occ_done, 0));
+    if (!any_first) {
+      CU_TRY(cudaStreamWaitEvent(ctx->lk_stream, ctx->up_done, 0));   // it reads the new pyramids
+      for (int i = 0; i < Context::PF_RING; i++)
+        if ((wait_evts >> i) & 1u) CU_TRY(cudaStreamWaitEvent(ctx->lk_stream, dev->pf_evt[i], 0));
+    }
+    CU_TRY(launch_lk(ctx->lk_stream, ctx->dv_lk2_items.d, lk_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
+                     ctx->dv_lk2_out.d, ctx->dv_lk2_status.d));
+    CU_TRY(cudaEventRecord(ctx->lk_done, ctx->lk_stream));
     CU_TRY(launch_dv_fast(st, X, dev->pyr_dev.d, job_slots, max_cw, max_ch));
     CU_TRY(launch_dv_topk(st, U, nu, max_c, X));
     CU_TRY(launch_dv_select(st, U, H, nheads, X, max_p));
@@ -2166,18 +2186,14 @@ int Pass::device_feed() {
     CU_TRY(launch_lk(st, ctx->dv_lk1_items.d, spl_slots, dev->pyr_dev.d, ctx->dv_sp_out.d, 30, 0.01, ctx->dv_lk1_out.d, ctx->dv_lk1_status.d,
                      ctx->dv_lk1_out.d, ctx->dv_lk1_status.d));
     CU_TRY(launch_dv_assign(st, U, H, nheads, X, max_p));
-    if (!any_first) CU_TRY(wait_new_frames());  // the temporal LK reads the new pyramids
-    // the temporal LK (the bulk of the feed's instructions) on the lane's low-priority stream, fenced by two events
-    CU_TRY(cudaEventRecord(ctx->lk_go, st));
-    CU_TRY(cudaStreamWaitEvent(ctx->lk_stream, ctx->lk_go, 0));
-    CU_TRY(launch_lk(ctx->lk_stream, ctx->dv_lk2_items.d, lk_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
-                     ctx->dv_lk2_out.d, ctx->dv_lk2_status.d));
-    CU_TRY(cudaEventRecord(ctx->lk_done, ctx->lk_stream));
+    if (!any_first) CU_TRY(wait_new_frames());
+    CU_TRY(launch_lk(st, ctx->dv_lk2n_items.d, sp_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
+                     ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, false, ctx->dv_lk2n_out.d));
     CU_TRY(cudaStreamWaitEvent(st, ctx->lk_done, 0));
     CU_TRY(launch_ransac(st, ctx->dv_rs_jobs.d, 2 * nu, max_p, ctx->dv_lk2_items.d, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, dev->cam_dev.d,
                          ctx->dv_p0n.d, ctx->dv_p1n.d, ctx->dv_p1n.d, ctx->dv_rs_mask.d, ctx->dv_rs_mask_raw.d));
     CU_TRY(launch_dv_merge(st, U, H, nheads, X, max_p));
-    ctx->stats[1] += 10;
+    ctx->stats[1] += 11;
   } else {
     CU_TRY(wait_new_frames());
   }

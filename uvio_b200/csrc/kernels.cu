@@ -394,7 +394,7 @@ constexpr int LK_WARPS_PER_BLOCK = 1;
 __global__ void LK_BOUNDS k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
                                                              const float *init_from_dev, int max_count, double eps_sq,
                                                              LkOut *out_host, uint8_t *status_host, LkOut *out_dev,
-                                                             uint8_t *status_dev) {
+                                                             uint8_t *status_dev, const int *out_idx) {
   __shared__ LkSmem sm[LK_WARPS_PER_BLOCK];
   const int wid = threadIdx.x >> 5, i = blockIdx.x * LK_WARPS_PER_BLOCK + wid;
   pdl_release_dependents();   // the RANSAC launch behind this one may start on what it can do without the tracks
@@ -423,10 +423,11 @@ __global__ void LK_BOUNDS k_lk(const LkItem *items, int n, const PyrDesc *pyr_ta
     atomicAdd(&wk[2], 1ull);
     if (work[2]) atomicAdd(&wk[3], (unsigned long long)work[2]);
     LkOut o{nx, ny};
-    out_host[i] = o;
-    status_host[i] = status;
-    out_dev[i] = o;
-    status_dev[i] = status;
+    const int at = out_idx ? out_idx[i] : i;     // results of a compact item list land where the full list has them
+    out_host[at] = o;
+    status_host[at] = status;
+    out_dev[at] = o;
+    status_dev[at] = status;
   }
 }
 
@@ -444,11 +445,12 @@ cudaError_t read_lk_work(unsigned long long out[4], int reset) {
 }
 
 cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
-                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool overlap) {
+                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool overlap,
+                      const int *out_idx) {
   if (n <= 0) return cudaSuccess;
   prof_mark(st, K_LK);
   cudaError_t e = launch_after(k_lk, dim3((n + LK_WARPS_PER_BLOCK - 1) / LK_WARPS_PER_BLOCK), dim3(LK_WARPS_PER_BLOCK * 32), 0, st, overlap,
-                               items, n, pyr_tab, init_from_dev, max_count, eps * eps, out_host, status_host, out_dev, status_dev);
+                               items, n, pyr_tab, init_from_dev, max_count, eps * eps, out_host, status_host, out_dev, status_dev, out_idx);
   prof_mark(st, -1);
   return e != cudaSuccess ? e : cudaGetLastError();
 }

@@ -15,6 +15,7 @@
 // The same text is compiled for the host by tests/hostsim (GroupSeq, one lane), where it runs against the golden sequences.
 #pragma once
 #include "fast_body.h"
+#include "image_body.h"   // Vec16
 #include "featdb_body.h"   // fdb_scan, fdb_min / fdb_add, fdb_ldi
 #include "kernels.h"
 #include "simt.h"
@@ -66,6 +67,7 @@ struct DvUnit {
   int sp_base;                                     // sub-pixel + stereo-LK slots of the left corners [sp_base, sp_base + CK), compact
   int spr_base;                                    // sub-pixel slots of the right corners [spr_base, spr_base + CK), by (cell, k); all left slots of a launch come first
   int lk_base;                                     // temporal-LK slots [lk_base, lk_base + 2P): left, right
+  int lkn_base;                                    // temporal-LK slots of this feed's new points [lkn_base, lkn_base + 2CK): left, right
   int rs_base;                                     // RANSAC jobs rs_base (left), rs_base + 1 (right)
   unsigned long long *currid;                      // TrackBase::currid of the tracker (device)
   unsigned long long *h_currid;                    // ... and its host mirror (mapped)
@@ -76,6 +78,7 @@ struct DvUnit {
   unsigned long long *tmp_ids;                     // [P]
   int *uctl;                                       // [0] selected left corners, [1] error flag
   DvObs *obs;                                      // mapped host memory: the update_feature calls of this feed, in order
+  DvObs *obs_dev;                                  // ... built here (device memory) and copied out in 16-byte words at the end
   int *n_obs;
   int obs_cap;
 };
@@ -92,7 +95,9 @@ struct DvGlobals {
   LkItem *lk1_items;              // stereo LK of new left corners, indexed like the sub-pixel slots
   const LkOut *lk1_out;
   const uint8_t *lk1_status;
-  LkItem *lk2_items;              // temporal LK
+  LkItem *lk2_items;              // temporal LK of the points kept by the occupancy pass (issued right after it)
+  LkItem *lk2n_items;             // temporal LK of the points detected in this feed, compact: unit slots [lkn_base, lkn_base + 2CK)
+  int *lk2n_out;                  // ... and where each result goes in lk2_out / lk2_status
   const LkOut *lk2_out;
   RansacJob *rs_jobs;
   const float *p1n;
@@ -426,6 +431,14 @@ UVIO_HD void dv_occupancy_side(G g, const DvUnit &U, const DvGlobals &X, const D
     S.ctl[0] = kept;
     S.ctl[4] = kept;
   }
+  // The temporal LK of the kept points does not depend on the detection: its items are ready now, so the (issue-bound) launch
+  // can run beside the (latency-bound) detection chain.  Whether perform_matching runs at all (>= 10 points, :848) is only
+  // known after the detection; if it does not, these tracks are simply not used.
+  for (int i = g.lane(); i < U.P; i += g.size()) {
+    LkItem it{0, 0, 0, 0, -1, -1};
+    if (!U.first && i < kept) it = LkItem{S.pts[2 * i], S.pts[2 * i + 1], S.pts[2 * i], S.pts[2 * i + 1], S.last_pyr, S.cur_pyr};
+    X.lk2_items[U.lk_base + side * U.P + i] = it;
+  }
   const int thr = 20 < (int)(0.5 * U.num_features) ? 20 : (int)(0.5 * U.num_features);
   const int need = U.num_features - kept;
   // mono returns when need < thr (:470); stereo detects when need > thr (:609, :785)
@@ -449,6 +462,7 @@ UVIO_HD void dv_occupancy(G g, const DvUnit &U, const DvGlobals &X, const DvSmem
       j.threshold = U.fast_threshold;
       X.fast_jobs[U.job_base + U.C + r] = j;
     }
+    for (int i = g.lane(); i < U.P; i += g.size()) X.lk2_items[U.lk_base + U.P + i] = LkItem{0, 0, 0, 0, -1, -1};
     g.sync();
   }
 }
@@ -707,11 +721,17 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
     const DvSide &S = U.s[side];
     const int n = S.ctl[0];
     const bool run = !U.first && n >= 10;                                   // :848-852
-    for (int i = g.lane(); i < U.P; i += g.size()) {
+    const int kept_old = S.ctl[4];
+    for (int j = g.lane(); j < U.C * U.K; j += g.size()) {                 // the points detected in this feed
+      const int i = kept_old + j;
       LkItem it{0, 0, 0, 0, -1, -1};
       if (run && i < n) it = LkItem{S.pts[2 * i], S.pts[2 * i + 1], S.pts[2 * i], S.pts[2 * i + 1], S.last_pyr, S.cur_pyr};
-      X.lk2_items[U.lk_base + side * U.P + i] = it;
+      X.lk2n_items[U.lkn_base + side * U.C * U.K + j] = it;
+      X.lk2n_out[U.lkn_base + side * U.C * U.K + j] = U.lk_base + side * U.P + i;
     }
+    if (run)                                                                // RANSAC undistorts the old positions from the item list
+      for (int i = kept_old + g.lane(); i < n; i += g.size())
+        X.lk2_items[U.lk_base + side * U.P + i] = LkItem{S.pts[2 * i], S.pts[2 * i + 1], S.pts[2 * i], S.pts[2 * i + 1], -1, -1};
     if (g.lane() == 0) {
       S.ctl[3] = run;
       RansacJob j;
@@ -724,11 +744,13 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
     }
     if (U.first) {
       for (int i = g.lane(); i < n; i += g.size()) {
-        S.pts_last[2 * i] = S.h_pts_last[2 * i] = S.pts[2 * i];
-        S.pts_last[2 * i + 1] = S.h_pts_last[2 * i + 1] = S.pts[2 * i + 1];
-        S.ids_last[i] = S.h_ids_last[i] = S.ids[i];
+        S.pts_last[2 * i] = S.pts[2 * i];
+        S.pts_last[2 * i + 1] = S.pts[2 * i + 1];
+        S.ids_last[i] = S.ids[i];
       }
-      if (g.lane() == 0) *S.n_last = *S.h_n_last = n;
+      if (g.lane() == 0) *S.n_last = n;
+      g.sync();
+      dv_publish_side(g, S, n);
     }
   }
   if (!U.stereo && g.lane() == 0) {                                         // the unused right slots of a mono unit
@@ -741,9 +763,27 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
     X.rs_jobs[U.rs_base + 1] = j;
   }
   if (!U.stereo)
-    for (int i = g.lane(); i < U.P; i += g.size()) X.lk2_items[U.lk_base + U.P + i] = LkItem{0, 0, 0, 0, -1, -1};
+    for (int j = g.lane(); j < U.C * U.K; j += g.size()) {
+      X.lk2n_items[U.lkn_base + U.C * U.K + j] = LkItem{0, 0, 0, 0, -1, -1};
+      X.lk2n_out[U.lkn_base + U.C * U.K + j] = U.lk_base + U.P;
+    }
   if (U.first && g.lane() == 0) *U.n_obs = 0;
   g.sync();
+}
+
+// Results leave for mapped host memory as one linear copy in 16-byte words (full PCIe write bursts), never as scattered stores.
+template <class G>
+UVIO_HD void dv_copy_out(G g, void *dst, const void *src, size_t bytes) {
+  const size_t n16 = (bytes + 15) / 16;                     // the arrays are 256-byte aligned and padded
+  Vec16 *d = (Vec16 *)dst;
+  const Vec16 *q = (const Vec16 *)src;
+  for (size_t i = g.lane(); i < n16; i += g.size()) d[i] = q[i];
+}
+template <class G>
+UVIO_HD void dv_publish_side(G g, const DvSide &S, int n) {
+  dv_copy_out(g, S.h_pts_last, S.pts_last, sizeof(float) * 2 * (size_t)n);
+  dv_copy_out(g, S.h_ids_last, S.ids_last, sizeof(unsigned long long) * (size_t)n);
+  if (g.lane() == 0) *S.h_n_last = n;
 }
 
 // ---- merge + database observations + pts_last / ids_last (TrackKLT.cpp:143-189, :285-381) -------------------------------------
@@ -752,9 +792,9 @@ UVIO_HD void dv_store_last(G g, const DvSide &S, const float *pts, const unsigne
   for (int i = g.lane(); i < n; i += g.size())
     if (keep[i]) {
       const int d = base + pos[i];
-      S.pts_last[2 * d] = S.h_pts_last[2 * d] = pts[2 * i];
-      S.pts_last[2 * d + 1] = S.h_pts_last[2 * d + 1] = pts[2 * i + 1];
-      S.ids_last[d] = S.h_ids_last[d] = ids[i];
+      S.pts_last[2 * d] = pts[2 * i];
+      S.pts_last[2 * d + 1] = pts[2 * i + 1];
+      S.ids_last[d] = ids[i];
     }
 }
 
@@ -784,15 +824,16 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm
       if (U.scr_a[i]) {
         const int d = U.scr_b[i];
         const LkOut p = X.lk2_out[offL + i];
-        L.pts_last[2 * d] = L.h_pts_last[2 * d] = p.x;
-        L.pts_last[2 * d + 1] = L.h_pts_last[2 * d + 1] = p.y;
-        L.ids_last[d] = L.h_ids_last[d] = L.ids[i];
-        if (d < U.obs_cap) U.obs[d] = DvObs{L.ids[i], L.cam_id, p.x, p.y, X.p1n[2 * (size_t)(offL + i)], X.p1n[2 * (size_t)(offL + i) + 1]};
+        L.pts_last[2 * d] = p.x;
+        L.pts_last[2 * d + 1] = p.y;
+        L.ids_last[d] = L.ids[i];
+        if (d < U.obs_cap) U.obs_dev[d] = DvObs{L.ids[i], L.cam_id, p.x, p.y, X.p1n[2 * (size_t)(offL + i)], X.p1n[2 * (size_t)(offL + i) + 1]};
       }
-    if (g.lane() == 0) {
-      *L.n_last = *L.h_n_last = total;
-      *U.n_obs = total;
-    }
+    if (g.lane() == 0) *L.n_last = total;
+    g.sync();
+    dv_publish_side(g, L, total);
+    dv_copy_out(g, U.obs, U.obs_dev, sizeof(DvObs) * (size_t)(total < U.obs_cap ? total : U.obs_cap));
+    if (g.lane() == 0) *U.n_obs = total;
     g.sync();
     return;
   }
@@ -828,10 +869,10 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm
     if (U.scr_a[i]) {
       const int d = U.scr_b[i];
       const LkOut p = X.lk2_out[offL + i];
-      L.pts_last[2 * d] = L.h_pts_last[2 * d] = p.x;
-      L.pts_last[2 * d + 1] = L.h_pts_last[2 * d + 1] = p.y;
-      L.ids_last[d] = L.h_ids_last[d] = L.ids[i];
-      if (d < U.obs_cap) U.obs[d] = DvObs{L.ids[i], L.cam_id, p.x, p.y, X.p1n[2 * (size_t)(offL + i)], X.p1n[2 * (size_t)(offL + i) + 1]};
+      L.pts_last[2 * d] = p.x;
+      L.pts_last[2 * d + 1] = p.y;
+      L.ids_last[d] = L.ids[i];
+      if (d < U.obs_cap) U.obs_dev[d] = DvObs{L.ids[i], L.cam_id, p.x, p.y, X.p1n[2 * (size_t)(offL + i)], X.p1n[2 * (size_t)(offL + i) + 1]};
     }
   g.sync();
   // right points paired with a left one come first, in the left loop's order
@@ -843,11 +884,11 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm
     if (U.scr_d[i]) {
       const int d = U.scr_b[i], ir = U.scr_c[i];
       const LkOut q = X.lk2_out[offR + ir];
-      R.pts_last[2 * d] = R.h_pts_last[2 * d] = q.x;
-      R.pts_last[2 * d + 1] = R.h_pts_last[2 * d + 1] = q.y;
-      R.ids_last[d] = R.h_ids_last[d] = R.ids[ir];
+      R.pts_last[2 * d] = q.x;
+      R.pts_last[2 * d + 1] = q.y;
+      R.ids_last[d] = R.ids[ir];
       if (totL + d < U.obs_cap)
-        U.obs[totL + d] = DvObs{R.ids[ir], R.cam_id, q.x, q.y, X.p1n[2 * (size_t)(offR + ir)], X.p1n[2 * (size_t)(offR + ir) + 1]};
+        U.obs_dev[totL + d] = DvObs{R.ids[ir], R.cam_id, q.x, q.y, X.p1n[2 * (size_t)(offR + ir)], X.p1n[2 * (size_t)(offR + ir) + 1]};
     }
   g.sync();
   // right loop (:341-354): tracked right points whose id is not in good_ids_right yet.  scr_a = kept
@@ -874,17 +915,22 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm
     if (U.scr_a[i]) {
       const int d = nPair + U.scr_b[i];
       const LkOut q = X.lk2_out[offR + i];
-      R.pts_last[2 * d] = R.h_pts_last[2 * d] = q.x;
-      R.pts_last[2 * d + 1] = R.h_pts_last[2 * d + 1] = q.y;
-      R.ids_last[d] = R.h_ids_last[d] = R.ids[i];
+      R.pts_last[2 * d] = q.x;
+      R.pts_last[2 * d + 1] = q.y;
+      R.ids_last[d] = R.ids[i];
       if (totL + d < U.obs_cap)
-        U.obs[totL + d] = DvObs{R.ids[i], R.cam_id, q.x, q.y, X.p1n[2 * (size_t)(offR + i)], X.p1n[2 * (size_t)(offR + i) + 1]};
+        U.obs_dev[totL + d] = DvObs{R.ids[i], R.cam_id, q.x, q.y, X.p1n[2 * (size_t)(offR + i)], X.p1n[2 * (size_t)(offR + i) + 1]};
     }
   if (g.lane() == 0) {
-    *L.n_last = *L.h_n_last = totL;
-    *R.n_last = *R.h_n_last = nPair + nSolo;
-    *U.n_obs = totL + nPair + nSolo;
+    *L.n_last = totL;
+    *R.n_last = nPair + nSolo;
   }
+  g.sync();
+  const int n_obs = totL + nPair + nSolo;
+  dv_publish_side(g, L, totL);
+  dv_publish_side(g, R, nPair + nSolo);
+  dv_copy_out(g, U.obs, U.obs_dev, sizeof(DvObs) * (size_t)(n_obs < U.obs_cap ? n_obs : U.obs_cap));
+  if (g.lane() == 0) *U.n_obs = n_obs;
   g.sync();
 }
 
