@@ -83,29 +83,34 @@ cudaError_t upload_subpix_mask(float *mask_dev, cudaStream_t) {
 }
 
 cudaError_t launch_subpix(cudaStream_t, const SubpixItem *items, int n, const PyrDesc *pyr_tab, const float *mask, float *out_xy,
-                          float *out_xy_dev) {
+                          float *out_xy_dev, const int *n_dev) {
   GroupSeq g;
   SubpixSmem s;
+  if (n_dev) n = *n_dev;
   for (int i = 0; i < n; i++) {
     if (items[i].pyr < 0) continue;   // an unused slot of the device-side pipeline
     float x = items[i].x, y = items[i].y;
     subpix_point(g, s, pyr_tab[items[i].pyr].lv[0], mask, 20, 0.001 * 0.001, x, y);
-    out_xy[2 * i] = x;
-    out_xy[2 * i + 1] = y;
-    if (out_xy_dev) { out_xy_dev[2 * i] = x; out_xy_dev[2 * i + 1] = y; }
+    const int at = n_dev ? items[i].pad : i;
+    out_xy[2 * at] = x;
+    out_xy[2 * at + 1] = y;
+    if (out_xy_dev) { out_xy_dev[2 * at] = x; out_xy_dev[2 * at + 1] = y; }
   }
   return 0;
 }
 
 cudaError_t launch_lk(cudaStream_t, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
-                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool, const int *out_idx) {
+                      double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool, const int *out_idx,
+                      const int *n_dev) {
   GroupSeq g;
   LkSmem s;
+  if (n_dev) n = *n_dev;
   for (int i = 0; i < n; i++) {
     const LkItem it = items[i];
     if (it.prev_pyr < 0) continue;    // an unused slot of the device-side pipeline
     float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
-    if (init_from_dev) { px = nx = init_from_dev[2 * i]; py = ny = init_from_dev[2 * i + 1]; }
+    const int at0 = out_idx ? out_idx[i] : i;
+    if (init_from_dev) { px = nx = init_from_dev[2 * at0]; py = ny = init_from_dev[2 * at0 + 1]; }
     const PyrDesc &P0 = pyr_tab[it.prev_pyr], &P1 = pyr_tab[it.next_pyr];
     LkParams prm{P0.nlv - 1, max_count, eps * eps, 1e-4};
     uint8_t st;
@@ -158,6 +163,7 @@ struct SimSmem {
 cudaError_t launch_dv_occupancy(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (getenv("UVIO_DV_TRACE")) fprintf(stderr, "[sim] device-side pipeline: %d trackers\n", n_heads);
   SimSmem sm;
+  for (int k = 0; k < 4; k++) X.n_items[k] = 0;
   for (int h = 0; h < n_heads; h++)
     for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_occupancy(GroupSeq(), units[u], X, sm.get(max_p));
   return 0;

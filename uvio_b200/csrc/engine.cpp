@@ -309,7 +309,7 @@ struct Lane {
   DevVec<SubpixItem> dv_sp_items;
   DevVec<float> dv_sp_out;
   DevVec<LkItem> dv_lk1_items, dv_lk2_items, dv_lk2n_items;
-  DevVec<int> dv_lk2n_out;
+  DevVec<int> dv_lk2n_out, dv_lk1_idx, dv_n_items;
   cudaEvent_t occ_done = nullptr;
   DevVec<LkOut> dv_lk1_out, dv_lk2_out;
   DevVec<uint8_t> dv_lk1_status, dv_lk2_status, dv_rs_mask, dv_rs_mask_raw;
@@ -2136,6 +2136,8 @@ int Pass::device_feed() {
   CU_TRY(ctx->dv_lk2_items.reserve((size_t)lk_slots));
   CU_TRY(ctx->dv_lk2n_items.reserve((size_t)sp_slots));
   CU_TRY(ctx->dv_lk2n_out.reserve((size_t)sp_slots));
+  CU_TRY(ctx->dv_lk1_idx.reserve((size_t)spl_slots));
+  CU_TRY(ctx->dv_n_items.reserve(8, true));
   CU_TRY(ctx->dv_lk2_out.reserve((size_t)lk_slots));
   CU_TRY(ctx->dv_lk2_status.reserve((size_t)lk_slots));
   CU_TRY(ctx->dv_rs_mask.reserve((size_t)lk_slots));
@@ -2147,7 +2149,8 @@ int Pass::device_feed() {
   X.fast_jobs = ctx->dv_fast_jobs.d; X.fast_out = ctx->dv_fast_out.d; X.fast_cnt = ctx->dv_fast_cnt.d;
   X.fast_active = ctx->dv_fast_active.d; X.fast_n_active = ctx->dv_fast_active.d + ctx->dv_fast_active.cap - 1;
   X.sp_items = ctx->dv_sp_items.d; X.sp_out = ctx->dv_sp_out.d;
-  X.lk1_items = ctx->dv_lk1_items.d; X.lk1_out = ctx->dv_lk1_out.d; X.lk1_status = ctx->dv_lk1_status.d;
+  X.lk1_items = ctx->dv_lk1_items.d; X.lk1_out = ctx->dv_lk1_idx.d; X.lk1_res = ctx->dv_lk1_out.d; X.lk1_status = ctx->dv_lk1_status.d;
+  X.n_items = ctx->dv_n_items.d;
   X.lk2_items = ctx->dv_lk2_items.d; X.lk2_out = ctx->dv_lk2_out.d;
   X.lk2n_items = ctx->dv_lk2n_items.d; X.lk2n_out = ctx->dv_lk2n_out.d;
   X.rs_jobs = ctx->dv_rs_jobs.d; X.p1n = ctx->dv_p1n.d; X.rs_mask = ctx->dv_rs_mask.d;
@@ -2182,13 +2185,13 @@ int Pass::device_feed() {
     CU_TRY(launch_dv_fast(st, X, dev->pyr_dev.d, job_slots, max_cw, max_ch));
     CU_TRY(launch_dv_topk(st, U, nu, max_c, X));
     CU_TRY(launch_dv_select(st, U, H, nheads, X, max_p));
-    CU_TRY(launch_subpix(st, ctx->dv_sp_items.d, sp_slots, dev->pyr_dev.d, ctx->sp_mask.d, ctx->dv_sp_out.d, nullptr));
+    CU_TRY(launch_subpix(st, ctx->dv_sp_items.d, sp_slots, dev->pyr_dev.d, ctx->sp_mask.d, ctx->dv_sp_out.d, nullptr, ctx->dv_n_items.d));
     CU_TRY(launch_lk(st, ctx->dv_lk1_items.d, spl_slots, dev->pyr_dev.d, ctx->dv_sp_out.d, 30, 0.01, ctx->dv_lk1_out.d, ctx->dv_lk1_status.d,
-                     ctx->dv_lk1_out.d, ctx->dv_lk1_status.d));
+                     ctx->dv_lk1_out.d, ctx->dv_lk1_status.d, false, ctx->dv_lk1_idx.d, ctx->dv_n_items.d + 1));
     CU_TRY(launch_dv_assign(st, U, H, nheads, X, max_p));
     if (!any_first) CU_TRY(wait_new_frames());
     CU_TRY(launch_lk(st, ctx->dv_lk2n_items.d, sp_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
-                     ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, false, ctx->dv_lk2n_out.d));
+                     ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, false, ctx->dv_lk2n_out.d, ctx->dv_n_items.d + 2));
     CU_TRY(cudaStreamWaitEvent(st, ctx->lk_done, 0));
     CU_TRY(launch_ransac(st, ctx->dv_rs_jobs.d, 2 * nu, max_p, ctx->dv_lk2_items.d, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, dev->cam_dev.d,
                          ctx->dv_p0n.d, ctx->dv_p1n.d, ctx->dv_p1n.d, ctx->dv_rs_mask.d, ctx->dv_rs_mask_raw.d));

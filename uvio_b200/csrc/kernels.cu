@@ -327,34 +327,41 @@ static cudaError_t launch_after(void (*kernel)(KArgs...), dim3 grid, dim3 block,
 }
 
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_subpix(const SubpixItem *items, int n, const PyrDesc *pyr_tab,
-                                                                 const float *mask, float *out_xy, float *out_xy_dev) {
+                                                                 const float *mask, float *out_xy, float *out_xy_dev, const int *n_dev) {
   __shared__ SubpixSmem sm[WARPS_PER_BLOCK];
   __shared__ float smask[SP_N];
   pdl_release_dependents();   // the stereo LK chained on this launch may fetch its items meanwhile
   for (int i = threadIdx.x; i < SP_N; i += blockDim.x) smask[i] = mask[i];
   __syncthreads();
-  const int wid = threadIdx.x >> 5, i = blockIdx.x * WARPS_PER_BLOCK + wid;
-  if (i >= n) return;
-  const SubpixItem it = items[i];
-  if (it.pyr < 0) return;   // an unused slot of the device-side pipeline
-  float x = it.x, y = it.y;
-  subpix_point(GroupWarp(), sm[wid], pyr_tab[it.pyr].lv[0], smask, 20, 0.001 * 0.001, x, y);
-  if ((threadIdx.x & 31) == 0) {
-    out_xy[2 * i] = x;
-    out_xy[2 * i + 1] = y;
-    if (out_xy_dev) {
-      out_xy_dev[2 * i] = x;
-      out_xy_dev[2 * i + 1] = y;
+  const int wid = threadIdx.x >> 5;
+  // n_dev: a compact item list built on the device (the device-side pipeline): its length is read here, warps stride over it
+  // and every item names the slot its result goes to; otherwise item i -> slot i, one warp each
+  if (n_dev) n = *n_dev;
+  for (int i = blockIdx.x * WARPS_PER_BLOCK + wid; i < n; i += gridDim.x * WARPS_PER_BLOCK) {
+    const SubpixItem it = items[i];
+    if (it.pyr < 0) continue;
+    float x = it.x, y = it.y;
+    subpix_point(GroupWarp(), sm[wid], pyr_tab[it.pyr].lv[0], smask, 20, 0.001 * 0.001, x, y);
+    if ((threadIdx.x & 31) == 0) {
+      const int at = n_dev ? it.pad : i;
+      out_xy[2 * at] = x;
+      out_xy[2 * at + 1] = y;
+      if (out_xy_dev) {
+        out_xy_dev[2 * at] = x;
+        out_xy_dev[2 * at + 1] = y;
+      }
     }
+    __syncwarp();
   }
 }
 
 cudaError_t launch_subpix(cudaStream_t st, const SubpixItem *items, int n, const PyrDesc *pyr_tab, const float *mask_dev,
-                          float *out_xy, float *out_xy_dev) {
+                          float *out_xy, float *out_xy_dev, const int *n_dev) {
   if (n <= 0) return cudaSuccess;
+  int blocks = (n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK;
+  if (n_dev && blocks > 148 * 4) blocks = 148 * 4;
   prof_mark(st, K_SUBPIX);
-  k_subpix<<<(n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, mask_dev, out_xy,
-                                                                                      out_xy_dev);
+  k_subpix<<<blocks, WARPS_PER_BLOCK * 32, 0, st>>>(items, n, pyr_tab, mask_dev, out_xy, out_xy_dev, n_dev);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
@@ -394,40 +401,48 @@ constexpr int LK_WARPS_PER_BLOCK = 1;
 __global__ void LK_BOUNDS k_lk(const LkItem *items, int n, const PyrDesc *pyr_tab,
                                                              const float *init_from_dev, int max_count, double eps_sq,
                                                              LkOut *out_host, uint8_t *status_host, LkOut *out_dev,
-                                                             uint8_t *status_dev, const int *out_idx) {
+                                                             uint8_t *status_dev, const int *out_idx, const int *n_dev) {
   __shared__ LkSmem sm[LK_WARPS_PER_BLOCK];
-  const int wid = threadIdx.x >> 5, i = blockIdx.x * LK_WARPS_PER_BLOCK + wid;
+  const int wid = threadIdx.x >> 5;
   pdl_release_dependents();   // the RANSAC launch behind this one may start on what it can do without the tracks
-  if (i >= n) return;
-  const LkItem it = items[i];
-  float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
-  if (it.prev_pyr < 0) return;   // an unused slot of the device-side pipeline (exiting counts as the PDL trigger)
-  pdl_wait();                 // the refined corners (init_from_dev) and the kernel before this one's use of out_dev / status_dev
-  if (init_from_dev) {
-    px = nx = init_from_dev[2 * i];
-    py = ny = init_from_dev[2 * i + 1];
-  }
-  const PyrDesc &P0 = pyr_tab[it.prev_pyr], &P1 = pyr_tab[it.next_pyr];
-  LkParams prm;
-  prm.max_level = P0.nlv - 1;
-  prm.max_count = max_count;
-  prm.eps_sq = eps_sq;
-  prm.min_eig = 1e-4;
-  uint8_t status;
-  int work[3] = {0, 0, 0};
-  lk_track_point(GroupWarp(), sm[wid], P0.lv, P1.lv, prm, px, py, nx, ny, status, work);
-  if ((threadIdx.x & 31) == 0) {
-    unsigned long long *wk = g_lk_work[blockIdx.x % LK_WORK_SLOTS];
-    atomicAdd(&wk[0], (unsigned long long)work[0]);
-    atomicAdd(&wk[1], (unsigned long long)work[1]);
-    atomicAdd(&wk[2], 1ull);
-    if (work[2]) atomicAdd(&wk[3], (unsigned long long)work[2]);
-    LkOut o{nx, ny};
+  // n_dev: a compact item list built on the device; its length is read here and the (single-warp) blocks stride over it
+  if (n_dev) n = *n_dev;
+  bool waited = false;
+  for (int i = blockIdx.x * LK_WARPS_PER_BLOCK + wid; i < n; i += gridDim.x * LK_WARPS_PER_BLOCK) {
+    const LkItem it = items[i];
+    float px = it.px, py = it.py, nx = it.nx, ny = it.ny;
+    if (it.prev_pyr < 0) continue;   // an unused slot of the device-side pipeline
+    if (!waited) {
+      pdl_wait();               // the refined corners (init_from_dev) and the kernel before this one's use of out_dev / status_dev
+      waited = true;
+    }
     const int at = out_idx ? out_idx[i] : i;     // results of a compact item list land where the full list has them
-    out_host[at] = o;
-    status_host[at] = status;
-    out_dev[at] = o;
-    status_dev[at] = status;
+    if (init_from_dev) {
+      px = nx = init_from_dev[2 * at];
+      py = ny = init_from_dev[2 * at + 1];
+    }
+    const PyrDesc &P0 = pyr_tab[it.prev_pyr], &P1 = pyr_tab[it.next_pyr];
+    LkParams prm;
+    prm.max_level = P0.nlv - 1;
+    prm.max_count = max_count;
+    prm.eps_sq = eps_sq;
+    prm.min_eig = 1e-4;
+    uint8_t status;
+    int work[3] = {0, 0, 0};
+    lk_track_point(GroupWarp(), sm[wid], P0.lv, P1.lv, prm, px, py, nx, ny, status, work);
+    if ((threadIdx.x & 31) == 0) {
+      unsigned long long *wk = g_lk_work[blockIdx.x % LK_WORK_SLOTS];
+      atomicAdd(&wk[0], (unsigned long long)work[0]);
+      atomicAdd(&wk[1], (unsigned long long)work[1]);
+      atomicAdd(&wk[2], 1ull);
+      if (work[2]) atomicAdd(&wk[3], (unsigned long long)work[2]);
+      LkOut o{nx, ny};
+      out_host[at] = o;
+      status_host[at] = status;
+      out_dev[at] = o;
+      status_dev[at] = status;
+    }
+    __syncwarp();
   }
 }
 
@@ -446,11 +461,13 @@ cudaError_t read_lk_work(unsigned long long out[4], int reset) {
 
 cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc *pyr_tab, const float *init_from_dev, int max_count,
                       double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev, bool overlap,
-                      const int *out_idx) {
+                      const int *out_idx, const int *n_dev) {
   if (n <= 0) return cudaSuccess;
+  int blocks = (n + LK_WARPS_PER_BLOCK - 1) / LK_WARPS_PER_BLOCK;
+  if (n_dev && blocks > 148 * 28) blocks = 148 * 28;   // one resident wave of single-warp blocks striding over the device-built list
   prof_mark(st, K_LK);
-  cudaError_t e = launch_after(k_lk, dim3((n + LK_WARPS_PER_BLOCK - 1) / LK_WARPS_PER_BLOCK), dim3(LK_WARPS_PER_BLOCK * 32), 0, st, overlap,
-                               items, n, pyr_tab, init_from_dev, max_count, eps * eps, out_host, status_host, out_dev, status_dev, out_idx);
+  cudaError_t e = launch_after(k_lk, dim3(blocks), dim3(LK_WARPS_PER_BLOCK * 32), 0, st, overlap,
+                               items, n, pyr_tab, init_from_dev, max_count, eps * eps, out_host, status_host, out_dev, status_dev, out_idx, n_dev);
   prof_mark(st, -1);
   return e != cudaSuccess ? e : cudaGetLastError();
 }
@@ -546,6 +563,7 @@ __device__ __forceinline__ DvSmem dv_smem(int P) {
 
 __global__ void __launch_bounds__(DV_THREADS) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
+  if (blockIdx.x == 0 && threadIdx.x < 4) X.n_items[threadIdx.x] = 0;   // the item lists select / assign append to (later kernels of this chain)
   for (int u = h.first; u < h.first + h.count; u++) dv_occupancy(GroupBlock(), units[u], X, dv_smem(P));
 }
 

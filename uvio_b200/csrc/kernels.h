@@ -78,14 +78,16 @@ cudaError_t launch_fast(cudaStream_t st, const FastJob *jobs, int njobs, int max
                         unsigned *ticket_dev, uint32_t *out_host, unsigned *count_host);
 
 cudaError_t launch_subpix(cudaStream_t st, const SubpixItem *items, int n, const PyrDesc *pyr_tab_dev, const float *mask_dev,
-                          float *out_xy /*2n*/, float *out_xy_dev /*2n, may be null*/);
+                          float *out_xy /*2n*/, float *out_xy_dev /*2n, may be null*/,
+                          const int *n_dev = nullptr /* device-built compact list: its length; item.pad = output slot */);
 
 // ---- tracking -----------------------------------------------------------------------------------------------------------
 // If init_from_dev != null, item i takes (px,py,nx,ny) from init_from_dev[2*i..] (used to chain subpix -> stereo LK).
 cudaError_t launch_lk(cudaStream_t st, const LkItem *items, int n, const PyrDesc *pyr_tab_dev, const float *init_from_dev,
                       int max_count, double eps, LkOut *out_host, uint8_t *status_host, LkOut *out_dev, uint8_t *status_dev,
                       bool overlap = false /* programmatic dependent launch: may start while the kernel before it in the stream runs */,
-                      const int *out_idx_dev = nullptr /* result i goes to out[out_idx[i]] instead of out[i] */);
+                      const int *out_idx_dev = nullptr /* result i goes to out[out_idx[i]] instead of out[i] */,
+                      const int *n_dev = nullptr /* device-built compact list: its length (n is then its capacity) */);
 
 // undistort old/new points of every job and run the fundamental-matrix RANSAC; mask = klt_status && inlier
 cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int max_n, const LkItem *items, const LkOut *lk_dev,

@@ -90,10 +90,12 @@ struct DvGlobals {
   uint32_t *fast_out;
   unsigned *fast_cnt;
   int *fast_active, *fast_n_active;  // job slots that hold a cell to scan, compacted (any order), and their number
-  SubpixItem *sp_items;
+  int *n_items;                   // [0] sub-pixel items, [1] stereo-LK items, [2] new-point temporal-LK items appended so far (zeroed by the occupancy kernel)
+  SubpixItem *sp_items;           // compact lists in any order: every item names the slot its result goes to
   const float *sp_out;            // [2 * slot]
-  LkItem *lk1_items;              // stereo LK of new left corners, indexed like the sub-pixel slots
-  const LkOut *lk1_out;
+  LkItem *lk1_items;              // stereo LK of new left corners; result slot = the corner's sub-pixel slot
+  int *lk1_out;
+  const LkOut *lk1_res;
   const uint8_t *lk1_status;
   LkItem *lk2_items;              // temporal LK of the points kept by the occupancy pass (issued right after it)
   LkItem *lk2n_items;             // temporal LK of the points detected in this feed, compact: unit slots [lkn_base, lkn_base + 2CK)
@@ -497,26 +499,24 @@ UVIO_HD void dv_select(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
   fdb_scan(g, U.scr_a, U.scr_b, CK, U.part);
   const int nsel = U.scr_b[CK];
   for (int idx = g.lane(); idx < CK; idx += g.size()) {
+    const int r = idx / U.K, k = idx - r * U.K;
     if (U.scr_a[idx]) {
-      const int r = idx / U.K, j = U.scr_b[idx];
+      const int j = U.scr_b[idx];
       float fx, fy;
       dv_corner_xy(U, L, r, L.top[idx], fx, fy);
-      X.sp_items[U.sp_base + j] = SubpixItem{fx, fy, L.det_pyr, 0};
-      // left -> right LK of the refined corner (TrackKLT.cpp:661-672): starts from the sub-pixel result of the same slot
-      X.lk1_items[U.sp_base + j] = LkItem{0, 0, 0, 0, U.stereo ? L.det_pyr : -1, U.stereo ? R.det_pyr : -1};
-    }
-    if (idx >= nsel) {
-      X.sp_items[U.sp_base + idx] = SubpixItem{0, 0, -1, 0};
-      X.lk1_items[U.sp_base + idx] = LkItem{0, 0, 0, 0, -1, -1};
+      X.sp_items[fdb_add_ret(&X.n_items[0], 1)] = SubpixItem{fx, fy, L.det_pyr, U.sp_base + j};
+      if (U.stereo) {   // left -> right LK of the refined corner (TrackKLT.cpp:661-672): starts from the sub-pixel result of the same slot
+        const int q = fdb_add_ret(&X.n_items[1], 1);
+        X.lk1_items[q] = LkItem{0, 0, 0, 0, L.det_pyr, R.det_pyr};
+        X.lk1_out[q] = U.sp_base + j;
+      }
     }
     // right: every top-K corner of every cell FAST ran on is refined (a superset of what the right top-up will take)
-    const int r = idx / U.K, k = idx - r * U.K;
-    SubpixItem it{0, 0, -1, 0};
     if (U.stereo && R.ctl[2] && r < R.ctl[1] && k < R.top_n[r]) {
+      SubpixItem it{0, 0, R.det_pyr, U.spr_base + idx};
       dv_corner_xy(U, R, r, R.top[idx], it.x, it.y);
-      it.pyr = R.det_pyr;
+      X.sp_items[fdb_add_ret(&X.n_items[0], 1)] = it;
     }
-    X.sp_items[U.spr_base + idx] = it;
   }
   if (g.lane() == 0) U.uctl[0] = nsel;
   g.sync();
@@ -582,7 +582,7 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
       int cls = 0;
       if (U.scr_b[j]) {
         const float x0 = refined[2 * j], y0 = refined[2 * j + 1];
-        const LkOut o = X.lk1_out[U.sp_base + j];
+        const LkOut o = X.lk1_res[U.sp_base + j];
         const bool oob_left = (int)x0 < 0 || (int)x0 >= L.w || (int)y0 < 0 || (int)y0 >= L.h;
         const bool oob_right = (int)o.x < 0 || (int)o.x >= R.w || (int)o.y < 0 || (int)o.y >= R.h;
         if (!oob_left && !oob_right && X.lk1_status[U.sp_base + j] == 1) cls = 2;
@@ -606,7 +606,7 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
     const int totalR = U.scr_b[nsel];
     for (int j = g.lane(); j < nsel; j += g.size())
       if (U.scr_d[j]) {
-        const LkOut o = X.lk1_out[U.sp_base + j];
+        const LkOut o = X.lk1_res[U.sp_base + j];
         const int d = U.scr_b[j];
         U.tmp_pts[2 * d] = o.x;
         U.tmp_pts[2 * d + 1] = o.y;
@@ -722,13 +722,12 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
     const int n = S.ctl[0];
     const bool run = !U.first && n >= 10;                                   // :848-852
     const int kept_old = S.ctl[4];
-    for (int j = g.lane(); j < U.C * U.K; j += g.size()) {                 // the points detected in this feed
-      const int i = kept_old + j;
-      LkItem it{0, 0, 0, 0, -1, -1};
-      if (run && i < n) it = LkItem{S.pts[2 * i], S.pts[2 * i + 1], S.pts[2 * i], S.pts[2 * i + 1], S.last_pyr, S.cur_pyr};
-      X.lk2n_items[U.lkn_base + side * U.C * U.K + j] = it;
-      X.lk2n_out[U.lkn_base + side * U.C * U.K + j] = U.lk_base + side * U.P + i;
-    }
+    if (run)
+      for (int i = kept_old + g.lane(); i < n; i += g.size()) {             // the points detected in this feed
+        const int q = fdb_add_ret(&X.n_items[2], 1);
+        X.lk2n_items[q] = LkItem{S.pts[2 * i], S.pts[2 * i + 1], S.pts[2 * i], S.pts[2 * i + 1], S.last_pyr, S.cur_pyr};
+        X.lk2n_out[q] = U.lk_base + side * U.P + i;
+      }
     if (run)                                                                // RANSAC undistorts the old positions from the item list
       for (int i = kept_old + g.lane(); i < n; i += g.size())
         X.lk2_items[U.lk_base + side * U.P + i] = LkItem{S.pts[2 * i], S.pts[2 * i + 1], S.pts[2 * i], S.pts[2 * i + 1], -1, -1};
@@ -762,11 +761,6 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
     j.run = 0;
     X.rs_jobs[U.rs_base + 1] = j;
   }
-  if (!U.stereo)
-    for (int j = g.lane(); j < U.C * U.K; j += g.size()) {
-      X.lk2n_items[U.lkn_base + U.C * U.K + j] = LkItem{0, 0, 0, 0, -1, -1};
-      X.lk2n_out[U.lkn_base + U.C * U.K + j] = U.lk_base + U.P;
-    }
   if (U.first && g.lane() == 0) *U.n_obs = 0;
   g.sync();
 }
