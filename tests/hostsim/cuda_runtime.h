@@ -3,6 +3,7 @@
 // launch_* functions are replaced by tests/hostsim/launch_sim.cpp, which runs the same kernel bodies with GroupSeq.
 // The product library is built by nvcc against the real runtime and never sees this file.
 #pragma once
+#define UVIO_NO_GRAPHS 1   // CUDA graphs have no host stand-in: the engine's plain-launch path is what the simulation runs
 #include <stdlib.h>
 #include <string.h>
 

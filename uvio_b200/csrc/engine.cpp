@@ -311,6 +311,11 @@ struct Lane {
   DevVec<LkItem> dv_lk1_items, dv_lk2_items, dv_lk2n_items;
   DevVec<int> dv_lk2n_out, dv_lk1_idx, dv_n_items;
   cudaEvent_t occ_done = nullptr;
+#ifndef UVIO_NO_GRAPHS
+  // the two kernel runs of the chain that have no external dependency inside them, captured once per batch shape
+  cudaGraphExec_t graph_detect = nullptr, graph_tail = nullptr;
+  unsigned long long graph_sig = 0, seen_sig = 0;
+#endif
   DevVec<LkOut> dv_lk1_out, dv_lk2_out;
   DevVec<uint8_t> dv_lk1_status, dv_lk2_status, dv_rs_mask, dv_rs_mask_raw;
   DevVec<RansacJob> dv_rs_jobs;
@@ -329,6 +334,10 @@ struct Lane {
     if (lk_go) cudaEventDestroy(lk_go);
     if (lk_done) cudaEventDestroy(lk_done);
     if (occ_done) cudaEventDestroy(occ_done);
+#ifndef UVIO_NO_GRAPHS
+    if (graph_detect) cudaGraphExecDestroy(graph_detect);
+    if (graph_tail) cudaGraphExecDestroy(graph_tail);
+#endif
   }
 };
 
@@ -2182,20 +2191,91 @@ int Pass::device_feed() {
     CU_TRY(launch_lk(ctx->lk_stream, ctx->dv_lk2_items.d, lk_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
                      ctx->dv_lk2_out.d, ctx->dv_lk2_status.d));
     CU_TRY(cudaEventRecord(ctx->lk_done, ctx->lk_stream));
-    CU_TRY(launch_dv_fast(st, X, dev->pyr_dev.d, job_slots, max_cw, max_ch));
-    CU_TRY(launch_dv_topk(st, U, nu, max_c, X));
-    CU_TRY(launch_dv_select(st, U, H, nheads, X, max_p));
-    CU_TRY(launch_subpix(st, ctx->dv_sp_items.d, sp_slots, dev->pyr_dev.d, ctx->sp_mask.d, ctx->dv_sp_out.d, nullptr, ctx->dv_n_items.d));
-    CU_TRY(launch_lk(st, ctx->dv_lk1_items.d, spl_slots, dev->pyr_dev.d, ctx->dv_sp_out.d, 30, 0.01, ctx->dv_lk1_out.d, ctx->dv_lk1_status.d,
-                     ctx->dv_lk1_out.d, ctx->dv_lk1_status.d, false, ctx->dv_lk1_idx.d, ctx->dv_n_items.d + 1));
-    CU_TRY(launch_dv_assign(st, U, H, nheads, X, max_p));
+    // The rest of the chain is two runs of kernels with nothing external between them: the detection (fast .. assign) and the
+    // tail (ransac, merge).  Once a batch shape has been seen twice they are replayed as CUDA graphs (one launch call each,
+    // no per-kernel launch gaps); what varies from feed to feed -- unit descriptors, item lists, counters -- lives in memory
+    // whose addresses do not change.  Shapes seen for the first time, first frames and profiled runs use plain launches.
+    auto detect_run = [&]() -> cudaError_t {
+      cudaError_t ce;
+      if ((ce = launch_dv_fast(st, X, dev->pyr_dev.d, job_slots, max_cw, max_ch)) != cudaSuccess) return ce;
+      if ((ce = launch_dv_topk(st, U, nu, max_c, X)) != cudaSuccess) return ce;
+      if ((ce = launch_dv_select(st, U, H, nheads, X, max_p)) != cudaSuccess) return ce;
+      if ((ce = launch_subpix(st, ctx->dv_sp_items.d, sp_slots, dev->pyr_dev.d, ctx->sp_mask.d, ctx->dv_sp_out.d, nullptr, ctx->dv_n_items.d)) != cudaSuccess) return ce;
+      if ((ce = launch_lk(st, ctx->dv_lk1_items.d, spl_slots, dev->pyr_dev.d, ctx->dv_sp_out.d, 30, 0.01, ctx->dv_lk1_out.d, ctx->dv_lk1_status.d,
+                          ctx->dv_lk1_out.d, ctx->dv_lk1_status.d, false, ctx->dv_lk1_idx.d, ctx->dv_n_items.d + 1)) != cudaSuccess) return ce;
+      return launch_dv_assign(st, U, H, nheads, X, max_p);
+    };
+    auto tail_run = [&]() -> cudaError_t {
+      cudaError_t ce = launch_ransac(st, ctx->dv_rs_jobs.d, 2 * nu, max_p, ctx->dv_lk2_items.d, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, dev->cam_dev.d,
+                                     ctx->dv_p0n.d, ctx->dv_p1n.d, ctx->dv_p1n.d, ctx->dv_rs_mask.d, ctx->dv_rs_mask_raw.d);
+      if (ce != cudaSuccess) return ce;
+      return launch_dv_merge(st, U, H, nheads, X, max_p);
+    };
+    bool use_graphs = false;
+#ifndef UVIO_NO_GRAPHS
+    static const bool graphs_on = [] {
+      const char *e = getenv("UVIO_KLT_GRAPHS");
+      return !(e && e[0] == '0');
+    }();
+    if (graphs_on && !ctx->prof_on && !any_first) {
+      unsigned long long sig = 1469598103934665603ull;
+      auto mix = [&](unsigned long long v) { sig = (sig ^ v) * 1099511628211ull; };
+      for (unsigned long long v : {(unsigned long long)nu, (unsigned long long)nheads, (unsigned long long)job_slots, (unsigned long long)sp_slots,
+                                   (unsigned long long)lk_slots, (unsigned long long)max_c, (unsigned long long)max_p, (unsigned long long)max_cw,
+                                   (unsigned long long)max_ch, (unsigned long long)(size_t)U, (unsigned long long)(size_t)H,
+                                   (unsigned long long)(size_t)X.fast_jobs, (unsigned long long)(size_t)X.fast_out, (unsigned long long)(size_t)X.fast_cnt,
+                                   (unsigned long long)(size_t)X.fast_active, (unsigned long long)(size_t)X.fast_n_active, (unsigned long long)(size_t)X.sp_items,
+                                   (unsigned long long)(size_t)X.sp_out, (unsigned long long)(size_t)X.lk1_items, (unsigned long long)(size_t)X.lk1_out,
+                                   (unsigned long long)(size_t)X.lk1_res, (unsigned long long)(size_t)X.lk1_status, (unsigned long long)(size_t)X.lk2_items,
+                                   (unsigned long long)(size_t)X.lk2n_items, (unsigned long long)(size_t)X.lk2n_out, (unsigned long long)(size_t)X.lk2_out,
+                                   (unsigned long long)(size_t)X.rs_jobs, (unsigned long long)(size_t)X.p1n, (unsigned long long)(size_t)X.rs_mask,
+                                   (unsigned long long)(size_t)X.n_items, (unsigned long long)(size_t)ctx->dv_lk2_status.d, (unsigned long long)(size_t)ctx->dv_p0n.d,
+                                   (unsigned long long)(size_t)ctx->dv_rs_mask_raw.d, (unsigned long long)(size_t)dev->pyr_dev.d,
+                                   (unsigned long long)(size_t)dev->cam_dev.d, (unsigned long long)(size_t)ctx->sp_mask.d})
+        mix(v);
+      if (sig == ctx->graph_sig && ctx->graph_detect && ctx->graph_tail) {
+        use_graphs = true;
+      } else if (sig == ctx->seen_sig) {       // second feed of this shape: capture (the plain launches of the first warmed everything up)
+        auto capture = [&](const std::function<cudaError_t()> &run, cudaGraphExec_t &exec) -> bool {
+          if (exec) { cudaGraphExecDestroy(exec); exec = nullptr; }
+          cudaGraph_t graph = nullptr;
+          if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
+          const cudaError_t ce = run();
+          const cudaError_t ee = cudaStreamEndCapture(st, &graph);
+          bool ok = ce == cudaSuccess && ee == cudaSuccess && graph != nullptr;
+          if (ok) ok = cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess;
+          if (graph) cudaGraphDestroy(graph);
+          if (!ok) { cudaGetLastError(); exec = nullptr; }
+          return ok;
+        };
+        if (capture(detect_run, ctx->graph_detect) && capture(tail_run, ctx->graph_tail)) {
+          ctx->graph_sig = sig;
+          use_graphs = true;
+        } else {
+          ctx->graph_sig = 0;
+        }
+      }
+      ctx->seen_sig = sig;
+    }
+#endif
+    if (use_graphs) {
+#ifndef UVIO_NO_GRAPHS
+      CU_TRY(cudaGraphLaunch(ctx->graph_detect, st));
+#endif
+    } else {
+      CU_TRY(detect_run());
+    }
     if (!any_first) CU_TRY(wait_new_frames());
     CU_TRY(launch_lk(st, ctx->dv_lk2n_items.d, sp_slots, dev->pyr_dev.d, nullptr, 30, 0.01, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d,
                      ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, false, ctx->dv_lk2n_out.d, ctx->dv_n_items.d + 2));
     CU_TRY(cudaStreamWaitEvent(st, ctx->lk_done, 0));
-    CU_TRY(launch_ransac(st, ctx->dv_rs_jobs.d, 2 * nu, max_p, ctx->dv_lk2_items.d, ctx->dv_lk2_out.d, ctx->dv_lk2_status.d, dev->cam_dev.d,
-                         ctx->dv_p0n.d, ctx->dv_p1n.d, ctx->dv_p1n.d, ctx->dv_rs_mask.d, ctx->dv_rs_mask_raw.d));
-    CU_TRY(launch_dv_merge(st, U, H, nheads, X, max_p));
+    if (use_graphs) {
+#ifndef UVIO_NO_GRAPHS
+      CU_TRY(cudaGraphLaunch(ctx->graph_tail, st));
+#endif
+    } else {
+      CU_TRY(tail_run());
+    }
     ctx->stats[1] += 11;
   } else {
     CU_TRY(wait_new_frames());
