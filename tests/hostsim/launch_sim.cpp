@@ -160,12 +160,21 @@ struct SimSmem {
     return DvSmem{a.data(), b.data(), p.data()};
   }
 };
-cudaError_t launch_dv_occupancy(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
+static DvUnit sim_unit(const DvUnit *units, int u, unsigned bits) {
+  DvUnit U = units[u];
+  dv_apply_feed(U, bits);
+  return U;
+}
+cudaError_t launch_dv_occupancy(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p,
+                                const DvFeedBits &bits) {
   if (getenv("UVIO_DV_TRACE")) fprintf(stderr, "[sim] device-side pipeline: %d trackers\n", n_heads);
   SimSmem sm;
   for (int k = 0; k < 4; k++) X.n_items[k] = 0;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_occupancy(GroupSeq(), units[u], X, sm.get(max_p));
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) {
+      X.feed_bits[u] = bits.v[u];
+      dv_occupancy(GroupSeq(), sim_unit(units, u, bits.v[u]), X, sm.get(max_p));
+    }
   return 0;
 }
 cudaError_t launch_dv_fast(cudaStream_t, const DvGlobals &X, const PyrDesc *pyr_tab, int, int, int) {
@@ -183,26 +192,26 @@ cudaError_t launch_dv_topk(cudaStream_t, const DvUnit *units, int n_units, int, 
   std::vector<uint32_t> buf(64);   // smaller than most cells: the in-place (global) sort path is exercised too
   for (int u = 0; u < n_units; u++)
     for (int side = 0; side < (units[u].stereo ? 2 : 1); side++)
-      for (int r = 0; r < units[u].C; r++) dv_topk(GroupSeq(), units[u], X, side, r, buf.data(), (int)buf.size());
+      for (int r = 0; r < units[u].C; r++) dv_topk(GroupSeq(), sim_unit(units, u, X.feed_bits[u]), X, side, r, buf.data(), (int)buf.size());
   return 0;
 }
 cudaError_t launch_dv_select(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   SimSmem sm;
   *X.fast_n_active = 0;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_select(GroupSeq(), units[u], X, sm.get(max_p));
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_select(GroupSeq(), sim_unit(units, u, X.feed_bits[u]), X, sm.get(max_p));
   return 0;
 }
 cudaError_t launch_dv_assign(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   SimSmem sm;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_assign(GroupSeq(), units[u], X, sm.get(max_p));
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_assign(GroupSeq(), sim_unit(units, u, X.feed_bits[u]), X, sm.get(max_p));
   return 0;
 }
 cudaError_t launch_dv_merge(cudaStream_t, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   SimSmem sm;
   for (int h = 0; h < n_heads; h++)
-    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_merge(GroupSeq(), units[u], X, sm.get(max_p));
+    for (int u = heads[h].first; u < heads[h].first + heads[h].count; u++) dv_merge(GroupSeq(), sim_unit(units, u, X.feed_bits[u]), X, sm.get(max_p));
   return 0;
 }
 

@@ -208,7 +208,6 @@ struct PreBuffers {              // job lists of one upload round (a lane's, or 
 struct Lane {
   Lane() {
     sp_items.prefer_mapped = lk_items.prefer_mapped = rs_jobs.prefer_mapped = true;
-    dv_units.prefer_mapped = dv_heads.prefer_mapped = true;   // read in place: a copy would queue behind the frames on the copy engine
     const char *e = getenv("UVIO_KLT_FAST_MAPPED");   // the FAST list is read by every tile block of a cell: copied (measured)
     fast_jobs.prefer_mapped = e && e[0] == '1';
   }
@@ -300,6 +299,9 @@ struct Lane {
   // device-side pipeline (Pass::device_feed): unit descriptors and the batch-wide job / result arrays, all in HBM
   JobVec<DvUnit> dv_units;
   JobVec<DvHead> dv_heads;
+  std::vector<DvUnit> dv_units_sent;   // what the device copies hold: descriptors go up only when the batch changed shape
+  std::vector<DvHead> dv_heads_sent;
+  DevVec<unsigned> dv_feed_bits;
   DevVec<FastJob> dv_fast_jobs;
   DevVec<uint32_t> dv_fast_out;
   DevVec<unsigned> dv_fast_cnt;
@@ -2051,8 +2053,16 @@ int Pass::device_feed() {
     if (e != OK) { ctx->cuda_err = dev->cuda_err; return e; }
   }
   const int nu = (int)units.size();
-  CU_TRY(ctx->dv_units.reserve((size_t)std::max(nu, 1)));
-  CU_TRY(ctx->dv_heads.reserve((size_t)std::max(n, 1)));
+  if (nu > DV_MAX_UNITS) return E_ARG;   // feed_batch cuts bigger batches into more groups
+  DvFeedBits feed_bits;
+  {
+    const DvUnit *du = ctx->dv_units.d;
+    const DvHead *dh = ctx->dv_heads.d;
+    CU_TRY(ctx->dv_units.reserve((size_t)std::max(nu, 1)));
+    CU_TRY(ctx->dv_heads.reserve((size_t)std::max(n, 1)));
+    if (du != ctx->dv_units.d) ctx->dv_units_sent.clear();   // the device copy moved: whatever it held is gone
+    if (dh != ctx->dv_heads.d) ctx->dv_heads_sent.clear();
+  }
   int job_slots = 0, sp_slots = 0, lk_slots = 0, max_c = 1, max_cw = 1, max_ch = 1, max_p = 1, nheads = 0;
   size_t fast_words = 0;
   bool any_first = false;
@@ -2067,7 +2077,7 @@ int Pass::device_feed() {
       memset(&U, 0, sizeof(U));
       const int unit_idx = u.stereo ? 0 : u.L.msg;
       U.stereo = u.stereo;
-      U.first = u.first && !u.failed;
+      unsigned fb = (unsigned)(u.first && !u.failed) | ((unsigned)rig.dv_wants_mirror << 1);
       any_first |= u.first;
       U.num_features = P.num_features;
       U.gx = P.grid_x; U.gy = P.grid_y; U.mpd = P.min_px_dist; U.fast_threshold = P.fast_threshold;
@@ -2086,10 +2096,10 @@ int Pass::device_feed() {
         DvSide &S = U.s[side];
         S.w = c.w; S.h = c.h;
         const int det_slot = u.first ? c.cur : c.last();
-        S.det_pyr = c.pyr[det_slot]; S.last_pyr = c.pyr[c.last()]; S.cur_pyr = c.pyr[c.cur];
+        for (int q = 0; q < PYR_SLOTS; q++) { S.pyr_slot[q] = c.pyr[q]; S.mask_slot[q] = m.mask[q]; }
+        static_assert(PYR_SLOTS == 3, "dv_apply_feed derives the last slot as (cur + 2) % 3");
+        fb |= dv_side_bits(det_slot, c.cur, c.mask_nonzero[det_slot], c.mask_nonzero[c.cur]) << (2 + 8 * side);
         S.cam_model = c.cam_model_idx; S.cam_id = c.cam_id; S.thr = 2.0 / c.max_focal;
-        S.det_mask = c.mask_nonzero[det_slot] ? m.mask[det_slot] : nullptr;
-        S.cur_mask = c.mask_nonzero[c.cur] ? m.mask[c.cur] : nullptr;
         S.pts_last = m.pts_last; S.ids_last = m.ids_last; S.n_last = m.n_last;
         S.pts = m.pts; S.ids = m.ids; S.close = m.close; S.first = m.first; S.grid = m.grid; S.cells = m.cells;
         S.top = m.top; S.top_n = m.top_n; S.ctl = m.ctl;
@@ -2109,7 +2119,7 @@ int Pass::device_feed() {
       lk_slots += 2 * D.P;
       max_c = std::max(max_c, D.C);
       max_p = std::max(max_p, D.P);
-      if (u.failed) { U.first = 1; U.num_features = 0; }   // (units of rejected messages never get here; kept for safety)
+      feed_bits.v[k] = fb;
       if (&rig != prev) {
         ctx->dv_heads.h[nheads++] = DvHead{k, 1};
         prev = &rig;
@@ -2163,8 +2173,18 @@ int Pass::device_feed() {
   X.lk2_items = ctx->dv_lk2_items.d; X.lk2_out = ctx->dv_lk2_out.d;
   X.lk2n_items = ctx->dv_lk2n_items.d; X.lk2n_out = ctx->dv_lk2n_out.d;
   X.rs_jobs = ctx->dv_rs_jobs.d; X.p1n = ctx->dv_p1n.d; X.rs_mask = ctx->dv_rs_mask.d;
-  CU_TRY(ctx->dv_units.upload(st, (size_t)nu));
-  CU_TRY(ctx->dv_heads.upload(st, (size_t)nheads));
+  // the descriptors live in device memory and go up only when they changed (a new batch shape, reallocated buffers): in
+  // steady state a feed uploads nothing but its frames -- what varies per feed travels in the occupancy kernel's parameters
+  if ((int)ctx->dv_units_sent.size() != nu || memcmp(ctx->dv_units_sent.data(), ctx->dv_units.h, sizeof(DvUnit) * (size_t)nu) != 0) {
+    CU_TRY(ctx->dv_units.upload(st, (size_t)nu));
+    ctx->dv_units_sent.assign(ctx->dv_units.h, ctx->dv_units.h + nu);
+  }
+  if ((int)ctx->dv_heads_sent.size() != nheads || memcmp(ctx->dv_heads_sent.data(), ctx->dv_heads.h, sizeof(DvHead) * (size_t)nheads) != 0) {
+    CU_TRY(ctx->dv_heads.upload(st, (size_t)nheads));
+    ctx->dv_heads_sent.assign(ctx->dv_heads.h, ctx->dv_heads.h + nheads);
+  }
+  CU_TRY(ctx->dv_feed_bits.reserve((size_t)DV_MAX_UNITS));
+  X.feed_bits = ctx->dv_feed_bits.d;
   // ---- the new frames go up and are pre-processed on the upload stream (frames announced by submit_batch are on their way) ----
   npre = (int)ctx->pre_items.size();
   {
@@ -2178,7 +2198,7 @@ int Pass::device_feed() {
     if (any_first) CU_TRY(wait_new_frames());   // first frames detect on the frame that is being uploaded (TrackKLT.cpp:110, :221)
     const DvUnit *U = ctx->dv_units.d;
     const DvHead *H = ctx->dv_heads.d;
-    CU_TRY(launch_dv_occupancy(st, U, H, nheads, X, max_p));
+    CU_TRY(launch_dv_occupancy(st, U, H, nheads, X, max_p, feed_bits));
     // The temporal LK of the points that survived the occupancy pass (the bulk of the feed's instructions) starts now, on the
     // lane's low-priority stream, beside the latency-bound detection chain; only the new points wait for the detection.
     CU_TRY(cudaEventRecord(ctx->occ_done, st));
@@ -2229,7 +2249,7 @@ int Pass::device_feed() {
                                    (unsigned long long)(size_t)X.lk1_res, (unsigned long long)(size_t)X.lk1_status, (unsigned long long)(size_t)X.lk2_items,
                                    (unsigned long long)(size_t)X.lk2n_items, (unsigned long long)(size_t)X.lk2n_out, (unsigned long long)(size_t)X.lk2_out,
                                    (unsigned long long)(size_t)X.rs_jobs, (unsigned long long)(size_t)X.p1n, (unsigned long long)(size_t)X.rs_mask,
-                                   (unsigned long long)(size_t)X.n_items, (unsigned long long)(size_t)ctx->dv_lk2_status.d, (unsigned long long)(size_t)ctx->dv_p0n.d,
+                                   (unsigned long long)(size_t)X.n_items, (unsigned long long)(size_t)X.feed_bits, (unsigned long long)(size_t)ctx->dv_lk2_status.d, (unsigned long long)(size_t)ctx->dv_p0n.d,
                                    (unsigned long long)(size_t)ctx->dv_rs_mask_raw.d, (unsigned long long)(size_t)dev->pyr_dev.d,
                                    (unsigned long long)(size_t)dev->cam_dev.d, (unsigned long long)(size_t)ctx->sp_mask.d})
         mix(v);
@@ -2308,6 +2328,7 @@ int Pass::device_collect() {
       ctx->stats[3] += 16ull * (size_t)c.dv_n_last;
     }
     rig.dv_mirror_stale = true;
+    rig.dv_mirror_published = rig.dv_wants_mirror;
     rig.currid = (size_t)*D.h_currid;   // the id counter's mirror (written by k_dv_assign)
   }
   ctx->stats[0] += (unsigned long long)n;
@@ -2325,6 +2346,7 @@ int Pass::device_collect() {
 }
 
 void dv_sync_mirror(Rig &rig) {
+  rig.dv_wants_mirror = true;   // whoever reads the last points once will do so again: later feeds publish them
   if (!rig.dv_mirror_stale || !rig.dv) return;
   DvRig &D = *rig.dv;
   for (size_t k = 0; k < rig.cams.size(); k++) {
@@ -2334,8 +2356,22 @@ void dv_sync_mirror(Rig &rig) {
     const int nl = c.dv_n_last;
     c.pts_last.resize((size_t)nl);
     c.ids_last.resize((size_t)nl);
-    if (nl) memcpy(c.pts_last.data(), m.h_pts_last, sizeof(Pt) * (size_t)nl);
-    for (int i = 0; i < nl; i++) c.ids_last[(size_t)i] = (size_t)m.h_ids_last[i];
+    if (!nl) continue;
+    if (rig.dv_mirror_published) {
+      memcpy(c.pts_last.data(), m.h_pts_last, sizeof(Pt) * (size_t)nl);
+      for (int i = 0; i < nl; i++) c.ids_last[(size_t)i] = (size_t)m.h_ids_last[i];
+    } else {                      // the feed did not publish: fetch from the device state (the feed that wrote it has been waited for)
+      std::vector<unsigned long long> ids((size_t)nl);
+      if (cudaSetDevice(rig.ctx->device) != cudaSuccess ||
+          cudaMemcpy(c.pts_last.data(), m.pts_last, sizeof(Pt) * (size_t)nl, cudaMemcpyDeviceToHost) != cudaSuccess ||
+          cudaMemcpy(ids.data(), m.ids_last, 8 * (size_t)nl, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        rig.last_error = E_CUDA;
+        c.pts_last.clear();
+        c.ids_last.clear();
+        continue;
+      }
+      for (int i = 0; i < nl; i++) c.ids_last[(size_t)i] = (size_t)ids[(size_t)i];
+    }
   }
   rig.dv_mirror_stale = false;
 }
@@ -2507,11 +2543,12 @@ int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
     // then one wait per group.  No host thread pool, no host bookkeeping between kernels.
     static const int max_groups = [] {
       const char *e = getenv("UVIO_KLT_GROUPS");
-      int v = e ? atoi(e) : 4;
+      int v = e ? atoi(e) : 2;
       return v < 1 ? 1 : (v > 16 ? 16 : v);
     }();
     for (auto &ln : ctx->lanes) cancel_ahead(*ln);
-    const int ng = std::max(1, std::min(std::min(max_groups, (int)ctx->lanes.size()), ((int)good.size() + 3) / 4));
+    const int need_groups = ((int)good.size() * 2 + DV_MAX_UNITS - 1) / DV_MAX_UNITS;   // a launch takes DV_MAX_UNITS units, a tracker has at most 2... per message image
+    const int ng = std::min((int)ctx->lanes.size(), std::max(1, std::max(need_groups, std::min(max_groups, ((int)good.size() + 3) / 4))));
     if (!ctx->bg_passes) ctx->bg_passes = new std::vector<Pass>;
     std::vector<Pass> &grp = *ctx->bg_passes;
     grp.clear();

@@ -110,6 +110,8 @@ class Rig {                     // one tracker = one TrackKLT instance
   CamState *find_cam(size_t id);
   struct DvRig *dv = nullptr;                       // device-side pipeline: the tracker's state and work areas in HBM (engine.cpp)
   bool dv_dirty = true;                             // pts_last / ids_last / currid changed on the host since the device copy was made
+  bool dv_wants_mirror = false;                     // somebody has read pts_last / ids_last: feeds publish them to mapped memory from now on
+  bool dv_mirror_published = false;                 // the last feed did
   bool dv_mirror_stale = false;                     // the last feed's pts_last / ids_last are still in mapped memory only (dv_sync_mirror)
   std::vector<std::pair<const Obs *, int>> dv_obs;  // the last feed's observations where the GPU wrote them (mapped memory), in order
   std::vector<Unit *> unit_pool;                    // scratch reused from feed to feed (keeps its vectors' capacity)

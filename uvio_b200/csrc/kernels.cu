@@ -561,10 +561,27 @@ __device__ __forceinline__ DvSmem dv_smem(int P) {
   return sm;
 }
 
-__global__ void __launch_bounds__(DV_THREADS) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
+// A block works on a private copy of its unit's descriptor in shared memory, with this feed's bits applied: the descriptor
+// array itself stays in device memory unchanged from feed to feed.
+__device__ __forceinline__ const DvUnit &dv_load_unit(DvUnit &sU, const DvUnit *units, int u, unsigned bits) {
+  __syncthreads();                                         // the previous unit's readers are done
+  const unsigned *src = (const unsigned *)&units[u];
+  unsigned *dst = (unsigned *)&sU;
+  for (int i = threadIdx.x; i < (int)(sizeof(DvUnit) / 4); i += blockDim.x) dst[i] = src[i];
+  __syncthreads();
+  if (threadIdx.x == 0) dv_apply_feed(sU, bits);
+  __syncthreads();
+  return sU;
+}
+
+__global__ void __launch_bounds__(DV_THREADS) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X, int P, DvFeedBits bits) {
+  __shared__ DvUnit sU;
   const DvHead h = heads[blockIdx.x];
   if (blockIdx.x == 0 && threadIdx.x < 4) X.n_items[threadIdx.x] = 0;   // the item lists select / assign append to (later kernels of this chain)
-  for (int u = h.first; u < h.first + h.count; u++) dv_occupancy(GroupBlock(), units[u], X, dv_smem(P));
+  for (int u = h.first; u < h.first + h.count; u++) {
+    if (threadIdx.x == 0) X.feed_bits[u] = bits.v[u];                   // for the kernels after this one (they may be replayed from a graph)
+    dv_occupancy(GroupBlock(), dv_load_unit(sU, units, u, bits.v[u]), X, dv_smem(P));
+  }
 }
 
 // FAST over the cells the occupancy kernel listed: a fixed grid walks (active job, tile) pairs
@@ -585,24 +602,32 @@ __global__ void __launch_bounds__(256) k_dv_fast(DvGlobals X, const PyrDesc *pyr
 // per-cell top-K in std::sort order: one block per job slot; grid = (2C max, units)
 __global__ void __launch_bounds__(DV_THREADS) k_dv_topk(const DvUnit *units, DvGlobals X) {
   __shared__ uint32_t buf[DV_TOPK_SMEM];
-  const DvUnit &U = units[blockIdx.y];
+  __shared__ DvUnit sU;
+  {
+    const DvUnit &G = units[blockIdx.y];
+    const int side0 = blockIdx.x / G.C;
+    if (side0 > 1 || (side0 == 1 && !G.stereo)) return;
+  }
+  const DvUnit &U = dv_load_unit(sU, units, blockIdx.y, X.feed_bits[blockIdx.y]);
   const int side = blockIdx.x / U.C, r = blockIdx.x - side * U.C;
-  if (side > 1 || (side == 1 && !U.stereo)) return;
   dv_topk(GroupBlock(), U, X, side, r, buf, DV_TOPK_SMEM);
 }
 
 __global__ void __launch_bounds__(DV_THREADS) k_dv_select(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
   if (blockIdx.x == 0 && threadIdx.x == 0) *X.fast_n_active = 0;   // FAST and the top-K are done with the list: re-armed for the next feed
-  for (int u = h.first; u < h.first + h.count; u++) dv_select(GroupBlock(), units[u], X, dv_smem(P));
+  __shared__ DvUnit sU;
+  for (int u = h.first; u < h.first + h.count; u++) dv_select(GroupBlock(), dv_load_unit(sU, units, u, X.feed_bits[u]), X, dv_smem(P));
 }
 __global__ void __launch_bounds__(DV_THREADS) k_dv_assign(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
-  for (int u = h.first; u < h.first + h.count; u++) dv_assign(GroupBlock(), units[u], X, dv_smem(P));
+  __shared__ DvUnit sU;
+  for (int u = h.first; u < h.first + h.count; u++) dv_assign(GroupBlock(), dv_load_unit(sU, units, u, X.feed_bits[u]), X, dv_smem(P));
 }
 __global__ void __launch_bounds__(DV_THREADS) k_dv_merge(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
-  for (int u = h.first; u < h.first + h.count; u++) dv_merge(GroupBlock(), units[u], X, dv_smem(P));
+  __shared__ DvUnit sU;
+  for (int u = h.first; u < h.first + h.count; u++) dv_merge(GroupBlock(), dv_load_unit(sU, units, u, X.feed_bits[u]), X, dv_smem(P));
 }
 
 template <class K>
@@ -612,12 +637,13 @@ static cudaError_t dv_smem_attr(K kernel, size_t bytes) {   // the attribute bel
 }
 static size_t dv_smem_bytes(int P) { return (size_t)P * 24; }
 
-cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
+cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p,
+                                const DvFeedBits &bits) {
   if (n_heads <= 0) return cudaSuccess;
   cudaError_t e = dv_smem_attr(k_dv_occupancy, dv_smem_bytes(max_p));
   if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_occupancy<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
+  k_dv_occupancy<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p, bits);
   prof_mark(st, -1);
   return cudaGetLastError();
 }

@@ -99,7 +99,9 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
 struct DvUnit;
 struct DvHead;
 struct DvGlobals;
-cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units_dev, const DvHead *heads_dev, int n_heads, const DvGlobals &X, int max_p);
+struct DvFeedBits;
+cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units_dev, const DvHead *heads_dev, int n_heads, const DvGlobals &X, int max_p,
+                                const DvFeedBits &bits /* by value in the kernel parameters: what changed since the last feed */);
 cudaError_t launch_dv_fast(cudaStream_t st, const DvGlobals &X, const PyrDesc *pyr_tab_dev, int n_slots, int max_cell_w, int max_cell_h);
 cudaError_t launch_dv_topk(cudaStream_t st, const DvUnit *units_dev, int n_units, int max_c, const DvGlobals &X);
 cudaError_t launch_dv_select(cudaStream_t st, const DvUnit *units_dev, const DvHead *heads_dev, int n_heads, const DvGlobals &X, int max_p);

@@ -31,12 +31,14 @@ struct DvObs {                    // == Obs / UvioObs
 
 struct DvSide {                   // one camera of a unit during one feed
   int w, h;
-  int det_pyr, last_pyr, cur_pyr; // pyramid table indices: detection image, temporal LK from / to
+  int pyr_slot[3];                // the camera's three pyramids (table indices); which is which in this feed comes with the feed bits
+  const uint8_t *mask_slot[3];    // device copies of the masks that go with them
+  int det_pyr, last_pyr, cur_pyr; // (derived per feed by dv_apply_feed) detection image, temporal LK from / to
   int cam_model;
   unsigned long long cam_id;
   double thr;                     // 2.0 / max focal length (TrackKLT.cpp:870-873)
-  const uint8_t *det_mask;        // mask of the detection image, pitch w (null = all zeros)
-  const uint8_t *cur_mask;        // mask of the message being fed (mono merge, :166)
+  const uint8_t *det_mask;        // (derived) mask of the detection image, pitch w (null = all zeros)
+  const uint8_t *cur_mask;        // (derived) mask of the message being fed (mono merge, :166)
   // persistent state (TrackBase.h:186-189 pts_last / ids_last), device memory
   float *pts_last;                // [2 * P]
   unsigned long long *ids_last;   // [P]
@@ -59,6 +61,7 @@ struct DvSide {                   // one camera of a unit during one feed
 
 struct DvUnit {
   int stereo, first;
+  int publish_last;                                // copy pts_last / ids_last to the host mirror at the end of the feed (someone reads them)
   int num_features, gx, gy, mpd, fast_threshold;   // TrackKLT ctor arguments (occupancy grid = gx x gy)
   int size_x, size_y, per_cell;                    // Grider_GRID geometry (Grider_GRID.h:88-100)
   int P, C, K;                                     // capacities: points per camera, cells, corners per cell
@@ -83,13 +86,37 @@ struct DvUnit {
   int obs_cap;
 };
 
-struct DvHead { int first, count; };   // the units of one tracker in this feed, handled by one block in order (they share currid)
+struct DvHead { int first, count; };
+
+// What changes from feed to feed in a unit's descriptor, packed in one word so that the descriptors themselves stay in device
+// memory untouched while the batch keeps its shape: bit 0 first frame, bit 1 publish pts_last / ids_last, then per side (8 bits
+// each, left from bit 2): detection slot (2), current slot (2), detection mask present (1), current mask present (1).
+constexpr int DV_MAX_UNITS = 256;                 // units per launch (a bigger batch is cut into more groups)
+struct DvFeedBits { unsigned v[DV_MAX_UNITS]; };
+UVIO_HD unsigned dv_side_bits(int det_slot, int cur_slot, bool det_mask, bool cur_mask) {
+  return (unsigned)det_slot | ((unsigned)cur_slot << 2) | ((unsigned)det_mask << 4) | ((unsigned)cur_mask << 5);
+}
+UVIO_HD void dv_apply_feed(DvUnit &U, unsigned bits) {
+  U.first = (int)(bits & 1u);
+  U.publish_last = (int)((bits >> 1) & 1u);
+  for (int side = 0; side < 2; side++) {
+    DvSide &S = U.s[side];
+    const unsigned b = bits >> (2 + 8 * side);
+    const int det = (int)(b & 3u), cur = (int)((b >> 2) & 3u);
+    S.det_pyr = S.pyr_slot[det];
+    S.cur_pyr = S.pyr_slot[cur];
+    S.last_pyr = S.pyr_slot[(cur + 2) % 3];
+    S.det_mask = ((b >> 4) & 1u) ? S.mask_slot[det] : nullptr;
+    S.cur_mask = ((b >> 5) & 1u) ? S.mask_slot[cur] : nullptr;
+  }
+}   // the units of one tracker in this feed, handled by one block in order (they share currid)
 
 struct DvGlobals {
   FastJob *fast_jobs;
   uint32_t *fast_out;
   unsigned *fast_cnt;
   int *fast_active, *fast_n_active;  // job slots that hold a cell to scan, compacted (any order), and their number
+  unsigned *feed_bits;            // [units] this feed's DvFeedBits, written by the occupancy kernel for the kernels after it
   int *n_items;                   // [0] sub-pixel items, [1] stereo-LK items, [2] new-point temporal-LK items appended so far (zeroed by the occupancy kernel)
   SubpixItem *sp_items;           // compact lists in any order: every item names the slot its result goes to
   const float *sp_out;            // [2 * slot]
@@ -749,7 +776,7 @@ UVIO_HD void dv_assign(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &s
       }
       if (g.lane() == 0) *S.n_last = n;
       g.sync();
-      dv_publish_side(g, S, n);
+      dv_publish_side(g, U, S, n);
     }
   }
   if (!U.stereo && g.lane() == 0) {                                         // the unused right slots of a mono unit
@@ -774,9 +801,11 @@ UVIO_HD void dv_copy_out(G g, void *dst, const void *src, size_t bytes) {
   for (size_t i = g.lane(); i < n16; i += g.size()) d[i] = q[i];
 }
 template <class G>
-UVIO_HD void dv_publish_side(G g, const DvSide &S, int n) {
-  dv_copy_out(g, S.h_pts_last, S.pts_last, sizeof(float) * 2 * (size_t)n);
-  dv_copy_out(g, S.h_ids_last, S.ids_last, sizeof(unsigned long long) * (size_t)n);
+UVIO_HD void dv_publish_side(G g, const DvUnit &U, const DvSide &S, int n) {
+  if (U.publish_last) {
+    dv_copy_out(g, S.h_pts_last, S.pts_last, sizeof(float) * 2 * (size_t)n);
+    dv_copy_out(g, S.h_ids_last, S.ids_last, sizeof(unsigned long long) * (size_t)n);
+  }
   if (g.lane() == 0) *S.h_n_last = n;
 }
 
@@ -825,7 +854,7 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm
       }
     if (g.lane() == 0) *L.n_last = total;
     g.sync();
-    dv_publish_side(g, L, total);
+    dv_publish_side(g, U, L, total);
     dv_copy_out(g, U.obs, U.obs_dev, sizeof(DvObs) * (size_t)(total < U.obs_cap ? total : U.obs_cap));
     if (g.lane() == 0) *U.n_obs = total;
     g.sync();
@@ -921,8 +950,8 @@ UVIO_HD void dv_merge(G g, const DvUnit &U, const DvGlobals &X, const DvSmem &sm
   }
   g.sync();
   const int n_obs = totL + nPair + nSolo;
-  dv_publish_side(g, L, totL);
-  dv_publish_side(g, R, nPair + nSolo);
+  dv_publish_side(g, U, L, totL);
+  dv_publish_side(g, U, R, nPair + nSolo);
   dv_copy_out(g, U.obs, U.obs_dev, sizeof(DvObs) * (size_t)(n_obs < U.obs_cap ? n_obs : U.obs_cap));
   if (g.lane() == 0) *U.n_obs = n_obs;
   g.sync();
