@@ -163,6 +163,59 @@ def pinned_hugepage_buffer(nbytes):
     return v
 
 
+def bind_near_gpu(local):
+    """Keep this rank's threads (and, by first touch, its frame ring) on the NUMA node the GPU's PCIe root hangs off:
+    with one rank per GPU on a two-socket host, uploads that cross the socket link share it with every other rank.
+    Applied only when sysfs names a node and at least four of its CPUs are in this process's affinity mask; returns what
+    was done for the JSON line."""
+    import torch
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return {"gpu_pci": bus, "numa_node": node, "bound": False}
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        mine = os.sched_getaffinity(0)
+        use = cpus & mine
+        if len(use) < 4 or use == mine:
+            return {"gpu_pci": bus, "numa_node": node, "bound": False, "cpus_allowed": len(mine), "cpus_on_node": len(use)}
+        os.sched_setaffinity(0, use)
+        return {"gpu_pci": bus, "numa_node": node, "bound": True, "cpus": len(use), "cpus_before": len(mine)}
+    except Exception as e:                                   # no sysfs entry, no permission: run unbound
+        return {"bound": False, "why": f"{type(e).__name__}: {e}"[:120]}
+
+
+def h2d_only_leg(hv, dev, device, feeds, dist):
+    """The uploads of the end-to-end leg and nothing else: one feed's frames per iteration, sliding through the same host
+    ring, every rank at once.  What it reaches is the ceiling the host's PCIe/memory fabric puts on the end-to-end figure."""
+    import torch
+    n_pool = hv.shape[0]
+    src = [torch.from_numpy(hv[t]) for t in range(n_pool)]
+    dst = dev[0]
+    for t in range(4):
+        dst.copy_(src[t % n_pool], non_blocking=True)
+    torch.cuda.synchronize(device)
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for t in range(feeds):
+        dst.copy_(src[pool_index(t, n_pool)], non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize(device)
+    sec = e0.elapsed_time(e1) / 1e3
+    if dist is not None:
+        tt = torch.tensor([sec], dtype=torch.float64, device=f"cuda:{device}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        sec = float(tt.item())
+        dist.barrier()
+    return sec
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------------
@@ -304,6 +357,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: the tracker has no CPU path")
     torch.cuda.set_device(local)
+    numa = bind_near_gpu(local) if os.environ.get("UVIO_BENCH_NUMA", "1") != "0" else {"bound": False, "why": "UVIO_BENCH_NUMA=0"}
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
@@ -335,6 +389,8 @@ def run_ours(args):
     sec, n_obs, clk, st, prof, wall = _run_leg(track, L, cfg, local, S, dev_pool, wf, tf, dist, obs_buf, counts, True, lk_only, announce)
     sec2, n_obs2, _c2, st2, _p2, wall2 = _run_leg(track, L, cfg, local, S, host_pool, wf, tf, dist, obs_buf, counts, False, lk_only, announce)
     sec3, _n3, _c3, st3, prof3, _w3 = _run_leg(track, L, cfg, local, S, dev_pool, R, min(tf, 4 * R), dist, obs_buf, counts, False, 1, announce)
+    sec_h2d = h2d_only_leg(hv, dev, local, min(tf, 8 * R), dist)
+    h2d_feed_bytes = float(S * 2 * h * w)
     lat = _latency_leg(track, L, cfg, local, host_pool, 60)
     lat_paced = _latency_leg(track, L, cfg, local, host_pool, 60, pause_s=0.003)
     # the one collective of the path: run statistics all-gathered over NCCL / NVLink
@@ -355,6 +411,11 @@ def run_ours(args):
                                           "masks": "NULL (documented as all zeros)"}),
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": st2["h2d_bytes"] / K,
                 "d2h_bytes_per_step": st2["d2h_bytes"] / K, "ms_per_step": 1e3 * sec2 / K, "ms_per_feed": 1e3 * sec2 / tf,
+                "upload_only": {"GB_per_s_per_gpu": h2d_feed_bytes * min(tf, 8 * R) / sec_h2d / 1e9,
+                                "frames_per_sec_ceiling": world * S * min(tf, 8 * R) / sec_h2d,
+                                "what": "the same frames copied from the same host ring with nothing else running, all ranks at "
+                                        "once (max over ranks): what the host's PCIe / memory fabric allows the end-to-end figure"},
+                "host_numa": numa,
                 "note": "uvio_klt_feed_batch + uvio_klt_get_new_observations_batch on pinned host frames (2 MiB-aligned transparent-huge-page "
                         "mapping, cudaHostRegister'ed)"
                         + ("; feed t+1 is announced with uvio_klt_submit_batch before feed t is issued, so its upload overlaps feed t "
