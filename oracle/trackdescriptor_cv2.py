@@ -155,6 +155,7 @@ class TrackDescriptorOracle:
         self.ids_last: Dict[int, List[int]] = {}
         self.desc_last: Dict[int, np.ndarray] = {}
         self.trace: Optional[dict] = None
+        self.ransac_sizes: List[int] = []          # symmetric matches handed to every robust_match so far, in call order
 
     def get_feature_database(self):
         return self.database
@@ -323,6 +324,7 @@ class TrackDescriptorOracle:
         _ratio_test(m01, self.knn_ratio)                                                  # :498-499
         _ratio_test(m10, self.knn_ratio)
         good = _symmetry_test(m01, m10)                                                   # :502-503
+        self.ransac_sizes.append(len(good))        # (test aid: 10..14 correspondences send cv::findFundamentalMat to LMedS)
         if len(good) < 10:                                                                # :517-518
             return []
         a = np.array([pts0[q] for (q, _t, _d) in good], np.float32)

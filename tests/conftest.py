@@ -44,12 +44,15 @@ SIM_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno
 def SIM_SOURCES():
     """engine + C ABIs over the CPU stand-ins of every launch wrapper (tests/hostsim)"""
     csrc = os.path.join(ROOT, "uvio_b200", "csrc")
-    return ([os.path.join(csrc, f) for f in ("engine.cpp", "abi.cpp", "featdb.cpp")] +
-            [os.path.join(SIM, f) for f in ("launch_sim.cpp", "featdb_sim.cpp")])
+    return ([os.path.join(csrc, f) for f in ("engine.cpp", "abi.cpp", "featdb.cpp", "desc_engine.cpp")] +
+            [os.path.join(SIM, f) for f in ("launch_sim.cpp", "featdb_sim.cpp", "desc_sim.cpp")])
 
 
 def sim_build(out, srcs, extra=()):
     import subprocess
+    if os.environ.get("UVIO_SIM_SANITIZE"):      # tools/asan_sim.sh: the same bodies under AddressSanitizer + UBSan
+        out = out.replace(os.sep + "_sim" + os.sep, os.sep + "_sim_asan" + os.sep)
+        extra = list(extra) + ["-fsanitize=address,undefined", "-fno-omit-frame-pointer", "-g", "-O1", "-fno-sanitize-recover=undefined"]
     os.makedirs(os.path.dirname(out), exist_ok=True)
     deps = srcs + [os.path.join(ROOT, "uvio_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "uvio_b200", "csrc"))]
     deps += [os.path.join(SIM, f) for f in os.listdir(SIM) if f.endswith((".cpp", ".h"))]

@@ -14,7 +14,7 @@ def _declared():
     for h in sorted(os.listdir(inc)):
         src = open(os.path.join(inc, h)).read()
         src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-        names |= set(re.findall(r"\b(uvio_(?:klt|featdb|tri)_\w+)\s*\(", src))
+        names |= set(re.findall(r"\b(uvio_(?:klt|featdb|tri|desc)_\w+)\s*\(", src))
     return sorted(names)
 
 

@@ -1,0 +1,159 @@
+"""the descriptor tracker (ov_core::TrackDescriptor) against oracle/trackdescriptor_cv2.py -- the
+reference's control flow restated line by line over the real cv2 kernels (ORB.compute, BFMatcher.knnMatch, findFundamentalMat).
+
+Bar: key-point positions, descriptors (256 bits each), camera ids and feature ids identical; normalised coordinates within
+1e-5.  One regime cannot be compared id for id: a robust_match that is left with 10..13 symmetric matches sends
+cv::findFundamentalMat to LMedS, whose outcome OpenCV itself does not reproduce under a one-ulp change of an input
+(profiles/r2_lmeds_probe.json).  Positions and descriptors of a frame do not depend on the temporal
+matches, so from the first such feed on the test keeps comparing everything but the ids.
+
+The same cases run (a) over the host simulation of the kernels (tests/hostsim, `not gpu`) and (b) on the GPU through the C ABI."""
+import os
+
+import numpy as np
+import pytest
+
+from uvio_b200 import configs, track
+from util import frames_for, log_arrays, masks_for
+
+
+def _lmeds(sizes):
+    return any(10 <= n <= 13 for n in sizes)
+
+
+def _run_case(make, cfg, n_frames, stream_id, mono=False, set_nf_at=None, knn_ratio=0.70):
+    from oracle.trackdescriptor_cv2 import make_descriptor_oracle
+    from uvio_b200 import desc
+    frames = frames_for(cfg, n_frames, stream_id=stream_id)
+    masks = masks_for(cfg)
+    o = make_descriptor_oracle(cfg, knn_ratio=knn_ratio)
+    t = make(cfg, knn_ratio=knn_ratio)
+    ids_comparable = True
+    compared_ids = 0
+    total_obs = 0
+    for k, (l, r) in enumerate(frames):
+        if set_nf_at and k in set_nf_at:
+            o.set_num_features(set_nf_at[k])
+            t.set_num_features(set_nf_at[k])
+        n0, g0, r0 = len(o.database.log), len(t.database.log), len(o.ransac_sizes)
+        cams = [0] if mono else [0, 1]
+        imgs = [l] if mono else [l, r]
+        o.feed_new_camera(0.05 * k, cams, imgs, masks[:len(cams)])
+        t.feed_new_camera(track.CameraData(0.05 * k, cams, imgs, masks[:len(cams)]))
+        sizes = o.ransac_sizes[r0:]
+        lr_lmeds = (not mono) and len(sizes) > 0 and 10 <= sizes[0] <= 13     # the stereo match of this frame: its points differ
+        if _lmeds(sizes):
+            ids_comparable = False
+        if lr_lmeds:
+            continue
+        oi, oc, ouv, oun = log_arrays(o.database.log[n0:])
+        gi, gc, guv, gun = log_arrays(t.database.log[g0:])
+        assert len(oi) == len(gi), f"frame {k}: {len(oi)} vs {len(gi)} observations"
+        assert (oc == gc).all() and (ouv == guv).all(), f"frame {k}: observation positions differ"
+        if len(oi):
+            assert np.abs(oun - gun).max() <= 1e-5
+        total_obs += len(oi)
+        if ids_comparable:
+            assert (oi == gi).all(), f"frame {k}: feature ids differ"
+            compared_ids += len(oi)
+        for cam in cams:
+            ids, uv, d = t._last(cam)
+            assert len(ids) == len(o.ids_last[cam])
+            assert (uv == o.pts_last[cam]).all(), f"frame {k} cam {cam}: pts_last differs"
+            assert (d == o.desc_last[cam]).all(), f"frame {k} cam {cam}: descriptors differ"
+            if ids_comparable:
+                assert (ids == np.array(o.ids_last[cam], np.uint64)).all(), f"frame {k} cam {cam}: ids_last differs"
+    t.close()
+    return total_obs, compared_ids
+
+
+CASES = [
+    ("EUROC_MAV", 8, 3, False),
+    ("EUROC_MAV", 6, 5, True),
+    ("TUM_VI", 5, 3, False),          # masks, equidistant model, reaches the LMedS regime at its 4th frame
+    ("RS_D455", 4, 2, False),         # CLAHE
+]
+
+
+@pytest.fixture()
+def sim_desc(sim_tracker):
+    """make(cfg) -> descriptor tracker over the host simulation (sim_tracker has pointed uvio_b200.track at the sim library)."""
+    from uvio_b200 import desc
+    yield lambda cfg, **kw: desc.make_descriptor_tracker(cfg, **kw)
+
+
+@pytest.mark.parametrize("name,n,stream,mono", CASES)
+def test_descriptor_tracker_matches_oracle_on_the_host_simulation(sim_desc, name, n, stream, mono):
+    obs, ids = _run_case(sim_desc, getattr(configs, name), n, stream, mono=mono)
+    assert obs > 100 and ids > 50
+
+
+def test_set_num_features_and_first_frames(sim_desc):
+    """25 features while initialising, then the full budget (VioManager.cpp:131, VioManagerHelper.cpp:124): the extraction grid,
+    K and the capacity of every list change between two feeds; pts_last / desc_last / ids_last survive the re-allocation."""
+    obs, _ = _run_case(sim_desc, configs.EUROC_MAV.with_(num_features=60), 6, 7, set_nf_at={3: 300})
+    assert obs > 100
+
+
+def test_error_codes_match_the_reference(sim_desc):
+    cfg = configs.EUROC_MAV
+    t = sim_desc(cfg)
+    (l, r), = frames_for(cfg, 1, stream_id=1)
+    z = np.zeros_like(l)
+    with pytest.raises(SystemExit):                         # sizes do not match: std::exit (TrackDescriptor.cpp:36-42)
+        t.feed_new_camera(track.CameraData(0.0, [0, 1], [l], [z, z]))
+    with pytest.raises(SystemExit):                         # three images on a stereo tracker (:57-58)
+        t.feed_new_camera(track.CameraData(0.0, [0, 1, 2], [l, r, l], [z, z, z]))
+    with pytest.raises(track.UvioError) as e:               # camera_calib.at() throws
+        t.feed_new_camera(track.CameraData(0.0, [0, 9], [l, r], [z, z]))
+    assert e.value.code == track.UVIO_E_CAMID
+    t.feed_new_camera(track.CameraData(0.0, [0, 1], [l, r], [z, z]))
+    with pytest.raises(track.UvioError) as e:
+        t.feed_new_camera(track.CameraData(0.05, [0, 1], [l[:-2], r[:-2]], [z[:-2], z[:-2]]))
+    assert e.value.code == track.UVIO_E_SIZE
+    t.close()
+
+
+# ---- the same on the GPU ------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,n,stream,mono", CASES + [("UZHFPV_INDOOR", 6, 4, False), ("HD_1000", 3, 1, False)])
+def test_descriptor_tracker_matches_oracle_on_the_gpu(name, n, stream, mono):
+    from uvio_b200 import desc
+    obs, ids = _run_case(lambda cfg, **kw: desc.make_descriptor_tracker(cfg, **kw), getattr(configs, name), n, stream, mono=mono)
+    assert obs > 100
+
+
+@pytest.mark.gpu
+def test_gpu_set_num_features():
+    from uvio_b200 import desc
+    obs, _ = _run_case(lambda cfg, **kw: desc.make_descriptor_tracker(cfg, **kw), configs.EUROC_MAV.with_(num_features=60), 6, 7, set_nf_at={3: 300})
+    assert obs > 100
+
+
+@pytest.mark.gpu
+def test_gpu_batch_equals_single_feeds():
+    """uvio_desc_feed_batch of 7 trackers (stereo and mono mixed) = the same trackers fed one at a time."""
+    from uvio_b200 import desc
+    cfg = configs.EUROC_MAV
+    masks = masks_for(cfg)
+    n_trk, n = 7, 4
+    seqs = [frames_for(cfg, n, stream_id=20 + s) for s in range(n_trk)]
+    mono = [s % 3 == 2 for s in range(n_trk)]
+
+    def msg(s, k):
+        l, r = seqs[s][k]
+        return track.CameraData(0.05 * k, [0], [l], masks[:1]) if mono[s] else track.CameraData(0.05 * k, [0, 1], [l, r], masks)
+
+    a = [desc.make_descriptor_tracker(cfg) for _ in range(n_trk)]
+    b = [desc.make_descriptor_tracker(cfg) for _ in range(n_trk)]
+    for k in range(n):
+        desc.feed_batch(a, [msg(s, k) for s in range(n_trk)])
+        for s in range(n_trk):
+            b[s].feed_new_camera(msg(s, k))
+    for s in range(n_trk):
+        assert a[s].database.log == b[s].database.log and len(a[s].database.log) > 50
+        for cam in ([0] if mono[s] else [0, 1]):
+            for x, y in zip(a[s]._last(cam), b[s]._last(cam)):
+                assert (x == y).all()
+    for t in a + b:
+        t.close()
