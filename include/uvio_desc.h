@@ -58,6 +58,8 @@ int uvio_desc_get_last(uvio_desc *h, size_t cam_id, size_t *ids, float *uv, int 
 int uvio_desc_get_last_descriptors(uvio_desc *h, size_t cam_id, uint8_t *desc, int cap, int *n);
 /* TrackBase::set_num_features (TrackBase.h:152). */
 int uvio_desc_set_num_features(uvio_desc *h, int n);
+/* TrackBase::change_feat_id (TrackBase.cpp:230-248), the part that sticks: every id_old in ids_last becomes id_new. */
+int uvio_desc_change_feat_id(uvio_desc *h, size_t id_old, size_t id_new);
 int uvio_desc_cuda_error(uvio_desc *h);
 /* CUDA-event time of the last feed (or batch) this tracker was part of, upload to results, in microseconds. */
 int uvio_desc_get_timing(uvio_desc *h, float *us);

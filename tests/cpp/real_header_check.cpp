@@ -6,6 +6,7 @@
 // them, and the estimator's calls through std::shared_ptr<TrackBase> bind (VioManager.cpp:133-135, VioManagerHelper.cpp:124,
 // :209-210, :235-237).  g++ -fsyntax-only; nothing is linked or run.
 #define UVIO_USE_REAL_OV_CORE
+#include "uvio_b200/cpp/TrackDescriptorGpu.h"
 #include "uvio_b200/cpp/TrackKLTGpu.h"
 
 int main() {
@@ -19,5 +20,11 @@ int main() {
   ov_core::CameraData message;
   trackFEATS->feed_new_camera(message);
   std::shared_ptr<ov_core::FeatureDatabase> db = trackFEATS->get_feature_database();
+  // the descriptor tracker behind the same base pointer (VioManager.cpp:137-140)
+  std::shared_ptr<ov_core::TrackBase> trackDESC(
+      new ov_core::TrackDescriptorGpu(cams, 25, 0, true, ov_core::TrackBase::HistogramMethod::HISTOGRAM, 20, 5, 5, 10, 0.70));
+  trackDESC->set_num_features(150);
+  trackDESC->feed_new_camera(message);
+  trackDESC->change_feat_id(1, 2);
   return (int)last_obs.size() + (int)last_ids.size() + (db ? 1 : 0);
 }

@@ -157,3 +157,50 @@ def test_gpu_batch_equals_single_feeds():
                 assert (x == y).all()
     for t in a + b:
         t.close()
+
+
+# ---- committed golden sequences (tests/golden/desc_*.npz, made by tests/golden/make_desc_golden.py): no cv2 at run time ----------
+def _check_golden(make, name):
+    from uvio_b200.synth import frames_checksum
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"desc_{name}.npz"))
+    cfg = {"euroc_mav": configs.EUROC_MAV, "euroc_mono": configs.EUROC_MAV, "uzhfpv_indoor": configs.UZHFPV_INDOOR}[name]
+    n, mono = int(g["n_frames"]), bool(g["mono"])
+    frames = frames_for(cfg, n, stream_id=int(g["stream_id"]))
+    assert frames_checksum([f for lr in frames for f in lr]) == int(g["frames_checksum"]), "synthetic generator drifted"
+    masks = masks_for(cfg)
+    t = make(cfg)
+    ok_until = int(g["ids_ok_until"])
+    total = 0
+    for k, (l, r) in enumerate(frames):
+        cams = [0] if mono else [0, 1]
+        t.feed_new_camera(track.CameraData(0.05 * k, cams, [l] if mono else [l, r], masks[:len(cams)]))
+        sizes = g[f"ransac_sizes_{k}"]
+        if (not mono) and len(sizes) and 10 <= sizes[0] <= 13:
+            continue
+        obs = t.new_observations()
+        assert np.array_equal(obs["cam_id"].astype(np.int8), g[f"cams_{k}"])
+        assert np.array_equal(np.c_[obs["u"], obs["v"]].reshape(-1, 2), g[f"uv_{k}"].reshape(-1, 2)), f"{name} frame {k}: positions differ"
+        if len(obs):
+            assert np.abs(np.c_[obs["un"], obs["vn"]] - g[f"uvn_{k}"]).max() <= 1e-5
+        if k < ok_until:
+            assert np.array_equal(obs["id"].astype(np.int64), g[f"ids_{k}"]), f"{name} frame {k}: ids differ"
+        for c in cams:
+            ids, uv, d = t._last(c)
+            assert np.array_equal(uv, g[f"last_uv_{k}_{c}"]) and np.array_equal(d, g[f"last_desc_{k}_{c}"]), f"{name} frame {k} cam {c}"
+            if k < ok_until:
+                assert np.array_equal(ids.astype(np.int64), g[f"last_ids_{k}_{c}"])
+        total += len(obs)
+    t.close()
+    assert total > 300 and ok_until >= 3
+
+
+@pytest.mark.parametrize("name", ["euroc_mav", "euroc_mono", "uzhfpv_indoor"])
+def test_golden_sequences_on_the_host_simulation(sim_desc, name):
+    _check_golden(sim_desc, name)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["euroc_mav", "euroc_mono", "uzhfpv_indoor"])
+def test_golden_sequences_on_the_gpu(name):
+    from uvio_b200 import desc
+    _check_golden(lambda cfg: desc.make_descriptor_tracker(cfg), name)

@@ -41,7 +41,7 @@ struct DescCam {                      // per camera id: TrackBase.h:180-189 img_
   int K = 0, size_x = 0, size_y = 0, ct_cols = 0, ct_rows = 0, ncells = 0, cell_cap = 0, P = 0;
   // device memory
   void *base = nullptr;
-  uint8_t *raw = nullptr, *eq = nullptr, *mask = nullptr;
+  uint8_t *eq = nullptr, *mask = nullptr;   // (the uploaded frame itself lives in the launch arena: it is consumed by k_preprocess)
   int raw_pitch = 0, eq_pitch = 0;
   bool mask_zero = false;
   DescSide side{};                    // the pointers of this camera's lists (everything but the per-launch indices)
@@ -173,7 +173,7 @@ int cam_alloc(DescRig &rig, DescCam &c, int P) {
   Carver cv;
   c.raw_pitch = (int)align_up(c.w, 16);
   c.eq_pitch = (int)align_up(c.w, 128);
-  const size_t o_raw = cv.take<uint8_t>((size_t)c.raw_pitch * c.h), o_eq = cv.take<uint8_t>((size_t)c.eq_pitch * c.h), o_mask = cv.take<uint8_t>((size_t)c.w * c.h);
+  const size_t o_eq = cv.take<uint8_t>((size_t)c.eq_pitch * c.h), o_mask = cv.take<uint8_t>((size_t)c.w * c.h);
   const size_t o_top = cv.take<uint32_t>((size_t)c.ncells * c.K), o_cn = cv.take<int>(c.ncells), o_cnt = cv.take<int>(8);
   const size_t o_kxy = cv.take<float>(2 * (size_t)P), o_kd = cv.take<uint32_t>(8 * (size_t)P);
   const size_t o_nxy = cv.take<float>(2 * (size_t)P), o_nd = cv.take<uint32_t>(8 * (size_t)P), o_nid = cv.take<unsigned long long>(P);
@@ -182,7 +182,6 @@ int cam_alloc(DescRig &rig, DescCam &c, int P) {
   CK(cudaMalloc((void **)&b, cv.off + 256));
   CK(cudaMemsetAsync(b, 0, cv.off + 256, ctx.st));
   c.base = b;
-  c.raw = (uint8_t *)(b + o_raw);
   c.eq = (uint8_t *)(b + o_eq);
   c.mask = (uint8_t *)(b + o_mask);
   c.mask_zero = true;
@@ -377,7 +376,7 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
   // ---- lay the launch tables out ------------------------------------------------------------------------------------------------------
   const int n_units = (int)plan.size();
   int n_sides = 0, n_jobs = 0, slots = 0, max_cells = 0, max_p = 0, max_cw = 0, max_ch = 0, max_band = 0, any_clahe = 0;
-  size_t corner_words = 0;
+  size_t corner_words = 0, raw_bytes = 0;
   for (const UnitPlan &p : plan)
     for (int k = 0; k < p.n_cam; k++) {
       const DescCam &c = p.rig->cams[p.cam[k]];
@@ -385,6 +384,7 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
       n_jobs += c.ncells;
       slots += c.P;
       corner_words += (size_t)c.ncells * c.cell_cap;
+      raw_bytes += (size_t)c.raw_pitch * c.h;
       max_cells = std::max(max_cells, c.ncells);
       max_p = std::max(max_p, c.P);
       max_cw = std::max(max_cw, c.size_x);
@@ -401,6 +401,7 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
   const size_t zero_bytes = ar.off - o_cnt;
   const size_t o_corners = ar.take<uint32_t>(corner_words), o_items = ar.take<SubpixItem>(slots), o_spout = ar.take<float>(2 * (size_t)slots);
   const size_t o_clahe = ar.take<uint8_t>(any_clahe ? (size_t)n_sides * 64 * 256 : 1);
+  const size_t o_raw = ar.take<uint8_t>(raw_bytes);      // the uploaded frames, in batch order: adjacent host frames go up as one copy
   if (ar.off + 256 > ctx.arena_bytes) {
     if (ctx.arena) cudaFree(ctx.arena);
     ctx.arena = nullptr;
@@ -442,9 +443,16 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
   CKF(cudaEventRecord(ctx.ev0, st));
   // ---- uploads and tables --------------------------------------------------------------------------------------------------------------
   int side_i = 0, job_i = 0, slot_i = 0;
-  size_t corner_i = 0;
-  int req_i = -1;
-  const DescRig *prev_rig = nullptr;
+  size_t corner_i = 0, raw_i = 0;
+  // copies whose source and destination both continue the previous one are merged (a batch of tightly packed frames is one copy)
+  uint8_t *pend_dst = nullptr;
+  const uint8_t *pend_src = nullptr;
+  size_t pend_bytes = 0;
+  auto flush = [&]() -> cudaError_t {
+    cudaError_t e = pend_bytes ? cudaMemcpyAsync(pend_dst, pend_src, pend_bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+    pend_bytes = 0;
+    return e;
+  };
   std::vector<const UvioFrame *> unit_frame(n_units);
   {
     int u = 0;
@@ -455,8 +463,6 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
       for (int q = 0; q < k; q++) unit_frame[u++] = reqs[i].f;
     }
   }
-  (void)req_i;
-  (void)prev_rig;
   for (int u = 0; u < n_units; u++) {
     const UnitPlan &p = plan[u];
     DescRig &rig = *p.rig;
@@ -491,8 +497,23 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
       if (is_device_ptr(f.img[mi])) {
         src = ImgView{f.img[mi], c.w, c.h, (int)f.img_stride[mi]};
       } else {
-        CKF(cudaMemcpy2DAsync(c.raw, c.raw_pitch, f.img[mi], f.img_stride[mi], c.w, c.h, cudaMemcpyHostToDevice, st));
-        src = ImgView{c.raw, c.w, c.h, c.raw_pitch};
+        uint8_t *raw = (uint8_t *)(A + o_raw) + raw_i;
+        const size_t span = (size_t)c.raw_pitch * c.h;
+        if ((size_t)c.raw_pitch == f.img_stride[mi] && c.raw_pitch == c.w) {
+          if (pend_bytes && pend_src + pend_bytes == f.img[mi] && pend_dst + pend_bytes == raw) {
+            pend_bytes += span;
+          } else {
+            CKF(flush());
+            pend_dst = raw;
+            pend_src = f.img[mi];
+            pend_bytes = span;
+          }
+        } else {
+          CKF(flush());
+          CKF(cudaMemcpy2DAsync(raw, c.raw_pitch, f.img[mi], f.img_stride[mi], c.w, c.h, cudaMemcpyHostToDevice, st));
+        }
+        src = ImgView{raw, c.w, c.h, c.raw_pitch};
+        raw_i += span;
       }
       // mask (TrackDescriptor.cpp:83, :204-205: the message's mask is the one Grider_FAST tests)
       const uint8_t *m = f.mask ? f.mask[mi] : nullptr;
@@ -536,6 +557,7 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
     U.thr[1] = 1.0 / c0.max_focal;
     U.thr[2] = 1.0 / c1.max_focal;
   }
+  CKF(flush());
   if (corner_i >= (size_t)0x7fffffff) return fail_cuda((int)cudaErrorInvalidValue);
   CKF(cudaMemcpyAsync(A, H, tab_bytes, cudaMemcpyHostToDevice, st));
   CKF(cudaMemsetAsync(A + o_cnt, 0, zero_bytes, st));
@@ -774,6 +796,27 @@ int uvio_desc_set_num_features(uvio_desc *h, int n) {
   if (!h || n <= 0) return UVIO_E_ARG;
   std::lock_guard<std::mutex> lk(h->rig->mtx);
   h->rig->prm.num_features = n;       // the extraction grid is re-derived at the next feed (Grider_FAST.h:83-103)
+  return UVIO_OK;
+  GUARD_END
+}
+
+int uvio_desc_change_feat_id(uvio_desc *h, size_t id_old, size_t id_new) {
+  GUARD_BEGIN
+  if (!h) return UVIO_E_ARG;
+  DescRig &rig = *h->rig;
+  std::lock_guard<std::mutex> lk(rig.mtx);
+  std::lock_guard<std::mutex> lc(rig.ctx->mtx);
+  if (cudaSetDevice(rig.ctx->device) != cudaSuccess) return UVIO_E_CUDA;
+  for (DescCam &c : rig.cams) {                       // TrackBase.cpp:241-247: every camera's ids_last
+    if (c.n_last <= 0 || !c.base) continue;
+    std::vector<unsigned long long> ids(c.n_last);
+    cudaError_t e = cudaMemcpy(ids.data(), c.side.la_ids, sizeof(unsigned long long) * c.n_last, cudaMemcpyDeviceToHost);
+    bool any = false;
+    for (auto &v : ids)
+      if (v == (unsigned long long)id_old) { v = (unsigned long long)id_new; any = true; }
+    if (e == cudaSuccess && any) e = cudaMemcpy(c.side.la_ids, ids.data(), sizeof(unsigned long long) * c.n_last, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { rig.cuda_error = (int)e; return UVIO_E_CUDA; }
+  }
   return UVIO_OK;
   GUARD_END
 }

@@ -37,6 +37,7 @@ def lib():
         L.uvio_desc_get_last.argtypes = [vp, sz, vp, vp, ci, C.POINTER(ci)]
         L.uvio_desc_get_last_descriptors.argtypes = [vp, sz, vp, ci, C.POINTER(ci)]
         L.uvio_desc_set_num_features.argtypes = [vp, ci]
+        L.uvio_desc_change_feat_id.argtypes = [vp, sz, sz]
         L.uvio_desc_cuda_error.argtypes = [vp]
         L.uvio_desc_get_timing.argtypes = [vp, C.POINTER(C.c_float)]
         _bound = L
@@ -137,6 +138,15 @@ class TrackDescriptor:
         rc = lib().uvio_desc_set_num_features(self._h, int(n))
         if rc != UVIO_OK:
             raise UvioError(rc, "uvio_desc_set_num_features")
+
+    def change_feat_id(self, id_old: int, id_new: int):
+        """TrackBase.cpp:230-248: only feat->featid and ids_last change."""
+        f = self.database.features_idlookup.get(id_old)
+        if f is not None:
+            f.featid = id_new
+        rc = lib().uvio_desc_change_feat_id(self._h, int(id_old), int(id_new))
+        if rc != UVIO_OK:
+            raise UvioError(rc, "uvio_desc_change_feat_id")
 
     def last_feed_us(self) -> float:
         v = C.c_float(0)
