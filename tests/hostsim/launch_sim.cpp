@@ -13,7 +13,7 @@
 namespace uvio {
 
 cudaError_t launch_preprocess(cudaStream_t, const PreJob *jobs, int njobs, const PyrDesc *pyr_tab, uint8_t *,
-                              int, int) {
+                              int, int, int, int, int) {
   GroupSeq g;
   for (int j = 0; j < njobs; j++) {
     const ImgView I = jobs[j].src;

@@ -1468,7 +1468,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
   HOSTPROF(s0_memcpy);
   const int nimg = (int)items.size();
   if (nimg == 0) return OK;
-  int any_clahe = 0, max_band = 0, ndown = 0, max_dw = 1, max_dh = 1, n_down_jobs = 0;
+  int any_clahe = 0, max_band = 0, ndown = 0, max_dw = 1, max_dh = 1, n_down_jobs = 0, max_w = 0, max_h = 0, max_nlv = 0;
   std::vector<char> on_dev((size_t)nimg, 0);
   for (auto &it : items) {
     any_clahe |= it.method == 2;
@@ -1504,6 +1504,9 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
     const HostImage &im = it.im;
     B.pre->h[j] = PreJob{ctx->raw_tab[it.downsample ? c.raw : c.raw_in[it.par]], c.pyr[it.slot], it.method};
     max_band = std::max(max_band, ((c.h + 7) / 8 + 1) * c.w);
+    max_w = std::max(max_w, c.w);
+    max_h = std::max(max_h, c.h);
+    max_nlv = std::max(max_nlv, ctx->pyr_tab[c.pyr[it.slot]].nlv);
     cudaPointerAttributes attr;
     const bool on_device = cudaPointerGetAttributes(&attr, im.p) == cudaSuccess &&
                            (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
@@ -1568,7 +1571,7 @@ static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, 
     }
     HOSTPROF(s0_launch_preprocess);
     CU_TRY(launch_preprocess(st, B.pre->d + g0, g1 - g0, ctx->pyr_dev.d, any_clahe ? B.clahe->d + (size_t)g0 * CLAHE_TILES * CLAHE_TILES * 256 : nullptr,
-                             any_clahe, max_band));
+                             any_clahe, max_band, max_w, max_h, max_nlv));
     stats[1] += (unsigned)(1 + 2 * any_clahe);
   }
   return OK;

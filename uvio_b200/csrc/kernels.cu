@@ -64,7 +64,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
 }
 
 __global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREADS, 1024 / PRE_THREADS)
-    k_preprocess(const PreJob *jobs, const PyrDesc *pyr_tab, int band_bytes) {
+    k_preprocess(const PreJob *jobs, const PyrDesc *pyr_tab, int band_bytes, int with_pyramid) {
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
   const PreJob job = jobs[blockIdx.y];
@@ -151,7 +151,7 @@ __global__ void __cluster_dims__(PRE_CLUSTER, 1, 1) __launch_bounds__(PRE_THREAD
   if (job.method != 2) lut_rows(g, lut, I, dst0, D0.pitch, r0, r1);   // CLAHE wrote level 0 already
   // pyramid: one lane per 4 x PD_ROWS output strip, the whole cluster per level
   const int gtid = rank * PRE_THREADS + threadIdx.x;
-  for (int l = 1; l < P.nlv; l++) {
+  for (int l = 1; l < P.nlv && with_pyramid; l++) {
     cluster.sync();   // level l-1 is complete (also keeps every block alive while its histogram may still be read)
     const ImgView S = P.lv[l - 1], D = P.lv[l];
     const int nsx = (D.w + PD_COLS - 1) / PD_COLS, nsy = (D.h + PD_ROWS - 1) / PD_ROWS;
@@ -193,8 +193,23 @@ __global__ void __launch_bounds__(256) k_clahe_apply(const PreJob *jobs, const P
       ((uint8_t *)D.p)[(size_t)y * D.pitch + x] = clahe_pixel(L, q, x, y, I.p[(size_t)y * I.pitch + x]);
 }
 
+// One pyramid level of every job in its own launch: one lane per 4 x 4 output strip, grid = (strip chunks, jobs).  With the
+// levels inside k_preprocess a cluster of 8 x 512 lanes walks 5,640 / 1,410 / 360 / 96 strips of a 752x480 frame between
+// cluster barriers (lanes mostly idle, 55 % of warp samples at the barriers); here every level of the whole batch is one
+// barrier-free launch that fills the GPU.
+__global__ void __launch_bounds__(256) k_pyrdown_level(const PreJob *jobs, const PyrDesc *pyr_tab, int level) {
+  const PyrDesc &P = pyr_tab[jobs[blockIdx.y].pyr];
+  if (level >= P.nlv) return;
+  const ImgView S = P.lv[level - 1], D = P.lv[level];
+  const int nsx = (D.w + PD_COLS - 1) / PD_COLS, nsy = (D.h + PD_ROWS - 1) / PD_ROWS;
+  for (int sidx = blockIdx.x * 256 + threadIdx.x; sidx < nsx * nsy; sidx += gridDim.x * 256) {
+    int sy = sidx / nsx, sx = sidx - sy * nsx;
+    pyrdown_strip(S, (uint8_t *)D.p, D.w, D.h, D.pitch, sx * PD_COLS, sy * PD_ROWS);
+  }
+}
+
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const PyrDesc *pyr_tab,
-                              uint8_t *clahe_lut, int any_clahe, int max_band_bytes) {
+                              uint8_t *clahe_lut, int any_clahe, int max_band_bytes, int max_w, int max_h, int max_nlv) {
   if (njobs <= 0) return cudaSuccess;
   // dynamic shared memory for the staged band of rows (0 = bands too large: the kernel reads global memory directly)
   int band_bytes = max_band_bytes <= PRE_MAX_BAND_BYTES ? (max_band_bytes + 127) / 128 * 128 : 0;
@@ -217,8 +232,21 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
     prof_mark(st, K_CLAHE_APPLY);
     k_clahe_apply<<<dim3(HIST_BANDS * 2, njobs), 256, 0, st>>>(jobs, pyr_tab, clahe_lut);
   }
+  // max_nlv > 1 with the frame size given: the pyramid levels go in launches of their own (UVIO_KLT_PYR=fused keeps them inside)
+  static const bool fused_env = [] { const char *e = getenv("UVIO_KLT_PYR"); return e && !strcmp(e, "fused"); }();
+  const bool split = max_nlv > 1 && max_w > 0 && max_h > 0 && !fused_env;
   prof_mark(st, K_PREPROCESS);
-  k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, band_bytes, st>>>(jobs, pyr_tab, band_bytes);
+  k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, band_bytes, st>>>(jobs, pyr_tab, band_bytes, split ? 0 : 1);
+  if (split) {
+    int w = max_w, h = max_h;
+    for (int l = 1; l < max_nlv; l++) {
+      w = (w + 1) / 2;
+      h = (h + 1) / 2;
+      const int strips = ((w + PD_COLS - 1) / PD_COLS) * ((h + PD_ROWS - 1) / PD_ROWS);
+      prof_mark(st, K_PYRDOWN);
+      k_pyrdown_level<<<dim3((strips + 255) / 256, njobs), 256, 0, st>>>(jobs, pyr_tab, l);
+    }
+  }
   prof_mark(st, -1);
   return cudaGetLastError();
 }

@@ -66,7 +66,8 @@ inline void prof_mark(cudaStream_t st, int kernel_id) {
 // ---- image-wide passes ------------------------------------------------------------------------------------------------
 // equalise (or copy) raw frames into level 0 of their pyramids and build the remaining levels: one cluster launch
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs, const PyrDesc *pyr_tab_dev, uint8_t *clahe_lut_dev /*njobs*64*256, CLAHE only*/, int any_clahe,
-                              int max_band_bytes /* max over the jobs of (ceil(h/8)+1) * w: the rows one block stages by TMA */);
+                              int max_band_bytes /* max over the jobs of (ceil(h/8)+1) * w: the rows one block stages by TMA */,
+                              int max_w = 0, int max_h = 0, int max_nlv = 0 /* largest frame and deepest pyramid of the jobs: the levels then go in launches of their own */);
 
 // cv::pyrDown(src, dst, Size(cols / 2.0, rows / 2.0)) of every job: the downsample_cameras step in front of the tracker
 cudaError_t launch_downsample(cudaStream_t st, const DownJob *jobs_dev, int njobs, int max_dst_w, int max_dst_h);
