@@ -204,3 +204,92 @@ def test_golden_sequences_on_the_host_simulation(sim_desc, name):
 def test_golden_sequences_on_the_gpu(name):
     from uvio_b200 import desc
     _check_golden(lambda cfg: desc.make_descriptor_tracker(cfg), name)
+
+
+# ---- edge cases: the same code paths the reference takes on degenerate input -----------------------------------------------------
+def _edge_sequence(make):
+    """blank frames (no corners at all), a frame masked out completely, then normal frames again: every list is empty for a
+    while (knnMatch on empty sets, robust_match below 10 matches, 'first frame' taken again after the track is lost)."""
+    from oracle.trackdescriptor_cv2 import make_descriptor_oracle
+    cfg = configs.EUROC_MAV
+    (a0, b0), (a1, b1), (a2, b2), (a3, b3), (a4, b4) = frames_for(cfg, 5, stream_id=9)
+    z = np.zeros_like(a0)
+    full = np.full_like(a0, 255)
+    blank = np.full_like(a0, 90)
+    seq = [(a0, b0, z, z), (blank, blank, z, z), (a1, b1, z, z), (a2, b2, full, full), (a2, b2, z, full), (a3, b3, z, z), (a4, b4, z, z)]
+    o = make_descriptor_oracle(cfg)
+    t = make(cfg)
+    for k, (l, r, ml, mr) in enumerate(seq):
+        n0, g0, r0 = len(o.database.log), len(t.database.log), len(o.ransac_sizes)
+        o.feed_new_camera(0.05 * k, [0, 1], [l, r], [ml, mr])
+        t.feed_new_camera(track.CameraData(0.05 * k, [0, 1], [l, r], [ml, mr]))
+        assert not any(10 <= s <= 13 for s in o.ransac_sizes[r0:]), "the edge sequence must stay out of the LMedS regime"
+        assert o.database.log[n0:] == [tuple(x) for x in t.database.log[g0:]] or _same_log(o.database.log[n0:], t.database.log[g0:]), f"frame {k}"
+        for cam in (0, 1):
+            ids, uv, d = t._last(cam)
+            assert len(ids) == len(o.ids_last[cam]), f"frame {k} cam {cam}: {len(ids)} vs {len(o.ids_last[cam])}"
+            assert (ids == np.array(o.ids_last[cam], np.uint64)).all() and (uv == o.pts_last[cam]).all() and (d == o.desc_last[cam]).all()
+    assert len(o.database.log) > 50
+    t.close()
+
+
+def _same_log(a, b):
+    oi, oc, ouv, oun = log_arrays(a)
+    gi, gc, guv, gun = log_arrays(b)
+    return len(oi) == len(gi) and (oi == gi).all() and (oc == gc).all() and (ouv == guv).all() and (len(oi) == 0 or np.abs(oun - gun).max() <= 1e-5)
+
+
+def test_blank_and_masked_frames_on_the_host_simulation(sim_desc):
+    _edge_sequence(sim_desc)
+
+
+@pytest.mark.gpu
+def test_blank_and_masked_frames_on_the_gpu():
+    from uvio_b200 import desc
+    _edge_sequence(lambda cfg: desc.make_descriptor_tracker(cfg))
+
+
+def test_tiny_image_keeps_nothing(sim_desc):
+    """An image no larger than twice ORB's 31-px edge: compute() drops every key point, nothing is ever tracked."""
+    cfg = configs.EUROC_MAV.with_(width=60, height=48, num_features=20)
+    t = sim_desc(cfg)
+    rng = np.random.default_rng(5)
+    for k in range(3):
+        l, r = (rng.integers(0, 256, (48, 60), dtype=np.uint8) for _ in range(2))
+        t.feed_new_camera(track.CameraData(0.05 * k, [0, 1], [l, r], [np.zeros_like(l), np.zeros_like(l)]))
+        assert len(t.new_observations()) == 0 and len(t._last(0)[0]) == 0
+    t.close()
+
+
+def _identical_frames(make):
+    """The same frame delivered twice: every temporal match joins identical positions, cv::findFundamentalMat asserts
+    (matrix.cpp:764, as in the KLT tracker's case: DESIGN.md section 5) and the reference, which does not catch it
+    (TrackDescriptor.cpp:533), terminates.  This tracker returns UVIO_OK and hands every id over (the zero-motion model fits all)."""
+    import cv2
+    from oracle.trackdescriptor_cv2 import make_descriptor_oracle
+    cfg = configs.EUROC_MAV
+    (l, r), = frames_for(cfg, 1, stream_id=11)
+    z = np.zeros_like(l)
+    o = make_descriptor_oracle(cfg)
+    o.feed_new_camera(0.0, [0, 1], [l, r], [z, z])
+    with pytest.raises(cv2.error):
+        o.feed_new_camera(0.05, [0, 1], [l, r], [z, z])
+    t = make(cfg)
+    t.feed_new_camera(track.CameraData(0.0, [0, 1], [l, r], [z, z]))
+    ids0 = t._last(0)[0].copy()
+    t.feed_new_camera(track.CameraData(0.05, [0, 1], [l, r], [z, z]))
+    obs = t.new_observations()
+    assert len(obs) == 2 * len(ids0) and len(ids0) > 20
+    kept = np.isin(obs["id"][::2], ids0).mean()
+    assert kept > 0.5, "identical frames: most features keep their ids"
+    t.close()
+
+
+def test_identical_frames_where_the_reference_would_terminate(sim_desc):
+    _identical_frames(sim_desc)
+
+
+@pytest.mark.gpu
+def test_identical_frames_on_the_gpu():
+    from uvio_b200 import desc
+    _identical_frames(lambda cfg: desc.make_descriptor_tracker(cfg))
