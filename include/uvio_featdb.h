@@ -73,6 +73,19 @@ int uvio_featdb_change_feat_id(uvio_featdb *db, size_t id_old, size_t id_new);
 /* FeatureDatabase::size (FeatureDatabase.h:138-141) and the number of stored measurements */
 int uvio_featdb_size(uvio_featdb *db, int *n_features, int *n_observations);
 
+/* ---- the same operations on n stores of one device in ONE launch (one block per store): what a host that runs many
+ * trackers side by side calls once per step instead of n times.  Results per store as in the single calls; the return value is
+ * the worst status, status[i] (may be NULL) the one of store i. ---- */
+/* counts[i] observations of store i, concatenated in obs; timestamps[i] its message time */
+int uvio_featdb_update_batch(uvio_featdb *const *dbs, int n, const double *timestamps, const UvioObs *obs, const int *counts, int *status);
+/* the observation lists come straight from the trackers' last (batched) feed */
+int uvio_featdb_update_from_trackers(uvio_featdb *const *dbs, uvio_klt *const *trackers, int n, const double *timestamps, int *status);
+/* one query kind for all; keys may be NULL unless kind = UVIO_FDB_GET_FEATURE; n_features / n_rows / n_observations[n] may be NULL */
+int uvio_featdb_query_batch(uvio_featdb *const *dbs, int n, int kind, const double *timestamps, const size_t *keys, int remove, int skip_deleted,
+                            int *n_features, int *n_rows, int *n_observations, int *status);
+/* mode 0 = cleanup, 1 = cleanup_measurements(timestamps[i]), 2 = cleanup_measurements_exact(timestamps[i]) */
+int uvio_featdb_cleanup_batch(uvio_featdb *const *dbs, int n, int mode, const double *timestamps, int *status);
+
 #ifdef __cplusplus
 }
 #endif

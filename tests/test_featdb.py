@@ -143,3 +143,58 @@ def test_featdb_gpu_edge_cases_and_tracker_feed(built_lib):
     for k, f in got.items():
         for c in f.timestamps:
             assert np.array_equal(f.uvs[c], np.array(host.features_idlookup[k].uvs[c], np.float32))
+
+
+# ---- batched calls: n stores in one launch = the same stores driven one at a time ------------------------------------------------
+def _batch_equals_single(n_frames=10):
+    from uvio_b200 import featdb
+    names = ["euroc_mav", "tum_vi", "euroc_mono", "rs_d455", "uzhfpv_indoor"]
+    gs = [load(nm) for nm in names]
+    a = [DeviceFeatureDatabase(max_observations=1 << 14, max_features=1 << 11) for _ in names]
+    b = [DeviceFeatureDatabase(max_observations=1 << 14, max_features=1 << 11) for _ in names]
+    for k in range(n_frames):
+        ts = [0.05 * k + 0.001 * i for i in range(len(names))]
+        lists = []
+        for g in gs:
+            ids, cams, uv, uvn = g[f"ids_{k}"], g[f"cams_{k}"], g[f"uv_{k}"], g[f"uvn_{k}"]
+            o = np.zeros(len(ids), track.OBS_DTYPE)
+            o["id"], o["cam_id"], o["u"], o["v"], o["un"], o["vn"] = ids, cams, uv[:, 0], uv[:, 1], uvn[:, 0], uvn[:, 1]
+            lists.append(o)
+        featdb.update_batch(a, ts, lists)
+        for d, t, o in zip(b, ts, lists):
+            d.update(t, o)
+        lost_a = featdb.query_batch(a, featdb.NOT_CONTAINING_NEWER, ts, skip_deleted=True)
+        for d, t, la in zip(b, ts, lost_a):
+            lb = d.features_not_containing_newer(t, False, True)
+            _same(la, [(f.key, f) for f in lb], f"frame {k} batch query")
+        for da, db_, la in zip(a, b, lost_a):
+            keys = [f.key for f in la][::2]
+            da.mark_to_delete(keys)
+            db_.mark_to_delete(keys)
+        featdb.cleanup_batch(a, 0)
+        for d in b:
+            d.cleanup()
+        if k > 4:
+            tm = [t - 0.25 for t in ts]
+            featdb.cleanup_batch(a, 1, tm)
+            for d, t in zip(b, tm):
+                d.cleanup_measurements(t)
+        counts = featdb.query_batch(a, featdb.ALL, ts, fetch=False)
+        for da, db_, c in zip(a, b, counts):
+            assert da.size() == db_.size() == c[0] and da.num_measurements() == db_.num_measurements() == c[2]
+            _same(list(da.get_internal_data().values()), [(f.key, f) for f in db_.get_internal_data().values()], f"frame {k} whole store")
+    o = np.zeros(2, track.OBS_DTYPE)
+    o["id"] = [5, 5]                                        # the same (id, camera) twice in one list: refused by the batched call
+    with pytest.raises(track.UvioError):
+        featdb.update_batch(a[:1], [9.0], [o])
+    assert sum(d.size() for d in a) > 100
+
+
+def test_featdb_batched_calls_host_simulation(sim_tracker):
+    sim_tracker
+    _batch_equals_single()
+
+
+@pytest.mark.gpu
+def test_featdb_batched_calls_gpu(built_lib):
+    _batch_equals_single()

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <mutex>
 #include <new>
+#include <functional>
 #include <set>
 #include <utility>
 #include <vector>
@@ -289,6 +290,183 @@ static int cleanup(uvio_featdb *db, int mode, double timestamp) {
 int uvio_featdb_cleanup(uvio_featdb *db) { return cleanup(db, 0, 0.0); }
 int uvio_featdb_cleanup_measurements(uvio_featdb *db, double timestamp) { return cleanup(db, 1, timestamp); }
 int uvio_featdb_cleanup_measurements_exact(uvio_featdb *db, double timestamp) { return cleanup(db, 2, timestamp); }
+
+}  // extern "C"
+
+// ---- batched entry points: the kernels take one block per store, so n stores cost one launch and one synchronisation ----------
+namespace {
+
+struct BatchCtx {                       // per device: the launch tables of one batched call (descriptors, arguments, staged input)
+  std::mutex mtx;
+  cudaStream_t st = nullptr;
+  char *host = nullptr, *dev = nullptr;
+  size_t cap = 0;
+};
+BatchCtx g_batch[64];
+
+int batch_reserve(BatchCtx &B, size_t bytes) {
+  if (!B.st && cudaStreamCreateWithFlags(&B.st, cudaStreamNonBlocking) != cudaSuccess) return UVIO_E_CUDA;
+  if (bytes <= B.cap) return UVIO_OK;
+  if (B.host) cudaFreeHost(B.host);
+  if (B.dev) cudaFree(B.dev);
+  B.host = B.dev = nullptr;
+  B.cap = 0;
+  const size_t want = bytes * 2;
+  if (cudaHostAlloc((void **)&B.host, want, cudaHostAllocDefault) != cudaSuccess || cudaMalloc((void **)&B.dev, want) != cudaSuccess) return UVIO_E_CUDA;
+  B.cap = want;
+  return UVIO_OK;
+}
+
+// locks every store (address order), checks they share a device, returns the device's batch context
+int batch_begin(uvio_featdb *const *dbs, int n, std::vector<std::unique_lock<std::mutex>> &locks, BatchCtx **out) {
+  if (!dbs || n <= 0) return UVIO_E_ARG;
+  for (int i = 0; i < n; i++) {
+    if (!dbs[i] || dbs[i]->device != dbs[0]->device) return UVIO_E_ARG;
+    for (int k = 0; k < i; k++)
+      if (dbs[k] == dbs[i]) return UVIO_E_ARG;
+  }
+  std::vector<uvio_featdb *> order(dbs, dbs + n);
+  std::sort(order.begin(), order.end(), [](uvio_featdb *a, uvio_featdb *b) { return std::less<uvio_featdb *>()(a, b); });
+  for (uvio_featdb *d : order) locks.emplace_back(d->mtx);
+  const int dev = dbs[0]->device;
+  if (dev < 0 || dev >= 64 || cudaSetDevice(dev) != cudaSuccess) return UVIO_E_CUDA;
+  *out = &g_batch[dev];
+  return UVIO_OK;
+}
+
+template <class Args>
+int batch_run(BatchCtx &B, uvio_featdb *const *dbs, int n, const std::vector<Args> &args, size_t extra_bytes, const void *extra,
+              cudaError_t (*launch)(cudaStream_t, const FdbStore *, const Args *, int), int *status, size_t extra_off) {
+  // table layout: [FdbStore x n][Args x n][extra]
+  const size_t o_args = (sizeof(FdbStore) * (size_t)n + 255) / 256 * 256;
+  FdbStore *hs = (FdbStore *)B.host;
+  for (int i = 0; i < n; i++) hs[i] = dbs[i]->S;
+  memcpy(B.host + o_args, args.data(), sizeof(Args) * (size_t)n);
+  (void)extra;
+  const size_t total = extra_off + extra_bytes;
+  FDB_TRY(cudaMemcpyAsync(B.dev, B.host, total, cudaMemcpyHostToDevice, B.st));
+  FDB_TRY(launch(B.st, (const FdbStore *)B.dev, (const Args *)(B.dev + o_args), n));
+  FDB_TRY(cudaStreamSynchronize(B.st));
+  int worst = UVIO_OK;
+  for (int i = 0; i < n; i++) {
+    const int rc = dbs[i]->cnt_h[3] == 0 ? UVIO_OK : UVIO_E_SIZE;
+    if (status) status[i] = rc;
+    worst = std::max(worst, rc);
+  }
+  return worst;
+}
+
+size_t batch_extra_off(int n, size_t args_size) {
+  const size_t o_args = (sizeof(FdbStore) * (size_t)n + 255) / 256 * 256;
+  return (o_args + args_size * (size_t)n + 255) / 256 * 256;
+}
+
+}  // namespace
+
+extern "C" {
+
+int uvio_featdb_update_batch(uvio_featdb *const *dbs, int n, const double *timestamps, const UvioObs *obs, const int *counts, int *status) {
+  if (!timestamps || !counts) return UVIO_E_ARG;
+  std::vector<std::unique_lock<std::mutex>> locks;
+  BatchCtx *Bp = nullptr;
+  int rc = batch_begin(dbs, n, locks, &Bp);
+  if (rc != UVIO_OK) return rc;
+  BatchCtx &B = *Bp;
+  std::lock_guard<std::mutex> lb(B.mtx);
+  size_t total = 0;
+  for (int i = 0; i < n; i++) {
+    if (counts[i] < 0 || counts[i] > dbs[i]->cap_in) return UVIO_E_SIZE;
+    total += (size_t)counts[i];
+  }
+  if (total && !obs) return UVIO_E_ARG;
+  const size_t off = batch_extra_off(n, sizeof(FdbUpdateArgs));
+  rc = batch_reserve(B, off + sizeof(FdbObsIn) * total + 256);
+  if (rc != UVIO_OK) return rc;
+  FdbObsIn *in = (FdbObsIn *)(B.host + off);
+  std::vector<FdbUpdateArgs> args(n);
+  // a batch may hold one observation per (id, camera) and store (the tracker's lists never repeat one): checked with a small
+  // open-addressing table per store; a list that does is refused here -- feed it through uvio_featdb_update, which cuts it
+  std::vector<unsigned long long> tab;
+  size_t at = 0;
+  for (int i = 0; i < n; i++) {
+    const int m = counts[i];
+    size_t cap = 16;
+    while (cap < 4 * (size_t)m) cap <<= 1;
+    tab.assign(cap, ~0ull);
+    for (int k = 0; k < m; k++) {
+      const UvioObs &o = obs[at + k];
+      if (o.cam_id >= (size_t)FDB_MAXCAM || (unsigned long long)o.id == FDB_EMPTY) return UVIO_E_ARG;
+      const unsigned long long key = ((unsigned long long)o.id << 2) | (unsigned long long)o.cam_id;
+      size_t h = (size_t)((key * 0x9E3779B97F4A7C15ull) >> 20) & (cap - 1);
+      while (tab[h] != ~0ull) {
+        if (tab[h] == key) return UVIO_E_ARG;
+        h = (h + 1) & (cap - 1);
+      }
+      tab[h] = key;
+      in[at + k] = FdbObsIn{(unsigned long long)o.id, (unsigned long long)o.cam_id, o.u, o.v, o.un, o.vn};
+    }
+    args[i] = FdbUpdateArgs{(const FdbObsIn *)(B.dev + off) + at, m, timestamps[i]};
+    at += (size_t)m;
+  }
+  return batch_run<FdbUpdateArgs>(B, dbs, n, args, sizeof(FdbObsIn) * total, nullptr, launch_fdb_update, status, off);
+}
+
+int uvio_featdb_update_from_trackers(uvio_featdb *const *dbs, uvio_klt *const *trackers, int n, const double *timestamps, int *status) {
+  if (!dbs || !trackers || n <= 0) return UVIO_E_ARG;
+  std::vector<int> counts(n, 0);
+  std::vector<UvioObs> all;
+  std::vector<UvioObs> tmp;
+  for (int i = 0; i < n; i++) {
+    int m = 0;
+    int rc = uvio_klt_get_new_observations(trackers[i], nullptr, 0, &m);
+    if (rc != UVIO_OK && rc != UVIO_E_SIZE) return rc;
+    tmp.resize((size_t)std::max(m, 1));
+    rc = uvio_klt_get_new_observations(trackers[i], tmp.data(), m, &m);
+    if (rc != UVIO_OK) return rc;
+    counts[i] = m;
+    all.insert(all.end(), tmp.begin(), tmp.begin() + m);
+  }
+  return uvio_featdb_update_batch(dbs, n, timestamps, all.data(), counts.data(), status);
+}
+
+int uvio_featdb_query_batch(uvio_featdb *const *dbs, int n, int kind, const double *timestamps, const size_t *keys, int remove, int skip_deleted,
+                            int *n_features, int *n_rows, int *n_observations, int *status) {
+  if (kind < 0 || kind > 4 || !timestamps || (kind == UVIO_FDB_GET_FEATURE && !keys)) return UVIO_E_ARG;
+  std::vector<std::unique_lock<std::mutex>> locks;
+  BatchCtx *Bp = nullptr;
+  int rc = batch_begin(dbs, n, locks, &Bp);
+  if (rc != UVIO_OK) return rc;
+  BatchCtx &B = *Bp;
+  std::lock_guard<std::mutex> lb(B.mtx);
+  const size_t off = batch_extra_off(n, sizeof(FdbQueryArgs));
+  rc = batch_reserve(B, off + 256);
+  if (rc != UVIO_OK) return rc;
+  std::vector<FdbQueryArgs> args(n);
+  for (int i = 0; i < n; i++) args[i] = FdbQueryArgs{kind, timestamps[i], keys ? (unsigned long long)keys[i] : 0ull, remove, skip_deleted};
+  rc = batch_run<FdbQueryArgs>(B, dbs, n, args, 0, nullptr, launch_fdb_query, status, off);
+  for (int i = 0; i < n; i++) {
+    if (n_features) n_features[i] = dbs[i]->cnt_h[8];
+    if (n_rows) n_rows[i] = dbs[i]->cnt_h[9];
+    if (n_observations) n_observations[i] = dbs[i]->cnt_h[10];
+  }
+  return rc;
+}
+
+int uvio_featdb_cleanup_batch(uvio_featdb *const *dbs, int n, int mode, const double *timestamps, int *status) {
+  if (mode < 0 || mode > 2 || (mode != 0 && !timestamps)) return UVIO_E_ARG;
+  std::vector<std::unique_lock<std::mutex>> locks;
+  BatchCtx *Bp = nullptr;
+  int rc = batch_begin(dbs, n, locks, &Bp);
+  if (rc != UVIO_OK) return rc;
+  BatchCtx &B = *Bp;
+  std::lock_guard<std::mutex> lb(B.mtx);
+  const size_t off = batch_extra_off(n, sizeof(FdbCleanupArgs));
+  rc = batch_reserve(B, off + 256);
+  if (rc != UVIO_OK) return rc;
+  std::vector<FdbCleanupArgs> args(n);
+  for (int i = 0; i < n; i++) args[i] = FdbCleanupArgs{mode, timestamps ? timestamps[i] : 0.0};
+  return batch_run<FdbCleanupArgs>(B, dbs, n, args, 0, nullptr, launch_fdb_cleanup, status, off);
+}
 
 int uvio_featdb_size(uvio_featdb *db, int *n_features, int *n_observations) {
   if (!db) return UVIO_E_ARG;

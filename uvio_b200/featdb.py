@@ -33,6 +33,10 @@ def _lib():
         L.uvio_featdb_cleanup_measurements_exact.argtypes = [vp, d]
         L.uvio_featdb_change_feat_id.argtypes = [vp, sz, sz]
         L.uvio_featdb_size.argtypes = [vp, C.POINTER(ci), C.POINTER(ci)]
+        L.uvio_featdb_update_batch.argtypes = [C.POINTER(vp), ci, vp, vp, vp, vp]
+        L.uvio_featdb_update_from_trackers.argtypes = [C.POINTER(vp), C.POINTER(vp), ci, vp, vp]
+        L.uvio_featdb_query_batch.argtypes = [C.POINTER(vp), ci, ci, vp, vp, ci, ci, vp, vp, vp, vp]
+        L.uvio_featdb_cleanup_batch.argtypes = [C.POINTER(vp), ci, ci, vp, vp]
         _bound = L
     return L
 
@@ -87,7 +91,9 @@ class DeviceFeatureDatabase:
         nf, nr, no = C.c_int(), C.c_int(), C.c_int()
         self._check(_lib().uvio_featdb_query(self._h, kind, float(timestamp), int(key), int(remove), int(skip_deleted), C.byref(nf),
                                              C.byref(nr), C.byref(no)), "uvio_featdb_query")
-        nf, nr, no = nf.value, nr.value, no.value
+        return self._fetch(nf.value, nr.value, no.value)
+
+    def _fetch(self, nf, nr, no) -> List[FeatureView]:
         featid, key_a = np.zeros(max(nf, 1), np.uint64), np.zeros(max(nf, 1), np.uint64)
         dele = np.zeros(max(nf, 1), np.uint8)
         row0, row_cam, off = np.zeros(nf + 1, np.int32), np.zeros(max(nr, 1), np.int32), np.zeros(nr + 1, np.int32)
@@ -144,3 +150,56 @@ class DeviceFeatureDatabase:
         nf, no = C.c_int(), C.c_int()
         _lib().uvio_featdb_size(self._h, C.byref(nf), C.byref(no))
         return no.value
+
+
+# ---- the same operations on many stores of one device in one launch (uvio_featdb_*_batch) ------------------------------------------
+def _handles(dbs):
+    return (C.c_void_p * len(dbs))(*[d._h for d in dbs])
+
+
+def _check_batch(rc, status, what):
+    if rc != track.UVIO_OK:
+        bad = [i for i, s in enumerate(status) if s != track.UVIO_OK]
+        raise track.UvioError(rc, f"{what} (stores {bad[:8]})")
+
+
+def update_batch(dbs, timestamps, obs_lists):
+    n = len(dbs)
+    ts = np.ascontiguousarray(timestamps, np.float64)
+    counts = np.array([len(o) for o in obs_lists], np.int32)
+    allobs = np.ascontiguousarray(np.concatenate([np.asarray(o, track.OBS_DTYPE) for o in obs_lists]) if n else np.zeros(0, track.OBS_DTYPE))
+    status = np.zeros(n, np.int32)
+    rc = _lib().uvio_featdb_update_batch(_handles(dbs), n, ts.ctypes.data, allobs.ctypes.data, counts.ctypes.data, status.ctypes.data)
+    _check_batch(rc, status, "uvio_featdb_update_batch")
+
+
+def update_from_trackers(dbs, trackers, timestamps):
+    n = len(dbs)
+    ts = np.ascontiguousarray(timestamps, np.float64)
+    status = np.zeros(n, np.int32)
+    hs = (C.c_void_p * n)(*[t._h for t in trackers])
+    rc = _lib().uvio_featdb_update_from_trackers(_handles(dbs), hs, n, ts.ctypes.data, status.ctypes.data)
+    _check_batch(rc, status, "uvio_featdb_update_from_trackers")
+
+
+def query_batch(dbs, kind, timestamps, keys=None, remove=False, skip_deleted=False, fetch=True):
+    """One query kind on every store in one launch; returns the per-store results (fetch=False: only the (features, rows,
+    observations) counts -- the results stay on the device for uvio_tri_triangulate_featdb)."""
+    n = len(dbs)
+    ts = np.ascontiguousarray(timestamps, np.float64)
+    ka = None if keys is None else np.ascontiguousarray(keys, np.uint64)
+    nf, nr, no, status = (np.zeros(n, np.int32) for _ in range(4))
+    rc = _lib().uvio_featdb_query_batch(_handles(dbs), n, int(kind), ts.ctypes.data, None if ka is None else ka.ctypes.data, int(remove), int(skip_deleted),
+                                        nf.ctypes.data, nr.ctypes.data, no.ctypes.data, status.ctypes.data)
+    _check_batch(rc, status, "uvio_featdb_query_batch")
+    if not fetch:
+        return list(zip(nf.tolist(), nr.tolist(), no.tolist()))
+    return [d._fetch(int(a), int(b), int(c)) for d, a, b, c in zip(dbs, nf, nr, no)]
+
+
+def cleanup_batch(dbs, mode=0, timestamps=None):
+    n = len(dbs)
+    ts = None if timestamps is None else np.ascontiguousarray(timestamps, np.float64)
+    status = np.zeros(n, np.int32)
+    rc = _lib().uvio_featdb_cleanup_batch(_handles(dbs), n, int(mode), None if ts is None else ts.ctypes.data, status.ctypes.data)
+    _check_batch(rc, status, "uvio_featdb_cleanup_batch")
