@@ -1463,8 +1463,7 @@ struct Pass {
 static int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, const std::vector<PreItem> &items, unsigned long long *stats,
                             int group = 0, cudaStream_t copy_st = nullptr, cudaEvent_t copied = nullptr) {
   const bool split = copy_st != nullptr && copy_st != st;
-  if (!split) copy_st = st;
-  else group = 0;
+  if (!split) copy_st = st;   // (with a copy stream the groups still apply: each group's kernels wait for its own copies only)
   HOSTPROF(s0_memcpy);
   const int nimg = (int)items.size();
   if (nimg == 0) return OK;
