@@ -429,7 +429,7 @@ def run_ours(args):
         "clocks": clk,
     }
     line["config"]["ms_per_feed_with_all_kernels_bracketed_by_events"] = 1e3 * sec3 / max(1, min(tf, 4 * R))
-    return line, (prof, prof3, st3), st, tf, S, cfg, rank, world, dist
+    return line, (prof, prof3, st3, min(tf, 4 * R)), st, tf, S, cfg, rank, world, dist
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -603,7 +603,7 @@ def _load_profile(name):
 
 
 def roofline_entry(profs, stats, feeds, S, cfg, clk):
-    prof_timed, prof_all, stats_all = profs
+    prof_timed, prof_all, stats_all, feeds_prof = profs                     # feeds_prof: feeds of the leg that bracketed every kernel
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak_hbm = float(json.load(open(peaks_path))["hbm_gbs"])
@@ -622,7 +622,7 @@ def roofline_entry(profs, stats, feeds, S, cfg, clk):
     if not in_timed:
         ms, launches = prof_all[name]
     entry = {"kernel": name, "launches": launches, "avg_launch_ms": ms / max(1, launches),
-             "kernel_time_share_of_gpu_time": share, "gpu_busy_ms_per_feed": total_ms / max(1, prof_all[name][1] / 2 if name == "k_lk" else 1),
+             "kernel_time_share_of_gpu_time": share, "gpu_busy_ms_per_feed": total_ms / max(1, feeds_prof),
              "timing": ("CUDA events around every launch of this kernel inside the timed region (resident leg), on the launching streams; "
                         "the shares come from a separate short leg with every kernel bracketed") if in_timed else
                        "separate profiling leg (the kernel was not bracketed in the timed region)"}
@@ -658,20 +658,23 @@ def roofline_entry(profs, stats, feeds, S, cfg, clk):
         else:
             entry.update({"bound": "latency", "achieved": None, "frac": None,
                           "note": "the dominant kernel is latency-bound per-tracker work with no meaningful byte or flop count"})
-    # ---- the image-wide pass ------------------------------------------------------------------------------------------------
+    # ---- the image-wide passes: equalisation (k_preprocess) and the pyramid levels (k_pyrdown: launches of their own) -------------------
     image_pass = None
     pms, pl = prof_all.get("k_preprocess", (0.0, 0))
+    dms, dl = prof_all.get("k_pyrdown", (0.0, 0))
     if pl > 0 and pms > 0:
-        feeds_all = max(1, prof_all["k_lk"][1] // 2) if prof_all.get("k_lk", (0, 0))[1] else feeds
-        imgs = 2 * S * feeds_all
-        per_img = 3 * P + (sig - lv[-1][0] * lv[-1][1]) + (sig - P)
-        if cfg.histogram == 2:
-            per_img += 3 * P                                                    # the CLAHE passes in front of it
-        ach = imgs * per_img / (pms / 1e3) / 1e9
-        image_pass = {"bound": "hbm", "kernel": "k_preprocess", "unit": "GB/s", "achieved": ach, "peak": peak_hbm, "peak_source": peak_src,
-                      "frac": ach / peak_hbm, "launches": pl, "avg_launch_ms": pms / pl, "images_per_launch": imgs / pl,
-                      "algorithmic_bytes_per_image": per_img, "traffic": None,
-                      "timing": "CUDA events around every launch, profiling leg (every kernel bracketed), on the launching stream"}
+        imgs = 2 * S * feeds_prof
+        eq_bytes = 3 * P + (3 * P if cfg.histogram == 2 else 0)                  # hist read + apply read + write (CLAHE: its two passes in front)
+        pyr_bytes = (sig - lv[-1][0] * lv[-1][1]) + (sig - P)                   # every level read once to be halved, every lower level written once
+        per_img = eq_bytes + pyr_bytes
+        ach = imgs * per_img / ((pms + dms) / 1e3) / 1e9
+        image_pass = {"bound": "hbm", "kernel": "k_preprocess + k_pyrdown" if dl else "k_preprocess", "unit": "GB/s", "achieved": ach, "peak": peak_hbm,
+                      "peak_source": peak_src, "frac": ach / peak_hbm, "launches": pl + dl, "avg_launch_ms": (pms + dms) / max(1, pl),
+                      "images_per_launch": imgs / pl, "algorithmic_bytes_per_image": per_img, "traffic": None,
+                      "parts": {"k_preprocess": {"ms": pms, "launches": pl, "GB_per_s": imgs * (eq_bytes if dl else per_img) / (pms / 1e3) / 1e9},
+                                "k_pyrdown": ({"ms": dms, "launches": dl, "GB_per_s": imgs * pyr_bytes / (dms / 1e3) / 1e9} if dl and dms > 0 else None)},
+                      "timing": "CUDA events around every launch, profiling leg (every kernel bracketed), on the launching stream; the launches share "
+                                "the GPU with the LK of the feed in flight, so these are durations under load, not the kernels alone"}
         cap, cap_path = _load_profile("preprocess_traffic.json")
         if cap:
             image_pass["traffic"] = (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["images_in_launch"] * imgs / pl

@@ -24,6 +24,8 @@ constexpr int FT_SW = FT_W + 2, FT_SH = FT_H + 2;     // score footprint (tile +
 struct FastSmem {
   uint8_t pix[FT_PH * FT_PW];
   uint8_t score[FT_SH * FT_SW];
+  uint16_t cand[FT_SH * FT_SW];   // score positions that pass the four-point pre-test, in no particular order
+  unsigned ncand;
 };
 
 struct FastJob {          // one grid cell of one image
@@ -39,6 +41,18 @@ UVIO_HD int fast_ring_off(int k, int pitch) {
   const int dx = k < 4 ? k : (k < 6 ? 3 : (k < 12 ? 8 - k : (k < 14 ? -3 : k - 16)));
   const int dy = k < 2 ? 3 : (k < 7 ? 4 - k : (k < 10 ? -3 : (k < 15 ? k - 12 : 3)));
   return dy * pitch + dx;
+}
+
+// Necessary condition for a 9-of-16 arc: any nine contiguous ring positions hold at least two of the four compass points
+// (k = 0, 4, 8, 12), so a corner has two of them darker than centre - t or two brighter than centre + t.  Five loads decide
+// for most pixels of a natural image that the sixteen-point test need not run.
+UVIO_HD bool fast_maybe(const uint8_t *p, int pitch, int threshold) {
+  const int v = p[0];
+  const int d0 = v - (int)p[fast_ring_off(0, pitch)], d4 = v - (int)p[fast_ring_off(4, pitch)], d8 = v - (int)p[fast_ring_off(8, pitch)],
+            d12 = v - (int)p[fast_ring_off(12, pitch)];
+  const int up = (d0 > threshold) + (d4 > threshold) + (d8 > threshold) + (d12 > threshold);
+  const int dn = (d0 < -threshold) + (d4 < -threshold) + (d8 < -threshold) + (d12 < -threshold);
+  return up >= 2 || dn >= 2;
 }
 
 // largest t' such that the pixel is still a corner at threshold t' (0 if it is not a corner at `threshold`)
@@ -96,14 +110,23 @@ UVIO_HD void fast_tile(G g, FastSmem &s, const ImgView &I, const FastJob &job, i
     int x = clampi(tx0 - 4 + xx, 0, job.w - 1), y = clampi(ty0 - 4 + yy, 0, job.h - 1);
     s.pix[i] = I.p[(size_t)(job.y0 + y) * I.pitch + job.x0 + x];
   }
+  if (g.lane() == 0) s.ncand = 0;
   g.sync();
+  // pass 1: the cheap pre-test on every score position; survivors are listed so that pass 2 runs on full warps (a warp in
+  // which one lane of 32 needs the sixteen-point test would otherwise pay for it in all of them)
   for (int i = g.lane(); i < FT_SH * FT_SW; i += g.size()) {
     int yy = i / FT_SW, xx = i - yy * FT_SW;
     int x = tx0 - 1 + xx, y = ty0 - 1 + yy;
-    int sc = 0;
-    if (x >= 3 && x < job.w - 3 && y >= 3 && y < job.h - 3)
-      sc = fast_score(s.pix + (yy + 3) * FT_PW + (xx + 3), FT_PW, threshold);
-    s.score[i] = (uint8_t)sc;
+    s.score[i] = 0;
+    if (x >= 3 && x < job.w - 3 && y >= 3 && y < job.h - 3 && fast_maybe(s.pix + (yy + 3) * FT_PW + (xx + 3), FT_PW, threshold))
+      s.cand[smem_add(&s.ncand, 1u)] = (uint16_t)i;
+  }
+  g.sync();
+  const int ncand = (int)s.ncand;
+  for (int c = g.lane(); c < ncand; c += g.size()) {
+    const int i = s.cand[c];
+    int yy = i / FT_SW, xx = i - yy * FT_SW;
+    s.score[i] = (uint8_t)fast_score(s.pix + (yy + 3) * FT_PW + (xx + 3), FT_PW, threshold);
   }
   g.sync();
   for (int i = g.lane(); i < FT_H * FT_W; i += g.size()) {

@@ -15,7 +15,9 @@ namespace uvio {
 #ifdef __CUDA_ARCH__
 __device__ __forceinline__ void smem_inc(unsigned *p) { atomicAdd(p, 1u); }
 __device__ __forceinline__ unsigned gmem_add(unsigned *p, unsigned v) { return atomicAdd(p, v); }
+__device__ __forceinline__ unsigned smem_add(unsigned *p, unsigned v) { return atomicAdd(p, v); }
 #else
+inline unsigned smem_add(unsigned *p, unsigned v) { unsigned o = *p; *p += v; return o; }
 inline void smem_inc(unsigned *p) { ++*p; }
 inline unsigned gmem_add(unsigned *p, unsigned v) { unsigned o = *p; *p += v; return o; }
 #endif
