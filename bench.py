@@ -250,7 +250,8 @@ def _frame_structs(track, base_ptr, n_pool, streams, h, w, keep):
     return steps
 
 
-def _run_leg(track, L, cfg, device, streams, pool, warm_feeds, timed_feeds, dist, obs_buf, counts, sample_clocks, prof_enable, announce=True):
+def _run_leg(track, L, cfg, device, streams, pool, warm_feeds, timed_feeds, dist, obs_buf, counts, sample_clocks, prof_enable, announce=True,
+             sync_after_submit=False):
     """warm_feeds + timed_feeds batched feeds on fresh trackers; returns (seconds max-over-ranks, n_obs, clocks, stats, profile).
     announce: feed t+1 is announced (uvio_klt_submit_batch: its upload and pre-processing start) right before feed t is
     issued, so every timed feed has exactly one upload inside the timed region -- the one of the feed after it."""
@@ -272,6 +273,9 @@ def _run_leg(track, L, cfg, device, streams, pool, warm_feeds, timed_feeds, dist
             rc = L.uvio_klt_submit_batch(hs, pool[pool_index(t + 1, n_pool)], streams)
             if rc != 0:
                 raise RuntimeError(f"uvio_klt_submit_batch failed: {rc}")
+            if sync_after_submit:               # the announced frames' image passes run to completion with the GPU to themselves
+                time.sleep(0.0005)              # (the library's uploader thread issues them: give it the time to, then wait for the device)
+                torch.cuda.synchronize(device)
         t1 = time.perf_counter()
         rc = L.uvio_klt_feed_batch(hs, pool[pool_index(t, n_pool)], streams)
         if rc != 0:
@@ -389,6 +393,9 @@ def run_ours(args):
     sec, n_obs, clk, st, prof, wall = _run_leg(track, L, cfg, local, S, dev_pool, wf, tf, dist, obs_buf, counts, True, lk_only, announce)
     sec2, n_obs2, _c2, st2, _p2, wall2 = _run_leg(track, L, cfg, local, S, host_pool, wf, tf, dist, obs_buf, counts, False, lk_only, announce)
     sec3, _n3, _c3, st3, prof3, _w3 = _run_leg(track, L, cfg, local, S, dev_pool, R, min(tf, 4 * R), dist, obs_buf, counts, False, 1, announce)
+    # leg 4: frames resident, every announcement followed by a device synchronisation before the feed is issued: the image-wide
+    # passes of the announced frames then run with the GPU to themselves, and their event brackets are the kernels' own durations
+    sec4, _n4, _c4, st4, prof4, _w4 = _run_leg(track, L, cfg, local, S, dev_pool, R, min(tf, 2 * R), dist, obs_buf, counts, False, 1, True, True)
     sec_h2d = h2d_only_leg(hv, dev, local, min(tf, 8 * R), dist)
     h2d_feed_bytes = float(S * 2 * h * w)
     lat = _latency_leg(track, L, cfg, local, host_pool, 60)
@@ -429,7 +436,7 @@ def run_ours(args):
         "clocks": clk,
     }
     line["config"]["ms_per_feed_with_all_kernels_bracketed_by_events"] = 1e3 * sec3 / max(1, min(tf, 4 * R))
-    return line, (prof, prof3, st3, min(tf, 4 * R)), st, tf, S, cfg, rank, world, dist
+    return line, (prof, prof3, st3, min(tf, 4 * R), prof4, min(tf, 2 * R)), st, tf, S, cfg, rank, world, dist
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -603,7 +610,7 @@ def _load_profile(name):
 
 
 def roofline_entry(profs, stats, feeds, S, cfg, clk):
-    prof_timed, prof_all, stats_all, feeds_prof = profs                     # feeds_prof: feeds of the leg that bracketed every kernel
+    prof_timed, prof_all, stats_all, feeds_prof, prof_alone, feeds_alone = profs   # feeds_prof: feeds of the leg that bracketed every kernel
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak_hbm = float(json.load(open(peaks_path))["hbm_gbs"])
@@ -622,7 +629,7 @@ def roofline_entry(profs, stats, feeds, S, cfg, clk):
     if not in_timed:
         ms, launches = prof_all[name]
     entry = {"kernel": name, "launches": launches, "avg_launch_ms": ms / max(1, launches),
-             "kernel_time_share_of_gpu_time": share, "gpu_busy_ms_per_feed": total_ms / max(1, feeds_prof),
+             "kernel_time_share_of_gpu_time": share, "sum_of_kernel_durations_ms_per_feed": total_ms / max(1, feeds_prof),
              "timing": ("CUDA events around every launch of this kernel inside the timed region (resident leg), on the launching streams; "
                         "the shares come from a separate short leg with every kernel bracketed") if in_timed else
                        "separate profiling leg (the kernel was not bracketed in the timed region)"}
@@ -643,6 +650,11 @@ def roofline_entry(profs, stats, feeds, S, cfg, clk):
                           "traffic": (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["features_in_launch"] * feats / max(1, launches),
                           "algorithmic_bytes_per_launch": (324 * stats["lk_point_levels"] + 256 * stats["lk_iterations"]) / max(1, launches),
                           "features_per_launch": feats / max(1, launches),
+                          "alone": ({"achieved": cap["smsp__inst_executed_sum"] / (cap["duration_us_sum"] * 1e-6) / 1e9,
+                                     "frac": cap["smsp__inst_executed_sum"] / (cap["duration_us_sum"] * 1e-6) / 1e9 / peak,
+                                     "what": "the same kernel with the GPU to itself: warp instructions / duration summed over every k_lk launch of the "
+                                             "capture (ncu serialises launches); `achieved` above divides by event-bracketed durations of launches that "
+                                             "share the SMs with the other kernels of two trackers' groups"} if cap.get("duration_us_sum") else None),
                           "note": "LK is an L2 / shared-memory gather with ordered fp32 accumulation: bound by instruction issue, not by HBM "
                                   "(traffic = DRAM bytes per launch scaled from the capture; algorithmic bytes = 324 B per point-level + 256 B "
                                   "per iteration, SURVEY 8(d), for reference)"})
@@ -658,27 +670,37 @@ def roofline_entry(profs, stats, feeds, S, cfg, clk):
         else:
             entry.update({"bound": "latency", "achieved": None, "frac": None,
                           "note": "the dominant kernel is latency-bound per-tracker work with no meaningful byte or flop count"})
-    # ---- the image-wide passes: equalisation (k_preprocess) and the pyramid levels (k_pyrdown: launches of their own) -------------------
+    # ---- the image-wide passes: equalisation (k_preprocess, k_clahe_*) and the pyramid levels (k_pyrdown: launches of their own) ------
+    # timed in the leg that synchronises the device after every announcement, so that the announced frames' passes run alone;
+    # in the throughput legs the same launches queue behind the LK blocks of the feed in flight and their event brackets
+    # measure the wait (reported as `under_load`)
     image_pass = None
-    pms, pl = prof_all.get("k_preprocess", (0.0, 0))
-    dms, dl = prof_all.get("k_pyrdown", (0.0, 0))
-    if pl > 0 and pms > 0:
-        imgs = 2 * S * feeds_prof
+    def _ms(pr, names):
+        return sum(pr.get(k, (0.0, 0))[0] for k in names), sum(pr.get(k, (0.0, 0))[1] for k in names)
+    eq_k, pyr_k = ("k_preprocess", "k_clahe_tiles", "k_clahe_apply"), ("k_pyrdown",)
+    ems, el = _ms(prof_alone, eq_k)
+    dms, dl = _ms(prof_alone, pyr_k)
+    if el > 0 and ems > 0:
+        imgs = 2 * S * feeds_alone
         eq_bytes = 3 * P + (3 * P if cfg.histogram == 2 else 0)                  # hist read + apply read + write (CLAHE: its two passes in front)
         pyr_bytes = (sig - lv[-1][0] * lv[-1][1]) + (sig - P)                   # every level read once to be halved, every lower level written once
         per_img = eq_bytes + pyr_bytes
-        ach = imgs * per_img / ((pms + dms) / 1e3) / 1e9
+        ach = imgs * per_img / ((ems + dms) / 1e3) / 1e9
+        pl = prof_alone.get("k_preprocess", (0.0, 1))[1]
+        ums, _ul = _ms(prof_all, eq_k + pyr_k)
         image_pass = {"bound": "hbm", "kernel": "k_preprocess + k_pyrdown" if dl else "k_preprocess", "unit": "GB/s", "achieved": ach, "peak": peak_hbm,
-                      "peak_source": peak_src, "frac": ach / peak_hbm, "launches": pl + dl, "avg_launch_ms": (pms + dms) / max(1, pl),
-                      "images_per_launch": imgs / pl, "algorithmic_bytes_per_image": per_img, "traffic": None,
-                      "parts": {"k_preprocess": {"ms": pms, "launches": pl, "GB_per_s": imgs * (eq_bytes if dl else per_img) / (pms / 1e3) / 1e9},
-                                "k_pyrdown": ({"ms": dms, "launches": dl, "GB_per_s": imgs * pyr_bytes / (dms / 1e3) / 1e9} if dl and dms > 0 else None)},
-                      "timing": "CUDA events around every launch, profiling leg (every kernel bracketed), on the launching stream; the launches share "
-                                "the GPU with the LK of the feed in flight, so these are durations under load, not the kernels alone"}
+                      "peak_source": peak_src, "frac": ach / peak_hbm, "launches": el + dl, "avg_launch_ms": (ems + dms) / max(1, pl),
+                      "images_per_launch": imgs / max(1, pl), "algorithmic_bytes_per_image": per_img, "traffic": None,
+                      "parts": {"equalise": {"ms": ems, "launches": el, "GB_per_s": imgs * (eq_bytes if dl else per_img) / (ems / 1e3) / 1e9},
+                                "pyramid": ({"ms": dms, "launches": dl, "GB_per_s": imgs * pyr_bytes / (dms / 1e3) / 1e9} if dl and dms > 0 else None)},
+                      "under_load": ({"achieved": 2 * S * feeds_prof * per_img / (ums / 1e3) / 1e9, "what": "the same launches in the announced legs, "
+                                      "queued behind the LK of the feed in flight (event brackets include the wait)"} if ums > 0 else None),
+                      "timing": "CUDA events around every launch, on the launching stream, in a leg that synchronises the device between the "
+                                "announcement of a feed (uvio_klt_submit_batch: its image passes) and the feed before it (resident frames)"}
         cap, cap_path = _load_profile("preprocess_traffic.json")
         if cap:
-            image_pass["traffic"] = (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["images_in_launch"] * imgs / pl
-            image_pass["traffic_source"] = cap_path + ": " + cap.get("capture", "")
+            image_pass["traffic"] = (cap["dram_bytes_read"] + cap["dram_bytes_write"]) / cap["images_in_launch"] * imgs / max(1, pl)
+            image_pass["traffic_source"] = cap_path + ": " + cap.get("capture", "") + " (DRAM bytes of the k_preprocess launch only)"
     entry["image_pass"] = image_pass
     return entry
 

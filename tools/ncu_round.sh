@@ -40,7 +40,7 @@ json.dump(out, open("gpurun_out/r2_lk_ncu.json", "w"), indent=1)
 print("k_lk:", out["smsp__inst_executed_sum"] / feats, "warp instructions per feature;", out)
 PY
 # one steady-state step with every tracker in one group: each kernel of the chain once, all streams in the launch
-UVIO_KLT_GROUPS=1 ncu --set full --clock-control none --import-source on -s 66 -c 12 -f -o gpurun_out/r2_step_full \
+UVIO_KLT_GROUPS=1 ncu --set full --clock-control none --import-source on -s 88 -c 16 -f -o gpurun_out/r2_step_full \
     python tools/profile_step.py > gpurun_out/r2_ncu_full.log 2>&1
 ncu -i gpurun_out/r2_step_full.ncu-rep --page raw --csv --print-units base > gpurun_out/r2_step_full_raw.csv 2>/dev/null
 python - <<'PY'
