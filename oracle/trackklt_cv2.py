@@ -79,7 +79,7 @@ class Cam:
 
     def undistort(self, pts: np.ndarray) -> np.ndarray:
         """undistort_cv on each point. The reference calls OpenCV once per point on a 1x1 Mat; OpenCV treats every
-        point independently, so one batched call returns the same floats (checked in tests/test_oracle.py)."""
+        point independently, so one batched call returns the same floats (checked by tests/test_oracle_golden.py::test_batched_undistort_equals_per_point_calls)."""
         pts = np.asarray(pts, np.float32).reshape(-1, 1, 2)
         if pts.shape[0] == 0:
             return np.zeros((0, 2), np.float32)

@@ -64,3 +64,17 @@ def test_std_sort_permutation_is_not_stable_but_is_a_permutation():
     p = std_sort_perm(r)
     assert sorted(p.tolist()) == list(range(500)) and np.all(np.diff(r[p]) <= 0)
     assert not np.array_equal(p, np.argsort(-r, kind="stable"))          # the tie order is libstdc++'s, not a stable sort's
+
+
+def test_batched_undistort_equals_per_point_calls():
+    """The reference undistorts one point per OpenCV call on a 1x1 Mat (cam/CamBase.h:108-116); the oracle makes one batched call.
+    OpenCV treats every point independently: the floats are the same."""
+    from oracle.trackklt_cv2 import Cam
+    rng = np.random.default_rng(8)
+    for cfg in (configs.EUROC_MAV, configs.TUM_VI):
+        c = cfg.cams[0]
+        cam = Cam(c.model, tuple(c.intrinsics), tuple(c.dist))
+        pts = np.c_[rng.uniform(0, cfg.width, 300), rng.uniform(0, cfg.height, 300)].astype(np.float32)
+        batched = cam.undistort(pts)
+        single = np.concatenate([cam.undistort(p.reshape(1, 2)) for p in pts])
+        assert np.array_equal(batched, single)
