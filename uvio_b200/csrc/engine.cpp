@@ -747,7 +747,11 @@ Context *context_for_device(int device, int *err) {
     }
     c->lanes.push_back(std::move(ln));
   }
-  if ((e = cudaStreamCreateWithPriority(&c->pf_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
+  // the kernels of announced batches (equalisation, pyramids): UVIO_KLT_UP_PRIO=high lets them overtake the LK blocks of the
+  // feed in flight, so that an announced frame is ready soon after its upload ends
+  const char *up_prio = getenv("UVIO_KLT_UP_PRIO");
+  const int pf_prio = (up_prio && !strcmp(up_prio, "low")) ? prio_lo : prio_hi;
+  if ((e = cudaStreamCreateWithPriority(&c->pf_stream, cudaStreamNonBlocking, pf_prio)) != cudaSuccess ||
       (e = cudaStreamCreateWithPriority(&c->pf_copy_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) {
     if (err) *err = (int)e;
     return nullptr;
