@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "desc.h"
+#include "nvtx_ranges.h"
 #include "subpix_body.h"
 
 using namespace uvio;
@@ -282,6 +283,7 @@ bool is_device_ptr(const void *p) {
 
 // TrackDescriptor::feed_new_camera for each request; returns the worst status
 int feed_batch(DescCtx &ctx, Req *reqs, int n) {
+  UVIO_NVTX("uvio_desc_feed_batch");
   std::lock_guard<std::mutex> lk(ctx.mtx);
   if (cudaSetDevice(ctx.device) != cudaSuccess) return UVIO_E_CUDA;
   std::vector<UnitPlan> plan;

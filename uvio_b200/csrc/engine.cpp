@@ -7,6 +7,7 @@
 //   round 3  temporal LK of every tracked point, undistortion, fundamental-matrix RANSAC
 // Between rounds the host runs the reference's order-dependent bookkeeping (hostlogic.h).
 #include "engine.h"
+#include "nvtx_ranges.h"
 
 #include <stdio.h>
 
@@ -2049,6 +2050,7 @@ int Pass::stage3() {
 // The host then copies the observation lists and the pts_last / ids_last mirrors out of mapped memory.
 // ---------------------------------------------------------------------------------------------------------------------
 int Pass::device_feed() {
+  UVIO_NVTX("device_feed: descriptors + launch chain");
   Context *dev = ctx->dev;
   int e = stage0_book();
   if (e != OK) return e;
@@ -2313,6 +2315,7 @@ int Pass::device_feed() {
 // second half of the device-side feed: wait for the chain, then point the trackers at what the GPU left in mapped memory
 // (observation lists, pts_last / ids_last mirrors); nothing is copied until somebody asks for it
 int Pass::device_collect() {
+  UVIO_NVTX("device_collect: wait + results");
   if (ctx->sync() != OK) return E_CUDA;
   seg(5);
   ctx->prof_fold();
@@ -2464,6 +2467,7 @@ void Context::uploader_loop() {
 }
 
 int submit_batch(Context *ctx, FeedRequest *reqs, int n) {
+  UVIO_NVTX("uvio_klt_submit_batch");
   HOSTPROF(submit_total);
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
@@ -2521,6 +2525,7 @@ void Context::forget_rig(Rig *rig) {
 }
 
 int feed_batch(Context *ctx, FeedRequest *reqs, int n) {
+  UVIO_NVTX("uvio_klt_feed_batch");
   HOSTPROF(fb_total);
   std::lock_guard<std::mutex> guard(ctx->mtx);
   if (cudaSetDevice(ctx->device) != cudaSuccess) return E_CUDA;
