@@ -44,7 +44,7 @@ SIM_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-Wno
 def SIM_SOURCES():
     """engine + C ABIs over the CPU stand-ins of every launch wrapper (tests/hostsim)"""
     csrc = os.path.join(ROOT, "uvio_b200", "csrc")
-    return ([os.path.join(csrc, f) for f in ("engine.cpp", "abi.cpp", "featdb.cpp", "desc_engine.cpp")] +
+    return ([os.path.join(csrc, f) for f in ("engine.cpp", "engine_upload.cpp", "engine_host.cpp", "engine_device.cpp", "engine_stages.cpp", "abi.cpp", "featdb.cpp", "desc_engine.cpp")] +
             [os.path.join(SIM, f) for f in ("launch_sim.cpp", "featdb_sim.cpp", "desc_sim.cpp")])
 
 

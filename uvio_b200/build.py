@@ -8,7 +8,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libuvio_klt.so")
-SOURCES = ["kernels.cu", "noalloc.cu", "featdb_kernels.cu", "tri_kernels.cu", "desc_kernels.cu", "engine.cpp", "abi.cpp", "featdb.cpp", "desc_engine.cpp"]
+SOURCES = ["kernels.cu", "noalloc.cu", "featdb_kernels.cu", "tri_kernels.cu", "desc_kernels.cu", "engine.cpp", "engine_upload.cpp", "engine_host.cpp", "engine_device.cpp", "engine_stages.cpp", "abi.cpp", "featdb.cpp", "desc_engine.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-fmad=false",              # the CPU tracker's OpenCV build never fuses a*b+c; parity needs the same roundings
