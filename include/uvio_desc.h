@@ -11,7 +11,8 @@
  *  - robust_match reads mask_rsc[i] even when findFundamentalMat found no model and left the mask empty (:536-539);
  *    here no match survives in that case.
  *  - a non-stereo tracker with several cameras is fed by cv::parallel_for_ (:50-55), its cameras drawing ids from one
- *    counter concurrently; here every camera takes one block of consecutive ids per frame.
+ *    counter concurrently (the id order changes from run to run); here the cameras take their ids one after the other in
+ *    message order, the same on every run.  Up to four cameras per message.
  *  - 10..14 symmetric matches send cv::findFundamentalMat to LMedS: see include/uvio_klt.h on that regime.
  */
 #ifndef UVIO_DESC_H_

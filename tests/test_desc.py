@@ -293,3 +293,36 @@ def test_identical_frames_where_the_reference_would_terminate(sim_desc):
 def test_identical_frames_on_the_gpu():
     from uvio_b200 import desc
     _identical_frames(lambda cfg: desc.make_descriptor_tracker(cfg))
+
+
+# ---- a non-stereo tracker fed two cameras in one message: feed_monocular per camera (TrackDescriptor.cpp:50-55) -------------------
+def _two_mono_cameras(make):
+    """The reference runs the cameras through cv::parallel_for_, each drawing ids from the shared counter; camera by camera in
+    message order is the order that does not change from run to run (the oracle's, and this tracker's)."""
+    from oracle.trackdescriptor_cv2 import make_descriptor_oracle
+    cfg = configs.EUROC_MAV.with_(use_stereo=False)
+    frames = frames_for(cfg, 5, stream_id=13)
+    masks = masks_for(cfg)
+    o = make_descriptor_oracle(cfg)
+    t = make(cfg)
+    for k, (l, r) in enumerate(frames):
+        n0, g0, r0 = len(o.database.log), len(t.database.log), len(o.ransac_sizes)
+        o.feed_new_camera(0.05 * k, [0, 1], [l, r], masks)
+        t.feed_new_camera(track.CameraData(0.05 * k, [0, 1], [l, r], masks))
+        assert not any(10 <= s <= 13 for s in o.ransac_sizes[r0:])
+        assert _same_log(o.database.log[n0:], t.database.log[g0:]), f"frame {k}"
+        for cam in (0, 1):
+            ids, uv, d = t._last(cam)
+            assert (ids == np.array(o.ids_last[cam], np.uint64)).all() and (uv == o.pts_last[cam]).all() and (d == o.desc_last[cam]).all()
+    assert len(o.database.log) > 800
+    t.close()
+
+
+def test_two_cameras_of_a_non_stereo_tracker_host_simulation(sim_desc):
+    _two_mono_cameras(sim_desc)
+
+
+@pytest.mark.gpu
+def test_two_cameras_of_a_non_stereo_tracker_gpu():
+    from uvio_b200 import desc
+    _two_mono_cameras(lambda cfg: desc.make_descriptor_tracker(cfg))

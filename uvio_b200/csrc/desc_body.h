@@ -53,7 +53,11 @@ struct DescUnit {                      // a stereo pair or one mono camera of on
   int gw[2], gh[2];                    // occupancy grid sizes (TrackDescriptor.cpp:374, :436-439)
   double knn_ratio;
   double thr[3];                       // 1 / max focal length of the two cameras of match job 0 (L->R), 1 (L->L), 2 (R->R)  (:530-533)
-  unsigned long long *currid;          // TrackBase::currid (shared by the units of one tracker)
+  unsigned long long *currid;          // TrackBase::currid after the feed (device copy, written by the tracker's last unit)
+  unsigned long long id_base;          // TrackBase::currid before this feed (the host mirrors it: every feed ends with a synchronisation)
+  const int *sib_cnt[3];               // a non-stereo tracker fed several cameras at once: the counters (DescSide::cnt) of its units BEFORE this
+                                       // one, in message order (null-terminated): their new points take their ids first
+  int last_of_rig;                     // this unit publishes the tracker's id counter
   int *grid;                           // mono occupancy grid (gw[0] * gh[0] words, DV_INF between feeds)
   int *m_q, *m_t;                      // [3P] the matches of the three jobs (queryIdx, trainIdx), in robust_match's order
   int *m_n;                            // [3]
@@ -341,7 +345,7 @@ UVIO_HD void desc_assign_stereo(G g, const DescUnit &U) {
   const DescSide &L = U.s[0], &R = U.s[1];
   const int n = fdb_ldi(&U.m_n[0]);
   const float mpd = (float)U.mpd;
-  const unsigned long long id0 = *U.currid;
+  const unsigned long long id0 = U.id_base;
   int off = 0;
   for (int base = 0; base < n; base += g.size()) {
     const int k = base + g.lane();
@@ -371,10 +375,7 @@ UVIO_HD void desc_assign_stereo(G g, const DescUnit &U) {
     off += tot;
   }
   g.sync();
-  if (g.lane() == 0) {
-    L.cnt[2] = R.cnt[2] = off;
-    *U.currid = id0 + (unsigned long long)off;
-  }
+  if (g.lane() == 0) L.cnt[2] = R.cnt[2] = off;
   g.sync();
 }
 
@@ -392,7 +393,6 @@ UVIO_HD void desc_assign_mono(G g, const DescUnit &U) {
     fdb_min(&U.grid[yg * U.gw[0] + xg], i);
   }
   g.sync();
-  unsigned long long id0 = 0;
   int off = 0;
   for (int base = 0; base < n; base += g.size()) {
     const int i = base + g.lane();
@@ -411,27 +411,19 @@ UVIO_HD void desc_assign_mono(G g, const DescUnit &U) {
       S.nw_xy[2 * pos] = S.kp_xy[2 * i];
       S.nw_xy[2 * pos + 1] = S.kp_xy[2 * i + 1];
       desc_copy_desc(S.nw_desc + (size_t)DESC_WORDS * pos, S.kp_desc + (size_t)DESC_WORDS * i);
-      S.nw_ids[pos] = (unsigned long long)pos;              // rank; the id counter is added below
+      S.nw_ids[pos] = (unsigned long long)pos;              // rank; desc_merge adds the id counter
     }
     off += tot;
   }
   g.sync();
-  // ids: the cameras of a non-stereo tracker share one counter and are fed in parallel by the reference (:50-55), each id
-  // drawn with ++currid: a block of consecutive ids per camera is one of the orders that can happen
+  // ids: ranks here; desc_merge adds the tracker's counter and the new points of the cameras before this one (the reference
+  // feeds the cameras of a non-stereo tracker in parallel, each id drawn with ++currid (:50-55): camera by camera in message
+  // order is one of the orders that can happen, and the one that does not change from run to run)
   if (g.lane() == 0) {
-#ifdef __CUDA_ARCH__
-    id0 = atomicAdd(U.currid, (unsigned long long)off);
-#else
-    id0 = *U.currid;
-    *U.currid += (unsigned long long)off;
-#endif
     U.m_n[0] = 0;
     S.cnt[2] = off;
-    *(unsigned long long *)(U.p0n) = id0;                   // broadcast through scratch
   }
   g.sync();
-  id0 = *(const unsigned long long *)(U.p0n);
-  for (int i = g.lane(); i < off; i += g.size()) S.nw_ids[i] += id0 + 1;
   for (int i = g.lane(); i < n; i += g.size()) {            // re-arm the grid
     const float px = S.kp_xy[2 * i], py = S.kp_xy[2 * i + 1];
     const int xg = (int)(px / mpd), yg = (int)(py / mpd);
@@ -448,6 +440,12 @@ UVIO_HD void desc_merge(G g, const DescUnit &U, const DescGlobals &X, int *inv) 
   const int n = fdb_ldi(&U.s[0].cnt[2]);
   const bool first = fdb_ldi(&U.s[0].cnt[3]) == 0 || (U.stereo && fdb_ldi(&U.s[1].cnt[3]) == 0);   // :208 / :86
   int n_obs = 0;
+  unsigned long long before = 0;                            // new points of this tracker's cameras that come before this one
+  for (int k = 0; k < 3 && U.sib_cnt[k]; k++) before += (unsigned long long)fdb_ldi(&U.sib_cnt[k][2]);
+  if (!U.stereo) {                                          // size_t temp = ++currid (:399), camera by camera
+    for (int i = g.lane(); i < n; i += g.size()) U.s[0].nw_ids[i] += U.id_base + before + 1;
+    g.sync();
+  }
   if (!first) {
     for (int i = g.lane(); i < sides * U.P; i += g.size()) inv[i] = -1;
     g.sync();
@@ -491,7 +489,8 @@ UVIO_HD void desc_merge(G g, const DescUnit &U, const DescGlobals &X, int *inv) 
     if (g.lane() == 0) S.cnt[3] = n;
   }
   if (g.lane() == 0) {
-    const unsigned long long c = *U.currid;
+    const unsigned long long c = U.id_base + before + (unsigned long long)n;
+    if (U.last_of_rig) *U.currid = c;
     U.head[0] = n_obs;
     U.head[1] = n;
     U.head[2] = (int)(unsigned)(c & 0xFFFFFFFFull);

@@ -67,6 +67,7 @@ struct DescRig {
   std::unordered_map<size_t, int> cam_index;
   std::vector<DescScratch> scratch;   // one per camera: a feed has at most that many units
   unsigned long long *currid_dev = nullptr;
+  unsigned long long currid = 0;      // host mirror of TrackBase::currid (every feed ends with a synchronisation)
   std::vector<UvioObs> obs;
   int cuda_error = 0;
   float last_us = 0.f;
@@ -306,6 +307,7 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
     rig.obs.clear();
     if (f.n_img <= 0 || !f.sensor_ids || !f.img || !f.img_stride || !f.width || !f.height) r.status = UVIO_E_BADMSG;   // :36-42
     else if (rig.prm.use_stereo && f.n_img > 2) r.status = UVIO_E_BADMSG;                                            // :57-58
+    else if (f.n_img > 4) r.status = UVIO_E_ARG;                         // (a non-stereo tracker takes up to four cameras per message here)
     if (r.status == UVIO_OK)
       for (int k = 0; k < f.n_img; k++) {
         auto it = rig.cam_index.find(f.sensor_ids[k]);
@@ -477,6 +479,13 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
     U.mpd = rig.prm.min_px_dist;
     U.knn_ratio = rig.prm.knn_ratio;
     U.currid = rig.currid_dev;
+    U.id_base = rig.currid;
+    U.last_of_rig = (u + 1 == n_units || plan[u + 1].rig != p.rig) ? 1 : 0;
+    {
+      int ns = 0;
+      for (int j = u - 1; j >= 0 && plan[j].rig == p.rig && ns < 3; j--) ns++;          // units of this tracker before this one
+      for (int k = 0; k < 3; k++) U.sib_cnt[k] = k < ns ? p.rig->cams[plan[u - ns + k].cam[0]].side.cnt : nullptr;
+    }
     U.grid = sc.grid;
     U.m_q = sc.m_q;
     U.m_t = sc.m_t;
@@ -589,6 +598,8 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
     const DvObs *ob = (const DvObs *)sc.host_base;
     const int n_obs = head[0];
     for (int k = 0; k < p.n_cam; k++) rig.cams[p.cam[k]].n_last = head[1];
+    if (u + 1 == n_units || plan[u + 1].rig != p.rig)
+      rig.currid = (unsigned long long)(unsigned)head[2] | ((unsigned long long)(unsigned)head[3] << 32);   // (the last unit's: all of the tracker's new ids)
     for (int i = 0; i < n_obs; i++) {
       UvioObs o;
       o.id = (size_t)ob[i].id;
@@ -678,6 +689,7 @@ int uvio_desc_create(const UvioDescParams *p, const UvioCamCalib *cams, int n_ca
     rig->cam_index[c.cam_id] = i;
   }
   const unsigned long long id0 = 4ull * (unsigned long long)p->num_aruco + 1;   // TrackBase.cpp:34
+  rig->currid = id0;
   if (cudaMalloc((void **)&rig->currid_dev, 256) != cudaSuccess ||
       cudaMemcpy(rig->currid_dev, &id0, sizeof(id0), cudaMemcpyHostToDevice) != cudaSuccess) {
     delete rig;
