@@ -208,6 +208,22 @@ __global__ void __launch_bounds__(256) k_pyrdown_level(const PreJob *jobs, const
   }
 }
 
+// Levels `first` .. nlv-1 of every job in ONE launch: one block per image walks the small levels (a 188x120 level is 1,410
+// strips: three rounds of a 512-lane block) with a block barrier between them, instead of a launch of a few microseconds each.
+__global__ void __launch_bounds__(512) k_pyrdown_tail(const PreJob *jobs, const PyrDesc *pyr_tab, int first) {
+  const PyrDesc &P = pyr_tab[jobs[blockIdx.x].pyr];
+  for (int level = first; level < P.nlv; level++) {
+    const ImgView S = P.lv[level - 1], D = P.lv[level];
+    const int nsx = (D.w + PD_COLS - 1) / PD_COLS, nsy = (D.h + PD_ROWS - 1) / PD_ROWS;
+    for (int sidx = threadIdx.x; sidx < nsx * nsy; sidx += blockDim.x) {
+      int sy = sidx / nsx, sx = sidx - sy * nsx;
+      pyrdown_strip(S, (uint8_t *)D.p, D.w, D.h, D.pitch, sx * PD_COLS, sy * PD_ROWS);
+    }
+    __threadfence_block();
+    __syncthreads();   // the level just written is the next one's source
+  }
+}
+
 cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, const PyrDesc *pyr_tab,
                               uint8_t *clahe_lut, int any_clahe, int max_band_bytes, int max_w, int max_h, int max_nlv) {
   if (njobs <= 0) return cudaSuccess;
@@ -238,13 +254,19 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs, int njobs, co
   prof_mark(st, K_PREPROCESS);
   k_preprocess<<<dim3(PRE_CLUSTER, njobs), PRE_THREADS, band_bytes, st>>>(jobs, pyr_tab, band_bytes, split ? 0 : 1);
   if (split) {
-    int w = max_w, h = max_h;
-    for (int l = 1; l < max_nlv; l++) {
+    // level 1 (and level 2 of large frames) fills the GPU as a launch of its own; the rest is one block per image
+    int w = max_w, h = max_h, l = 1;
+    for (; l < max_nlv; l++) {
       w = (w + 1) / 2;
       h = (h + 1) / 2;
       const int strips = ((w + PD_COLS - 1) / PD_COLS) * ((h + PD_ROWS - 1) / PD_ROWS);
+      if (l > 1 && strips <= 4096) break;
       prof_mark(st, K_PYRDOWN);
       k_pyrdown_level<<<dim3((strips + 255) / 256, njobs), 256, 0, st>>>(jobs, pyr_tab, l);
+    }
+    if (l < max_nlv) {
+      prof_mark(st, K_PYRDOWN);
+      k_pyrdown_tail<<<njobs, 512, 0, st>>>(jobs, pyr_tab, l);
     }
   }
   prof_mark(st, -1);
