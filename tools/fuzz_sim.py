@@ -1,0 +1,86 @@
+"""Randomised parity sweep on the host simulation (no GPU): random image sizes, grids, feature budgets, thresholds, masks, mono /
+stereo, histogram methods; both trackers against their oracles for a few frames each.  A KLT case stops comparing at the first
+feed whose RANSAC runs on 10..13 points (LMedS regime), a descriptor case keeps comparing positions.
+
+    python tools/fuzz_sim.py [cases] [seed]
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import cv2
+import numpy as np
+
+import conftest
+from uvio_b200 import configs, desc, track
+from uvio_b200.synth import SynthStereoStream, circular_mask
+from util import log_arrays
+
+lib = conftest.sim_build(os.path.join(conftest.SIM, "_sim", "libuvio_klt_sim.so"), conftest.SIM_SOURCES(), ["-I", conftest.SIM])
+track.LIB_PATH = lib
+track._lib = None
+from oracle.trackdescriptor_cv2 import make_descriptor_oracle
+from oracle.trackklt_cv2 import make_oracle
+
+n_cases = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 0)
+bad = 0
+for case in range(n_cases):
+    w = int(rng.integers(20, 60)) * 8 + int(rng.integers(0, 8)) * int(rng.integers(0, 2))
+    h = int(rng.integers(16, 48)) * 8 + int(rng.integers(0, 8)) * int(rng.integers(0, 2))
+    base = configs.TUM_VI if rng.random() < 0.4 else configs.EUROC_MAV
+    cfg = base.with_(width=w, height=h, num_features=int(rng.choice([12, 30, 60, 120, 250])), fast_threshold=int(rng.choice([10, 20, 35])),
+                     grid_x=int(rng.integers(2, 8)), grid_y=int(rng.integers(2, 7)), min_px_dist=int(rng.choice([5, 8, 10, 15])),
+                     histogram=int(rng.integers(0, 3)), pyr_levels=int(rng.choice([3, 5])), use_stereo=bool(rng.random() < 0.7))
+    mono_msg = (not cfg.use_stereo) or rng.random() < 0.2
+    masked = rng.random() < 0.4
+    which = "desc" if rng.random() < 0.4 else "klt"
+    s = SynthStereoStream(w, h, int(rng.integers(0, 1000)), events=bool(rng.random() < 0.5))
+    m = circular_mask(w, h) if masked else np.zeros((h, w), np.uint8)
+    frames = [s.frame(k) for k in range(5)]
+    tag = f"case {case}: {which} {w}x{h} nf={cfg.num_features} grid={cfg.grid_x}x{cfg.grid_y} thr={cfg.fast_threshold} mpd={cfg.min_px_dist} hist={cfg.histogram} lv={cfg.pyr_levels} stereo={cfg.use_stereo} mono_msg={mono_msg} mask={masked}"
+    try:
+        if which == "klt":
+            o, t = make_oracle(cfg), track.make_tracker(cfg)
+        else:
+            o, t = make_descriptor_oracle(cfg), desc.make_descriptor_tracker(cfg)
+        ids_ok = True
+        for k, (l, r) in enumerate(frames):
+            cams, imgs, ms = ([0], [l], [m]) if mono_msg else ([0, 1], [l, r], [m, m])
+            n0, g0 = len(o.database.log), len(t.database.log)
+            r0 = len(getattr(o, "ransac_sizes", []))
+            try:
+                o.feed_new_camera(0.05 * k, cams, imgs, ms)
+            except cv2.error:
+                break                                    # identical correspondences: the reference would terminate
+            t.feed_new_camera(track.CameraData(0.05 * k, cams, imgs, ms))
+            if which == "desc":
+                sizes = o.ransac_sizes[r0:]
+                if any(10 <= x <= 13 for x in sizes):
+                    ids_ok = False
+                    if not mono_msg and cfg.use_stereo and 10 <= sizes[0] <= 13:
+                        break
+            else:
+                # KLT: 10..13 points handed to RANSAC in this feed -> the masks may differ from here on
+                n_pts = [len(v) for v in o.pts_last.values()]
+                if any(10 <= x <= 13 for x in n_pts):
+                    ids_ok = False
+            oi, oc, ouv, oun = log_arrays(o.database.log[n0:])
+            gi, gc, guv, gun = log_arrays(t.database.log[g0:])
+            if not ids_ok and which == "klt":
+                break
+            assert len(oi) == len(gi), f"frame {k}: {len(oi)} vs {len(gi)} observations"
+            assert (oc == gc).all() and np.abs(ouv - guv).max(initial=0) <= (0.01 if which == "klt" else 0), f"frame {k}: positions"
+            if ids_ok:
+                assert (oi == gi).all(), f"frame {k}: ids"
+        t.close()
+        print("ok  ", tag)
+    except AssertionError as e:
+        bad += 1
+        print("FAIL", tag, "->", e)
+    except (track.UvioError, SystemExit) as e:
+        print("skip", tag, "->", type(e).__name__, e)
+print("failures", bad, "of", n_cases)
+sys.exit(1 if bad else 0)
