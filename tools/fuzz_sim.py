@@ -21,8 +21,20 @@ from util import log_arrays
 lib = conftest.sim_build(os.path.join(conftest.SIM, "_sim", "libuvio_klt_sim.so"), conftest.SIM_SOURCES(), ["-I", conftest.SIM])
 track.LIB_PATH = lib
 track._lib = None
+import oracle.trackklt_cv2 as _klt
 from oracle.trackdescriptor_cv2 import make_descriptor_oracle
 from oracle.trackklt_cv2 import make_oracle
+
+_ransac_n = []                          # sizes of the KLT oracle's findFundamentalMat calls (10..13 = the LMedS regime)
+_orig_ransac = _klt.fundamental_ransac_mask
+
+
+def _spy(p0n, p1n, thr):
+    _ransac_n.append(len(p0n))
+    return _orig_ransac(p0n, p1n, thr)
+
+
+_klt.fundamental_ransac_mask = _spy
 
 n_cases = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 0)
@@ -51,6 +63,7 @@ for case in range(n_cases):
             cams, imgs, ms = ([0], [l], [m]) if mono_msg else ([0, 1], [l, r], [m, m])
             n0, g0 = len(o.database.log), len(t.database.log)
             r0 = len(getattr(o, "ransac_sizes", []))
+            del _ransac_n[:]
             try:
                 o.feed_new_camera(0.05 * k, cams, imgs, ms)
             except cv2.error:
@@ -63,9 +76,7 @@ for case in range(n_cases):
                     if not mono_msg and cfg.use_stereo and 10 <= sizes[0] <= 13:
                         break
             else:
-                # KLT: 10..13 points handed to RANSAC in this feed -> the masks may differ from here on
-                n_pts = [len(v) for v in o.pts_last.values()]
-                if any(10 <= x <= 13 for x in n_pts):
+                if any(10 <= x <= 13 for x in _ransac_n):   # 10..13 points handed to RANSAC in this feed -> the masks may differ from here on
                     ids_ok = False
             oi, oc, ouv, oun = log_arrays(o.database.log[n0:])
             gi, gc, guv, gun = log_arrays(t.database.log[g0:])
