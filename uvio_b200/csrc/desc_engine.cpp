@@ -577,7 +577,9 @@ int feed_batch(DescCtx &ctx, Req *reqs, int n) {
   const DescUnit *d_units = (const DescUnit *)(A + o_units);
   // ---- the chain -------------------------------------------------------------------------------------------------------------------------
   CKF(launch_preprocess(st, d_pre, n_sides, d_pyr, (uint8_t *)(A + o_clahe), any_clahe, max_band));
-  CKF(launch_fast(st, X.fast_jobs, n_jobs, max_cw, max_ch, d_pyr, X.fast_out, X.fast_cnt, ticket, X.fast_out, X.fast_cnt + 0 /* count "host" copy: see below */));
+  // k_fast hands each cell's list and count to a second pair of pointers (mapped host memory in the KLT host pipeline): here both
+  // pairs name the same device arrays, the lists stay where they were appended and the count is rewritten in place
+  CKF(launch_fast(st, X.fast_jobs, n_jobs, max_cw, max_ch, d_pyr, X.fast_out, X.fast_cnt, ticket, X.fast_out, X.fast_cnt));
   CKF(launch_desc_topk(st, d_units, n_units, max_cells, X));
   CKF(launch_desc_gather(st, d_units, n_units, X));
   CKF(launch_subpix(st, X.sp_items, slots, d_pyr, ctx.sp_mask, X.sp_out, nullptr, X.n_sp));
