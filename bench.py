@@ -385,13 +385,20 @@ def run_ours(args):
     host_pool = _frame_structs(track, hv.ctypes.data, NP, S, h, w, keep)
     obs_buf = np.zeros((S, 4096), track.OBS_DTYPE)
     counts = (C.c_int * S)()
-    # leg 1: frames resident in HBM; leg 2: end to end from pinned host memory (upload + results inside the timed region).
-    # Both legs time only the dominant kernel (k_lk: two event records around each of its launches); leg 3 repeats leg 1
-    # with every kernel bracketed by events to get the per-kernel shares -- its throughput is not reported.
+    # leg 1: frames resident in HBM; leg 2: end to end from pinned host memory (upload + results inside the timed region).  Both
+    # run the way a caller runs the library: no event records between kernels (bracketing the k_lk launches costs 5 % and keeps
+    # the chain from replaying its CUDA graphs: 72.0 k / 65.4 k frames/s without against 68.1 k / 61.8 k with, UVIO_BENCH_LKPROF=1).
+    # leg 1b repeats leg 1 -- same frames, same warm-up, same number of feeds -- with two event records around every launch of the
+    # dominant kernel (k_lk): the kernel's live duration for the roofline.  leg 3 brackets every kernel for the shares.
     lk_only = 1 | ((1 << track.KERNEL_NAMES.index("k_lk")) << 1)
+    in_legs = lk_only if os.environ.get("UVIO_BENCH_LKPROF", "0") == "1" else 0
     wf, tf = W * R, K * R
-    sec, n_obs, clk, st, prof, wall = _run_leg(track, L, cfg, local, S, dev_pool, wf, tf, dist, obs_buf, counts, True, lk_only, announce)
-    sec2, n_obs2, _c2, st2, _p2, wall2 = _run_leg(track, L, cfg, local, S, host_pool, wf, tf, dist, obs_buf, counts, False, lk_only, announce)
+    sec, n_obs, clk, st, prof, wall = _run_leg(track, L, cfg, local, S, dev_pool, wf, tf, dist, obs_buf, counts, True, in_legs, announce)
+    sec2, n_obs2, _c2, st2, _p2, wall2 = _run_leg(track, L, cfg, local, S, host_pool, wf, tf, dist, obs_buf, counts, False, in_legs, announce)
+    if in_legs:
+        sec1b, st1b, prof1b = sec, st, prof
+    else:
+        sec1b, _n1b, _c1b, st1b, prof1b, _w1b = _run_leg(track, L, cfg, local, S, dev_pool, wf, tf, dist, obs_buf, counts, False, lk_only, announce)
     sec3, _n3, _c3, st3, prof3, _w3 = _run_leg(track, L, cfg, local, S, dev_pool, R, min(tf, 4 * R), dist, obs_buf, counts, False, 1, announce)
     # leg 4: frames resident, every announcement followed by a device synchronisation before the feed is issued: the image-wide
     # passes of the announced frames then run with the GPU to themselves, and their event brackets are the kernels' own durations
@@ -436,7 +443,8 @@ def run_ours(args):
         "clocks": clk,
     }
     line["config"]["ms_per_feed_with_all_kernels_bracketed_by_events"] = 1e3 * sec3 / max(1, min(tf, 4 * R))
-    return line, (prof, prof3, st3, min(tf, 4 * R), prof4, min(tf, 2 * R)), st, tf, S, cfg, rank, world, dist
+    line["config"]["ms_per_feed_with_k_lk_bracketed_by_events"] = 1e3 * sec1b / tf
+    return line, (prof1b, prof3, st3, min(tf, 4 * R), prof4, min(tf, 2 * R)), st1b, tf, S, cfg, rank, world, dist
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -630,8 +638,9 @@ def roofline_entry(profs, stats, feeds, S, cfg, clk):
         ms, launches = prof_all[name]
     entry = {"kernel": name, "launches": launches, "avg_launch_ms": ms / max(1, launches),
              "kernel_time_share_of_gpu_time": share, "sum_of_kernel_durations_ms_per_feed": total_ms / max(1, feeds_prof),
-             "timing": ("CUDA events around every launch of this kernel inside the timed region (resident leg), on the launching streams; "
-                        "the shares come from a separate short leg with every kernel bracketed") if in_timed else
+             "timing": ("CUDA events around every launch of this kernel, on the launching streams, in a leg of its own that repeats the timed "
+                        "region of `value` (same frames, warm-up and number of feeds; config.ms_per_feed_with_k_lk_bracketed_by_events): the "
+                        "throughput legs carry no event records; the shares come from a short leg with every kernel bracketed") if in_timed else
                        "separate profiling leg (the kernel was not bracketed in the timed region)"}
     if name == "k_lk":
         cap, cap_path = _load_profile("lk_ncu.json")

@@ -120,7 +120,7 @@ Context *context_for_device(int device, int *err) {
   const char *up_prio = getenv("UVIO_KLT_UP_PRIO");
   const int pf_prio = (up_prio && !strcmp(up_prio, "low")) ? prio_lo : prio_hi;
   if ((e = cudaStreamCreateWithPriority(&c->pf_stream, cudaStreamNonBlocking, pf_prio)) != cudaSuccess ||
-      (e = cudaStreamCreateWithPriority(&c->pf_copy_stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess) {
+      (e = cudaStreamCreateWithPriority(&c->pf_copy_stream, cudaStreamNonBlocking, getenv("UVIO_KLT_COPY_PRIO_LOW") ? prio_lo : prio_hi)) != cudaSuccess) {
     if (err) *err = (int)e;
     return nullptr;
   }

@@ -70,6 +70,20 @@ cudaError_t launch_preprocess(cudaStream_t st, const PreJob *jobs_dev, int njobs
                               int max_w = 0, int max_h = 0, int max_nlv = 0 /* largest frame and deepest pyramid of the jobs: the levels then go in launches of their own */);
 
 // cv::pyrDown(src, dst, Size(cols / 2.0, rows / 2.0)) of every job: the downsample_cameras step in front of the tracker
+// pyramid launches launch_preprocess makes for frames of at most max_w x max_h with max_nlv levels (level 1, and level 2 of
+// large frames, as launches of their own; the remaining levels in one): for the launch statistics
+inline int pyramid_launches(int max_w, int max_h, int max_nlv) {
+  if (max_nlv <= 1 || max_w <= 0 || max_h <= 0) return 0;
+  int w = max_w, h = max_h, l = 1, n = 0;
+  for (; l < max_nlv; l++) {
+    w = (w + 1) / 2;
+    h = (h + 1) / 2;
+    if (l > 1 && ((w + 3) / 4) * ((h + 3) / 4) <= 4096) break;
+    n++;
+  }
+  return n + (l < max_nlv ? 1 : 0);
+}
+
 cudaError_t launch_downsample(cudaStream_t st, const DownJob *jobs_dev, int njobs, int max_dst_w, int max_dst_h);
 
 // ---- detection ----------------------------------------------------------------------------------------------------------
