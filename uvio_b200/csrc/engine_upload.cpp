@@ -31,11 +31,12 @@ int issue_preprocess(Context *ctx, cudaStream_t st, const PreBuffers &B, const s
   // A long copy is cut into pieces: the feed that runs meanwhile needs the same PCIe link for its launches and its results, and
   // a transfer of many megabytes ahead of them stretches its chain (round 1: ~100 us per host round trip behind a 20 MB copy,
   // tools/pcie_probe.py).  Between pieces the link takes their requests.  Measured with the device-side pipeline (64 streams,
-  // UVIO_KLT_COPYPROF): 1 MiB pieces upload at 42 GB/s beside the kernels, 2 MiB at 47, 8 MiB at 52, whole batches at 54; the
-  // end-to-end rate peaks at 2 - 2.5 MiB (62.2 k frames/s against 58.1 k at 1 MiB, 61.1 k at 3 MiB, 56.0 k at 8 MiB).
+  // UVIO_KLT_COPYPROF): 1 MiB pieces upload at 42 GB/s beside the kernels, 2 MiB at 47, 3 MiB at 49, 8 MiB at 51, whole batches
+  // at 54; with the chain replaying its CUDA graphs the end-to-end rate peaks at 3 - 4 MiB (67.4 k frames/s; 65.0 k at 2 MiB,
+  // 66.5 k at 8 MiB; 58 k at round 1's 1 MiB).
   static const size_t piece = [] {
     const char *e = getenv("UVIO_KLT_UPLOAD_PIECE");
-    long v = e ? atol(e) : (2l << 20);
+    long v = e ? atol(e) : (3l << 20);
     return (size_t)(v < 4096 ? 4096 : v);
   }();
   // UVIO_KLT_COPY_STREAMS=2: a second stream (and copy engine) for every other piece of an announced batch
