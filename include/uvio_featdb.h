@@ -18,6 +18,7 @@
 #ifndef UVIO_FEATDB_H_
 #define UVIO_FEATDB_H_
 
+#include "uvio_desc.h"
 #include "uvio_klt.h"
 
 #ifdef __cplusplus
@@ -80,6 +81,8 @@ int uvio_featdb_size(uvio_featdb *db, int *n_features, int *n_observations);
 int uvio_featdb_update_batch(uvio_featdb *const *dbs, int n, const double *timestamps, const UvioObs *obs, const int *counts, int *status);
 /* the observation lists come straight from the trackers' last (batched) feed */
 int uvio_featdb_update_from_trackers(uvio_featdb *const *dbs, uvio_klt *const *trackers, int n, const double *timestamps, int *status);
+/* the same for descriptor trackers (include/uvio_desc.h) */
+int uvio_featdb_update_from_desc_trackers(uvio_featdb *const *dbs, uvio_desc *const *trackers, int n, const double *timestamps, int *status);
 /* one query kind for all; keys may be NULL unless kind = UVIO_FDB_GET_FEATURE; n_features / n_rows / n_observations[n] may be NULL */
 int uvio_featdb_query_batch(uvio_featdb *const *dbs, int n, int kind, const double *timestamps, const size_t *keys, int remove, int skip_deleted,
                             int *n_features, int *n_rows, int *n_observations, int *status);

@@ -198,3 +198,41 @@ def test_featdb_batched_calls_host_simulation(sim_tracker):
 @pytest.mark.gpu
 def test_featdb_batched_calls_gpu(built_lib):
     _batch_equals_single()
+
+
+# ---- stores fed straight from the trackers' last batched feed (both tracker kinds) ------------------------------------------------
+def _from_trackers(make_klt, make_desc):
+    from uvio_b200 import configs, featdb
+    from uvio_b200.track import CameraData
+    from util import frames_for, masks_for
+    cfg = configs.EUROC_MAV
+    masks = masks_for(cfg)
+    for make in (make_klt, make_desc):
+        trks = [make(cfg) for _ in range(3)]
+        dbs = [DeviceFeatureDatabase(max_observations=1 << 13, max_features=1 << 11) for _ in trks]
+        seqs = [frames_for(cfg, 4, stream_id=30 + s) for s in range(3)]
+        for k in range(4):
+            for t, sq in zip(trks, seqs):
+                t.feed_new_camera(CameraData(0.05 * k, [0, 1], list(sq[k]), masks))
+            featdb.update_from_trackers(dbs, trks, [0.05 * k] * 3)
+        for t, d in zip(trks, dbs):
+            host = t.get_feature_database()                              # the Python mirror the binding fills with the same observations
+            got = d.get_internal_data()
+            assert set(got) == set(host.features_idlookup) and len(got) > 20
+            for key, f in got.items():
+                for c in f.timestamps:
+                    assert np.array_equal(f.uvs[c], np.array(host.features_idlookup[key].uvs[c], np.float32))
+        for t in trks:
+            t.close()
+
+
+def test_stores_fed_from_trackers_host_simulation(sim_tracker):
+    from uvio_b200 import desc
+    _from_trackers(lambda cfg: sim_tracker(cfg), lambda cfg: desc.make_descriptor_tracker(cfg))
+
+
+@pytest.mark.gpu
+def test_stores_fed_from_trackers_gpu(built_lib):
+    from uvio_b200 import desc
+    from uvio_b200.track import make_tracker
+    _from_trackers(lambda cfg: make_tracker(cfg), lambda cfg: desc.make_descriptor_tracker(cfg))

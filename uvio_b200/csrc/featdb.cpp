@@ -429,6 +429,23 @@ int uvio_featdb_update_from_trackers(uvio_featdb *const *dbs, uvio_klt *const *t
   return uvio_featdb_update_batch(dbs, n, timestamps, all.data(), counts.data(), status);
 }
 
+int uvio_featdb_update_from_desc_trackers(uvio_featdb *const *dbs, uvio_desc *const *trackers, int n, const double *timestamps, int *status) {
+  if (!dbs || !trackers || n <= 0) return UVIO_E_ARG;
+  std::vector<int> counts(n, 0);
+  std::vector<UvioObs> all, tmp;
+  for (int i = 0; i < n; i++) {
+    int m = 0;
+    int rc = uvio_desc_get_new_observations(trackers[i], nullptr, 0, &m);
+    if (rc != UVIO_OK && rc != UVIO_E_SIZE) return rc;
+    tmp.resize((size_t)std::max(m, 1));
+    rc = uvio_desc_get_new_observations(trackers[i], tmp.data(), m, &m);
+    if (rc != UVIO_OK) return rc;
+    counts[i] = m;
+    all.insert(all.end(), tmp.begin(), tmp.begin() + m);
+  }
+  return uvio_featdb_update_batch(dbs, n, timestamps, all.data(), counts.data(), status);
+}
+
 int uvio_featdb_query_batch(uvio_featdb *const *dbs, int n, int kind, const double *timestamps, const size_t *keys, int remove, int skip_deleted,
                             int *n_features, int *n_rows, int *n_observations, int *status) {
   if (kind < 0 || kind > 4 || !timestamps || (kind == UVIO_FDB_GET_FEATURE && !keys)) return UVIO_E_ARG;

@@ -35,6 +35,7 @@ def _lib():
         L.uvio_featdb_size.argtypes = [vp, C.POINTER(ci), C.POINTER(ci)]
         L.uvio_featdb_update_batch.argtypes = [C.POINTER(vp), ci, vp, vp, vp, vp]
         L.uvio_featdb_update_from_trackers.argtypes = [C.POINTER(vp), C.POINTER(vp), ci, vp, vp]
+        L.uvio_featdb_update_from_desc_trackers.argtypes = [C.POINTER(vp), C.POINTER(vp), ci, vp, vp]
         L.uvio_featdb_query_batch.argtypes = [C.POINTER(vp), ci, ci, vp, vp, ci, ci, vp, vp, vp, vp]
         L.uvio_featdb_cleanup_batch.argtypes = [C.POINTER(vp), ci, ci, vp, vp]
         _bound = L
@@ -178,7 +179,8 @@ def update_from_trackers(dbs, trackers, timestamps):
     ts = np.ascontiguousarray(timestamps, np.float64)
     status = np.zeros(n, np.int32)
     hs = (C.c_void_p * n)(*[t._h for t in trackers])
-    rc = _lib().uvio_featdb_update_from_trackers(_handles(dbs), hs, n, ts.ctypes.data, status.ctypes.data)
+    fn = _lib().uvio_featdb_update_from_desc_trackers if type(trackers[0]).__name__ == "TrackDescriptor" else _lib().uvio_featdb_update_from_trackers
+    rc = fn(_handles(dbs), hs, n, ts.ctypes.data, status.ctypes.data)
     _check_batch(rc, status, "uvio_featdb_update_from_trackers")
 
 
