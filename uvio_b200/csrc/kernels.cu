@@ -599,6 +599,9 @@ cudaError_t launch_ransac(cudaStream_t st, const RansacJob *jobs, int njobs, int
 // Device-side bookkeeping (track_body.h): the kernels between the pixel kernels of a feed.  One block per tracker.
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int DV_THREADS = 256;
+constexpr int DV_THREADS_MAX = 1024;   // per-tracker bookkeeping blocks of trackers with more than 512 points per camera (their O(N^2) membership loops and
+                                       // scans are spread over four times the lanes; the kernels need at most 48 registers)
+static int dv_threads(int max_p) { return max_p > 512 ? DV_THREADS_MAX : DV_THREADS; }
 constexpr int DV_TOPK_SMEM = 4096;   // corner words a cell's top-K block sorts in shared memory (more: in the job's own global region)
 
 // dynamic shared memory of the bookkeeping kernels: two id lists and one point list of P entries each (DvSmem)
@@ -624,7 +627,8 @@ __device__ __forceinline__ const DvUnit &dv_load_unit(DvUnit &sU, const DvUnit *
   return sU;
 }
 
-__global__ void __launch_bounds__(DV_THREADS) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X, int P, DvFeedBits bits) {
+template <int T>
+__global__ void __launch_bounds__(T) k_dv_occupancy(const DvUnit *units, const DvHead *heads, DvGlobals X, int P, DvFeedBits bits) {
   __shared__ DvUnit sU;
   const DvHead h = heads[blockIdx.x];
   if (blockIdx.x == 0 && threadIdx.x < 4) X.n_items[threadIdx.x] = 0;   // the item lists select / assign append to (later kernels of this chain)
@@ -663,18 +667,21 @@ __global__ void __launch_bounds__(DV_THREADS) k_dv_topk(const DvUnit *units, DvG
   dv_topk(GroupBlock(), U, X, side, r, buf, DV_TOPK_SMEM);
 }
 
-__global__ void __launch_bounds__(DV_THREADS) k_dv_select(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
+template <int T>
+__global__ void __launch_bounds__(T) k_dv_select(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
   if (blockIdx.x == 0 && threadIdx.x == 0) *X.fast_n_active = 0;   // FAST and the top-K are done with the list: re-armed for the next feed
   __shared__ DvUnit sU;
   for (int u = h.first; u < h.first + h.count; u++) dv_select(GroupBlock(), dv_load_unit(sU, units, u, X.feed_bits[u]), X, dv_smem(P));
 }
-__global__ void __launch_bounds__(DV_THREADS) k_dv_assign(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
+template <int T>
+__global__ void __launch_bounds__(T) k_dv_assign(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
   __shared__ DvUnit sU;
   for (int u = h.first; u < h.first + h.count; u++) dv_assign(GroupBlock(), dv_load_unit(sU, units, u, X.feed_bits[u]), X, dv_smem(P));
 }
-__global__ void __launch_bounds__(DV_THREADS) k_dv_merge(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
+template <int T>
+__global__ void __launch_bounds__(T) k_dv_merge(const DvUnit *units, const DvHead *heads, DvGlobals X, int P) {
   const DvHead h = heads[blockIdx.x];
   __shared__ DvUnit sU;
   for (int u = h.first; u < h.first + h.count; u++) dv_merge(GroupBlock(), dv_load_unit(sU, units, u, X.feed_bits[u]), X, dv_smem(P));
@@ -690,10 +697,11 @@ static size_t dv_smem_bytes(int P) { return (size_t)P * 24; }
 cudaError_t launch_dv_occupancy(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p,
                                 const DvFeedBits &bits) {
   if (n_heads <= 0) return cudaSuccess;
-  cudaError_t e = dv_smem_attr(k_dv_occupancy, dv_smem_bytes(max_p));
+  cudaError_t e = dv_threads(max_p) == DV_THREADS ? dv_smem_attr(k_dv_occupancy<DV_THREADS>, dv_smem_bytes(max_p)) : dv_smem_attr(k_dv_occupancy<DV_THREADS_MAX>, dv_smem_bytes(max_p));
   if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_occupancy<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p, bits);
+  if (dv_threads(max_p) == DV_THREADS) k_dv_occupancy<DV_THREADS><<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p, bits);
+  else k_dv_occupancy<DV_THREADS_MAX><<<n_heads, DV_THREADS_MAX, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p, bits);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
@@ -716,28 +724,31 @@ cudaError_t launch_dv_topk(cudaStream_t st, const DvUnit *units, int n_units, in
 }
 cudaError_t launch_dv_select(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (n_heads <= 0) return cudaSuccess;
-  cudaError_t e = dv_smem_attr(k_dv_select, dv_smem_bytes(max_p));
+  cudaError_t e = dv_threads(max_p) == DV_THREADS ? dv_smem_attr(k_dv_select<DV_THREADS>, dv_smem_bytes(max_p)) : dv_smem_attr(k_dv_select<DV_THREADS_MAX>, dv_smem_bytes(max_p));
   if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_select<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
+  if (dv_threads(max_p) == DV_THREADS) k_dv_select<DV_THREADS><<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
+  else k_dv_select<DV_THREADS_MAX><<<n_heads, DV_THREADS_MAX, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
 cudaError_t launch_dv_assign(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (n_heads <= 0) return cudaSuccess;
-  cudaError_t e = dv_smem_attr(k_dv_assign, dv_smem_bytes(max_p));
+  cudaError_t e = dv_threads(max_p) == DV_THREADS ? dv_smem_attr(k_dv_assign<DV_THREADS>, dv_smem_bytes(max_p)) : dv_smem_attr(k_dv_assign<DV_THREADS_MAX>, dv_smem_bytes(max_p));
   if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_assign<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
+  if (dv_threads(max_p) == DV_THREADS) k_dv_assign<DV_THREADS><<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
+  else k_dv_assign<DV_THREADS_MAX><<<n_heads, DV_THREADS_MAX, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
 cudaError_t launch_dv_merge(cudaStream_t st, const DvUnit *units, const DvHead *heads, int n_heads, const DvGlobals &X, int max_p) {
   if (n_heads <= 0) return cudaSuccess;
-  cudaError_t e = dv_smem_attr(k_dv_merge, dv_smem_bytes(max_p));
+  cudaError_t e = dv_threads(max_p) == DV_THREADS ? dv_smem_attr(k_dv_merge<DV_THREADS>, dv_smem_bytes(max_p)) : dv_smem_attr(k_dv_merge<DV_THREADS_MAX>, dv_smem_bytes(max_p));
   if (e != cudaSuccess) return e;
   prof_mark(st, K_DV_LOGIC);
-  k_dv_merge<<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
+  if (dv_threads(max_p) == DV_THREADS) k_dv_merge<DV_THREADS><<<n_heads, DV_THREADS, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
+  else k_dv_merge<DV_THREADS_MAX><<<n_heads, DV_THREADS_MAX, dv_smem_bytes(max_p), st>>>(units, heads, X, max_p);
   prof_mark(st, -1);
   return cudaGetLastError();
 }
